@@ -1,0 +1,128 @@
+/* TEST INFRASTRUCTURE ONLY -- CPU oracle for MOM6 advect_tracer.
+ *
+ * C interface of the CPU restatement of
+ *   /root/reference/src/tracer/MOM_tracer_advect.F90:52-1087
+ * (advect_tracer, advect_x, advect_y).  Only tests/, __graft_entry__.smoke()
+ * and bench.py's cpu_baseline / --impl reference legs may load this library;
+ * the product path (mom6_b200/) never does.
+ *
+ * PARITY UNPINNED: the reference ships no golden vectors for this path and
+ * no Fortran compiler exists in the build container, so this restatement has
+ * not been checked against an execution of the reference itself.  Its
+ * fidelity rests on statement-by-statement review plus the reference's own
+ * relational standards (layout / rotation / rescaling / threading invariance,
+ * SURVEY.md section 4), which tests/ checks on the oracle itself.
+ *
+ * All arrays use the reference's Fortran layout (column major, i fastest):
+ *   h-point  (isd:ied,   jsd:jed,   nk)
+ *   u-point  (IsdB:IedB, jsd:jed,   nk)
+ *   v-point  (isd:ied,   JsdB:JedB, nk)
+ * with the integer bounds passed exactly as the Fortran model holds them.
+ */
+#ifndef MOM6_ADVECT_REF_H
+#define MOM6_ADVECT_REF_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ocean_grid_type + verticalGrid_type members read by the path
+ * (src/core/MOM_grid.F90:25-105, src/core/MOM_verticalGrid.F90:212-215). */
+typedef struct {
+  int isc, iec, jsc, jec;
+  int isd, ied, jsd, jed;
+  int IsdB, IedB, JsdB, JedB;
+  int nk;
+  int first_direction;
+  const double *areaT;    /* (isd:ied, jsd:jed) */
+  const double *IareaT;   /* (isd:ied, jsd:jed) */
+  const double *mask2dT;  /* (isd:ied, jsd:jed) */
+  const double *mask2dCu; /* (IsdB:IedB, jsd:jed) */
+  const double *mask2dCv; /* (isd:ied, JsdB:JedB) */
+  double Angstrom_H;
+  double H_subroundoff;
+} ora_grid;
+
+/* tracer_advect_CS (MOM_tracer_advect.F90:30-40). */
+typedef struct {
+  double dt; /* baroclinic DT; only used for max_iter */
+  int usePPM;
+  int useHuynh;
+  int useHuynhStencilBug;
+} ora_cs;
+
+/* tracer_type members read by the path (MOM_tracer_types.F90:9-119).
+ * NULL pointer == unassociated. */
+typedef struct {
+  double *t;            /* (isd:ied, jsd:jed, nk) */
+  double *ad_x;         /* (IsdB:IedB, jsd:jed, nk) */
+  double *ad_y;         /* (isd:ied, JsdB:JedB, nk) */
+  double *ad2d_x;       /* (IsdB:IedB, jsd:jed) */
+  double *ad2d_y;       /* (isd:ied, JsdB:JedB) */
+  double *advection_xy; /* (isd:ied, jsd:jed, nk) */
+  double conc_underflow;
+} ora_tracer;
+
+/* Stand-ins for do_group_pass (MOM_tracer_advect.F90:206) and
+ * sum_across_PEs (:305).  ctx is passed through untouched. */
+typedef void (*ora_pass_fn)(void *ctx, double *uhr, double *vhr, double *hprev,
+                            ora_tracer *Tr, int ntr);
+typedef void (*ora_sum_fn)(void *ctx, int *domore_k, int nz);
+
+/* Domain description used by the built-in group-pass emulation: a pi x pj
+ * block layout of a global nig x njg grid, MOM_domains.F90:184-191. */
+typedef struct {
+  int nig, njg;       /* global computational-domain size */
+  int cyclic_x, cyclic_y, tripolar_n;
+  int symmetric;      /* symmetric memory (u/v arrays carry the extra 0 index) */
+} ora_domain;
+
+/* One rank of an emulated multi-PE run. */
+typedef struct {
+  ora_grid G;
+  int ioff, joff;     /* global index = local index + off (of h points) */
+  ora_tracer *Tr;     /* ntr entries */
+  const double *h_end, *uhtr, *vhtr;
+  double *vol_prev;   /* nullable */
+  double *uhr_out, *vhr_out; /* nullable */
+  int n_iter;         /* out: iterations taken */
+} ora_rank;
+
+/* advect_tracer, MOM_tracer_advect.F90:52-324.
+ *  x_first_in: -1 absent, 0 false, 1 true.   max_iter_in: <0 absent.
+ *  update_vol_prev: -1 absent, 0 false, 1 true.
+ *  pass/sum may be NULL only if dom != NULL (built-in single-rank pass).
+ *  nthreads: OpenMP threads over k (where the reference threads, :147,214,247).
+ * returns 0, or 1 if CS/Reg unassociated (the reference's FATAL). */
+int ora_advect_tracer(const ora_grid *G, const ora_cs *CS, ora_tracer *Tr, int ntr,
+                      const double *h_end, const double *uhtr, const double *vhtr,
+                      double dt, int x_first_in, double *vol_prev, int max_iter_in,
+                      int update_vol_prev, double *uhr_out, double *vhr_out,
+                      const ora_domain *dom, ora_pass_fn pass, ora_sum_fn sum,
+                      void *ctx, int *n_iter_out, int nthreads);
+
+/* Emulated multi-PE run: all ranks advance in lock step (one thread each),
+ * exchanging halos through the emulated group pass.  Same optional-argument
+ * conventions as above. */
+int ora_advect_tracer_multi(int nranks, ora_rank *ranks, const ora_domain *dom,
+                            const ora_cs *CS, int ntr, double dt, int x_first_in,
+                            int max_iter_in, int update_vol_prev);
+
+/* Emulated do_group_pass for an arbitrary set of ranks (exposed for tests).
+ * fields of rank r: uhr[r], vhr[r] (C-grid vector pair), hprev[r], Tr of rank. */
+void ora_group_pass(int nranks, ora_rank *ranks, const ora_domain *dom,
+                    double **uhr, double **vhr, double **hprev, int ntr);
+
+/* MOM bitcount checksum of a 2-D/3-D array section
+ * (src/framework/MOM_checksums.F90:2407-2414 bitcount, :1396-1404 use). */
+long long ora_bitcount_chksum(const double *a, long long n);
+
+/* Extended-fixed-point reproducing sum (src/framework/MOM_coms.F90:28-37,
+ * 508-560): returns the six int64 limbs of sum(a[0..n)). */
+void ora_efp_sum(const double *a, long long n, long long limbs[6]);
+double ora_efp_to_real(const long long limbs[6]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
