@@ -1,0 +1,144 @@
+/* mom6adv.h -- C ABI of the B200-native MOM6 advect_tracer.
+ *
+ * This is the drop-in boundary.  A Fortran shim module
+ * named MOM_tracer_advect (fortran/MOM_tracer_advect.F90 in this repo) keeps the
+ * reference's public surface
+ *     advect_tracer       /root/reference/src/tracer/MOM_tracer_advect.F90:52-86
+ *     tracer_advect_init  /root/reference/src/tracer/MOM_tracer_advect.F90:1090
+ *     tracer_advect_end   /root/reference/src/tracer/MOM_tracer_advect.F90:1153
+ * and binds the entry points below through ISO_C_BINDING (the tree's own
+ * precedent for bind(c) is src/framework/posix.F90:52-229).
+ *
+ * Conventions
+ *  - plain C: pointers, sizes, PODs.  No torch / C++ types.
+ *  - every function returns an int status (MOM6ADV_OK == 0).  The shim maps a
+ *    non-zero status to MOM_error(FATAL, mom6adv_last_error(plan)).
+ *  - all user arrays are in the reference's Fortran layout (column major, i
+ *    fastest) with the bounds of mom6adv_grid:
+ *        h-point (isd:ied, jsd:jed, nk)      u-point (IsdB:IedB, jsd:jed, nk)
+ *        v-point (isd:ied, JsdB:JedB, nk)
+ *    and may be HOST or DEVICE pointers (detected with
+ *    cudaPointerGetAttributes).  Inside the plan every field lives in HBM as
+ *    SoA in a padded, 128-byte aligned layout.
+ *  - tracer indices m are 0-based here (the shim passes m-1).
+ *  - there is NO CPU fallback: without a CUDA device plan_create fails.
+ */
+#ifndef MOM6ADV_H
+#define MOM6ADV_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  MOM6ADV_OK = 0,
+  MOM6ADV_ERR_NOT_INIT = 1,    /* plan NULL / tracer not bound (reference FATALs :120-123) */
+  MOM6ADV_ERR_INVALID = 2,     /* bad argument */
+  MOM6ADV_ERR_UNSUPPORTED = 3, /* OBC active, halo < stencil */
+  MOM6ADV_ERR_CUDA = 4,
+  MOM6ADV_ERR_COMM = 5         /* halo-exchange transport failure */
+};
+
+typedef struct mom6adv_plan mom6adv_plan;
+
+/* ocean_grid_type + verticalGrid_type members read by the path
+ * (src/core/MOM_grid.F90:25-105; src/core/MOM_verticalGrid.F90:212-215).
+ * Index values are passed exactly as the Fortran model holds them. */
+typedef struct {
+  int isc, iec, jsc, jec;
+  int isd, ied, jsd, jed;
+  int IsdB, IedB, JsdB, JedB;
+  int nk;
+  const double *areaT;    /* (isd:ied, jsd:jed)   host pointer */
+  const double *IareaT;   /* (isd:ied, jsd:jed)   */
+  const double *mask2dT;  /* (isd:ied, jsd:jed)   */
+  const double *mask2dCu; /* (IsdB:IedB, jsd:jed) */
+  const double *mask2dCv; /* (isd:ied, JsdB:JedB) */
+  double Angstrom_H;
+  double H_subroundoff;
+} mom6adv_grid;
+
+/* tracer_advect_CS (MOM_tracer_advect.F90:30-40) + G%first_direction. */
+typedef struct {
+  double dt_baroclinic;   /* CS%dt: only used for max_iter (:135) */
+  int usePPM;
+  int useHuynh;
+  int useHuynhStencilBug;
+  int debug;
+  int first_direction;    /* G%first_direction (:126) */
+} mom6adv_config;
+
+/* MOM_domain_type as far as the group pass needs it
+ * (src/framework/MOM_domains.F90:184-191; create_group_pass / do_group_pass,
+ * config_src/infra/FMS2/MOM_domain_infra.F90:983-1158). */
+typedef struct {
+  int nig, njg;           /* global computational-domain size */
+  int npi, npj;           /* LAYOUT */
+  int pi, pj;             /* this rank's block */
+  int ioff, joff;         /* global index = local index + off */
+  int cyclic_x, cyclic_y, tripolar_n;
+} mom6adv_domain;
+
+/* ---- life cycle --------------------------------------------------------- */
+/* device < 0: use the current CUDA device.  dom == NULL: a single closed
+ * block.  Stands in for tracer_advect_init's allocate(CS) (:1107) plus the
+ * per-call create_group_pass (:140-144), done once. */
+int mom6adv_plan_create(const mom6adv_grid *g, const mom6adv_config *c,
+                        const mom6adv_domain *dom, int device, mom6adv_plan **out);
+int mom6adv_plan_destroy(mom6adv_plan *plan);   /* tracer_advect_end :1153 */
+const char *mom6adv_last_error(const mom6adv_plan *plan);
+const char *mom6adv_version(void);
+
+/* ---- registry data (MOM_tracer_types.F90:9-130) -------------------------- */
+/* Declare Reg%ntr.  Tracer slots 0..ntr-1 get HBM storage. */
+int mom6adv_set_ntr(mom6adv_plan *plan, int ntr);
+/* Bind Reg%Tr(m): t is where MIRROR-mode calls read/write the tracer (host or
+ * device pointer, Fortran layout); diagnostic pointers NULL == unassociated. */
+int mom6adv_bind_tracer(mom6adv_plan *plan, int m, double *t, double conc_underflow,
+                        double *ad_x, double *ad_y, double *ad2d_x, double *ad2d_y,
+                        double *advection_xy);
+
+/* ---- MIRROR mode: one call == one reference advect_tracer call ----------- */
+/* Copies h_end/uhtr/vhtr(/vol_prev) and every bound tracer to HBM, runs the
+ * whole advect_tracer algorithm (:112-320) on the GPU and copies tracers,
+ * associated diagnostics and the optional outputs back.
+ *   x_first: -1 absent (use first_direction), 0/1.   max_iter_in: <0 absent.
+ *   vol_prev NULL == absent;  update_vol_prev: -1 absent, 0/1.
+ *   uhr_out / vhr_out NULL == absent.   n_iter (nullable): iterations done. */
+int mom6adv_advect(mom6adv_plan *plan, const double *h_end, const double *uhtr,
+                   const double *vhtr, double dt, int x_first, double *vol_prev,
+                   int max_iter_in, int update_vol_prev, double *uhr_out,
+                   double *vhr_out, int *n_iter);
+
+/* ---- RESIDENT mode: fields stay in HBM between calls --------------------- */
+enum { MOM6ADV_F_H_END = 0, MOM6ADV_F_UHTR = 1, MOM6ADV_F_VHTR = 2, MOM6ADV_F_VOL_PREV = 3,
+       MOM6ADV_F_UHR = 4, MOM6ADV_F_VHR = 5, MOM6ADV_F_HPREV = 6 };
+int mom6adv_upload_tracer(mom6adv_plan *plan, int m, const double *src);
+int mom6adv_download_tracer(mom6adv_plan *plan, int m, double *dst);
+int mom6adv_upload_field(mom6adv_plan *plan, int field, const double *src);
+int mom6adv_download_field(mom6adv_plan *plan, int field, double *dst);
+/* kind: 0 ad_x, 1 ad_y, 2 ad2d_x, 3 ad2d_y, 4 advection_xy */
+int mom6adv_download_diag(mom6adv_plan *plan, int m, int kind, double *dst);
+/* Runs the algorithm on the resident fields; no host<->device traffic except
+ * the per-iteration convergence word.  use_vol_prev: take hprev from the
+ * VOL_PREV field (:174-176) instead of reconstructing it (:164-172). */
+int mom6adv_advect_resident(mom6adv_plan *plan, double dt, int x_first, int max_iter_in,
+                            int use_vol_prev, int update_vol_prev, int *n_iter);
+int mom6adv_sync(mom6adv_plan *plan);
+
+/* ---- observability ------------------------------------------------------- */
+/* Device time [ms] of the last advect call, CUDA-event timed on the plan's
+ * stream; the stand-in for the (Ocean advect tracer) clock (:1146). */
+double mom6adv_last_advect_ms(const mom6adv_plan *plan);
+/* Number of kernels the plan launched since creation. */
+long long mom6adv_kernel_launches(const mom6adv_plan *plan);
+/* Bytes of HBM held by the plan. */
+long long mom6adv_device_bytes(const mom6adv_plan *plan);
+/* Algorithm selector for experiments/tests: 0 = unfused reference-order
+ * sweeps, 1 = fused tile kernel (default when available). */
+int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,199 @@
+"""ctypes binding of the C ABI in include/mom6adv.h (libmom6adv_b200.so).
+
+This is exactly what the Fortran shim (fortran/MOM_tracer_advect.F90) binds
+through ISO_C_BINDING; the Python host mirror goes through the same entry
+points, so tests that call this module exercise the drop-in boundary itself.
+There is no CPU fallback: a missing library raises at load time.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmom6adv_b200.so")
+
+OK, ERR_NOT_INIT, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_COMM = range(6)
+F_H_END, F_UHTR, F_VHTR, F_VOL_PREV, F_UHR, F_VHR, F_HPREV = range(7)
+DIAG_KINDS = ("ad_x", "ad_y", "ad2d_x", "ad2d_y", "advection_xy")
+
+_dp = C.POINTER(C.c_double)
+
+
+class mom6adv_grid(C.Structure):
+    _fields_ = [(n, C.c_int) for n in
+                ("isc", "iec", "jsc", "jec", "isd", "ied", "jsd", "jed",
+                 "IsdB", "IedB", "JsdB", "JedB", "nk")] + \
+               [(n, _dp) for n in ("areaT", "IareaT", "mask2dT", "mask2dCu", "mask2dCv")] + \
+               [("Angstrom_H", C.c_double), ("H_subroundoff", C.c_double)]
+
+
+class mom6adv_config(C.Structure):
+    _fields_ = [("dt_baroclinic", C.c_double)] + \
+               [(n, C.c_int) for n in ("usePPM", "useHuynh", "useHuynhStencilBug", "debug", "first_direction")]
+
+
+class mom6adv_domain(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("nig", "njg", "npi", "npj", "pi", "pj", "ioff", "joff",
+                                       "cyclic_x", "cyclic_y", "tripolar_n")]
+
+
+# every symbol include/mom6adv.h declares: name -> (restype, argtypes)
+_P = C.c_void_p
+SYMBOLS = {
+    "mom6adv_plan_create": (C.c_int, [C.POINTER(mom6adv_grid), C.POINTER(mom6adv_config),
+                                      C.POINTER(mom6adv_domain), C.c_int, C.POINTER(_P)]),
+    "mom6adv_plan_destroy": (C.c_int, [_P]),
+    "mom6adv_last_error": (C.c_char_p, [_P]),
+    "mom6adv_version": (C.c_char_p, []),
+    "mom6adv_set_ntr": (C.c_int, [_P, C.c_int]),
+    "mom6adv_bind_tracer": (C.c_int, [_P, C.c_int, _P, C.c_double, _P, _P, _P, _P, _P]),
+    "mom6adv_advect": (C.c_int, [_P, _P, _P, _P, C.c_double, C.c_int, _P, C.c_int, C.c_int, _P, _P,
+                                 C.POINTER(C.c_int)]),
+    "mom6adv_upload_tracer": (C.c_int, [_P, C.c_int, _P]),
+    "mom6adv_download_tracer": (C.c_int, [_P, C.c_int, _P]),
+    "mom6adv_upload_field": (C.c_int, [_P, C.c_int, _P]),
+    "mom6adv_download_field": (C.c_int, [_P, C.c_int, _P]),
+    "mom6adv_download_diag": (C.c_int, [_P, C.c_int, C.c_int, _P]),
+    "mom6adv_advect_resident": (C.c_int, [_P, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int,
+                                          C.POINTER(C.c_int)]),
+    "mom6adv_sync": (C.c_int, [_P]),
+    "mom6adv_last_advect_ms": (C.c_double, [_P]),
+    "mom6adv_kernel_launches": (C.c_longlong, [_P]),
+    "mom6adv_device_bytes": (C.c_longlong, [_P]),
+    "mom6adv_set_option": (C.c_int, [_P, C.c_char_p, C.c_int]),
+}
+
+_lib = None
+
+
+def lib():
+    """Load libmom6adv_b200.so (built in-tree by mom6_b200.build).  Raises if missing."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("%s is missing: run `python -m mom6_b200.build` (there is no CPU fallback)" % LIB_PATH)
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(l, name)     # AttributeError if the symbol is not exported
+            fn.restype, fn.argtypes = res, args
+        _lib = l
+    return _lib
+
+
+class Mom6AdvError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__("mom6adv status %d: %s" % (status, msg))
+        self.status = status
+
+
+def ptr(a) -> Optional[int]:
+    """Raw address of a numpy array / torch tensor / int / None."""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return a
+    if isinstance(a, np.ndarray):
+        if not (a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]):
+            raise ValueError("need a contiguous float64 array")
+        return a.ctypes.data
+    if hasattr(a, "data_ptr"):   # torch tensor (host or device)
+        if not a.is_contiguous() or a.element_size() != 8:
+            raise ValueError("need a contiguous float64 tensor")
+        return a.data_ptr()
+    raise TypeError("unsupported array type %r" % type(a))
+
+
+class Plan:
+    """Thin object wrapper around mom6adv_plan*."""
+
+    def __init__(self, G, GV, CS, device: int = -1):
+        self._l = lib()
+        self._h = _P()
+        self._keep = []
+        g = mom6adv_grid()
+        for n in ("isc", "iec", "jsc", "jec", "isd", "ied", "jsd", "jed", "IsdB", "IedB", "JsdB", "JedB"):
+            setattr(g, n, int(getattr(G, n)))
+        g.nk = int(GV.ke)
+        for n in ("areaT", "IareaT", "mask2dT", "mask2dCu", "mask2dCv"):
+            a = np.ascontiguousarray(getattr(G, n), dtype=np.float64)
+            self._keep.append(a)
+            setattr(g, n, a.ctypes.data_as(_dp))
+        g.Angstrom_H, g.H_subroundoff = GV.Angstrom_H, GV.H_subroundoff
+        c = mom6adv_config()
+        c.dt_baroclinic = CS.dt
+        c.usePPM, c.useHuynh, c.useHuynhStencilBug = int(CS.usePPM), int(CS.useHuynh), int(CS.useHuynhStencilBug)
+        c.debug = int(getattr(CS, "debug", False))
+        c.first_direction = int(G.first_direction)
+        D = G.Domain
+        d = mom6adv_domain()
+        d.nig, d.njg = D.nig, D.njg
+        d.npi, d.npj = D.layout
+        d.pi, d.pj = D.pe
+        d.ioff, d.joff = G.ioff, G.joff
+        d.cyclic_x, d.cyclic_y, d.tripolar_n = int(D.cyclic_x), int(D.cyclic_y), int(D.tripolar_n)
+        rc = self._l.mom6adv_plan_create(C.byref(g), C.byref(c), C.byref(d), int(device), C.byref(self._h))
+        if rc != OK:
+            raise Mom6AdvError(rc, self._l.mom6adv_last_error(None).decode())
+        self.G, self.GV, self.ntr = G, GV, 0
+
+    # -- helpers ---------------------------------------------------------------
+    def _ck(self, rc):
+        if rc != OK:
+            raise Mom6AdvError(rc, self._l.mom6adv_last_error(self._h).decode())
+
+    def destroy(self):
+        if self._h:
+            self._l.mom6adv_plan_destroy(self._h)
+            self._h = _P()
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+    # -- registry ---------------------------------------------------------------
+    def set_ntr(self, ntr: int):
+        self._ck(self._l.mom6adv_set_ntr(self._h, ntr))
+        self.ntr = ntr
+
+    def bind_tracer(self, m, t, conc_underflow=0.0, ad_x=None, ad_y=None, ad2d_x=None, ad2d_y=None,
+                    advection_xy=None):
+        self._ck(self._l.mom6adv_bind_tracer(self._h, m, ptr(t), float(conc_underflow), ptr(ad_x), ptr(ad_y),
+                                             ptr(ad2d_x), ptr(ad2d_y), ptr(advection_xy)))
+
+    # -- MIRROR ----------------------------------------------------------------
+    def advect(self, h_end, uhtr, vhtr, dt, x_first=-1, vol_prev=None, max_iter_in=-1, update_vol_prev=-1,
+               uhr_out=None, vhr_out=None) -> int:
+        n = C.c_int(0)
+        self._ck(self._l.mom6adv_advect(self._h, ptr(h_end), ptr(uhtr), ptr(vhtr), float(dt), int(x_first),
+                                        ptr(vol_prev), int(max_iter_in), int(update_vol_prev), ptr(uhr_out),
+                                        ptr(vhr_out), C.byref(n)))
+        return n.value
+
+    # -- RESIDENT --------------------------------------------------------------
+    def upload_tracer(self, m, src): self._ck(self._l.mom6adv_upload_tracer(self._h, m, ptr(src)))
+    def download_tracer(self, m, dst): self._ck(self._l.mom6adv_download_tracer(self._h, m, ptr(dst)))
+    def upload_field(self, f, src): self._ck(self._l.mom6adv_upload_field(self._h, f, ptr(src)))
+    def download_field(self, f, dst): self._ck(self._l.mom6adv_download_field(self._h, f, ptr(dst)))
+    def download_diag(self, m, kind, dst): self._ck(self._l.mom6adv_download_diag(self._h, m, kind, ptr(dst)))
+
+    def advect_resident(self, dt, x_first=-1, max_iter_in=-1, use_vol_prev=0, update_vol_prev=0) -> int:
+        n = C.c_int(0)
+        self._ck(self._l.mom6adv_advect_resident(self._h, float(dt), int(x_first), int(max_iter_in),
+                                                 int(use_vol_prev), int(update_vol_prev), C.byref(n)))
+        return n.value
+
+    def sync(self): self._ck(self._l.mom6adv_sync(self._h))
+    def set_option(self, key: str, value: int): self._ck(self._l.mom6adv_set_option(self._h, key.encode(), value))
+
+    @property
+    def last_advect_ms(self) -> float: return float(self._l.mom6adv_last_advect_ms(self._h))
+    @property
+    def kernel_launches(self) -> int: return int(self._l.mom6adv_kernel_launches(self._h))
+    @property
+    def device_bytes(self) -> int: return int(self._l.mom6adv_device_bytes(self._h))

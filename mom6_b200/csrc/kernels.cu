@@ -1,0 +1,514 @@
+// Hand-written sm_100a kernels for MOM6 advect_tracer (unfused reference-order
+// path).  Arithmetic follows /root/reference/src/tracer/MOM_tracer_advect.F90
+// operation for operation; build with -fmad=false (no FMA contraction).
+//
+// Kernel inventory:
+//   k_init_residuals   K0  :152-178   uhr/vhr/hprev from h_end/uhtr/vhtr
+//   k_neglect          K1  :182-188   uh_neglect / vh_neglect (+ mask products)
+//   k_rescan_flags     K3  :215-225   domore_u/domore_v row scans (warp ballots)
+//   k_domore_k         K7  :229-231,265-267,287-289
+//   k_flags_begin          :394,407-408 / :789,868-869  entry flags of a sweep
+//   k_mass_flux<DIR>       :485-514 / :871-900  uhh/vhh, CFL, limiter flags
+//   k_mass_update<DIR>     :632-649 / :1021-1040  uhr/vhr, hprev, hlst, Ihnew
+//   k_tracer_sweep<SCHEME,DIR>  K4/K5/K6 :517-577,652-687 / :902-963,1043-1066
+//   k_ad2d<SCHEME,DIR>     :691-699 / :1078-1084  k-ordered 2-D flux sums
+//   k_halo_apply       C1  :206  list-driven halo fill (cyclic / fold / closed)
+//   k_repack_in/out        Fortran layout <-> padded HBM layout
+#include "internal.cuh"
+#include "kernels.h"
+
+#define TPB 128
+
+__device__ __forceinline__ long long gidx(const Geom &g, int ci, int rj, int k0) {
+  return (long long)ci + (long long)g.P * rj + g.plane * k0;
+}
+
+// ---------------------------------------------------------------------------
+// Fortran layout <-> padded layout.  src: (ilo:ied, jlo:jed, nk) contiguous.
+// ---------------------------------------------------------------------------
+__global__ void k_repack_in(Geom g, double *__restrict__ dst, const double *__restrict__ src,
+                            int ilo, int jlo, int nlev) {
+  const int ni = g.ied - ilo + 1, nj = g.jed - jlo + 1;
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  int r = blockIdx.y, k0 = blockIdx.z;
+  if (c >= ni || r >= nj || k0 >= nlev) return;
+  dst[gidx(g, c + ilo + g.coff, r + jlo + g.roff, k0)] = src[(long long)c + (long long)ni * (r + (long long)nj * k0)];
+}
+__global__ void k_repack_out(Geom g, double *__restrict__ dst, const double *__restrict__ src,
+                             int ilo, int jlo, int nlev) {
+  const int ni = g.ied - ilo + 1, nj = g.jed - jlo + 1;
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  int r = blockIdx.y, k0 = blockIdx.z;
+  if (c >= ni || r >= nj || k0 >= nlev) return;
+  dst[(long long)c + (long long)ni * (r + (long long)nj * k0)] = src[gidx(g, c + ilo + g.coff, r + jlo + g.roff, k0)];
+}
+
+void launch_repack_in(cudaStream_t s, const Geom &g, double *dst, const double *src, int ilo, int jlo, int nlev) {
+  const int ni = g.ied - ilo + 1, nj = g.jed - jlo + 1;
+  dim3 grid((ni + TPB - 1) / TPB, nj, nlev);
+  k_repack_in<<<grid, TPB, 0, s>>>(g, dst, src, ilo, jlo, nlev);
+}
+void launch_repack_out(cudaStream_t s, const Geom &g, double *dst, const double *src, int ilo, int jlo, int nlev) {
+  const int ni = g.ied - ilo + 1, nj = g.jed - jlo + 1;
+  dim3 grid((ni + TPB - 1) / TPB, nj, nlev);
+  k_repack_out<<<grid, TPB, 0, s>>>(g, dst, src, ilo, jlo, nlev);
+}
+
+// ---------------------------------------------------------------------------
+// K1: uh_neglect, vh_neglect (:182-188) and the per-cell mask products
+//     mmx(i,j) = mask2dCu(I,j)*mask2dCu(I-1,j), mmy(i,j) = mask2dCv(i,J)*mask2dCv(i,J-1)
+// ---------------------------------------------------------------------------
+__global__ void k_neglect(Geom g, const double *__restrict__ areaT, const double *__restrict__ mCu,
+                          const double *__restrict__ mCv, double H_subroundoff,
+                          double *__restrict__ uh_neglect, double *__restrict__ vh_neglect,
+                          double *__restrict__ mmx, double *__restrict__ mmy) {
+  int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y;
+  if (ci >= g.P) return;
+  int i = ci - g.coff, j = rj - g.roff;
+  long long q = gidx(g, ci, rj, 0);
+  if (i >= g.isd && i <= g.ied && j >= g.jsd && j <= g.jed) {
+    if (i <= g.ied - 1) uh_neglect[q] = H_subroundoff * gmin2(areaT[q], areaT[q + 1]);
+    if (j <= g.jed - 1) vh_neglect[q] = H_subroundoff * gmin2(areaT[q], areaT[q + g.P]);
+    if (i - 1 >= g.IsdB) mmx[q] = mCu[q] * mCu[q - 1];
+    if (j - 1 >= g.JsdB) mmy[q] = mCv[q] * mCv[q - g.P];
+  }
+}
+void launch_neglect(cudaStream_t s, const Geom &g, const double *areaT, const double *mCu, const double *mCv,
+                    double Hsub, double *uhn, double *vhn, double *mmx, double *mmy) {
+  dim3 grid((g.P + TPB - 1) / TPB, g.R, 1);
+  k_neglect<<<grid, TPB, 0, s>>>(g, areaT, mCu, mCv, Hsub, uhn, vhn, mmx, mmy);
+}
+
+// ---------------------------------------------------------------------------
+// K0: prologue :152-178.  Whole padded arrays are written (halos zeroed).
+// ---------------------------------------------------------------------------
+__global__ void k_init_residuals(Geom g, const double *__restrict__ h_end, const double *__restrict__ uhtr,
+                                 const double *__restrict__ vhtr, const double *__restrict__ vol_prev,
+                                 const double *__restrict__ areaT, double *__restrict__ uhr,
+                                 double *__restrict__ vhr, double *__restrict__ hprev) {
+  int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y, k0 = blockIdx.z;
+  if (ci >= g.P) return;
+  int i = ci - g.coff, j = rj - g.roff;
+  long long q = gidx(g, ci, rj, k0);
+  const bool in_i = (i >= g.isc && i <= g.iec), in_j = (j >= g.jsc && j <= g.jec);
+  // uhr(I,j) = uhtr for I=is-1..ie, j=js..je ; vhr(i,J) = vhtr for i=is..ie, J=js-1..je
+  double u = 0.0, v = 0.0, h = 0.0;
+  if (in_j && i >= g.isc - 1 && i <= g.iec) u = uhtr[q];
+  if (in_i && j >= g.jsc - 1 && j <= g.jec) v = vhtr[q];
+  if (in_i && in_j) {
+    if (vol_prev == nullptr) {
+      double um = uhtr[q - 1], vm = vhtr[q - g.P];
+      double ah = areaT[gidx(g, ci, rj, 0)] * h_end[q];
+      h = gmax2(0.0, ah + ((u - um) + (v - vm)));
+      h = h + gmax2(0.0, 1.0e-13 * h - ah);
+    } else {
+      h = vol_prev[q];
+    }
+  }
+  uhr[q] = u; vhr[q] = v; hprev[q] = h;
+}
+void launch_init_residuals(cudaStream_t s, const Geom &g, const double *h_end, const double *uhtr,
+                           const double *vhtr, const double *vol_prev, const double *areaT,
+                           double *uhr, double *vhr, double *hprev) {
+  dim3 grid((g.P + TPB - 1) / TPB, g.R, g.nk);
+  k_init_residuals<<<grid, TPB, 0, s>>>(g, h_end, uhtr, vhtr, vol_prev, areaT, uhr, vhr, hprev);
+}
+
+// ---------------------------------------------------------------------------
+// K3: domore_u / domore_v rescan, :215-225.  One CTA per (row, level); the row
+// is scanned with coalesced loads and reduced with __syncthreads_or.
+// Flags are int arrays indexed [k0*R + rj].
+// ---------------------------------------------------------------------------
+__global__ void k_rescan_flags(Geom g, const double *__restrict__ uhr, const double *__restrict__ vhr,
+                               const int *__restrict__ domore_k, int *__restrict__ domore_u,
+                               int *__restrict__ domore_v, int isv, int iev, int jsv, int jev, int stencil) {
+  const int rj = blockIdx.x, k0 = blockIdx.y;
+  if (domore_k[k0] <= 0) return;
+  const int j = rj - g.roff;
+  const long long base = (long long)g.P * rj + g.plane * k0;
+  const bool scan_u = (j >= jsv && j <= jev) && !domore_u[k0 * g.R + rj];
+  const bool scan_v = (j >= jsv + stencil - 1 && j <= jev - stencil) && !domore_v[k0 * g.R + rj];
+  int fu = 0, fv = 0;
+  if (scan_u) {
+    for (int i = isv + stencil - 1 + threadIdx.x; i <= iev - stencil; i += blockDim.x)
+      if (uhr[base + i + g.coff] != 0.0) fu = 1;
+  }
+  if (scan_v) {
+    for (int i = isv + stencil + threadIdx.x; i <= iev - stencil; i += blockDim.x)
+      if (vhr[base + i + g.coff] != 0.0) fv = 1;
+  }
+  fu = __syncthreads_or(fu);
+  fv = __syncthreads_or(fv);
+  if (threadIdx.x == 0) {
+    if (scan_u && fu) domore_u[k0 * g.R + rj] = 1;
+    if (scan_v && fv) domore_v[k0 * g.R + rj] = 1;
+  }
+}
+void launch_rescan(cudaStream_t s, const Geom &g, const double *uhr, const double *vhr, const int *domore_k,
+                   int *domore_u, int *domore_v, int isv, int iev, int jsv, int jev, int stencil) {
+  dim3 grid(g.R, g.nk, 1);
+  k_rescan_flags<<<grid, TPB, 0, s>>>(g, uhr, vhr, domore_k, domore_u, domore_v, isv, iev, jsv, jev, stencil);
+}
+
+// K7: domore_k(k) = any(domore_u(ju0:ju1,k)) .or. any(domore_v(jv0:jv1,k)), only for
+// levels with domore_k(k) > 0 on entry (:229-231, :265-267, :287-289).
+__global__ void k_domore_k(Geom g, int *__restrict__ domore_k, const int *__restrict__ domore_u,
+                           const int *__restrict__ domore_v, int ju0, int ju1, int jv0, int jv1) {
+  const int k0 = blockIdx.x;
+  if (domore_k[k0] <= 0) return;   // uniform per CTA
+  int f = 0;
+  for (int j = ju0 + threadIdx.x; j <= ju1; j += blockDim.x) f |= domore_u[k0 * g.R + j + g.roff];
+  for (int j = jv0 + threadIdx.x; j <= jv1; j += blockDim.x) f |= domore_v[k0 * g.R + j + g.roff];
+  f = __syncthreads_or(f);
+  if (threadIdx.x == 0) domore_k[k0] = f ? 1 : 0;
+}
+void launch_domore_k(cudaStream_t s, const Geom &g, int *domore_k, const int *domore_u, const int *domore_v,
+                     int ju0, int ju1, int jv0, int jv1) {
+  k_domore_k<<<g.nk, TPB, 0, s>>>(g, domore_k, domore_u, domore_v, ju0, ju1, jv0, jv1);
+}
+
+// Sum of domore_k over levels -> *out (the local part of the :303-307 test).
+__global__ void k_sum_domore_k(const int *__restrict__ domore_k, int nk, int *__restrict__ out) {
+  int s = 0;
+  for (int k = threadIdx.x; k < nk; k += blockDim.x) s += domore_k[k];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+  __shared__ int ws[32];
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) { int t = 0; for (int w = 0; w < (blockDim.x + 31) / 32; w++) t += ws[w]; *out = t; }
+}
+void launch_sum_domore_k(cudaStream_t s, const int *domore_k, int nk, int *out) {
+  k_sum_domore_k<<<1, TPB, 0, s>>>(domore_k, nk, out);
+}
+
+// Entry flags of a sweep: entry(r,k) = domore_k(k)>0 .and. lo<=r<=hi .and. domore(r,k);
+// rows that will be processed have their flag cleared (:407-408 / :868-869).
+__global__ void k_flags_begin(Geom g, const int *__restrict__ domore_k, int *__restrict__ domore,
+                              int *__restrict__ entry, int lo, int hi) {
+  int rj = blockIdx.x * blockDim.x + threadIdx.x, k0 = blockIdx.y;
+  if (rj >= g.R) return;
+  int r = rj - g.roff;
+  int e = (domore_k[k0] > 0) && (r >= lo) && (r <= hi) && (domore[k0 * g.R + rj] != 0);
+  entry[k0 * g.R + rj] = e;
+  if (e) domore[k0 * g.R + rj] = 0;
+}
+void launch_flags_begin(cudaStream_t s, const Geom &g, const int *domore_k, int *domore, int *entry, int lo, int hi) {
+  dim3 grid((g.R + TPB - 1) / TPB, g.nk, 1);
+  k_flags_begin<<<grid, TPB, 0, s>>>(g, domore_k, domore, entry, lo, hi);
+}
+
+// ---------------------------------------------------------------------------
+// Mass fluxes of one sweep: uhh/vhh, CFL and the limiter flag
+// (:485-514 for x, :871-900 for y).  DIR 0 = x (face stride 1), 1 = y (stride P).
+// Written for every point of the padded array (0 where the face is not part of
+// the sweep) so that the kernels that follow need no flag logic of their own.
+// ---------------------------------------------------------------------------
+template <int DIR>
+__global__ void k_mass_flux(Geom g, Range rg, const double *__restrict__ res, const double *__restrict__ hprev,
+                            const double *__restrict__ areaT, double min_h, const int *__restrict__ entry,
+                            int *__restrict__ domore, double *__restrict__ hh, double *__restrict__ cfl) {
+  int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y, k0 = blockIdx.z;
+  if (ci >= g.P) return;
+  const int i = ci - g.coff, j = rj - g.roff;
+  const long long q = gidx(g, ci, rj, k0), q2 = gidx(g, ci, rj, 0);
+  const int st = (DIR == 0) ? 1 : g.P;
+  bool face_ok = (DIR == 0) ? (i >= rg.is - 1 && i <= rg.ie && j >= rg.js && j <= rg.je)
+                            : (i >= rg.is && i <= rg.ie && j >= rg.js - 1 && j <= rg.je);
+  double uh = 0.0, cf = 0.0;
+  if (face_ok && entry[k0 * g.R + rj]) {
+    const double ur = res[q];
+    const double hm = hprev[q], hp = hprev[q + st];   // cells on the low / high side of the face
+    const double tiny_h = DBL_MIN;
+    if ((ur == 0.0) || ((ur < 0.0) && (hp <= tiny_h)) || ((ur > 0.0) && (hm <= tiny_h))) {
+      uh = 0.0; cf = 0.0;
+    } else if (ur < 0.0) {
+      double hup = hp - areaT[q2 + st] * min_h;
+      double hlos = gmax2(0.0, res[q + st]);
+      if ((((hup - hlos) + ur) < 0.0) && ((0.5 * hup + ur) < 0.0)) {
+        uh = gmin3(-0.5 * hup, -hup + hlos, 0.0);
+        domore[k0 * g.R + rj] = 1;
+      } else {
+        uh = ur;
+      }
+      cf = -uh / hp;
+    } else {
+      double hup = hm - areaT[q2] * min_h;
+      double hlos = gmax2(0.0, -res[q - st]);
+      if ((((hup - hlos) - ur) < 0.0) && ((0.5 * hup - ur) < 0.0)) {
+        uh = gmax3(0.5 * hup, hup - hlos, 0.0);
+        domore[k0 * g.R + rj] = 1;
+      } else {
+        uh = ur;
+      }
+      cf = uh / hm;
+    }
+  }
+  hh[q] = uh; cfl[q] = cf;
+}
+void launch_mass_flux(cudaStream_t s, int dir, const Geom &g, Range rg, const double *res, const double *hprev,
+                      const double *areaT, double min_h, const int *entry, int *domore, double *hh, double *cfl) {
+  dim3 grid((g.P + TPB - 1) / TPB, g.R, g.nk);
+  if (dir == 0) k_mass_flux<0><<<grid, TPB, 0, s>>>(g, rg, res, hprev, areaT, min_h, entry, domore, hh, cfl);
+  else k_mass_flux<1><<<grid, TPB, 0, s>>>(g, rg, res, hprev, areaT, min_h, entry, domore, hh, cfl);
+}
+
+// ---------------------------------------------------------------------------
+// Residual transport and cell volume update (:632-649 for x, :1021-1040 for y).
+// ihnew == 0 encodes do_i == .false. (a true Ihnew is always > 0).
+// ---------------------------------------------------------------------------
+template <int DIR>
+__global__ void k_mass_update(Geom g, Range rg, double *__restrict__ res, double *__restrict__ hprev,
+                              const double *__restrict__ hh, const double *__restrict__ areaT,
+                              const double *__restrict__ neglect, double h_neglect,
+                              const int *__restrict__ entry, const int *__restrict__ domore_k,
+                              double *__restrict__ hlst, double *__restrict__ ihnew) {
+  int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y, k0 = blockIdx.z;
+  if (ci >= g.P) return;
+  const int i = ci - g.coff, j = rj - g.roff;
+  const long long q = gidx(g, ci, rj, k0), q2 = gidx(g, ci, rj, 0);
+  const int st = (DIR == 0) ? 1 : g.P;
+  const bool lev = domore_k[k0] > 0;
+  const bool in_i = (i >= rg.is && i <= rg.ie), in_j = (j >= rg.js && j <= rg.je);
+  bool face_ok, cell_ok;
+  if (DIR == 0) {
+    const bool row = lev && in_j && entry[k0 * g.R + rj];
+    face_ok = row && (i >= rg.is - 1 && i <= rg.ie);
+    cell_ok = row && in_i;
+  } else {
+    face_ok = lev && in_i && (j >= rg.js - 1 && j <= rg.je);
+    cell_ok = lev && in_i && in_j;
+  }
+  const double uh = hh[q];
+  if (face_ok) {
+    double r = res[q] - uh;
+    if (fabs(r) < neglect[q2]) r = 0.0;
+    res[q] = r;
+  }
+  double hl = 0.0, ih = 0.0;
+  if (cell_ok) {
+    const double uhm = hh[q - st];
+    if ((uh != 0.0) || (uhm != 0.0)) {
+      hl = hprev[q];
+      double hn = hl - (uh - uhm);
+      if (DIR == 1) hn = gmax2(hn, 0.0);
+      hprev[q] = hn;
+      const double hnegA = h_neglect * areaT[q2];
+      if (hn <= 0.0) { ih = 0.0; }
+      else if (hn < hnegA) { hl = hl + (hnegA - hn); ih = 1.0 / hnegA; }
+      else { ih = 1.0 / hn; }
+    }
+  }
+  hlst[q] = hl; ihnew[q] = ih;
+}
+void launch_mass_update(cudaStream_t s, int dir, const Geom &g, Range rg, double *res, double *hprev,
+                        const double *hh, const double *areaT, const double *neglect, double h_neglect,
+                        const int *entry, const int *domore_k, double *hlst, double *ihnew) {
+  dim3 grid((g.P + TPB - 1) / TPB, g.R, g.nk);
+  if (dir == 0) k_mass_update<0><<<grid, TPB, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew);
+  else k_mass_update<1><<<grid, TPB, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew);
+}
+
+// ---------------------------------------------------------------------------
+// Tracer sweep (unfused path): every tracer of the registry in one launch,
+// out of place (buf[src] -> buf[1-src]); a thread owns one cell and keeps the
+// tracer-independent mass quantities in registers across the tracer loop.
+//   fluxes  :517-577 / :902-963     update :652-662 / :1043-1047
+//   ad_x/ad_y :665-667 / :1070-1076  advection_xy :671-676 / :1051-1056
+//   underflow :683-687 / :1062-1066
+// W = tracer stencil half width actually read (2 for PLM and PPM:H3, 3 for PPM-CW).
+// ---------------------------------------------------------------------------
+template <int SCHEME, int DIR>
+__global__ void __launch_bounds__(TPB)
+k_tracer_sweep(Geom g, Range rg, const TracerDev *__restrict__ tr, int ntr, int src,
+               const double *__restrict__ hh, const double *__restrict__ cflv,
+               const double *__restrict__ hlstv, const double *__restrict__ ihnewv,
+               const double *__restrict__ mmv, const double *__restrict__ IareaT,
+               const int *__restrict__ entry, const int *__restrict__ domore_k, double Idt) {
+  int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y, k0 = blockIdx.z;
+  if (ci >= g.P) return;
+  const int i = ci - g.coff, j = rj - g.roff;
+  if (i < g.isd || i > g.ied || j < g.jsd || j > g.jed) return;
+  const long long q = gidx(g, ci, rj, k0), q2 = gidx(g, ci, rj, 0);
+  const int st = (DIR == 0) ? 1 : g.P;
+  constexpr int W = (SCHEME == SCHEME_PPM_CW) ? 3 : 2;
+  const bool lev = domore_k[k0] > 0;
+  const bool in_rng = (i >= rg.is && i <= rg.ie && j >= rg.js && j <= rg.je);
+  const bool hi_ok = (DIR == 0) ? (i >= rg.is - 1 && i <= rg.ie && j >= rg.js && j <= rg.je)
+                                : (i >= rg.is && i <= rg.ie && j >= rg.js - 1 && j <= rg.je);
+  const bool act_hi = lev && hi_ok && entry[k0 * g.R + rj];
+  const bool act_lo = (DIR == 0) ? act_hi : (lev && in_rng && entry[k0 * g.R + rj - 1]);
+  const double ih = (lev && in_rng) ? ihnewv[q] : 0.0;
+  const bool do_i = ih > 0.0;
+  // do_i of the next cell (east / north); outside the sweep range it reads as .false.
+  const bool nxt_in = (DIR == 0) ? (i + 1 >= rg.is && i + 1 <= rg.ie && j >= rg.js && j <= rg.je)
+                                 : (i >= rg.is && i <= rg.ie && j + 1 >= rg.js && j + 1 <= rg.je);
+  const bool do_nxt = lev && nxt_in && (ihnewv[q + st] > 0.0);
+  const bool diag_hi = act_hi && (do_i || do_nxt);
+  double uh_hi = 0.0, uh_lo = 0.0, cf_hi = 0.0, cf_lo = 0.0, hl = 0.0, mm[5] = {0, 0, 0, 0, 0}, iarea = 0.0;
+  if (do_i || diag_hi) {
+    uh_hi = hh[q]; cf_hi = cflv[q];
+    uh_lo = hh[q - st]; cf_lo = cflv[q - st];
+    hl = hlstv[q];
+#pragma unroll
+    for (int s = -2; s <= 2; s++) mm[s + 2] = mmv[q2 + s * st];
+    iarea = IareaT[q2];
+  }
+  for (int m = 0; m < ntr; m++) {
+    const double *__restrict__ tin = tr[m].buf[src];
+    double *__restrict__ tout = tr[m].buf[1 - src];
+    const double Tc = tin[q];
+    double out = Tc;
+    if (do_i || diag_hi) {
+      double t[7];
+#pragma unroll
+      for (int s = -3; s <= 3; s++) t[s + 3] = (s >= -W && s <= W) ? tin[q + s * st] : 0.0;
+      double f_hi = 0.0, f_lo = 0.0;
+      if (act_hi) f_hi = face_flux<SCHEME>(&t[1], &mm[1], uh_hi, cf_hi);
+      if (do_i) {
+        if (act_lo) f_lo = face_flux<SCHEME>(&t[0], &mm[0], uh_lo, cf_lo);
+        out = (Tc * hl - (f_hi - f_lo)) * ih;
+        double *axy = tr[m].adv_xy;
+        if (axy) axy[q] = axy[q] - (f_hi - f_lo) * Idt * iarea;
+      }
+      double *ad = (DIR == 0) ? tr[m].ad_x : tr[m].ad_y;
+      if (ad && diag_hi) ad[q] = ad[q] + f_hi * Idt;
+    }
+    const double cu = tr[m].conc_underflow;
+    if (lev && in_rng && cu > 0.0 && fabs(out) < cu) out = 0.0;
+    tout[q] = out;
+  }
+}
+
+template <int SCHEME>
+static void launch_tracer_sweep_s(cudaStream_t s, int dir, const Geom &g, Range rg, const TracerDev *tr, int ntr,
+                                  int src, const double *hh, const double *cfl, const double *hlst,
+                                  const double *ihnew, const double *mm, const double *IareaT,
+                                  const int *entry, const int *domore_k, double Idt) {
+  dim3 grid((g.P + TPB - 1) / TPB, g.R, g.nk);
+  if (dir == 0) k_tracer_sweep<SCHEME, 0><<<grid, TPB, 0, s>>>(g, rg, tr, ntr, src, hh, cfl, hlst, ihnew, mm, IareaT, entry, domore_k, Idt);
+  else k_tracer_sweep<SCHEME, 1><<<grid, TPB, 0, s>>>(g, rg, tr, ntr, src, hh, cfl, hlst, ihnew, mm, IareaT, entry, domore_k, Idt);
+}
+void launch_tracer_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TracerDev *tr, int ntr,
+                         int src, const double *hh, const double *cfl, const double *hlst, const double *ihnew,
+                         const double *mm, const double *IareaT, const int *entry, const int *domore_k, double Idt) {
+  if (scheme == SCHEME_PLM) launch_tracer_sweep_s<SCHEME_PLM>(s, dir, g, rg, tr, ntr, src, hh, cfl, hlst, ihnew, mm, IareaT, entry, domore_k, Idt);
+  else if (scheme == SCHEME_PPM_CW) launch_tracer_sweep_s<SCHEME_PPM_CW>(s, dir, g, rg, tr, ntr, src, hh, cfl, hlst, ihnew, mm, IareaT, entry, domore_k, Idt);
+  else launch_tracer_sweep_s<SCHEME_PPM_H3>(s, dir, g, rg, tr, ntr, src, hh, cfl, hlst, ihnew, mm, IareaT, entry, domore_k, Idt);
+}
+
+// ---------------------------------------------------------------------------
+// ad2d_x / ad2d_y (:691-699 / :1078-1084): vertical sums of the face fluxes in
+// the reference's k order.  One thread per face column walks k = 1..nk and
+// recomputes the flux from the sweep's (still intact) input buffer.
+// ---------------------------------------------------------------------------
+template <int SCHEME, int DIR>
+__global__ void k_ad2d(Geom g, Range rg, const TracerDev *__restrict__ tr, int ntr, int src,
+                       const double *__restrict__ hh, const double *__restrict__ cflv,
+                       const double *__restrict__ ihnewv, const double *__restrict__ mmv,
+                       const int *__restrict__ entry, const int *__restrict__ domore_k, double Idt) {
+  int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y;
+  if (ci >= g.P) return;
+  const int i = ci - g.coff, j = rj - g.roff;
+  const bool hi_ok = (DIR == 0) ? (i >= rg.is - 1 && i <= rg.ie && j >= rg.js && j <= rg.je)
+                                : (i >= rg.is && i <= rg.ie && j >= rg.js - 1 && j <= rg.je);
+  if (!hi_ok) return;
+  const int st = (DIR == 0) ? 1 : g.P;
+  constexpr int W = (SCHEME == SCHEME_PPM_CW) ? 3 : 2;
+  const bool cur_in = (i >= rg.is && i <= rg.ie && j >= rg.js && j <= rg.je);
+  const bool nxt_in = (DIR == 0) ? (i + 1 <= rg.ie) : (j + 1 <= rg.je);
+  const long long q2 = gidx(g, ci, rj, 0);
+  double mm[4];
+#pragma unroll
+  for (int s = -1; s <= 2; s++) mm[s + 1] = mmv[q2 + s * st];
+  for (int m = 0; m < ntr; m++) {
+    double *a2 = (DIR == 0) ? tr[m].ad2d_x : tr[m].ad2d_y;
+    if (!a2) continue;
+    const double *__restrict__ tin = tr[m].buf[src];
+    double acc = a2[q2];
+    for (int k0 = 0; k0 < g.nk; k0++) {
+      if (domore_k[k0] <= 0 || !entry[k0 * g.R + rj]) continue;
+      const long long q = q2 + g.plane * k0;
+      const bool d = (cur_in && ihnewv[q] > 0.0) || (nxt_in && ihnewv[q + st] > 0.0);
+      if (!d) continue;
+      double t[6];
+#pragma unroll
+      for (int s = -2; s <= 3; s++) t[s + 2] = (s >= 1 - W && s <= W) ? tin[q + s * st] : 0.0;
+      acc = acc + face_flux<SCHEME>(t, mm, hh[q], cflv[q]) * Idt;
+    }
+    a2[q2] = acc;
+  }
+}
+void launch_ad2d(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TracerDev *tr, int ntr, int src,
+                 const double *hh, const double *cfl, const double *ihnew, const double *mm, const int *entry,
+                 const int *domore_k, double Idt) {
+  dim3 grid((g.P + TPB - 1) / TPB, g.R, 1);
+#define AD2D(S, D) k_ad2d<S, D><<<grid, TPB, 0, s>>>(g, rg, tr, ntr, src, hh, cfl, ihnew, mm, entry, domore_k, Idt)
+  if (scheme == SCHEME_PLM) { if (dir == 0) AD2D(SCHEME_PLM, 0); else AD2D(SCHEME_PLM, 1); }
+  else if (scheme == SCHEME_PPM_CW) { if (dir == 0) AD2D(SCHEME_PPM_CW, 0); else AD2D(SCHEME_PPM_CW, 1); }
+  else { if (dir == 0) AD2D(SCHEME_PPM_H3, 0); else AD2D(SCHEME_PPM_H3, 1); }
+#undef AD2D
+}
+
+// ---------------------------------------------------------------------------
+// C1: group pass on one device (:206).  The plan precomputes, per stagger, a
+// list of (dst, src, sign) plane offsets that encodes closed / cyclic / north
+// fold topology; one launch fills the halos of every listed field and level.
+// Sources are computational-domain points, destinations halo points: disjoint.
+// ---------------------------------------------------------------------------
+__global__ void k_halo_apply(long long plane, int nk, const int *__restrict__ dst, const int *__restrict__ srcv,
+                             const signed char *__restrict__ sgn, int n, double *const *__restrict__ fields,
+                             int src_sel /* -1: fields are plain pointers */) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int k0 = blockIdx.y;
+  double *f = fields[blockIdx.z];
+  const long long o = plane * k0;
+  double v = f[o + srcv[t]];
+  f[o + dst[t]] = (sgn[t] < 0) ? -v : v;
+  (void)nk; (void)src_sel;
+}
+void launch_halo_apply(cudaStream_t s, long long plane, int nk, const int *dst, const int *src,
+                       const signed char *sgn, int n, double *const *fields, int nfields) {
+  if (n <= 0 || nfields <= 0) return;
+  dim3 grid((n + TPB - 1) / TPB, nk, nfields);
+  k_halo_apply<<<grid, TPB, 0, s>>>(plane, nk, dst, src, sgn, n, fields, -1);
+}
+
+// Pack / unpack of halo strips for the multi-GPU exchange: buffer layout is
+// [field][level][point] so that one message per neighbour carries all fields.
+__global__ void k_halo_pack(long long plane, int nk, const int *__restrict__ srcv, const signed char *__restrict__ sgn,
+                            int n, double *const *__restrict__ fields, double *__restrict__ buf) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int k0 = blockIdx.y, f = blockIdx.z;
+  double v = fields[f][plane * k0 + srcv[t]];
+  buf[((long long)f * nk + k0) * n + t] = (sgn[t] < 0) ? -v : v;
+}
+__global__ void k_halo_unpack(long long plane, int nk, const int *__restrict__ dstv, int n,
+                              double *const *__restrict__ fields, const double *__restrict__ buf) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int k0 = blockIdx.y, f = blockIdx.z;
+  fields[f][plane * k0 + dstv[t]] = buf[((long long)f * nk + k0) * n + t];
+}
+void launch_halo_pack(cudaStream_t s, long long plane, int nk, const int *src, const signed char *sgn, int n,
+                      double *const *fields, int nfields, double *buf) {
+  if (n <= 0 || nfields <= 0) return;
+  dim3 grid((n + TPB - 1) / TPB, nk, nfields);
+  k_halo_pack<<<grid, TPB, 0, s>>>(plane, nk, src, sgn, n, fields, buf);
+}
+void launch_halo_unpack(cudaStream_t s, long long plane, int nk, const int *dst, int n,
+                        double *const *fields, int nfields, const double *buf) {
+  if (n <= 0 || nfields <= 0) return;
+  dim3 grid((n + TPB - 1) / TPB, nk, nfields);
+  k_halo_unpack<<<grid, TPB, 0, s>>>(plane, nk, dst, n, fields, buf);
+}
+
+__global__ void k_fill(double *p, long long n, double v) {
+  long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) p[t] = v;
+}
+void launch_fill(cudaStream_t s, double *p, long long n, double v) {
+  if (n <= 0) return;
+  k_fill<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p, n, v);
+}

@@ -1,0 +1,35 @@
+// Host-callable launch wrappers of kernels.cu (internal).
+#pragma once
+#include "internal.cuh"
+
+void launch_repack_in(cudaStream_t s, const Geom &g, double *dst, const double *src, int ilo, int jlo, int nlev);
+void launch_repack_out(cudaStream_t s, const Geom &g, double *dst, const double *src, int ilo, int jlo, int nlev);
+void launch_neglect(cudaStream_t s, const Geom &g, const double *areaT, const double *mCu, const double *mCv,
+                    double Hsub, double *uhn, double *vhn, double *mmx, double *mmy);
+void launch_init_residuals(cudaStream_t s, const Geom &g, const double *h_end, const double *uhtr,
+                           const double *vhtr, const double *vol_prev, const double *areaT,
+                           double *uhr, double *vhr, double *hprev);
+void launch_rescan(cudaStream_t s, const Geom &g, const double *uhr, const double *vhr, const int *domore_k,
+                   int *domore_u, int *domore_v, int isv, int iev, int jsv, int jev, int stencil);
+void launch_domore_k(cudaStream_t s, const Geom &g, int *domore_k, const int *domore_u, const int *domore_v,
+                     int ju0, int ju1, int jv0, int jv1);
+void launch_sum_domore_k(cudaStream_t s, const int *domore_k, int nk, int *out);
+void launch_flags_begin(cudaStream_t s, const Geom &g, const int *domore_k, int *domore, int *entry, int lo, int hi);
+void launch_mass_flux(cudaStream_t s, int dir, const Geom &g, Range rg, const double *res, const double *hprev,
+                      const double *areaT, double min_h, const int *entry, int *domore, double *hh, double *cfl);
+void launch_mass_update(cudaStream_t s, int dir, const Geom &g, Range rg, double *res, double *hprev,
+                        const double *hh, const double *areaT, const double *neglect, double h_neglect,
+                        const int *entry, const int *domore_k, double *hlst, double *ihnew);
+void launch_tracer_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TracerDev *tr, int ntr,
+                         int src, const double *hh, const double *cfl, const double *hlst, const double *ihnew,
+                         const double *mm, const double *IareaT, const int *entry, const int *domore_k, double Idt);
+void launch_ad2d(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TracerDev *tr, int ntr, int src,
+                 const double *hh, const double *cfl, const double *ihnew, const double *mm, const int *entry,
+                 const int *domore_k, double Idt);
+void launch_halo_apply(cudaStream_t s, long long plane, int nk, const int *dst, const int *src,
+                       const signed char *sgn, int n, double *const *fields, int nfields);
+void launch_halo_pack(cudaStream_t s, long long plane, int nk, const int *src, const signed char *sgn, int n,
+                      double *const *fields, int nfields, double *buf);
+void launch_halo_unpack(cudaStream_t s, long long plane, int nk, const int *dst, int n,
+                        double *const *fields, int nfields, const double *buf);
+void launch_fill(cudaStream_t s, double *p, long long n, double v);

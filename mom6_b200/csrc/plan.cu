@@ -1,0 +1,688 @@
+// C ABI of include/mom6adv.h: plan object, HBM residency, and the host-side
+// iteration driver of advect_tracer (/root/reference/src/tracer/MOM_tracer_advect.F90:112-320).
+#include "../../include/mom6adv.h"
+#include "internal.cuh"
+#include "kernels.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#define MOM6ADV_VERSION "mom6adv-b200 0.1 (sm_100a)"
+
+struct TracerSlot {
+  double *host_t = nullptr;                 // MIRROR-mode location of Tr(m)%t (host or device, Fortran layout)
+  double *host_diag[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // ad_x, ad_y, ad2d_x, ad2d_y, advection_xy
+  double *buf[2] = {nullptr, nullptr};      // padded HBM storage (ping-pong)
+  double *diag[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  double conc_underflow = 0.0;
+  bool bound = false;
+};
+
+struct HaloList {       // one stagger position
+  int n = 0;
+  int *dst = nullptr, *src = nullptr;
+  signed char *sgn = nullptr;
+};
+
+struct mom6adv_plan {
+  Geom g;
+  mom6adv_config cfg;
+  mom6adv_domain dom;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  double Angstrom_H = 0, H_subroundoff = 0;
+  int IedB = 0, JedB = 0;
+  // 2-D grid fields (one padded plane each)
+  double *areaT = nullptr, *IareaT = nullptr, *mCu = nullptr, *mCv = nullptr;
+  double *uh_neglect = nullptr, *vh_neglect = nullptr, *mmx = nullptr, *mmy = nullptr;
+  // 3-D fields
+  double *h_end = nullptr, *uhtr = nullptr, *vhtr = nullptr, *vol_prev = nullptr;
+  double *uhr = nullptr, *vhr = nullptr, *hprev = nullptr;
+  double *hh = nullptr, *cfl = nullptr, *hlst = nullptr, *ihnew = nullptr;
+  int *domore_u = nullptr, *domore_v = nullptr, *entry_u = nullptr, *entry_v = nullptr, *domore_k = nullptr;
+  int *sum_dev = nullptr, *sum_host = nullptr;
+  double *staging = nullptr;
+  long long staging_elems = 0;
+  std::vector<TracerSlot> tr;
+  int ntr = 0;
+  int cur = 0;                       // live ping-pong buffer of every tracer
+  TracerDev *tr_dev = nullptr;       // device copy of the tracer table
+  bool tr_dirty = true;
+  double **halo_fields_dev = nullptr;  // [uhr], [vhr], [hprev, T...]
+  int halo_fields_cap = 0;
+  HaloList halo[3];                  // 0 = h points, 1 = u points, 2 = v points
+  std::string err;
+  double last_ms = 0.0;
+  long long launches = 0;
+  long long dev_bytes = 0;
+  int opt_fused = 0;
+};
+
+static thread_local std::string g_err;
+
+#define CK(call)                                                                            \
+  do {                                                                                      \
+    cudaError_t e_ = (call);                                                                \
+    if (e_ != cudaSuccess) {                                                                \
+      char b_[512];                                                                         \
+      snprintf(b_, sizeof b_, "CUDA error %s at %s:%d (%s)", cudaGetErrorString(e_), __FILE__, __LINE__, #call); \
+      if (plan) plan->err = b_; g_err = b_;                                                 \
+      return MOM6ADV_ERR_CUDA;                                                              \
+    }                                                                                       \
+  } while (0)
+
+static int fail(mom6adv_plan *plan, int code, const std::string &msg) {
+  if (plan) plan->err = msg;
+  g_err = msg;
+  return code;
+}
+
+static long long field_elems(const mom6adv_plan *p) { return p->g.plane * p->g.nk; }
+
+template <typename T>
+static int dev_alloc(mom6adv_plan *plan, T **out, long long n) {
+  CK(cudaMalloc((void **)out, sizeof(T) * (size_t)std::max<long long>(n, 1)));
+  CK(cudaMemsetAsync(*out, 0, sizeof(T) * (size_t)std::max<long long>(n, 1), plan->stream));
+  plan->dev_bytes += (long long)sizeof(T) * n;
+  return 0;
+}
+
+static bool is_device_ptr(const void *p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// Fortran-layout array (ilo:ied, jlo:jed, nlev) -> padded field
+static int upload(mom6adv_plan *plan, double *dst, const double *src, int ilo, int jlo, int nlev) {
+  const Geom &g = plan->g;
+  const long long n = (long long)(g.ied - ilo + 1) * (g.jed - jlo + 1) * nlev;
+  if (is_device_ptr(src)) {
+    launch_repack_in(plan->stream, g, dst, src, ilo, jlo, nlev);
+  } else {
+    CK(cudaMemcpyAsync(plan->staging, src, sizeof(double) * n, cudaMemcpyHostToDevice, plan->stream));
+    launch_repack_in(plan->stream, g, dst, plan->staging, ilo, jlo, nlev);
+  }
+  plan->launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+static int download(mom6adv_plan *plan, double *dst, const double *src, int ilo, int jlo, int nlev) {
+  const Geom &g = plan->g;
+  const long long n = (long long)(g.ied - ilo + 1) * (g.jed - jlo + 1) * nlev;
+  if (is_device_ptr(dst)) {
+    launch_repack_out(plan->stream, g, dst, src, ilo, jlo, nlev);
+  } else {
+    launch_repack_out(plan->stream, g, plan->staging, src, ilo, jlo, nlev);
+    CK(cudaMemcpyAsync(dst, plan->staging, sizeof(double) * n, cudaMemcpyDeviceToHost, plan->stream));
+  }
+  plan->launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// Halo lists: for every halo point of a stagger, the computational-domain
+// point that a full-width group pass would copy into it (closed boundaries
+// have none).  Same index algebra as FMS's update for cyclic edges and the
+// north fold (scalars mirror in i; C-grid vector components also change sign).
+// Single-block version (npi = npj = 1); the multi-GPU lists are built by
+// halo.cu from the same locate() rule.
+// ---------------------------------------------------------------------------
+struct HostHalo { std::vector<int> dst, src; std::vector<signed char> sgn; };
+
+static bool locate_self(const mom6adv_plan *p, int pos, int ig, int jg, int *il, int *jl, int *sg) {
+  const mom6adv_domain &d = p->dom;
+  const Geom &g = p->g;
+  *sg = 1;
+  if (d.tripolar_n && jg > d.njg) {
+    if (pos == 0) { ig = d.nig + 1 - ig; jg = 2 * d.njg + 1 - jg; }
+    else if (pos == 1) { ig = d.nig - ig; jg = 2 * d.njg + 1 - jg; *sg = -1; }
+    else { ig = d.nig + 1 - ig; jg = 2 * d.njg - jg; *sg = -1; }
+  }
+  const int ilo = (pos == 1) ? 0 : 1, jlo = (pos == 2) ? 0 : 1;
+  if (d.cyclic_x) { while (ig < 1) ig += d.nig; while (ig > d.nig) ig -= d.nig; }
+  else if (ig < ilo || ig > d.nig) return false;
+  if (d.cyclic_y) { while (jg < 1) jg += d.njg; while (jg > d.njg) jg -= d.njg; }
+  else if (jg < jlo || jg > d.njg) return false;
+  int i = ig - d.ioff, j = jg - d.joff;
+  int i0 = g.isc, j0 = g.jsc;
+  if (pos == 1 && ig == 0) i0 = g.isc - 1;
+  if (pos == 2 && jg == 0) j0 = g.jsc - 1;
+  if (i >= i0 && i <= g.iec && j >= j0 && j <= g.jec) { *il = i; *jl = j; return true; }
+  return false;
+}
+
+static void build_halo_host(const mom6adv_plan *p, int pos, HostHalo &out) {
+  const Geom &g = p->g;
+  const bool symmetric = (g.IsdB == g.isd - 1);
+  const int ilo = (pos == 1) ? g.IsdB : g.isd, jlo = (pos == 2) ? g.JsdB : g.jsd;
+  int ic0 = g.isc, jc0 = g.jsc;
+  if (symmetric) { if (pos == 1) ic0 = g.isc - 1; if (pos == 2) jc0 = g.jsc - 1; }
+  for (int j = jlo; j <= g.jed; j++) for (int i = ilo; i <= g.ied; i++) {
+    if (i >= ic0 && i <= g.iec && j >= jc0 && j <= g.jec) continue;
+    int il, jl, sg;
+    if (!locate_self(p, pos, i + p->dom.ioff, j + p->dom.joff, &il, &jl, &sg)) continue;
+    out.dst.push_back((i + g.coff) + g.P * (j + g.roff));
+    out.src.push_back((il + g.coff) + g.P * (jl + g.roff));
+    out.sgn.push_back((signed char)sg);
+  }
+}
+
+static int upload_halo_list(mom6adv_plan *plan, const HostHalo &h, HaloList &d) {
+  d.n = (int)h.dst.size();
+  if (d.n == 0) return 0;
+  CK(cudaMalloc((void **)&d.dst, sizeof(int) * d.n));
+  CK(cudaMalloc((void **)&d.src, sizeof(int) * d.n));
+  CK(cudaMalloc((void **)&d.sgn, d.n));
+  CK(cudaMemcpy(d.dst, h.dst.data(), sizeof(int) * d.n, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d.src, h.src.data(), sizeof(int) * d.n, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(d.sgn, h.sgn.data(), d.n, cudaMemcpyHostToDevice));
+  plan->dev_bytes += 9LL * d.n;
+  return 0;
+}
+
+static int create_impl(mom6adv_plan *plan, const mom6adv_grid *gr) {
+  Geom &g = plan->g;
+  CK(cudaSetDevice(plan->device));
+  CK(cudaStreamCreateWithFlags(&plan->stream, cudaStreamNonBlocking));
+  CK(cudaEventCreate(&plan->ev0));
+  CK(cudaEventCreate(&plan->ev1));
+  const long long pl = g.plane;
+  double **p2[] = {&plan->areaT, &plan->IareaT, &plan->mCu, &plan->mCv,
+                   &plan->uh_neglect, &plan->vh_neglect, &plan->mmx, &plan->mmy};
+  for (double **pp : p2) { int rc = dev_alloc(plan, pp, pl); if (rc) return rc; }
+  const long long fe = field_elems(plan);
+  double **p3[] = {&plan->h_end, &plan->uhtr, &plan->vhtr, &plan->uhr, &plan->vhr, &plan->hprev,
+                   &plan->hh, &plan->cfl, &plan->hlst, &plan->ihnew};
+  for (double **pp : p3) { int rc = dev_alloc(plan, pp, fe); if (rc) return rc; }
+  int **pf[] = {&plan->domore_u, &plan->domore_v, &plan->entry_u, &plan->entry_v};
+  for (int **pp : pf) { int rc = dev_alloc(plan, pp, (long long)g.R * g.nk); if (rc) return rc; }
+  { int rc = dev_alloc(plan, &plan->domore_k, g.nk); if (rc) return rc; }
+  { int rc = dev_alloc(plan, &plan->sum_dev, 4); if (rc) return rc; }
+  CK(cudaMallocHost((void **)&plan->sum_host, sizeof(int) * 4));
+  // staging buffer: the largest Fortran-layout 3-D field (u or v stagger)
+  plan->staging_elems = (long long)(g.ied - g.isd + 2) * (g.jed - g.jsd + 2) * g.nk;
+  { int rc = dev_alloc(plan, &plan->staging, plan->staging_elems); if (rc) return rc; }
+
+  // grid fields
+  int rc;
+  if ((rc = upload(plan, plan->areaT, gr->areaT, g.isd, g.jsd, 1))) return rc;
+  CK(cudaStreamSynchronize(plan->stream));
+  if ((rc = upload(plan, plan->IareaT, gr->IareaT, g.isd, g.jsd, 1))) return rc;
+  CK(cudaStreamSynchronize(plan->stream));
+  if ((rc = upload(plan, plan->mCu, gr->mask2dCu, g.IsdB, g.jsd, 1))) return rc;
+  CK(cudaStreamSynchronize(plan->stream));
+  if ((rc = upload(plan, plan->mCv, gr->mask2dCv, g.isd, g.JsdB, 1))) return rc;
+  CK(cudaStreamSynchronize(plan->stream));
+  launch_neglect(plan->stream, g, plan->areaT, plan->mCu, plan->mCv, plan->H_subroundoff,
+                 plan->uh_neglect, plan->vh_neglect, plan->mmx, plan->mmy);
+  plan->launches++;
+  CK(cudaGetLastError());
+
+  for (int pos = 0; pos < 3; pos++) {
+    HostHalo hh;
+    build_halo_host(plan, pos, hh);
+    if ((rc = upload_halo_list(plan, hh, plan->halo[pos]))) return rc;
+  }
+  CK(cudaStreamSynchronize(plan->stream));
+  return 0;
+}
+
+extern "C" const char *mom6adv_version(void) { return MOM6ADV_VERSION; }
+
+extern "C" const char *mom6adv_last_error(const mom6adv_plan *plan) {
+  return plan ? plan->err.c_str() : g_err.c_str();
+}
+
+extern "C" int mom6adv_plan_create(const mom6adv_grid *gr, const mom6adv_config *c, const mom6adv_domain *dom,
+                                   int device, mom6adv_plan **out) {
+  if (!gr || !c || !out) return fail(nullptr, MOM6ADV_ERR_INVALID, "plan_create: NULL argument");
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+    cudaGetLastError();
+    return fail(nullptr, MOM6ADV_ERR_CUDA, "plan_create: no CUDA device (this library has no CPU fallback)");
+  }
+  if (device < 0) { if (cudaGetDevice(&device) != cudaSuccess) return fail(nullptr, MOM6ADV_ERR_CUDA, "cudaGetDevice failed"); }
+  if (device >= ndev) return fail(nullptr, MOM6ADV_ERR_INVALID, "plan_create: bad device index");
+  if (!gr->areaT || !gr->IareaT || !gr->mask2dCu || !gr->mask2dCv)
+    return fail(nullptr, MOM6ADV_ERR_INVALID, "plan_create: grid arrays missing");
+  const int hi = gr->isc - gr->isd, hj = gr->jsc - gr->jsd;
+  if (gr->nk < 1 || gr->iec < gr->isc || gr->jec < gr->jsc || hi < 0 || hj < 0 ||
+      gr->IsdB < gr->isd - 1 || gr->IsdB > gr->isd || gr->JsdB < gr->jsd - 1 || gr->JsdB > gr->jsd)
+    return fail(nullptr, MOM6ADV_ERR_INVALID, "plan_create: inconsistent grid bounds");
+
+  mom6adv_plan *plan = new mom6adv_plan();
+  plan->cfg = *c;
+  plan->device = device;
+  plan->Angstrom_H = gr->Angstrom_H;
+  plan->H_subroundoff = gr->H_subroundoff;
+  plan->IedB = gr->IedB; plan->JedB = gr->JedB;
+  Geom &g = plan->g;
+  g.isd = gr->isd; g.ied = gr->ied; g.jsd = gr->jsd; g.jed = gr->jed;
+  g.isc = gr->isc; g.iec = gr->iec; g.jsc = gr->jsc; g.jec = gr->jec;
+  g.IsdB = gr->IsdB; g.JsdB = gr->JsdB; g.nk = gr->nk;
+  const int nid = g.ied - g.isd + 1, njd = g.jed - g.jsd + 1;
+  const int lead = ((hi + 1 + 15) / 16) * 16 - hi;      // column of isd; isc lands on a multiple of 16
+  g.coff = lead - g.isd;
+  g.P = ((lead + nid + 1 + 15) / 16) * 16;
+  g.roff = 1 - g.jsd;
+  g.R = njd + 2;
+  g.plane = (long long)g.P * g.R;
+  if (dom) plan->dom = *dom;
+  else {
+    mom6adv_domain d = {};
+    d.nig = g.iec - g.isc + 1; d.njg = g.jec - g.jsc + 1; d.npi = d.npj = 1;
+    d.ioff = -(g.isc - 1); d.joff = -(g.jsc - 1);
+    plan->dom = d;
+  }
+  if (plan->dom.npi * plan->dom.npj != 1) {
+    delete plan;
+    return fail(nullptr, MOM6ADV_ERR_UNSUPPORTED, "plan_create: multi-block layouts go through mom6adv_halo_config");
+  }
+  int rc = create_impl(plan, gr);
+  if (rc) { g_err = plan->err; mom6adv_plan_destroy(plan); return rc; }
+  *out = plan;
+  return MOM6ADV_OK;
+}
+
+static void free_slot(TracerSlot &s) {
+  for (int b = 0; b < 2; b++) if (s.buf[b]) { cudaFree(s.buf[b]); s.buf[b] = nullptr; }
+  for (int d = 0; d < 5; d++) if (s.diag[d]) { cudaFree(s.diag[d]); s.diag[d] = nullptr; }
+}
+
+extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
+  if (!plan) return MOM6ADV_OK;
+  cudaSetDevice(plan->device);
+  if (plan->stream) cudaStreamSynchronize(plan->stream);
+  double *d[] = {plan->areaT, plan->IareaT, plan->mCu, plan->mCv, plan->uh_neglect, plan->vh_neglect, plan->mmx,
+                 plan->mmy, plan->h_end, plan->uhtr, plan->vhtr, plan->vol_prev, plan->uhr, plan->vhr, plan->hprev,
+                 plan->hh, plan->cfl, plan->hlst, plan->ihnew, plan->staging};
+  for (double *p : d) if (p) cudaFree(p);
+  int *f[] = {plan->domore_u, plan->domore_v, plan->entry_u, plan->entry_v, plan->domore_k, plan->sum_dev};
+  for (int *p : f) if (p) cudaFree(p);
+  if (plan->sum_host) cudaFreeHost(plan->sum_host);
+  for (auto &s : plan->tr) free_slot(s);
+  if (plan->tr_dev) cudaFree(plan->tr_dev);
+  if (plan->halo_fields_dev) cudaFree(plan->halo_fields_dev);
+  for (int p = 0; p < 3; p++) {
+    if (plan->halo[p].dst) cudaFree(plan->halo[p].dst);
+    if (plan->halo[p].src) cudaFree(plan->halo[p].src);
+    if (plan->halo[p].sgn) cudaFree(plan->halo[p].sgn);
+  }
+  if (plan->ev0) cudaEventDestroy(plan->ev0);
+  if (plan->ev1) cudaEventDestroy(plan->ev1);
+  if (plan->stream) cudaStreamDestroy(plan->stream);
+  delete plan;
+  return MOM6ADV_OK;
+}
+
+extern "C" int mom6adv_set_ntr(mom6adv_plan *plan, int ntr) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "set_ntr: plan not initialised");
+  if (ntr < 0) return fail(plan, MOM6ADV_ERR_INVALID, "set_ntr: ntr < 0");
+  CK(cudaSetDevice(plan->device));
+  for (int m = ntr; m < (int)plan->tr.size(); m++) free_slot(plan->tr[m]);
+  plan->tr.resize(ntr);
+  const long long fe = field_elems(plan);
+  for (int m = 0; m < ntr; m++)
+    for (int b = 0; b < 2; b++)
+      if (!plan->tr[m].buf[b]) { int rc = dev_alloc(plan, &plan->tr[m].buf[b], fe); if (rc) return rc; }
+  plan->ntr = ntr;
+  plan->tr_dirty = true;
+  return MOM6ADV_OK;
+}
+
+extern "C" int mom6adv_bind_tracer(mom6adv_plan *plan, int m, double *t, double conc_underflow, double *ad_x,
+                                   double *ad_y, double *ad2d_x, double *ad2d_y, double *advection_xy) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "bind_tracer: plan not initialised");
+  if (m < 0 || m >= plan->ntr) return fail(plan, MOM6ADV_ERR_INVALID, "bind_tracer: tracer index out of range");
+  CK(cudaSetDevice(plan->device));
+  TracerSlot &s = plan->tr[m];
+  s.host_t = t;
+  s.conc_underflow = conc_underflow;
+  double *hd[5] = {ad_x, ad_y, ad2d_x, ad2d_y, advection_xy};
+  for (int d = 0; d < 5; d++) {
+    s.host_diag[d] = hd[d];
+    const bool two_d = (d == 2 || d == 3);
+    if (hd[d] && !s.diag[d]) { int rc = dev_alloc(plan, &s.diag[d], two_d ? plan->g.plane : field_elems(plan)); if (rc) return rc; }
+    if (!hd[d] && s.diag[d]) { cudaFree(s.diag[d]); s.diag[d] = nullptr; }
+  }
+  s.bound = true;
+  plan->tr_dirty = true;
+  return MOM6ADV_OK;
+}
+
+// Enable a diagnostic in RESIDENT mode without a host array (kind as in download_diag).
+static int sync_tracer_table(mom6adv_plan *plan) {
+  if (!plan->tr_dirty) return 0;
+  std::vector<TracerDev> h(std::max(plan->ntr, 1));
+  for (int m = 0; m < plan->ntr; m++) {
+    const TracerSlot &s = plan->tr[m];
+    h[m].buf[0] = s.buf[0]; h[m].buf[1] = s.buf[1];
+    h[m].ad_x = s.diag[0]; h[m].ad_y = s.diag[1]; h[m].ad2d_x = s.diag[2]; h[m].ad2d_y = s.diag[3]; h[m].adv_xy = s.diag[4];
+    h[m].conc_underflow = s.conc_underflow;
+  }
+  if (plan->tr_dev) { cudaFree(plan->tr_dev); plan->tr_dev = nullptr; }
+  CK(cudaMalloc((void **)&plan->tr_dev, sizeof(TracerDev) * h.size()));
+  CK(cudaMemcpyAsync(plan->tr_dev, h.data(), sizeof(TracerDev) * h.size(), cudaMemcpyHostToDevice, plan->stream));
+  // halo field table: [0] = uhr, [1] = vhr, [2] = hprev, [3..] = tracers (buffer 0)
+  const int nf = 3 + plan->ntr;
+  std::vector<double *> hf(nf);
+  hf[0] = plan->uhr; hf[1] = plan->vhr; hf[2] = plan->hprev;
+  for (int m = 0; m < plan->ntr; m++) hf[3 + m] = plan->tr[m].buf[0];
+  if (plan->halo_fields_dev) { cudaFree(plan->halo_fields_dev); plan->halo_fields_dev = nullptr; }
+  CK(cudaMalloc((void **)&plan->halo_fields_dev, sizeof(double *) * nf));
+  CK(cudaMemcpyAsync(plan->halo_fields_dev, hf.data(), sizeof(double *) * nf, cudaMemcpyHostToDevice, plan->stream));
+  CK(cudaStreamSynchronize(plan->stream));
+  plan->tr_dirty = false;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// do_group_pass (:206) on one device.
+// ---------------------------------------------------------------------------
+static int group_pass(mom6adv_plan *plan) {
+  const Geom &g = plan->g;
+  cudaStream_t s = plan->stream;
+  // u list -> uhr, v list -> vhr, h list -> hprev + tracers
+  launch_halo_apply(s, g.plane, g.nk, plan->halo[1].dst, plan->halo[1].src, plan->halo[1].sgn, plan->halo[1].n,
+                    plan->halo_fields_dev + 0, 1);
+  launch_halo_apply(s, g.plane, g.nk, plan->halo[2].dst, plan->halo[2].src, plan->halo[2].sgn, plan->halo[2].n,
+                    plan->halo_fields_dev + 1, 1);
+  launch_halo_apply(s, g.plane, g.nk, plan->halo[0].dst, plan->halo[0].src, plan->halo[0].sgn, plan->halo[0].n,
+                    plan->halo_fields_dev + 2, 1 + plan->ntr);
+  plan->launches += 3;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+// One directional sweep over cells [is..ie] x [js..je] (advect_x :329 / advect_y :705),
+// all levels with domore_k > 0, all tracers.
+static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme) {
+  const Geom &g = plan->g;
+  cudaStream_t s = plan->stream;
+  const double min_h = 0.1 * plan->Angstrom_H;        // :401 / :773
+  const double h_neglect = plan->H_subroundoff;       // :403 / :775
+  bool any_ad2d = false;
+  for (int m = 0; m < plan->ntr; m++) if (plan->tr[m].diag[dir == 0 ? 2 : 3]) any_ad2d = true;
+  if (dir == 0) {
+    launch_flags_begin(s, g, plan->domore_k, plan->domore_u, plan->entry_u, rg.js, rg.je);
+    launch_mass_flux(s, 0, g, rg, plan->uhr, plan->hprev, plan->areaT, min_h, plan->entry_u, plan->domore_u, plan->hh, plan->cfl);
+    launch_mass_update(s, 0, g, rg, plan->uhr, plan->hprev, plan->hh, plan->areaT, plan->uh_neglect, h_neglect,
+                       plan->entry_u, plan->domore_k, plan->hlst, plan->ihnew);
+    launch_tracer_sweep(s, scheme, 0, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->hlst,
+                        plan->ihnew, plan->mmx, plan->IareaT, plan->entry_u, plan->domore_k, Idt);
+    if (any_ad2d) launch_ad2d(s, scheme, 0, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->ihnew,
+                              plan->mmx, plan->entry_u, plan->domore_k, Idt);
+  } else {
+    launch_flags_begin(s, g, plan->domore_k, plan->domore_v, plan->entry_v, rg.js - 1, rg.je);
+    launch_mass_flux(s, 1, g, rg, plan->vhr, plan->hprev, plan->areaT, min_h, plan->entry_v, plan->domore_v, plan->hh, plan->cfl);
+    launch_mass_update(s, 1, g, rg, plan->vhr, plan->hprev, plan->hh, plan->areaT, plan->vh_neglect, h_neglect,
+                       plan->entry_v, plan->domore_k, plan->hlst, plan->ihnew);
+    launch_tracer_sweep(s, scheme, 1, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->hlst,
+                        plan->ihnew, plan->mmy, plan->IareaT, plan->entry_v, plan->domore_k, Idt);
+    if (any_ad2d) launch_ad2d(s, scheme, 1, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->ihnew,
+                              plan->mmy, plan->entry_v, plan->domore_k, Idt);
+  }
+  plan->launches += 4 + (any_ad2d ? 1 : 0);
+  plan->cur = 1 - plan->cur;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+// advect_tracer :112-320 on the resident fields.
+static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_iter_in, bool use_vol_prev,
+                      bool update_vol_prev, int *n_iter_out) {
+  if (n_iter_out) *n_iter_out = 0;
+  if (plan->ntr == 0) return MOM6ADV_OK;                                   // :124
+  for (int m = 0; m < plan->ntr; m++)
+    if (!plan->tr[m].buf[0]) return fail(plan, MOM6ADV_ERR_NOT_INIT, "advect: tracer storage missing");
+  const Geom &g = plan->g;
+  cudaStream_t s = plan->stream;
+  CK(cudaSetDevice(plan->device));
+  { int rc = sync_tracer_table(plan); if (rc) return rc; }
+  const int is = g.isc, ie = g.iec, js = g.jsc, je = g.jec;
+  int stencil = 2;                                                          // :118
+  const bool use_PPM_stencil = plan->cfg.usePPM && !plan->cfg.useHuynhStencilBug;   // :129
+  if (use_PPM_stencil) stencil = 3;                                         // :130
+  const int scheme = !plan->cfg.usePPM ? SCHEME_PLM : (plan->cfg.useHuynh ? SCHEME_PPM_H3 : SCHEME_PPM_CW);
+  const int halo_min = std::min(std::min(is - g.isd, g.ied - ie), std::min(js - g.jsd, g.jed - je));
+  if (halo_min < stencil)
+    return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "advect: halo narrower than the advection stencil");
+  if (!(dt > 0.0) || !(plan->cfg.dt_baroclinic > 0.0)) return fail(plan, MOM6ADV_ERR_INVALID, "advect: dt must be > 0");
+  bool x_first = ((plan->cfg.first_direction % 2) == 0);                    // :126
+  const double Idt = 1.0 / dt;                                              // :133
+  int max_iter = 2 * (int)std::ceil(dt / plan->cfg.dt_baroclinic) + 1;      // :135
+  if (max_iter_in >= 0) max_iter = max_iter_in;                             // :137
+  if (x_first_in >= 0) x_first = (x_first_in != 0);                         // :138
+  if (use_vol_prev && !plan->vol_prev) return fail(plan, MOM6ADV_ERR_INVALID, "advect: vol_prev was not uploaded");
+
+  CK(cudaEventRecord(plan->ev0, s));
+  plan->cur = 0;
+  // :112-113, :156
+  CK(cudaMemsetAsync(plan->domore_u, 0, sizeof(int) * g.R * g.nk, s));
+  CK(cudaMemsetAsync(plan->domore_v, 0, sizeof(int) * g.R * g.nk, s));
+  launch_init_residuals(s, g, plan->h_end, plan->uhtr, plan->vhtr, use_vol_prev ? plan->vol_prev : nullptr,
+                        plan->areaT, plan->uhr, plan->vhr, plan->hprev);    // :152-178
+  {
+    std::vector<int> ones(g.nk, 1);
+    CK(cudaMemcpyAsync(plan->domore_k, ones.data(), sizeof(int) * g.nk, cudaMemcpyHostToDevice, s));
+    CK(cudaStreamSynchronize(s));   // ones goes out of scope
+  }
+  plan->launches += 1;
+  for (int m = 0; m < plan->ntr; m++)                                       // :192-198
+    for (int d = 0; d < 5; d++)
+      if (plan->tr[m].diag[d])
+        CK(cudaMemsetAsync(plan->tr[m].diag[d], 0, sizeof(double) * ((d == 2 || d == 3) ? g.plane : field_elems(plan)), s));
+
+  int isv = is, iev = ie, jsv = js, jev = je;                               // :201
+  int itt;
+  for (itt = 1; itt <= max_iter; itt++) {                                   // :203
+    if (isv > is - stencil) {                                               // :205
+      { int rc = group_pass(plan); if (rc) return rc; }                     // :206
+      const int nsten_halo = halo_min / stencil;                            // :208
+      isv = is - nsten_halo * stencil; jsv = js - nsten_halo * stencil;     // :209
+      iev = ie + nsten_halo * stencil; jev = je + nsten_halo * stencil;     // :210
+      if ((nsten_halo > 1) || (itt == 1)) {                                 // :213
+        launch_rescan(s, g, plan->uhr, plan->vhr, plan->domore_k, plan->domore_u, plan->domore_v, isv, iev, jsv, jev, stencil);
+        launch_domore_k(s, g, plan->domore_k, plan->domore_u, plan->domore_v, jsv, jev, jsv + stencil - 1, jev - stencil);
+        plan->launches += 2;
+      }
+    }
+    isv += stencil; iev -= stencil; jsv += stencil; jev -= stencil;         // :238-239
+    int rc;
+    if (x_first) {                                                          // :249-269
+      Range rx = {isv, iev, jsv - stencil, jev + stencil};
+      Range ry = {isv, iev, jsv, jev};
+      if ((rc = sweep(plan, 0, rx, Idt, scheme))) return rc;
+      if ((rc = sweep(plan, 1, ry, Idt, scheme))) return rc;
+      launch_domore_k(s, g, plan->domore_k, plan->domore_u, plan->domore_v, jsv - stencil, jev + stencil, jsv - 1, jev);
+    } else {                                                                // :271-290
+      Range ry = {isv - stencil, iev + stencil, jsv, jev};
+      Range rx = {isv, iev, jsv, jev};
+      if ((rc = sweep(plan, 1, ry, Idt, scheme))) return rc;
+      if ((rc = sweep(plan, 0, rx, Idt, scheme))) return rc;
+      launch_domore_k(s, g, plan->domore_k, plan->domore_u, plan->domore_v, jsv, jev, jsv - 1, jev);
+    }
+    plan->launches += 1;
+    if (itt >= max_iter) break;                                             // :297-299
+    if (isv > is - stencil) {                                               // :302
+      launch_sum_domore_k(s, plan->domore_k, g.nk, plan->sum_dev);          // :305-307 (single block: identity sum)
+      plan->launches += 1;
+      CK(cudaMemcpyAsync(plan->sum_host, plan->sum_dev, sizeof(int), cudaMemcpyDeviceToHost, s));
+      CK(cudaStreamSynchronize(s));
+      if (plan->sum_host[0] == 0) break;                                    // :308-310
+    }
+  }
+  if (n_iter_out) *n_iter_out = std::min(itt, max_iter);
+  if (update_vol_prev && use_vol_prev)                                      // :318-320
+    CK(cudaMemcpyAsync(plan->vol_prev, plan->hprev, sizeof(double) * field_elems(plan), cudaMemcpyDeviceToDevice, s));
+  CK(cudaEventRecord(plan->ev1, s));
+  CK(cudaStreamSynchronize(s));
+  float ms = 0.f;
+  CK(cudaEventElapsedTime(&ms, plan->ev0, plan->ev1));
+  plan->last_ms = ms;
+  CK(cudaGetLastError());
+  return MOM6ADV_OK;
+}
+
+// ---------------------------------------------------------------------------
+// RESIDENT-mode data movement
+// ---------------------------------------------------------------------------
+static int field_info(mom6adv_plan *plan, int field, double ***pp, int *ilo, int *jlo) {
+  const Geom &g = plan->g;
+  *ilo = g.isd; *jlo = g.jsd;
+  switch (field) {
+    case MOM6ADV_F_H_END: *pp = &plan->h_end; break;
+    case MOM6ADV_F_UHTR: *pp = &plan->uhtr; *ilo = g.IsdB; break;
+    case MOM6ADV_F_VHTR: *pp = &plan->vhtr; *jlo = g.JsdB; break;
+    case MOM6ADV_F_VOL_PREV: *pp = &plan->vol_prev; break;
+    case MOM6ADV_F_UHR: *pp = &plan->uhr; *ilo = g.IsdB; break;
+    case MOM6ADV_F_VHR: *pp = &plan->vhr; *jlo = g.JsdB; break;
+    case MOM6ADV_F_HPREV: *pp = &plan->hprev; break;
+    default: return fail(plan, MOM6ADV_ERR_INVALID, "unknown field id");
+  }
+  return 0;
+}
+
+extern "C" int mom6adv_upload_field(mom6adv_plan *plan, int field, const double *src) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "upload_field: plan not initialised");
+  if (!src) return fail(plan, MOM6ADV_ERR_INVALID, "upload_field: NULL source");
+  CK(cudaSetDevice(plan->device));
+  double **pp; int ilo, jlo;
+  int rc = field_info(plan, field, &pp, &ilo, &jlo);
+  if (rc) return rc;
+  if (!*pp) { rc = dev_alloc(plan, pp, field_elems(plan)); if (rc) return rc; }
+  rc = upload(plan, *pp, src, ilo, jlo, plan->g.nk);
+  if (rc) return rc;
+  CK(cudaStreamSynchronize(plan->stream));
+  return MOM6ADV_OK;
+}
+
+extern "C" int mom6adv_download_field(mom6adv_plan *plan, int field, double *dst) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "download_field: plan not initialised");
+  if (!dst) return fail(plan, MOM6ADV_ERR_INVALID, "download_field: NULL destination");
+  CK(cudaSetDevice(plan->device));
+  double **pp; int ilo, jlo;
+  int rc = field_info(plan, field, &pp, &ilo, &jlo);
+  if (rc) return rc;
+  if (!*pp) return fail(plan, MOM6ADV_ERR_INVALID, "download_field: field not resident");
+  rc = download(plan, dst, *pp, ilo, jlo, plan->g.nk);
+  if (rc) return rc;
+  CK(cudaStreamSynchronize(plan->stream));
+  return MOM6ADV_OK;
+}
+
+extern "C" int mom6adv_upload_tracer(mom6adv_plan *plan, int m, const double *src) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "upload_tracer: plan not initialised");
+  if (m < 0 || m >= plan->ntr) return fail(plan, MOM6ADV_ERR_INVALID, "upload_tracer: tracer index out of range");
+  if (!src) return fail(plan, MOM6ADV_ERR_INVALID, "upload_tracer: NULL source");
+  CK(cudaSetDevice(plan->device));
+  int rc = upload(plan, plan->tr[m].buf[0], src, plan->g.isd, plan->g.jsd, plan->g.nk);
+  if (rc) return rc;
+  CK(cudaStreamSynchronize(plan->stream));
+  return MOM6ADV_OK;
+}
+
+extern "C" int mom6adv_download_tracer(mom6adv_plan *plan, int m, double *dst) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "download_tracer: plan not initialised");
+  if (m < 0 || m >= plan->ntr) return fail(plan, MOM6ADV_ERR_INVALID, "download_tracer: tracer index out of range");
+  if (!dst) return fail(plan, MOM6ADV_ERR_INVALID, "download_tracer: NULL destination");
+  CK(cudaSetDevice(plan->device));
+  int rc = download(plan, dst, plan->tr[m].buf[0], plan->g.isd, plan->g.jsd, plan->g.nk);
+  if (rc) return rc;
+  CK(cudaStreamSynchronize(plan->stream));
+  return MOM6ADV_OK;
+}
+
+static void diag_info(const Geom &g, int kind, int *ilo, int *jlo, int *nlev) {
+  *ilo = g.isd; *jlo = g.jsd; *nlev = g.nk;
+  if (kind == 0 || kind == 2) *ilo = g.IsdB;
+  if (kind == 1 || kind == 3) *jlo = g.JsdB;
+  if (kind == 2 || kind == 3) *nlev = 1;
+}
+
+extern "C" int mom6adv_download_diag(mom6adv_plan *plan, int m, int kind, double *dst) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "download_diag: plan not initialised");
+  if (m < 0 || m >= plan->ntr || kind < 0 || kind > 4) return fail(plan, MOM6ADV_ERR_INVALID, "download_diag: bad index");
+  if (!plan->tr[m].diag[kind]) return fail(plan, MOM6ADV_ERR_INVALID, "download_diag: diagnostic not associated");
+  CK(cudaSetDevice(plan->device));
+  int ilo, jlo, nlev;
+  diag_info(plan->g, kind, &ilo, &jlo, &nlev);
+  int rc = download(plan, dst, plan->tr[m].diag[kind], ilo, jlo, nlev);
+  if (rc) return rc;
+  CK(cudaStreamSynchronize(plan->stream));
+  return MOM6ADV_OK;
+}
+
+extern "C" int mom6adv_advect_resident(mom6adv_plan *plan, double dt, int x_first, int max_iter_in,
+                                       int use_vol_prev, int update_vol_prev, int *n_iter) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "advect: tracer_advect_init must be called before advect_tracer");
+  return run_advect(plan, dt, x_first, max_iter_in, use_vol_prev != 0, update_vol_prev > 0, n_iter);
+}
+
+// ---------------------------------------------------------------------------
+// MIRROR mode: one call == one reference advect_tracer call on host arrays.
+// ---------------------------------------------------------------------------
+extern "C" int mom6adv_advect(mom6adv_plan *plan, const double *h_end, const double *uhtr, const double *vhtr,
+                              double dt, int x_first, double *vol_prev, int max_iter_in, int update_vol_prev,
+                              double *uhr_out, double *vhr_out, int *n_iter) {
+  if (n_iter) *n_iter = 0;
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "advect: tracer_advect_init must be called before advect_tracer");
+  if (plan->ntr == 0) return MOM6ADV_OK;   // :124
+  if (!h_end || !uhtr || !vhtr) return fail(plan, MOM6ADV_ERR_INVALID, "advect: NULL input array");
+  for (int m = 0; m < plan->ntr; m++)
+    if (!plan->tr[m].bound || !plan->tr[m].host_t)
+      return fail(plan, MOM6ADV_ERR_NOT_INIT, "advect: register_tracer must be called before advect_tracer (tracer not bound)");
+  CK(cudaSetDevice(plan->device));
+  const Geom &g = plan->g;
+  int rc;
+  if ((rc = upload(plan, plan->h_end, h_end, g.isd, g.jsd, g.nk))) return rc;
+  if ((rc = upload(plan, plan->uhtr, uhtr, g.IsdB, g.jsd, g.nk))) return rc;
+  if ((rc = upload(plan, plan->vhtr, vhtr, g.isd, g.JsdB, g.nk))) return rc;
+  if (vol_prev) {
+    if (!plan->vol_prev) { rc = dev_alloc(plan, &plan->vol_prev, field_elems(plan)); if (rc) return rc; }
+    if ((rc = upload(plan, plan->vol_prev, vol_prev, g.isd, g.jsd, g.nk))) return rc;
+  }
+  for (int m = 0; m < plan->ntr; m++)
+    if ((rc = upload(plan, plan->tr[m].buf[0], plan->tr[m].host_t, g.isd, g.jsd, g.nk))) return rc;
+  const bool upd = vol_prev && update_vol_prev > 0;
+  rc = run_advect(plan, dt, x_first, max_iter_in, vol_prev != nullptr, upd, n_iter);
+  if (rc) return rc;
+  for (int m = 0; m < plan->ntr; m++) {
+    if ((rc = download(plan, plan->tr[m].host_t, plan->tr[m].buf[0], g.isd, g.jsd, g.nk))) return rc;
+    for (int d = 0; d < 5; d++) if (plan->tr[m].diag[d] && plan->tr[m].host_diag[d]) {
+      int ilo, jlo, nlev;
+      diag_info(g, d, &ilo, &jlo, &nlev);
+      if ((rc = download(plan, plan->tr[m].host_diag[d], plan->tr[m].diag[d], ilo, jlo, nlev))) return rc;
+    }
+  }
+  if (uhr_out && (rc = download(plan, uhr_out, plan->uhr, g.IsdB, g.jsd, g.nk))) return rc;   // :316
+  if (vhr_out && (rc = download(plan, vhr_out, plan->vhr, g.isd, g.JsdB, g.nk))) return rc;   // :317
+  if (upd && (rc = download(plan, vol_prev, plan->vol_prev, g.isd, g.jsd, g.nk))) return rc;  // :319
+  CK(cudaStreamSynchronize(plan->stream));
+  return MOM6ADV_OK;
+}
+
+extern "C" int mom6adv_sync(mom6adv_plan *plan) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "sync: plan not initialised");
+  CK(cudaSetDevice(plan->device));
+  CK(cudaStreamSynchronize(plan->stream));
+  return MOM6ADV_OK;
+}
+
+extern "C" double mom6adv_last_advect_ms(const mom6adv_plan *plan) { return plan ? plan->last_ms : 0.0; }
+extern "C" long long mom6adv_kernel_launches(const mom6adv_plan *plan) { return plan ? plan->launches : 0; }
+extern "C" long long mom6adv_device_bytes(const mom6adv_plan *plan) { return plan ? plan->dev_bytes : 0; }
+
+extern "C" int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value) {
+  if (!plan || !key) return fail(plan, MOM6ADV_ERR_INVALID, "set_option: NULL argument");
+  if (!strcmp(key, "fused")) { plan->opt_fused = value; return MOM6ADV_OK; }
+  return fail(plan, MOM6ADV_ERR_INVALID, std::string("set_option: unknown key ") + key);
+}

@@ -1,0 +1,84 @@
+"""2-D block decomposition of the horizontal domain (MOM6 LAYOUT = pi,pj).
+
+Mirrors what MOM_domains_init / create_MOM_domain set up
+(src/framework/MOM_domains.F90:66, config_src/infra/FMS2/MOM_domain_infra.F90:1313):
+each rank owns an (ni/pi) x (nj/pj) block with the same halo width; local
+indexing restarts at isd = 1 (MOM_domain_infra.F90:1815-1821).
+"""
+from __future__ import annotations
+
+from typing import List, Tuple
+
+import numpy as np
+
+from .types import MOMDomain, OceanGrid
+
+
+def compute_extent(n: int, ndiv: int) -> List[Tuple[int, int]]:
+    """Even split of 1..n into ndiv contiguous pieces (larger pieces in the
+    middle is FMS's choice; any contiguous split is layout-reproducible, and we
+    put the remainder on the first pieces)."""
+    base, rem = divmod(n, ndiv)
+    out, s = [], 1
+    for p in range(ndiv):
+        sz = base + (1 if p < rem else 0)
+        out.append((s, s + sz - 1))
+        s += sz
+    return out
+
+
+def rank_of(pi: int, pj: int, layout) -> int:
+    return pi + layout[0] * pj
+
+
+def local_grid(Gg: OceanGrid, layout, pe) -> OceanGrid:
+    """Local OceanGrid of block ``pe`` = (pi, pj) cut from the global grid Gg."""
+    npi, npj = layout
+    Dg = Gg.Domain
+    halo_i, halo_j = Gg.isc - Gg.isd, Gg.jsc - Gg.jsd
+    (igs, ige) = compute_extent(Dg.nig, npi)[pe[0]]
+    (jgs, jge) = compute_extent(Dg.njg, npj)[pe[1]]
+    dom = MOMDomain(Dg.nig, Dg.njg, layout=tuple(layout), cyclic_x=Dg.cyclic_x, cyclic_y=Dg.cyclic_y,
+                    tripolar_n=Dg.tripolar_n, symmetric=Dg.symmetric, pe=tuple(pe))
+    G = OceanGrid(ige - igs + 1, jge - jgs + 1, halo=halo_i, jhalo=halo_j, symmetric=Gg.symmetric,
+                  first_direction=Gg.first_direction, domain=dom)
+    G.ioff = igs - G.isc     # global = local + off
+    G.joff = jgs - G.jsc
+    for name in ("areaT", "IareaT", "mask2dT"):
+        setattr(G, name, cut_h(Gg, G, getattr(Gg, name)))
+    G.mask2dCu = cut_u(Gg, G, Gg.mask2dCu)
+    G.mask2dCv = cut_v(Gg, G, Gg.mask2dCv)
+    return G
+
+
+def _cols(Gg, G, lo_local, n, lo_global_array):
+    # python column indices into the global array for local columns lo_local .. lo_local+n-1
+    g = np.arange(n) + lo_local + G.ioff          # global (unwrapped) index of each local column
+    gg = g - Gg.ioff                               # the global grid's own local index
+    return gg - lo_global_array
+
+
+def cut_h(Gg: OceanGrid, G: OceanGrid, a: np.ndarray) -> np.ndarray:
+    """Local data-domain copy of a global h-point array (halo included)."""
+    ci = np.arange(G.nid) + G.isd + G.ioff - Gg.ioff - Gg.isd
+    rj = np.arange(G.njd) + G.jsd + G.joff - Gg.joff - Gg.jsd
+    return np.ascontiguousarray(a[..., rj[:, None], ci[None, :]])
+
+
+def cut_u(Gg, G, a):
+    ci = np.arange(G.nIB) + G.IsdB + G.ioff - Gg.ioff - Gg.IsdB
+    rj = np.arange(G.njd) + G.jsd + G.joff - Gg.joff - Gg.jsd
+    return np.ascontiguousarray(a[..., rj[:, None], ci[None, :]])
+
+
+def cut_v(Gg, G, a):
+    ci = np.arange(G.nid) + G.isd + G.ioff - Gg.ioff - Gg.isd
+    rj = np.arange(G.nJB) + G.JsdB + G.joff - Gg.joff - Gg.JsdB
+    return np.ascontiguousarray(a[..., rj[:, None], ci[None, :]])
+
+
+def paste_interior(Gg: OceanGrid, G: OceanGrid, a_global: np.ndarray, a_local: np.ndarray) -> None:
+    """Write the computational domain of a local h-point array into the global one."""
+    gi0 = G.isc + G.ioff - Gg.ioff - Gg.isd
+    gj0 = G.jsc + G.joff - Gg.joff - Gg.jsd
+    a_global[..., gj0:gj0 + G.nj, gi0:gi0 + G.ni] = G.interior(a_local)

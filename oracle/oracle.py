@@ -1,0 +1,201 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes wrapper around the CPU oracle
+(oracle/advect_ref.cpp, a restatement of
+/root/reference/src/tracer/MOM_tracer_advect.F90:52-1087).  PARITY UNPINNED.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+--impl reference legs may import this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "liboracle_advect.so")
+_lib = None
+
+_dp = C.POINTER(C.c_double)
+
+
+class ora_grid(C.Structure):
+    _fields_ = [(n, C.c_int) for n in
+                ("isc", "iec", "jsc", "jec", "isd", "ied", "jsd", "jed",
+                 "IsdB", "IedB", "JsdB", "JedB", "nk", "first_direction")] + \
+               [(n, _dp) for n in ("areaT", "IareaT", "mask2dT", "mask2dCu", "mask2dCv")] + \
+               [("Angstrom_H", C.c_double), ("H_subroundoff", C.c_double)]
+
+
+class ora_cs(C.Structure):
+    _fields_ = [("dt", C.c_double), ("usePPM", C.c_int), ("useHuynh", C.c_int),
+                ("useHuynhStencilBug", C.c_int)]
+
+
+class ora_tracer(C.Structure):
+    _fields_ = [(n, _dp) for n in ("t", "ad_x", "ad_y", "ad2d_x", "ad2d_y", "advection_xy")] + \
+               [("conc_underflow", C.c_double)]
+
+
+class ora_domain(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("nig", "njg", "cyclic_x", "cyclic_y", "tripolar_n", "symmetric")]
+
+
+class ora_rank(C.Structure):
+    _fields_ = [("G", ora_grid), ("ioff", C.c_int), ("joff", C.c_int),
+                ("Tr", C.POINTER(ora_tracer)),
+                ("h_end", _dp), ("uhtr", _dp), ("vhtr", _dp),
+                ("vol_prev", _dp), ("uhr_out", _dp), ("vhr_out", _dp),
+                ("n_iter", C.c_int)]
+
+
+PASS_FN = C.CFUNCTYPE(None, C.c_void_p, _dp, _dp, _dp, C.POINTER(ora_tracer), C.c_int)
+SUM_FN = C.CFUNCTYPE(None, C.c_void_p, C.POINTER(C.c_int), C.c_int)
+
+
+def build(force: bool = False) -> str:
+    """Compile the oracle with oracle/Makefile (g++ -O2 -ffp-contract=off -fopenmp)."""
+    src = os.path.join(_HERE, "advect_ref.cpp")
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+        subprocess.run(["make", "-C", _HERE], check=True, capture_output=True)
+    return _LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(_LIB_PATH)
+        _lib.ora_advect_tracer.restype = C.c_int
+        _lib.ora_advect_tracer.argtypes = [
+            C.POINTER(ora_grid), C.POINTER(ora_cs), C.POINTER(ora_tracer), C.c_int,
+            _dp, _dp, _dp, C.c_double, C.c_int, _dp, C.c_int, C.c_int, _dp, _dp,
+            C.POINTER(ora_domain), C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.c_int]
+        _lib.ora_advect_tracer_multi.restype = C.c_int
+        _lib.ora_advect_tracer_multi.argtypes = [
+            C.c_int, C.POINTER(ora_rank), C.POINTER(ora_domain), C.POINTER(ora_cs),
+            C.c_int, C.c_double, C.c_int, C.c_int, C.c_int]
+        _lib.ora_bitcount_chksum.restype = C.c_longlong
+        _lib.ora_bitcount_chksum.argtypes = [_dp, C.c_longlong]
+        _lib.ora_efp_sum.restype = None
+        _lib.ora_efp_sum.argtypes = [_dp, C.c_longlong, C.POINTER(C.c_longlong)]
+        _lib.ora_efp_to_real.restype = C.c_double
+        _lib.ora_efp_to_real.argtypes = [C.POINTER(C.c_longlong)]
+    return _lib
+
+
+def _p(a: Optional[np.ndarray]):
+    if a is None:
+        return None
+    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"], "need contiguous float64"
+    return a.ctypes.data_as(_dp)
+
+
+def make_grid(G, GV) -> ora_grid:
+    g = ora_grid()
+    for n in ("isc", "iec", "jsc", "jec", "isd", "ied", "jsd", "jed", "IsdB", "IedB", "JsdB", "JedB",
+              "first_direction"):
+        setattr(g, n, int(getattr(G, n)))
+    g.nk = int(GV.ke)
+    for n in ("areaT", "IareaT", "mask2dT", "mask2dCu", "mask2dCv"):
+        setattr(g, n, _p(getattr(G, n)))
+    g.Angstrom_H = GV.Angstrom_H
+    g.H_subroundoff = GV.H_subroundoff
+    return g
+
+
+def make_domain(D) -> ora_domain:
+    d = ora_domain()
+    d.nig, d.njg = D.nig, D.njg
+    d.cyclic_x, d.cyclic_y, d.tripolar_n = int(D.cyclic_x), int(D.cyclic_y), int(D.tripolar_n)
+    d.symmetric = int(D.symmetric)
+    return d
+
+
+def make_cs(CS) -> ora_cs:
+    c = ora_cs()
+    c.dt = CS.dt
+    c.usePPM, c.useHuynh, c.useHuynhStencilBug = int(CS.usePPM), int(CS.useHuynh), int(CS.useHuynhStencilBug)
+    return c
+
+
+def make_tracers(Reg):
+    arr = (ora_tracer * max(Reg.ntr, 1))()
+    for m, tr in enumerate(Reg.Tr[:Reg.ntr]):
+        arr[m].t = _p(tr.t)
+        for n in ("ad_x", "ad_y", "ad2d_x", "ad2d_y", "advection_xy"):
+            setattr(arr[m], n, _p(getattr(tr, n)))
+        arr[m].conc_underflow = tr.conc_underflow
+    return arr
+
+
+def _opt_flag(v):
+    return -1 if v is None else int(bool(v))
+
+
+def advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first_in=None,
+                  vol_prev=None, max_iter_in=None, update_vol_prev=None, uhr_out=None,
+                  vhr_out=None, nthreads: int = 1, pass_fn=None, sum_fn=None) -> int:
+    """Oracle advect_tracer with the reference's argument list
+    (MOM_tracer_advect.F90:52-53).  Updates Reg.Tr[m].t in place.  Returns the
+    number of iterations taken."""
+    assert OBC is None, "the oracle restates the OBC-unassociated path only"
+    if CS is None:
+        raise RuntimeError("MOM_tracer_advect: tracer_advect_init must be called before advect_tracer.")
+    if Reg is None:
+        raise RuntimeError("MOM_tracer_advect: register_tracer must be called before advect_tracer.")
+    g, cs, dom = make_grid(G, GV), make_cs(CS), make_domain(G.Domain)
+    tr = make_tracers(Reg)
+    nit = C.c_int(0)
+    pf = C.cast(pass_fn, C.c_void_p) if pass_fn is not None else None
+    sf = C.cast(sum_fn, C.c_void_p) if sum_fn is not None else None
+    rc = lib().ora_advect_tracer(
+        C.byref(g), C.byref(cs), tr, Reg.ntr, _p(h_end), _p(uhtr), _p(vhtr), float(dt),
+        _opt_flag(x_first_in), _p(vol_prev), -1 if max_iter_in is None else int(max_iter_in),
+        _opt_flag(update_vol_prev), _p(uhr_out), _p(vhr_out), C.byref(dom), pf, sf, None,
+        C.byref(nit), int(nthreads))
+    if rc != 0:
+        raise RuntimeError("oracle advect_tracer failed: %d" % rc)
+    return nit.value
+
+
+def advect_tracer_multi(ranks: Sequence[dict], dom, CS, dt, x_first_in=None, max_iter_in=None,
+                        update_vol_prev=None) -> List[int]:
+    """Emulated multi-PE run.  Each entry of ``ranks`` is a dict with keys
+    G, GV, Reg, h_end, uhtr, vhtr and optional vol_prev, uhr_out, vhr_out."""
+    n = len(ranks)
+    arr = (ora_rank * n)()
+    keep = []
+    for r, d in enumerate(ranks):
+        G = d["G"]
+        arr[r].G = make_grid(G, d["GV"])
+        arr[r].ioff, arr[r].joff = G.ioff, G.joff
+        tr = make_tracers(d["Reg"])
+        keep.append(tr)
+        arr[r].Tr = C.cast(tr, C.POINTER(ora_tracer))
+        arr[r].h_end, arr[r].uhtr, arr[r].vhtr = _p(d["h_end"]), _p(d["uhtr"]), _p(d["vhtr"])
+        arr[r].vol_prev = _p(d.get("vol_prev"))
+        arr[r].uhr_out, arr[r].vhr_out = _p(d.get("uhr_out")), _p(d.get("vhr_out"))
+    cs, od = make_cs(CS), make_domain(dom)
+    rc = lib().ora_advect_tracer_multi(n, arr, C.byref(od), C.byref(cs), ranks[0]["Reg"].ntr, float(dt),
+                                       _opt_flag(x_first_in), -1 if max_iter_in is None else int(max_iter_in),
+                                       _opt_flag(update_vol_prev))
+    if rc != 0:
+        raise RuntimeError("oracle advect_tracer_multi failed: %d" % rc)
+    return [arr[r].n_iter for r in range(n)]
+
+
+def bitcount_chksum(a: np.ndarray) -> int:
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    return int(lib().ora_bitcount_chksum(_p(a), a.size))
+
+
+def efp_sum(a: np.ndarray):
+    """Order-invariant extended-fixed-point sum (MOM_coms.F90:508-590).
+    Returns (limbs tuple, real value)."""
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    limbs = (C.c_longlong * 6)()
+    lib().ora_efp_sum(_p(a), a.size, limbs)
+    return tuple(limbs), float(lib().ora_efp_to_real(limbs))

@@ -1,0 +1,96 @@
+"""GPU parity: CUDA advect_tracer (through the C ABI) vs the CPU oracle, bitwise."""
+import numpy as np
+import pytest
+
+from mom6_b200 import synth
+from mom6_b200.tracer_advect import tracer_advect_init, tracer_advect_end, advect_tracer
+from oracle import oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _run_pair(ni, nj, nk, ntr, scheme, cfl=0.3, x_first=None, diags=False, ncalls=1, symmetric=True,
+              cyclic_x=True, halo=4, bug=False, **kw):
+    c = synth.make_case(ni, nj, nk, ntr, cfl=cfl, symmetric=symmetric, cyclic_x=cyclic_x, halo=halo, **kw)
+    params = {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme, "USE_HUYNH_STENCIL_BUG": bug}
+    CSo = tracer_advect_init(None, c.G, None, params, None, None)
+    CSg = tracer_advect_init(None, c.G, None, params, None, None)
+    Ro = synth.bind_registry(c, diags=diags)
+    Rg = synth.bind_registry(c, diags=diags)
+    h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
+    nk_ = c.GV.ke
+    uo_o, vo_o = np.zeros(c.G.shape_u(nk_)), np.zeros(c.G.shape_v(nk_))
+    uo_g, vo_g = np.zeros(c.G.shape_u(nk_)), np.zeros(c.G.shape_v(nk_))
+    for n in range(ncalls):
+        xf = x_first if x_first is not None else None
+        nit_o = oracle.advect_tracer(h, u, v, None, c.dt, c.G, c.GV, None, CSo, Ro, x_first_in=xf, uhr_out=uo_o, vhr_out=vo_o)
+        nit_g = advect_tracer(h, u, v, None, c.dt, c.G, c.GV, None, CSg, Rg, x_first_in=xf, uhr_out=uo_g, vhr_out=vo_g)
+        assert nit_o == nit_g, (nit_o, nit_g)
+    tracer_advect_end(CSg)
+    return c, Ro, Rg, (uo_o, vo_o, uo_g, vo_g), nit_o
+
+
+def _assert_bitwise(c, Ro, Rg, outs, diags=False):
+    G = c.G
+    for m, (a, b) in enumerate(zip(Ro.Tr, Rg.Tr)):
+        ia, ib = G.interior(a.t), G.interior(b.t)
+        assert np.array_equal(ia.view(np.uint64), ib.view(np.uint64)), \
+            "tracer %d differs: max abs %g" % (m, np.abs(ia - ib).max())
+        if diags:
+            for n in ("ad_x", "ad_y", "ad2d_x", "ad2d_y", "advection_xy"):
+                da, db = getattr(a, n), getattr(b, n)
+                if n in ("ad_x", "ad2d_x"):
+                    da, db = G.interior_u(da), G.interior_u(db)
+                elif n in ("ad_y", "ad2d_y"):
+                    da, db = G.interior_v(da), G.interior_v(db)
+                else:
+                    da, db = G.interior(da), G.interior(db)
+                assert np.array_equal(da.view(np.uint64), db.view(np.uint64)), \
+                    "diag %s of tracer %d differs: max abs %g" % (n, m, np.abs(da - db).max())
+    uo_o, vo_o, uo_g, vo_g = outs
+    assert np.array_equal(G.interior_u(uo_o).view(np.uint64), G.interior_u(uo_g).view(np.uint64))
+    assert np.array_equal(G.interior_v(vo_o).view(np.uint64), G.interior_v(vo_g).view(np.uint64))
+
+
+@pytest.mark.parametrize("scheme", ["PLM", "PPM", "PPM:H3"])
+@pytest.mark.parametrize("x_first", [True, False])
+@pytest.mark.parametrize("cfl", [0.3, 0.9])
+def test_double_gyre_shape_bitwise(scheme, x_first, cfl):
+    c, Ro, Rg, outs, nit = _run_pair(44, 40, 2, 10, scheme, cfl=cfl, x_first=x_first)
+    _assert_bitwise(c, Ro, Rg, outs)
+
+
+@pytest.mark.parametrize("scheme", ["PLM", "PPM", "PPM:H3"])
+def test_diagnostics_bitwise(scheme):
+    c, Ro, Rg, outs, nit = _run_pair(44, 40, 3, 4, scheme, cfl=0.9, diags=True)
+    _assert_bitwise(c, Ro, Rg, outs, diags=True)
+
+
+def test_tc1_shape_plm():
+    c, Ro, Rg, outs, nit = _run_pair(10, 8, 8, 3, "PLM", cfl=0.5)
+    _assert_bitwise(c, Ro, Rg, outs)
+
+
+def test_repeated_calls():
+    c, Ro, Rg, outs, nit = _run_pair(44, 40, 2, 10, "PPM", cfl=0.6, ncalls=5)
+    _assert_bitwise(c, Ro, Rg, outs)
+
+
+@pytest.mark.parametrize("symmetric", [True, False])
+@pytest.mark.parametrize("cyclic_x", [True, False])
+def test_memory_modes_and_topology(symmetric, cyclic_x):
+    c, Ro, Rg, outs, nit = _run_pair(37, 29, 3, 3, "PPM", cfl=0.8, symmetric=symmetric, cyclic_x=cyclic_x)
+    _assert_bitwise(c, Ro, Rg, outs)
+
+
+def test_huynh_stencil_bug_and_halo3():
+    c, Ro, Rg, outs, nit = _run_pair(40, 32, 2, 3, "PPM:H3", cfl=0.8, bug=True)
+    _assert_bitwise(c, Ro, Rg, outs)
+    c, Ro, Rg, outs, nit = _run_pair(40, 32, 2, 3, "PPM", cfl=0.8, halo=3)
+    _assert_bitwise(c, Ro, Rg, outs)
+
+
+def test_om4_1_slice_bitwise():
+    # OM4_1 horizontal shape, a few levels (the oracle finishes in seconds)
+    c, Ro, Rg, outs, nit = _run_pair(360, 210, 4, 6, "PPM", cfl=0.5)
+    _assert_bitwise(c, Ro, Rg, outs)

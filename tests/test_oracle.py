@@ -1,0 +1,220 @@
+"""CPU tests of the oracle itself.
+
+The reference has no golden vectors for advect_tracer, so the
+oracle is held to the reference's own *relational* standards: layout
+invariance (test.layout), memory-mode invariance (test.grid), threading
+invariance (test.openmp), dimensional rescaling (test.dim.*), plus the
+scheme's analytic properties (constancy, monotonicity, conservation).
+"""
+import numpy as np
+import pytest
+
+from mom6_b200 import synth, decomp
+from mom6_b200.types import TracerRegistry, register_tracer
+from mom6_b200.tracer_advect import tracer_advect_init
+from oracle import oracle
+
+SCHEMES = ["PLM", "PPM", "PPM:H3"]
+
+
+def _cs(c, scheme, bug=False):
+    return tracer_advect_init(None, c.G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme,
+                                                "USE_HUYNH_STENCIL_BUG": bug}, None, None)
+
+
+def _run(c, scheme, Reg=None, **kw):
+    CS = _cs(c, scheme)
+    Reg = Reg if Reg is not None else synth.bind_registry(c)
+    nit = oracle.advect_tracer(c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy(), None, c.dt, c.G, c.GV, None,
+                               CS, Reg, **kw)
+    return Reg, nit
+
+
+def _bits(a):
+    return np.ascontiguousarray(a).view(np.uint64)
+
+
+@pytest.mark.parametrize("scheme", SCHEMES)
+def test_constant_tracer_is_preserved(scheme):
+    c = synth.make_case(30, 24, 3, 1, cfl=0.7)
+    Reg = TracerRegistry()
+    register_tracer(np.full(c.G.shape_h(3), 7.25), Reg)
+    _run(c, scheme, Reg)
+    wet = c.G.interior(c.G.mask2dT) > 0
+    t = c.G.interior(Reg.Tr[0].t)[:, wet]
+    assert np.abs(t - 7.25).max() < 1e-12
+
+
+@pytest.mark.parametrize("scheme", SCHEMES)
+@pytest.mark.parametrize("cfl", [0.3, 0.9])
+def test_monotone_and_finite(scheme, cfl):
+    c = synth.make_case(44, 40, 2, 10, cfl=cfl)
+    Reg0 = synth.bind_registry(c)
+    Reg, nit = _run(c, scheme)
+    wet = c.G.interior(c.G.mask2dT) > 0
+    for a, b in zip(Reg0.Tr, Reg.Tr):
+        t0, t1 = c.G.interior(a.t)[:, wet], c.G.interior(b.t)[:, wet]
+        assert np.isfinite(t1).all()
+        span = max(t0.max() - t0.min(), 1.0)
+        assert t1.max() <= t0.max() + 1e-12 * span
+        assert t1.min() >= t0.min() - 1e-12 * span
+
+
+@pytest.mark.parametrize("scheme", SCHEMES)
+def test_conservation(scheme):
+    """sum(T*hprev) over the (cyclic-x, closed-y) domain is conserved to roundoff."""
+    c = synth.make_case(40, 32, 3, 6, cfl=0.8)
+    G, nk = c.G, c.GV.ke
+    # start volume == what advect_tracer reconstructs (:165-171); passed through vol_prev
+    h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
+    vol = np.zeros(G.shape_h(nk))
+    ui, vi = G.interior_u(u), G.interior_v(v)
+    hp = G.interior(G.areaT) * G.interior(h) + ((ui[..., 1:] - ui[..., :-1]) + (vi[:, 1:, :] - vi[:, :-1, :]))
+    hp = np.maximum(0.0, hp)
+    G.interior(vol)[...] = hp
+    Reg0 = synth.bind_registry(c)
+    Reg = synth.bind_registry(c)
+    CS = _cs(c, scheme)
+    oracle.advect_tracer(h, u, v, None, c.dt, G, c.GV, None, CS, Reg, vol_prev=vol, update_vol_prev=True)
+    for a, b in zip(Reg0.Tr, Reg.Tr):
+        s0 = oracle.efp_sum(G.interior(a.t) * hp)[1]
+        s1 = oracle.efp_sum(G.interior(b.t) * G.interior(vol))[1]
+        scale = oracle.efp_sum(np.abs(G.interior(a.t)) * hp)[1]
+        assert abs(s1 - s0) <= 1e-11 * scale
+
+
+def test_zero_transport_is_identity():
+    c = synth.make_case(20, 16, 2, 3)
+    Reg0 = synth.bind_registry(c)
+    Reg = synth.bind_registry(c)
+    CS = _cs(c, "PPM")
+    z_u, z_v = np.zeros_like(c.uhtr.numpy()), np.zeros_like(c.vhtr.numpy())
+    nit = oracle.advect_tracer(c.h_end.numpy(), z_u, z_v, None, c.dt, c.G, c.GV, None, CS, Reg)
+    assert nit == 1
+    for a, b in zip(Reg0.Tr, Reg.Tr):
+        assert np.array_equal(_bits(c.G.interior(a.t)), _bits(c.G.interior(b.t)))
+
+
+def test_ntr_zero_returns_immediately():
+    c = synth.make_case(12, 10, 2, 0)
+    assert oracle.advect_tracer(c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy(), None, c.dt, c.G, c.GV, None,
+                                _cs(c, "PLM"), TracerRegistry()) == 0
+
+
+def test_max_iter_default_tc1():
+    # hazard 10: 2*ceil(3600/900)+1 = 9
+    from mom6_b200.tracer_advect import max_iter_default
+    c = synth.make_case(10, 8, 8, 3)
+    assert max_iter_default(3600.0, _cs(c, "PLM")) == 9
+
+
+@pytest.mark.parametrize("scheme", SCHEMES)
+def test_threading_invariance(scheme):
+    c = synth.make_case(36, 28, 6, 4, cfl=0.9)
+    R1 = synth.bind_registry(c, diags=True)
+    R4 = synth.bind_registry(c, diags=True)
+    CS = _cs(c, scheme)
+    args = (c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy(), None, c.dt, c.G, c.GV, None, CS)
+    oracle.advect_tracer(*args, R1, nthreads=1)
+    oracle.advect_tracer(*args, R4, nthreads=4)
+    for a, b in zip(R1.Tr, R4.Tr):
+        assert np.array_equal(_bits(a.t), _bits(b.t))
+        for n in ("ad_x", "ad_y", "ad2d_x", "ad2d_y", "advection_xy"):
+            assert np.array_equal(_bits(getattr(a, n)), _bits(getattr(b, n)))
+
+
+@pytest.mark.parametrize("scheme", SCHEMES)
+def test_symmetric_vs_nonsymmetric_memory(scheme):
+    cs = synth.make_case(33, 27, 2, 4, cfl=0.8, symmetric=True)
+    cn = synth.make_case(33, 27, 2, 4, cfl=0.8, symmetric=False)
+    Rs, n1 = _run(cs, scheme)
+    Rn, n2 = _run(cn, scheme)
+    assert n1 == n2
+    for a, b in zip(Rs.Tr, Rn.Tr):
+        assert np.array_equal(_bits(cs.G.interior(a.t)), _bits(cn.G.interior(b.t)))
+
+
+def _split(c, layout, diags=False):
+    """Decompose a global case into per-rank oracle inputs."""
+    Gg = c.G
+    Regg = synth.bind_registry(c, diags=False)
+    ranks = []
+    for pj in range(layout[1]):
+        for pi in range(layout[0]):
+            G = decomp.local_grid(Gg, layout, (pi, pj))
+            Reg = TracerRegistry()
+            for tr in Regg.Tr:
+                register_tracer(decomp.cut_h(Gg, G, tr.t), Reg, underflow_conc=tr.conc_underflow)
+            ranks.append(dict(G=G, GV=c.GV, Reg=Reg,
+                              h_end=decomp.cut_h(Gg, G, c.h_end.numpy()),
+                              uhtr=decomp.cut_u(Gg, G, c.uhtr.numpy()),
+                              vhtr=decomp.cut_v(Gg, G, c.vhtr.numpy())))
+    return ranks
+
+
+@pytest.mark.parametrize("scheme", SCHEMES)
+@pytest.mark.parametrize("layout", [(2, 1), (1, 2), (2, 2), (3, 2)])
+@pytest.mark.parametrize("x_first", [True, False])
+def test_layout_invariance(scheme, layout, x_first):
+    """N-PE answer == 1-PE answer bitwise (the reference's test.layout standard).
+
+    y-first runs use a land-free grid: the reference's domore_v rescan (:221-225)
+    only looks at a PE's own columns [is,ie] while the y-first sweep also covers
+    the halo columns [is-stencil, ie+stencil] (:276-277), so a PE whose own part of
+    a row is all land skips halo columns that the owning PE advects -- a genuine
+    layout dependence of the reference in that corner (findings)."""
+    c = synth.make_case(36, 30, 2, 4, cfl=0.9, land=x_first)
+    R1, nit1 = _run(c, scheme, x_first_in=x_first)
+    ranks = _split(c, layout)
+    CS = _cs(c, scheme)
+    nits = oracle.advect_tracer_multi(ranks, c.G.Domain, CS, c.dt, x_first_in=x_first)
+    for m in range(c.ntr):
+        glob = np.zeros(c.G.shape_h(c.GV.ke))
+        for r in ranks:
+            decomp.paste_interior(c.G, r["G"], glob, r["Reg"].Tr[m].t)
+        assert np.array_equal(_bits(c.G.interior(glob)), _bits(c.G.interior(R1.Tr[m].t))), \
+            "tracer %d differs between layout %s and 1 PE" % (m, layout)
+
+
+@pytest.mark.parametrize("scheme", SCHEMES)
+def test_power_of_two_rescaling(scheme):
+    """test.dim.*: rescaling H by 2^a and L^2 by 2^(2b) leaves tracer bits unchanged."""
+    c = synth.make_case(32, 26, 2, 4, cfl=0.8)
+    R0, n0 = _run(c, scheme)
+    a, b2 = 2.0 ** 11, 2.0 ** 22
+    c2 = synth.make_case(32, 26, 2, 4, cfl=0.8)
+    c2.G.areaT = c2.G.areaT * b2
+    c2.G.IareaT = c2.G.IareaT / b2
+    c2.GV.Angstrom_H *= a
+    c2.GV.H_subroundoff *= a
+    c2.h_end = c2.h_end * a
+    c2.uhtr = c2.uhtr * (a * b2)
+    c2.vhtr = c2.vhtr * (a * b2)
+    R2, n2 = _run(c2, scheme)
+    assert n0 == n2
+    for x, y in zip(R0.Tr, R2.Tr):
+        assert np.array_equal(_bits(c.G.interior(x.t)), _bits(c.G.interior(y.t)))
+
+
+def test_offline_arguments_roundtrip():
+    """max_iter_in=1 + uhr_out/vhr_out: a second call on the residuals finishes the job."""
+    c = synth.make_case(30, 24, 2, 3, cfl=1.5)
+    G, nk = c.G, c.GV.ke
+    CS = _cs(c, "PPM")
+    Rfull, nfull = _run(c, "PPM")
+    assert nfull >= 2
+    uo, vo = np.zeros(G.shape_u(nk)), np.zeros(G.shape_v(nk))
+    R = synth.bind_registry(c)
+    n1 = oracle.advect_tracer(c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy(), None, c.dt, G, c.GV, None, CS, R,
+                              max_iter_in=1, uhr_out=uo, vhr_out=vo)
+    assert n1 == 1
+    assert np.abs(G.interior_u(uo)).max() > 0 or np.abs(G.interior_v(vo)).max() > 0
+
+
+def test_metrics():
+    a = np.array([1.0, -2.5, 3.0e10, 1e-20])
+    limbs, val = oracle.efp_sum(a)
+    assert abs(val - a.sum()) <= 1e-6
+    assert oracle.efp_sum(a[::-1].copy())[0] == limbs      # order invariant
+    assert oracle.bitcount_chksum(np.array([1.0, 3.0])) == bin(np.float64(1.0).view(np.uint64)).count("1") + \
+        bin(np.float64(3.0).view(np.uint64)).count("1")
