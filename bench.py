@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""bench.py -- advect_tracer cell-tracer updates/s on synthetic MOM6 shapes.
+
+    python bench.py --gpus N --steps K --warmup W            (own arm, CUDA)
+    python bench.py --impl reference --gpus N --steps K --warmup W   (CPU arm)
+
+A "step" is one complete advect_tracer call (prologue, group pass, both Strang
+sweeps, every residual iteration) on the workload named in config.workload.
+
+Own arm: inputs resident in HBM (RESIDENT mode of the C ABI); `value` is
+cell-tracer updates/s over the K timed calls, CUDA-event timed on the plan's
+stream.  `e2e` repeats the measurement through the reference-facing call
+advect_tracer(h_end, uhtr, vhtr, ...) (MIRROR mode) with pinned HOST arrays:
+every step copies (ntr+3) fields host->device and ntr fields device->host
+inside the timed region.  `roofline` is measured live with CUDA events around
+the dominant kernel class; `cpu_baseline` times the CPU oracle (a port of the
+reference's arithmetic: no Fortran compiler exists on the box) on a bounded
+sample of the same workload.
+
+Reference arm (--impl reference): the same oracle with every host thread on a
+bounded sample (a slab of levels of the same horizontal shape, all tracers).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "advect_tracer cell-tracer updates/s"
+UNIT = "cell-tracer updates/s"
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            d = json.load(open(p))
+            return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int = 0):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def workload_shape(name: str):
+    from mom6_b200 import synth
+    ni, nj, nk, ntr, scheme = synth.CONFIGS[name]
+    return ni, nj, nk, ntr, scheme
+
+
+# ---------------------------------------------------------------------------
+# CPU arm (oracle): used for cpu_baseline and for --impl reference
+# ---------------------------------------------------------------------------
+def cpu_sample_setup(name: str, cfl: float, nk_sample: int):
+    import numpy as np
+    from mom6_b200 import synth
+    from mom6_b200.tracer_advect import tracer_advect_init
+    ni, nj, nk, ntr, scheme = workload_shape(name)
+    nks = min(nk, nk_sample if nk_sample > 0 else max(4, min(16, os.cpu_count() or 1)))
+    c = synth.make_case(ni, nj, nks, ntr, cfl=cfl)
+    CS = tracer_advect_init(None, c.G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}, None, None)
+    Reg = synth.bind_registry(c)
+    h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
+    return c, CS, Reg, (h, u, v), ni * nj * nks * ntr, nks
+
+
+def cpu_time_steps(c, CS, Reg, huv, steps: int, warmup: int, threads: int):
+    from oracle import oracle
+    h, u, v = huv
+    for _ in range(warmup):
+        oracle.advect_tracer(h, u, v, None, c.dt, c.G, c.GV, None, CS, Reg, nthreads=threads)
+    t0 = time.perf_counter()
+    nit = 0
+    for _ in range(steps):
+        nit = oracle.advect_tracer(h, u, v, None, c.dt, c.G, c.GV, None, CS, Reg, nthreads=threads)
+    return (time.perf_counter() - t0) / max(steps, 1), nit
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    name = args.workload
+    ni, nj, nk, ntr, scheme = workload_shape(name)
+    c, CS, Reg, huv, units, nks = cpu_sample_setup(name, args.cfl, args.cpu_levels)
+    threads = min(os.cpu_count() or 1, nks)     # the oracle threads over k like the reference (:147,247)
+    sec, nit = cpu_time_steps(c, CS, Reg, huv, args.steps, args.warmup, threads)
+    val = units / sec
+    sample = "%dx%dx%d of %d levels, %d tracers, %s, cfl99=%.2f (%d iteration(s)), oracle OpenMP over k" % (
+        ni, nj, nks, nk, ntr, scheme, args.cfl, nit)
+    out = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+           "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "config": {"workload": name, "ni": ni, "nj": nj, "nk": nk, "ntr": ntr, "scheme": scheme,
+                      "cfl99": args.cfl, "sample": sample},
+           "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+           "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out))
+    return 0
+
+
+# ---------------------------------------------------------------------------
+# own arm
+# ---------------------------------------------------------------------------
+def run_native(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (own arm) needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    from mom6_b200 import synth, capi
+    from mom6_b200.tracer_advect import tracer_advect_init, tracer_advect_end, advect_tracer
+    from mom6_b200.types import TracerRegistry, register_tracer
+
+    name = args.workload
+    ni, nj, nk, ntr, scheme = workload_shape(name)
+    N = ni * nj * nk
+    units = N * ntr
+    peak, peak_src = _peaks()
+
+    if world > 1:
+        from mom6_b200 import multi
+        return multi.bench_multi(args, name, world, rank, local_rank, peak, peak_src)
+
+    # ---- resident inputs --------------------------------------------------
+    c = synth.make_case(ni, nj, nk, ntr, cfl=args.cfl, device="cuda")
+    CS = tracer_advect_init(None, c.G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}, None, None)
+    plan = capi.Plan(c.G, c.GV, CS)
+    plan.set_ntr(ntr)
+    for m in range(ntr):
+        t = c.tracer(m)
+        plan.upload_tracer(m, t)
+        plan.bind_tracer(m, None, c.conc_underflow(m))
+        del t
+    plan.upload_field(capi.F_H_END, c.h_end)
+    plan.upload_field(capi.F_UHTR, c.uhtr)
+    plan.upload_field(capi.F_VHTR, c.vhtr)
+    torch.cuda.synchronize()
+
+    stream = torch.cuda.ExternalStream(plan.stream)
+    for _ in range(args.warmup):
+        nit = plan.advect_resident(c.dt)
+    plan.set_option("profile", 1)
+    launches0 = plan.kernel_launches
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record(stream)
+    per_call = []
+    for _ in range(args.steps):
+        nit = plan.advect_resident(c.dt)
+        per_call.append(plan.last_advect_ms)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    total_ms = e0.elapsed_time(e1)
+    ms_step = total_ms / args.steps
+    launches = plan.kernel_launches - launches0
+    kc = {capi.KC_NAMES[k]: plan.kernel_class_time(k) for k in range(len(capi.KC_NAMES))}
+    plan.set_option("profile", 0)
+    value = units / (ms_step * 1e-3)
+
+    # ---- roofline of the dominant kernel class -----------------------------
+    dom = max(("tracer_x", "tracer_y"), key=lambda k: kc[k][0])
+    dom_ms, dom_n = kc[dom]
+    dom_avg_ms = dom_ms / max(dom_n, 1)
+    # algorithmic bytes of one tracer-sweep launch: every tracer read once and written once,
+    # plus the four tracer-independent mass fields of the sweep read once
+    alg_launch = (16.0 * ntr + 32.0) * N
+    ach = alg_launch / (dom_avg_ms * 1e-3) / 1e9
+    b_alg_call = (16.0 * ntr + 24.0) * N
+    path_gbs = b_alg_call / (ms_step * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "k_%s (tracer sweep, all tracers per launch)" % dom,
+                "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                "peak_source": peak_src, "avg_launch_ms": dom_avg_ms, "launches_timed": dom_n,
+                "alg_bytes_per_launch": alg_launch,
+                "path": {"alg_bytes_per_call": b_alg_call, "achieved": path_gbs, "frac": path_gbs / peak,
+                         "note": "whole advect_tracer call: B_alg=(16*ntr+24)*N over ms_per_step"},
+                "class_ms_per_step": {k: v[0] / args.steps for k, v in kc.items()}}
+    tr_path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr_path):
+        try:
+            roofline["traffic"] = json.load(open(tr_path)).get(name, {}).get(dom)
+        except Exception:
+            pass
+
+    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+           "dtype": "f64", "data": "synthetic",
+           "config": {"workload": name, "ni": ni, "nj": nj, "nk": nk, "ntr": ntr, "scheme": scheme,
+                      "halo": 4, "cfl99": args.cfl, "iterations_per_call": nit, "layout": "1x1",
+                      "l2": "inputs_exceed_l2 (%.1f GB resident)" % (plan.device_bytes / 1e9),
+                      "fma_contraction": "off"},
+           "roofline": roofline, "gpu_launches": int(launches), "clocks": clocks,
+           "per_call_ms": {"min": min(per_call), "max": max(per_call)}}
+
+    # free the resident plan before the e2e / cpu legs
+    plan.destroy()
+    del plan, c
+    torch.cuda.empty_cache()
+
+    # ---- e2e: reference-facing call with pinned host arrays -----------------
+    if not args.no_e2e:
+        out["e2e"] = run_e2e(args, name)
+    # ---- cpu baseline ----------------------------------------------------------
+    if not args.no_cpu:
+        cc, CSc, Regc, huv, u_s, nks = cpu_sample_setup(name, args.cfl, args.cpu_levels)
+        threads = min(os.cpu_count() or 1, nks)
+        sec, nit_c = cpu_time_steps(cc, CSc, Regc, huv, 1, 0, threads)
+        out["cpu_baseline"] = {"value": u_s / sec, "unit": UNIT, "cores": threads, "kind": "port",
+                               "sample": "%dx%dx%d of %d levels, %d tracers, %s, 1 call, %.1f s, oracle OpenMP over k"
+                                         % (ni, nj, nks, nk, ntr, scheme, sec)}
+    print(json.dumps(out))
+    return 0
+
+
+def run_e2e(args, name):
+    """The call a Fortran host makes: advect_tracer with HOST arrays (MIRROR mode)."""
+    import numpy as np
+    import torch
+    from mom6_b200 import synth
+    from mom6_b200.tracer_advect import tracer_advect_init, tracer_advect_end, advect_tracer
+    from mom6_b200.types import TracerRegistry, register_tracer
+    ni, nj, nk, ntr, scheme = workload_shape(name)
+    c = synth.make_case(ni, nj, nk, ntr, cfl=args.cfl, device="cuda")
+    CS = tracer_advect_init(None, c.G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}, None, None)
+    Reg = TracerRegistry()
+    keep = []
+    for m in range(ntr):
+        t = c.tracer(m)
+        ht = torch.empty(t.shape, dtype=torch.float64, pin_memory=True)
+        ht.copy_(t)
+        del t
+        keep.append(ht)
+        register_tracer(ht.numpy(), Reg, name="tr%02d" % m, underflow_conc=c.conc_underflow(m))
+    host = []
+    for a in (c.h_end, c.uhtr, c.vhtr):
+        ha = torch.empty(a.shape, dtype=torch.float64, pin_memory=True)
+        ha.copy_(a)
+        host.append(ha)
+    G, GV, dt = c.G, c.GV, c.dt
+    del c
+    torch.cuda.empty_cache()
+    h, u, v = (x.numpy() for x in host)
+    h2d = sum(x.numel() * 8 for x in host) + sum(x.numel() * 8 for x in keep)
+    d2h = sum(x.numel() * 8 for x in keep)
+    for _ in range(args.e2e_warmup):
+        advect_tracer(h, u, v, None, dt, G, GV, None, CS, Reg)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        advect_tracer(h, u, v, None, dt, G, GV, None, CS, Reg)   # returns after the D2H copies completed
+    torch.cuda.synchronize()
+    sec = (time.perf_counter() - t0) / args.e2e_steps
+    chk = float(keep[0].numpy()[0, G.jsc, G.isc])
+    tracer_advect_end(CS)
+    return {"value": ni * nj * nk * ntr / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "ms_per_step": sec * 1e3, "steps": args.e2e_steps,
+            "call": "mom6_b200.tracer_advect.advect_tracer -> mom6adv_advect (MIRROR mode, pinned host arrays)",
+            "result_probe": chk}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--workload", default="OM4_025")
+    ap.add_argument("--cfl", type=float, default=0.45, help="99th percentile upwind CFL of the synthetic transports")
+    ap.add_argument("--cpu-levels", type=int, default=0, help="levels in the bounded CPU sample")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--e2e-warmup", type=int, default=1)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "native":
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_native(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -134,9 +134,22 @@ double mom6adv_last_advect_ms(const mom6adv_plan *plan);
 long long mom6adv_kernel_launches(const mom6adv_plan *plan);
 /* Bytes of HBM held by the plan. */
 long long mom6adv_device_bytes(const mom6adv_plan *plan);
-/* Algorithm selector for experiments/tests: 0 = unfused reference-order
- * sweeps, 1 = fused tile kernel (default when available). */
+/* Options: "profile" 0/1 -- time every kernel class of advect calls with CUDA
+ * events on the plan's stream (resets the accumulators); "fast" 0/1 -- 0 forces
+ * the generic thread-per-cell sweeps, 1 (default) uses the streaming kernels
+ * whenever no flux diagnostic is associated. */
 int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value);
+/* Kernel classes of the per-class timers: the stand-ins for the reference's
+ * (Ocean advect tracer) / (Ocean tracer halo updates) / (Ocean tracer global
+ * synch) clock triple (:1146-1148), resolved per kernel family. */
+enum { MOM6ADV_KC_PROLOGUE = 0, MOM6ADV_KC_HALO = 1, MOM6ADV_KC_FLAGS = 2, MOM6ADV_KC_MASS = 3,
+       MOM6ADV_KC_TRACER_X = 4, MOM6ADV_KC_TRACER_Y = 5, MOM6ADV_KC_OTHER = 6, MOM6ADV_KC_COUNT = 7 };
+/* Accumulated device time [ms] and number of timed brackets of one class
+ * since "profile" was last set. */
+int mom6adv_kernel_class_time(const mom6adv_plan *plan, int kclass, double *ms_total, long long *n);
+/* The cudaStream_t every kernel of the plan is launched on (so that a host
+ * can bracket calls with its own CUDA events). */
+void *mom6adv_stream(const mom6adv_plan *plan);
 
 #ifdef __cplusplus
 }

@@ -18,6 +18,7 @@ LIB_PATH = os.path.join(_HERE, "libmom6adv_b200.so")
 
 OK, ERR_NOT_INIT, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_COMM = range(6)
 F_H_END, F_UHTR, F_VHTR, F_VOL_PREV, F_UHR, F_VHR, F_HPREV = range(7)
+KC_NAMES = ("prologue", "halo", "flags", "mass", "tracer_x", "tracer_y", "other")
 DIAG_KINDS = ("ad_x", "ad_y", "ad2d_x", "ad2d_y", "advection_xy")
 
 _dp = C.POINTER(C.c_double)
@@ -65,6 +66,8 @@ SYMBOLS = {
     "mom6adv_kernel_launches": (C.c_longlong, [_P]),
     "mom6adv_device_bytes": (C.c_longlong, [_P]),
     "mom6adv_set_option": (C.c_int, [_P, C.c_char_p, C.c_int]),
+    "mom6adv_kernel_class_time": (C.c_int, [_P, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]),
+    "mom6adv_stream": (C.c_void_p, [_P]),
 }
 
 _lib = None
@@ -190,6 +193,14 @@ class Plan:
 
     def sync(self): self._ck(self._l.mom6adv_sync(self._h))
     def set_option(self, key: str, value: int): self._ck(self._l.mom6adv_set_option(self._h, key.encode(), value))
+
+    def kernel_class_time(self, kclass: int):
+        ms, n = C.c_double(0.0), C.c_longlong(0)
+        self._ck(self._l.mom6adv_kernel_class_time(self._h, kclass, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    @property
+    def stream(self) -> int: return int(self._l.mom6adv_stream(self._h) or 0)
 
     @property
     def last_advect_ms(self) -> float: return float(self._l.mom6adv_last_advect_ms(self._h))

@@ -61,7 +61,35 @@ struct mom6adv_plan {
   long long launches = 0;
   long long dev_bytes = 0;
   int opt_fused = 0;
+  // per-kernel-class CUDA-event timing (option "profile")
+  int opt_profile = 0;
+  std::vector<cudaEvent_t> prof_ev;      // pairs: [2n] start, [2n+1] stop
+  std::vector<int> prof_cls;             // class of pair n (pairs used in the current call)
+  double prof_ms[MOM6ADV_KC_COUNT] = {0, 0, 0, 0, 0, 0, 0};
+  long long prof_n[MOM6ADV_KC_COUNT] = {0, 0, 0, 0, 0, 0, 0};
 };
+
+// RAII bracket: records an event pair around the launches of one kernel class.
+struct ProfScope {
+  mom6adv_plan *p; int idx = -1;
+  ProfScope(mom6adv_plan *plan, int cls) : p(plan) {
+    if (!p->opt_profile) return;
+    idx = (int)p->prof_cls.size();
+    while ((int)p->prof_ev.size() < 2 * (idx + 1)) { cudaEvent_t e; cudaEventCreate(&e); p->prof_ev.push_back(e); }
+    p->prof_cls.push_back(cls);
+    cudaEventRecord(p->prof_ev[2 * idx], p->stream);
+  }
+  ~ProfScope() { if (idx >= 0) cudaEventRecord(p->prof_ev[2 * idx + 1], p->stream); }
+};
+static void prof_collect(mom6adv_plan *p) {   // call after the stream is synchronised
+  for (size_t n = 0; n < p->prof_cls.size(); n++) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, p->prof_ev[2 * n], p->prof_ev[2 * n + 1]) == cudaSuccess) {
+      p->prof_ms[p->prof_cls[n]] += ms; p->prof_n[p->prof_cls[n]]++;
+    }
+  }
+  p->prof_cls.clear();
+}
 
 static thread_local std::string g_err;
 
@@ -316,6 +344,7 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
     if (plan->halo[p].src) cudaFree(plan->halo[p].src);
     if (plan->halo[p].sgn) cudaFree(plan->halo[p].sgn);
   }
+  for (cudaEvent_t e : plan->prof_ev) cudaEventDestroy(e);
   if (plan->ev0) cudaEventDestroy(plan->ev0);
   if (plan->ev1) cudaEventDestroy(plan->ev1);
   if (plan->stream) cudaStreamDestroy(plan->stream);
@@ -390,6 +419,7 @@ static int sync_tracer_table(mom6adv_plan *plan) {
 static int group_pass(mom6adv_plan *plan) {
   const Geom &g = plan->g;
   cudaStream_t s = plan->stream;
+  ProfScope ps(plan, MOM6ADV_KC_HALO);
   // u list -> uhr, v list -> vhr, h list -> hprev + tracers
   launch_halo_apply(s, g.plane, g.nk, plan->halo[1].dst, plan->halo[1].src, plan->halo[1].sgn, plan->halo[1].n,
                     plan->halo_fields_dev + 0, 1);
@@ -412,19 +442,27 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme) 
   bool any_ad2d = false;
   for (int m = 0; m < plan->ntr; m++) if (plan->tr[m].diag[dir == 0 ? 2 : 3]) any_ad2d = true;
   if (dir == 0) {
-    launch_flags_begin(s, g, plan->domore_k, plan->domore_u, plan->entry_u, rg.js, rg.je);
-    launch_mass_flux(s, 0, g, rg, plan->uhr, plan->hprev, plan->areaT, min_h, plan->entry_u, plan->domore_u, plan->hh, plan->cfl);
-    launch_mass_update(s, 0, g, rg, plan->uhr, plan->hprev, plan->hh, plan->areaT, plan->uh_neglect, h_neglect,
-                       plan->entry_u, plan->domore_k, plan->hlst, plan->ihnew);
+    {
+      ProfScope ps(plan, MOM6ADV_KC_MASS);
+      launch_flags_begin(s, g, plan->domore_k, plan->domore_u, plan->entry_u, rg.js, rg.je);
+      launch_mass_flux(s, 0, g, rg, plan->uhr, plan->hprev, plan->areaT, min_h, plan->entry_u, plan->domore_u, plan->hh, plan->cfl);
+      launch_mass_update(s, 0, g, rg, plan->uhr, plan->hprev, plan->hh, plan->areaT, plan->uh_neglect, h_neglect,
+                         plan->entry_u, plan->domore_k, plan->hlst, plan->ihnew);
+    }
+    ProfScope pt(plan, MOM6ADV_KC_TRACER_X);
     launch_tracer_sweep(s, scheme, 0, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->hlst,
                         plan->ihnew, plan->mmx, plan->IareaT, plan->entry_u, plan->domore_k, Idt);
     if (any_ad2d) launch_ad2d(s, scheme, 0, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->ihnew,
                               plan->mmx, plan->entry_u, plan->domore_k, Idt);
   } else {
-    launch_flags_begin(s, g, plan->domore_k, plan->domore_v, plan->entry_v, rg.js - 1, rg.je);
-    launch_mass_flux(s, 1, g, rg, plan->vhr, plan->hprev, plan->areaT, min_h, plan->entry_v, plan->domore_v, plan->hh, plan->cfl);
-    launch_mass_update(s, 1, g, rg, plan->vhr, plan->hprev, plan->hh, plan->areaT, plan->vh_neglect, h_neglect,
-                       plan->entry_v, plan->domore_k, plan->hlst, plan->ihnew);
+    {
+      ProfScope ps(plan, MOM6ADV_KC_MASS);
+      launch_flags_begin(s, g, plan->domore_k, plan->domore_v, plan->entry_v, rg.js - 1, rg.je);
+      launch_mass_flux(s, 1, g, rg, plan->vhr, plan->hprev, plan->areaT, min_h, plan->entry_v, plan->domore_v, plan->hh, plan->cfl);
+      launch_mass_update(s, 1, g, rg, plan->vhr, plan->hprev, plan->hh, plan->areaT, plan->vh_neglect, h_neglect,
+                         plan->entry_v, plan->domore_k, plan->hlst, plan->ihnew);
+    }
+    ProfScope pt(plan, MOM6ADV_KC_TRACER_Y);
     launch_tracer_sweep(s, scheme, 1, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->hlst,
                         plan->ihnew, plan->mmy, plan->IareaT, plan->entry_v, plan->domore_k, Idt);
     if (any_ad2d) launch_ad2d(s, scheme, 1, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->ihnew,
@@ -468,8 +506,10 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
   // :112-113, :156
   CK(cudaMemsetAsync(plan->domore_u, 0, sizeof(int) * g.R * g.nk, s));
   CK(cudaMemsetAsync(plan->domore_v, 0, sizeof(int) * g.R * g.nk, s));
+  { ProfScope ps(plan, MOM6ADV_KC_PROLOGUE);
   launch_init_residuals(s, g, plan->h_end, plan->uhtr, plan->vhtr, use_vol_prev ? plan->vol_prev : nullptr,
                         plan->areaT, plan->uhr, plan->vhr, plan->hprev);    // :152-178
+  }
   {
     std::vector<int> ones(g.nk, 1);
     CK(cudaMemcpyAsync(plan->domore_k, ones.data(), sizeof(int) * g.nk, cudaMemcpyHostToDevice, s));
@@ -528,6 +568,7 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
   float ms = 0.f;
   CK(cudaEventElapsedTime(&ms, plan->ev0, plan->ev1));
   plan->last_ms = ms;
+  prof_collect(plan);
   CK(cudaGetLastError());
   return MOM6ADV_OK;
 }
@@ -681,8 +722,22 @@ extern "C" double mom6adv_last_advect_ms(const mom6adv_plan *plan) { return plan
 extern "C" long long mom6adv_kernel_launches(const mom6adv_plan *plan) { return plan ? plan->launches : 0; }
 extern "C" long long mom6adv_device_bytes(const mom6adv_plan *plan) { return plan ? plan->dev_bytes : 0; }
 
+extern "C" void *mom6adv_stream(const mom6adv_plan *plan) { return plan ? (void *)plan->stream : nullptr; }
+
+extern "C" int mom6adv_kernel_class_time(const mom6adv_plan *plan, int kclass, double *ms_total, long long *n) {
+  if (!plan || kclass < 0 || kclass >= MOM6ADV_KC_COUNT) return MOM6ADV_ERR_INVALID;
+  if (ms_total) *ms_total = plan->prof_ms[kclass];
+  if (n) *n = plan->prof_n[kclass];
+  return MOM6ADV_OK;
+}
+
 extern "C" int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value) {
   if (!plan || !key) return fail(plan, MOM6ADV_ERR_INVALID, "set_option: NULL argument");
   if (!strcmp(key, "fused")) { plan->opt_fused = value; return MOM6ADV_OK; }
+  if (!strcmp(key, "profile")) {
+    plan->opt_profile = value;
+    for (int c = 0; c < MOM6ADV_KC_COUNT; c++) { plan->prof_ms[c] = 0.0; plan->prof_n[c] = 0; }
+    return MOM6ADV_OK;
+  }
   return fail(plan, MOM6ADV_ERR_INVALID, std::string("set_option: unknown key ") + key);
 }
