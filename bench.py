@@ -101,6 +101,9 @@ class ClockSampler:
 
 def workload_shape(name: str):
     from mom6_b200 import synth
+    if "," in name:          # ad-hoc "ni,nj,nk,ntr[,scheme]" (profiling runs)
+        f = name.split(",")
+        return int(f[0]), int(f[1]), int(f[2]), int(f[3]), (f[4] if len(f) > 4 else "PPM")
     ni, nj, nk, ntr, scheme = synth.CONFIGS[name]
     return ni, nj, nk, ntr, scheme
 

@@ -30,6 +30,15 @@ struct TracerDev {
   double conc_underflow;
 };
 
+// Tracer table passed by value to the streaming kernels (constant bank).
+#define MOM6ADV_MAXT 64
+struct TrTable {
+  const double *src[MOM6ADV_MAXT];
+  double *dst[MOM6ADV_MAXT];
+  double cu[MOM6ADV_MAXT];       // conc_underflow
+  int n;
+};
+
 // ---- gfortran intrinsic semantics (argument-order compare-select) -----------
 __device__ __forceinline__ double gmax2(double a, double b) { return (b > a) ? b : a; }
 __device__ __forceinline__ double gmin2(double a, double b) { return (b < a) ? b : a; }

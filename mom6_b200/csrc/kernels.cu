@@ -206,7 +206,8 @@ void launch_flags_begin(cudaStream_t s, const Geom &g, const int *domore_k, int 
 template <int DIR>
 __global__ void k_mass_flux(Geom g, Range rg, const double *__restrict__ res, const double *__restrict__ hprev,
                             const double *__restrict__ areaT, double min_h, const int *__restrict__ entry,
-                            int *__restrict__ domore, double *__restrict__ hh, double *__restrict__ cfl) {
+                            int *__restrict__ domore, double *__restrict__ hh, double *__restrict__ cfl,
+                            double *__restrict__ hcv, double *__restrict__ gv, int plm) {
   int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y, k0 = blockIdx.z;
   if (ci >= g.P) return;
   const int i = ci - g.coff, j = rj - g.roff;
@@ -244,12 +245,17 @@ __global__ void k_mass_flux(Geom g, Range rg, const double *__restrict__ res, co
     }
   }
   hh[q] = uh; cfl[q] = cf;
+  if (hcv) {      // per-face factors of the flux formulas, shared by every tracer (streaming kernels)
+    hcv[q] = 0.5 * cf;                                   // 0.5*CFL          (:551,554 / :937,941)
+    gv[q] = plm ? (1. - cf) : (1. - (2. / 3.) * cf);     // 1-CFL (:565,569) or 1-2/3*CFL
+  }
 }
 void launch_mass_flux(cudaStream_t s, int dir, const Geom &g, Range rg, const double *res, const double *hprev,
-                      const double *areaT, double min_h, const int *entry, int *domore, double *hh, double *cfl) {
+                      const double *areaT, double min_h, const int *entry, int *domore, double *hh, double *cfl,
+                      double *hc, double *gq, int plm) {
   dim3 grid((g.P + TPB - 1) / TPB, g.R, g.nk);
-  if (dir == 0) k_mass_flux<0><<<grid, TPB, 0, s>>>(g, rg, res, hprev, areaT, min_h, entry, domore, hh, cfl);
-  else k_mass_flux<1><<<grid, TPB, 0, s>>>(g, rg, res, hprev, areaT, min_h, entry, domore, hh, cfl);
+  if (dir == 0) k_mass_flux<0><<<grid, TPB, 0, s>>>(g, rg, res, hprev, areaT, min_h, entry, domore, hh, cfl, hc, gq, plm);
+  else k_mass_flux<1><<<grid, TPB, 0, s>>>(g, rg, res, hprev, areaT, min_h, entry, domore, hh, cfl, hc, gq, plm);
 }
 
 // ---------------------------------------------------------------------------

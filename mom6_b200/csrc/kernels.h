@@ -16,7 +16,8 @@ void launch_domore_k(cudaStream_t s, const Geom &g, int *domore_k, const int *do
 void launch_sum_domore_k(cudaStream_t s, const int *domore_k, int nk, int *out);
 void launch_flags_begin(cudaStream_t s, const Geom &g, const int *domore_k, int *domore, int *entry, int lo, int hi);
 void launch_mass_flux(cudaStream_t s, int dir, const Geom &g, Range rg, const double *res, const double *hprev,
-                      const double *areaT, double min_h, const int *entry, int *domore, double *hh, double *cfl);
+                      const double *areaT, double min_h, const int *entry, int *domore, double *hh, double *cfl,
+                      double *hc, double *gq, int plm);
 void launch_mass_update(cudaStream_t s, int dir, const Geom &g, Range rg, double *res, double *hprev,
                         const double *hh, const double *areaT, const double *neglect, double h_neglect,
                         const int *entry, const int *domore_k, double *hlst, double *ihnew);
@@ -33,3 +34,12 @@ void launch_halo_pack(cudaStream_t s, long long plane, int nk, const int *src, c
 void launch_halo_unpack(cudaStream_t s, long long plane, int nk, const int *dst, int n,
                         double *const *fields, int nfields, const double *buf);
 void launch_fill(cudaStream_t s, double *p, long long n, double v);
+
+// fast.cu: streaming tracer sweeps
+int x_fast_tiles(const Geom &g, int wbase);
+void launch_x_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
+                   const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm, const int *entry,
+                   const int *domore_k, int wbase);
+void launch_y_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
+                   const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm, const int *entry,
+                   const int *domore_k);

@@ -43,7 +43,7 @@ struct mom6adv_plan {
   // 3-D fields
   double *h_end = nullptr, *uhtr = nullptr, *vhtr = nullptr, *vol_prev = nullptr;
   double *uhr = nullptr, *vhr = nullptr, *hprev = nullptr;
-  double *hh = nullptr, *cfl = nullptr, *hlst = nullptr, *ihnew = nullptr;
+  double *hh = nullptr, *cfl = nullptr, *hlst = nullptr, *ihnew = nullptr, *hc = nullptr, *gq = nullptr;
   int *domore_u = nullptr, *domore_v = nullptr, *entry_u = nullptr, *entry_v = nullptr, *domore_k = nullptr;
   int *sum_dev = nullptr, *sum_host = nullptr;
   double *staging = nullptr;
@@ -61,6 +61,8 @@ struct mom6adv_plan {
   long long launches = 0;
   long long dev_bytes = 0;
   int opt_fused = 0;
+  int opt_fast = 1;
+  int wbase = 0;                     // first column of the first x tile (fast.cu)
   // per-kernel-class CUDA-event timing (option "profile")
   int opt_profile = 0;
   std::vector<cudaEvent_t> prof_ev;      // pairs: [2n] start, [2n+1] stop
@@ -227,7 +229,7 @@ static int create_impl(mom6adv_plan *plan, const mom6adv_grid *gr) {
   for (double **pp : p2) { int rc = dev_alloc(plan, pp, pl); if (rc) return rc; }
   const long long fe = field_elems(plan);
   double **p3[] = {&plan->h_end, &plan->uhtr, &plan->vhtr, &plan->uhr, &plan->vhr, &plan->hprev,
-                   &plan->hh, &plan->cfl, &plan->hlst, &plan->ihnew};
+                   &plan->hh, &plan->cfl, &plan->hlst, &plan->ihnew, &plan->hc, &plan->gq};
   for (double **pp : p3) { int rc = dev_alloc(plan, pp, fe); if (rc) return rc; }
   int **pf[] = {&plan->domore_u, &plan->domore_v, &plan->entry_u, &plan->entry_v};
   for (int **pp : pf) { int rc = dev_alloc(plan, pp, (long long)g.R * g.nk); if (rc) return rc; }
@@ -297,9 +299,13 @@ extern "C" int mom6adv_plan_create(const mom6adv_grid *gr, const mom6adv_config 
   g.isc = gr->isc; g.iec = gr->iec; g.jsc = gr->jsc; g.jec = gr->jec;
   g.IsdB = gr->IsdB; g.JsdB = gr->JsdB; g.nk = gr->nk;
   const int nid = g.ied - g.isd + 1, njd = g.jed - g.jsd + 1;
-  const int lead = ((hi + 1 + 15) / 16) * 16 - hi;      // column of isd; isc lands on a multiple of 16
+  int lead = ((hi + 1 + 15) / 16) * 16 - hi;            // column of isd; isc lands on a multiple of 16
+  if (lead < 4) lead += 16;
   g.coff = lead - g.isd;
-  g.P = ((lead + nid + 1 + 15) / 16) * 16;
+  // x tiles of the streaming kernel: 128 columns from wbase + 120*n, 120 useful (lanes 1..30)
+  plan->wbase = (lead - 4) & ~3;
+  const int ntx = (lead + nid - 1 - (plan->wbase + 4)) / 120 + 1;
+  g.P = ((std::max(lead + nid + 1, plan->wbase + 120 * (ntx - 1) + 128) + 15) / 16) * 16;
   g.roff = 1 - g.jsd;
   g.R = njd + 2;
   g.plane = (long long)g.P * g.R;
@@ -331,7 +337,7 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   if (plan->stream) cudaStreamSynchronize(plan->stream);
   double *d[] = {plan->areaT, plan->IareaT, plan->mCu, plan->mCv, plan->uh_neglect, plan->vh_neglect, plan->mmx,
                  plan->mmy, plan->h_end, plan->uhtr, plan->vhtr, plan->vol_prev, plan->uhr, plan->vhr, plan->hprev,
-                 plan->hh, plan->cfl, plan->hlst, plan->ihnew, plan->staging};
+                 plan->hh, plan->cfl, plan->hlst, plan->ihnew, plan->hc, plan->gq, plan->staging};
   for (double *p : d) if (p) cudaFree(p);
   int *f[] = {plan->domore_u, plan->domore_v, plan->entry_u, plan->entry_v, plan->domore_k, plan->sum_dev};
   for (int *p : f) if (p) cudaFree(p);
@@ -400,14 +406,16 @@ static int sync_tracer_table(mom6adv_plan *plan) {
   if (plan->tr_dev) { cudaFree(plan->tr_dev); plan->tr_dev = nullptr; }
   CK(cudaMalloc((void **)&plan->tr_dev, sizeof(TracerDev) * h.size()));
   CK(cudaMemcpyAsync(plan->tr_dev, h.data(), sizeof(TracerDev) * h.size(), cudaMemcpyHostToDevice, plan->stream));
-  // halo field table: [0] = uhr, [1] = vhr, [2] = hprev, [3..] = tracers (buffer 0)
+  // halo field tables, one per ping-pong buffer b: [0] = uhr, [1] = vhr, [2] = hprev, [3..] = tracers (buffer b)
   const int nf = 3 + plan->ntr;
-  std::vector<double *> hf(nf);
-  hf[0] = plan->uhr; hf[1] = plan->vhr; hf[2] = plan->hprev;
-  for (int m = 0; m < plan->ntr; m++) hf[3 + m] = plan->tr[m].buf[0];
+  std::vector<double *> hf(2 * nf);
+  for (int b = 0; b < 2; b++) {
+    hf[b * nf + 0] = plan->uhr; hf[b * nf + 1] = plan->vhr; hf[b * nf + 2] = plan->hprev;
+    for (int m = 0; m < plan->ntr; m++) hf[b * nf + 3 + m] = plan->tr[m].buf[b];
+  }
   if (plan->halo_fields_dev) { cudaFree(plan->halo_fields_dev); plan->halo_fields_dev = nullptr; }
-  CK(cudaMalloc((void **)&plan->halo_fields_dev, sizeof(double *) * nf));
-  CK(cudaMemcpyAsync(plan->halo_fields_dev, hf.data(), sizeof(double *) * nf, cudaMemcpyHostToDevice, plan->stream));
+  CK(cudaMalloc((void **)&plan->halo_fields_dev, sizeof(double *) * 2 * nf));
+  CK(cudaMemcpyAsync(plan->halo_fields_dev, hf.data(), sizeof(double *) * 2 * nf, cudaMemcpyHostToDevice, plan->stream));
   CK(cudaStreamSynchronize(plan->stream));
   plan->tr_dirty = false;
   return 0;
@@ -420,13 +428,14 @@ static int group_pass(mom6adv_plan *plan) {
   const Geom &g = plan->g;
   cudaStream_t s = plan->stream;
   ProfScope ps(plan, MOM6ADV_KC_HALO);
-  // u list -> uhr, v list -> vhr, h list -> hprev + tracers
+  // u list -> uhr, v list -> vhr, h list -> hprev + tracers (live buffer)
+  double **tab = plan->halo_fields_dev + plan->cur * (3 + plan->ntr);
   launch_halo_apply(s, g.plane, g.nk, plan->halo[1].dst, plan->halo[1].src, plan->halo[1].sgn, plan->halo[1].n,
-                    plan->halo_fields_dev + 0, 1);
+                    tab + 0, 1);
   launch_halo_apply(s, g.plane, g.nk, plan->halo[2].dst, plan->halo[2].src, plan->halo[2].sgn, plan->halo[2].n,
-                    plan->halo_fields_dev + 1, 1);
+                    tab + 1, 1);
   launch_halo_apply(s, g.plane, g.nk, plan->halo[0].dst, plan->halo[0].src, plan->halo[0].sgn, plan->halo[0].n,
-                    plan->halo_fields_dev + 2, 1 + plan->ntr);
+                    tab + 2, 1 + plan->ntr);
   plan->launches += 3;
   CK(cudaGetLastError());
   return 0;
@@ -439,13 +448,51 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme) 
   cudaStream_t s = plan->stream;
   const double min_h = 0.1 * plan->Angstrom_H;        // :401 / :773
   const double h_neglect = plan->H_subroundoff;       // :403 / :775
-  bool any_ad2d = false;
-  for (int m = 0; m < plan->ntr; m++) if (plan->tr[m].diag[dir == 0 ? 2 : 3]) any_ad2d = true;
+  bool any_ad2d = false, any_diag = false;
+  for (int m = 0; m < plan->ntr; m++) {
+    if (plan->tr[m].diag[dir == 0 ? 2 : 3]) any_ad2d = true;
+    for (int d = 0; d < 5; d++) if (plan->tr[m].diag[d]) any_diag = true;
+  }
+  if (plan->opt_fast && !any_diag) {
+    // streaming kernels (fast.cu): mass fields as below, then all tracers in chunks of MOM6ADV_MAXT
+    const bool x = (dir == 0);
+    int *dom = x ? plan->domore_u : plan->domore_v, *ent = x ? plan->entry_u : plan->entry_v;
+    double *res = x ? plan->uhr : plan->vhr;
+    {
+      ProfScope ps(plan, MOM6ADV_KC_MASS);
+      launch_flags_begin(s, g, plan->domore_k, dom, ent, x ? rg.js : rg.js - 1, rg.je);
+      launch_mass_flux(s, dir, g, rg, res, plan->hprev, plan->areaT, min_h, ent, dom, plan->hh, plan->cfl,
+                       plan->hc, plan->gq, scheme == SCHEME_PLM);
+      launch_mass_update(s, dir, g, rg, res, plan->hprev, plan->hh, plan->areaT, x ? plan->uh_neglect : plan->vh_neglect,
+                         h_neglect, ent, plan->domore_k, plan->hlst, plan->ihnew);
+      plan->launches += 3;
+    }
+    ProfScope pt(plan, x ? MOM6ADV_KC_TRACER_X : MOM6ADV_KC_TRACER_Y);
+    for (int m0 = 0; m0 < plan->ntr; m0 += MOM6ADV_MAXT) {
+      TrTable tt;
+      tt.n = std::min(MOM6ADV_MAXT, plan->ntr - m0);
+      for (int m = 0; m < tt.n; m++) {
+        const TracerSlot &ts = plan->tr[m0 + m];
+        tt.src[m] = ts.buf[plan->cur];
+        tt.dst[m] = x ? ts.buf[1 - plan->cur] : ts.buf[plan->cur];
+        tt.cu[m] = ts.conc_underflow;
+      }
+      if (x) launch_x_fast(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
+                           plan->domore_k, plan->wbase);
+      else launch_y_fast(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmy, ent,
+                         plan->domore_k);
+      plan->launches++;
+    }
+    if (x) plan->cur = 1 - plan->cur;      // x is out of place, y in place
+    CK(cudaGetLastError());
+    return 0;
+  }
   if (dir == 0) {
     {
       ProfScope ps(plan, MOM6ADV_KC_MASS);
       launch_flags_begin(s, g, plan->domore_k, plan->domore_u, plan->entry_u, rg.js, rg.je);
-      launch_mass_flux(s, 0, g, rg, plan->uhr, plan->hprev, plan->areaT, min_h, plan->entry_u, plan->domore_u, plan->hh, plan->cfl);
+      launch_mass_flux(s, 0, g, rg, plan->uhr, plan->hprev, plan->areaT, min_h, plan->entry_u, plan->domore_u, plan->hh, plan->cfl,
+                       nullptr, nullptr, 0);
       launch_mass_update(s, 0, g, rg, plan->uhr, plan->hprev, plan->hh, plan->areaT, plan->uh_neglect, h_neglect,
                          plan->entry_u, plan->domore_k, plan->hlst, plan->ihnew);
     }
@@ -458,7 +505,8 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme) 
     {
       ProfScope ps(plan, MOM6ADV_KC_MASS);
       launch_flags_begin(s, g, plan->domore_k, plan->domore_v, plan->entry_v, rg.js - 1, rg.je);
-      launch_mass_flux(s, 1, g, rg, plan->vhr, plan->hprev, plan->areaT, min_h, plan->entry_v, plan->domore_v, plan->hh, plan->cfl);
+      launch_mass_flux(s, 1, g, rg, plan->vhr, plan->hprev, plan->areaT, min_h, plan->entry_v, plan->domore_v, plan->hh, plan->cfl,
+                       nullptr, nullptr, 0);
       launch_mass_update(s, 1, g, rg, plan->vhr, plan->hprev, plan->hh, plan->areaT, plan->vh_neglect, h_neglect,
                          plan->entry_v, plan->domore_k, plan->hlst, plan->ihnew);
     }
@@ -502,7 +550,6 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
   if (use_vol_prev && !plan->vol_prev) return fail(plan, MOM6ADV_ERR_INVALID, "advect: vol_prev was not uploaded");
 
   CK(cudaEventRecord(plan->ev0, s));
-  plan->cur = 0;
   // :112-113, :156
   CK(cudaMemsetAsync(plan->domore_u, 0, sizeof(int) * g.R * g.nk, s));
   CK(cudaMemsetAsync(plan->domore_v, 0, sizeof(int) * g.R * g.nk, s));
@@ -625,7 +672,7 @@ extern "C" int mom6adv_upload_tracer(mom6adv_plan *plan, int m, const double *sr
   if (m < 0 || m >= plan->ntr) return fail(plan, MOM6ADV_ERR_INVALID, "upload_tracer: tracer index out of range");
   if (!src) return fail(plan, MOM6ADV_ERR_INVALID, "upload_tracer: NULL source");
   CK(cudaSetDevice(plan->device));
-  int rc = upload(plan, plan->tr[m].buf[0], src, plan->g.isd, plan->g.jsd, plan->g.nk);
+  int rc = upload(plan, plan->tr[m].buf[plan->cur], src, plan->g.isd, plan->g.jsd, plan->g.nk);
   if (rc) return rc;
   CK(cudaStreamSynchronize(plan->stream));
   return MOM6ADV_OK;
@@ -636,7 +683,7 @@ extern "C" int mom6adv_download_tracer(mom6adv_plan *plan, int m, double *dst) {
   if (m < 0 || m >= plan->ntr) return fail(plan, MOM6ADV_ERR_INVALID, "download_tracer: tracer index out of range");
   if (!dst) return fail(plan, MOM6ADV_ERR_INVALID, "download_tracer: NULL destination");
   CK(cudaSetDevice(plan->device));
-  int rc = download(plan, dst, plan->tr[m].buf[0], plan->g.isd, plan->g.jsd, plan->g.nk);
+  int rc = download(plan, dst, plan->tr[m].buf[plan->cur], plan->g.isd, plan->g.jsd, plan->g.nk);
   if (rc) return rc;
   CK(cudaStreamSynchronize(plan->stream));
   return MOM6ADV_OK;
@@ -692,12 +739,12 @@ extern "C" int mom6adv_advect(mom6adv_plan *plan, const double *h_end, const dou
     if ((rc = upload(plan, plan->vol_prev, vol_prev, g.isd, g.jsd, g.nk))) return rc;
   }
   for (int m = 0; m < plan->ntr; m++)
-    if ((rc = upload(plan, plan->tr[m].buf[0], plan->tr[m].host_t, g.isd, g.jsd, g.nk))) return rc;
+    if ((rc = upload(plan, plan->tr[m].buf[plan->cur], plan->tr[m].host_t, g.isd, g.jsd, g.nk))) return rc;
   const bool upd = vol_prev && update_vol_prev > 0;
   rc = run_advect(plan, dt, x_first, max_iter_in, vol_prev != nullptr, upd, n_iter);
   if (rc) return rc;
   for (int m = 0; m < plan->ntr; m++) {
-    if ((rc = download(plan, plan->tr[m].host_t, plan->tr[m].buf[0], g.isd, g.jsd, g.nk))) return rc;
+    if ((rc = download(plan, plan->tr[m].host_t, plan->tr[m].buf[plan->cur], g.isd, g.jsd, g.nk))) return rc;
     for (int d = 0; d < 5; d++) if (plan->tr[m].diag[d] && plan->tr[m].host_diag[d]) {
       int ilo, jlo, nlev;
       diag_info(g, d, &ilo, &jlo, &nlev);
@@ -734,6 +781,7 @@ extern "C" int mom6adv_kernel_class_time(const mom6adv_plan *plan, int kclass, d
 extern "C" int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value) {
   if (!plan || !key) return fail(plan, MOM6ADV_ERR_INVALID, "set_option: NULL argument");
   if (!strcmp(key, "fused")) { plan->opt_fused = value; return MOM6ADV_OK; }
+  if (!strcmp(key, "fast")) { plan->opt_fast = value; return MOM6ADV_OK; }
   if (!strcmp(key, "profile")) {
     plan->opt_profile = value;
     for (int c = 0; c < MOM6ADV_KC_COUNT; c++) { plan->prof_ms[c] = 0.0; plan->prof_n[c] = 0; }

@@ -37,6 +37,8 @@ class TracerAdvectCS:
     useHuynhStencilBug: bool = False
     # GPU plan cache (stands in for pass_uhr_vhr_t_hprev, :39)
     _plan: Any = field(default=None, repr=False)
+    # mom6adv_set_option(key, value) pairs applied when the plan is created (tests / experiments)
+    gpu_options: dict = field(default_factory=dict, repr=False)
 
     @property
     def stencil(self) -> int:
@@ -109,6 +111,8 @@ def _ensure_plan(G, GV, CS, Reg, device: int = -1):
     plan = CS._plan
     if plan is None:
         plan = capi.Plan(G, GV, CS, device=device)
+        for k, v in CS.gpu_options.items():
+            plan.set_option(k, int(v))
         plan._sig = None
         CS._plan = plan
     sig = _registry_signature(Reg)

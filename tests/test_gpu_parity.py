@@ -10,11 +10,12 @@ pytestmark = pytest.mark.gpu
 
 
 def _run_pair(ni, nj, nk, ntr, scheme, cfl=0.3, x_first=None, diags=False, ncalls=1, symmetric=True,
-              cyclic_x=True, halo=4, bug=False, **kw):
+              cyclic_x=True, halo=4, bug=False, fast=1, **kw):
     c = synth.make_case(ni, nj, nk, ntr, cfl=cfl, symmetric=symmetric, cyclic_x=cyclic_x, halo=halo, **kw)
     params = {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme, "USE_HUYNH_STENCIL_BUG": bug}
     CSo = tracer_advect_init(None, c.G, None, params, None, None)
     CSg = tracer_advect_init(None, c.G, None, params, None, None)
+    CSg.gpu_options["fast"] = fast
     Ro = synth.bind_registry(c, diags=diags)
     Rg = synth.bind_registry(c, diags=diags)
     h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
@@ -94,3 +95,58 @@ def test_om4_1_slice_bitwise():
     # OM4_1 horizontal shape, a few levels (the oracle finishes in seconds)
     c, Ro, Rg, outs, nit = _run_pair(360, 210, 4, 6, "PPM", cfl=0.5)
     _assert_bitwise(c, Ro, Rg, outs)
+
+
+# ---- streaming (fast) kernels vs generic kernels vs oracle -------------------------------------
+@pytest.mark.parametrize("scheme", ["PLM", "PPM", "PPM:H3"])
+@pytest.mark.parametrize("fast", [0, 1])
+def test_generic_and_streaming_kernels_both_bitwise(scheme, fast):
+    c, Ro, Rg, outs, nit = _run_pair(44, 40, 2, 10, scheme, cfl=0.9, fast=fast)
+    _assert_bitwise(c, Ro, Rg, outs)
+
+
+@pytest.mark.parametrize("scheme", ["PLM", "PPM", "PPM:H3"])
+@pytest.mark.parametrize("x_first", [True, False])
+def test_many_x_tiles(scheme, x_first):
+    # 300 columns = 3 warp tiles of the x kernel; 70 tracers = 2 tracer-table chunks
+    c, Ro, Rg, outs, nit = _run_pair(300, 37, 2, 70 if scheme == "PPM" else 5, scheme, cfl=0.9, x_first=x_first)
+    _assert_bitwise(c, Ro, Rg, outs)
+
+
+@pytest.mark.parametrize("halo,scheme", [(2, "PLM"), (3, "PPM"), (5, "PPM"), (6, "PLM"), (7, "PPM:H3")])
+def test_halo_widths(halo, scheme):
+    c, Ro, Rg, outs, nit = _run_pair(50, 33, 2, 3, scheme, cfl=0.9, halo=halo)
+    _assert_bitwise(c, Ro, Rg, outs)
+
+
+def test_closed_domain_no_land():
+    c, Ro, Rg, outs, nit = _run_pair(130, 31, 3, 4, "PPM", cfl=1.4, cyclic_x=False, land=False)
+    assert nit >= 2
+    _assert_bitwise(c, Ro, Rg, outs)
+
+
+def test_resident_mode_matches_mirror_mode():
+    """RESIDENT-mode calls (fields stay in HBM) give the same bits as MIRROR-mode calls."""
+    from mom6_b200 import capi
+    c = synth.make_case(60, 44, 3, 5, cfl=0.9)
+    params = {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": "PPM"}
+    CSo = tracer_advect_init(None, c.G, None, params, None, None)
+    Ro = synth.bind_registry(c)
+    h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
+    for _ in range(3):
+        oracle.advect_tracer(h, u, v, None, c.dt, c.G, c.GV, None, CSo, Ro)
+    CS = tracer_advect_init(None, c.G, None, params, None, None)
+    p = capi.Plan(c.G, c.GV, CS)
+    p.set_ntr(c.ntr)
+    R0 = synth.bind_registry(c)
+    for m in range(c.ntr):
+        p.upload_tracer(m, R0.Tr[m].t)
+        p.bind_tracer(m, None, c.conc_underflow(m))
+    p.upload_field(capi.F_H_END, h); p.upload_field(capi.F_UHTR, u); p.upload_field(capi.F_VHTR, v)
+    for _ in range(3):
+        p.advect_resident(c.dt)
+    for m in range(c.ntr):
+        out = np.zeros_like(R0.Tr[m].t)
+        p.download_tracer(m, out)
+        assert np.array_equal(c.G.interior(out).view(np.uint64), c.G.interior(Ro.Tr[m].t).view(np.uint64))
+    p.destroy()
