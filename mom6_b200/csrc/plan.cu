@@ -305,7 +305,7 @@ extern "C" int mom6adv_plan_create(const mom6adv_grid *gr, const mom6adv_config 
   // x tiles of the streaming kernel: 128 columns from wbase + 120*n, 120 useful (lanes 1..30)
   plan->wbase = (lead - 4) & ~3;
   const int ntx = (lead + nid - 1 - (plan->wbase + 4)) / 120 + 1;
-  g.P = ((std::max(lead + nid + 1, plan->wbase + 120 * (ntx - 1) + 128) + 15) / 16) * 16;
+  g.P = ((std::max(lead + nid + 1, plan->wbase + 120 * (ntx - 1) + 128) + 63) / 64) * 64;   // y tiles are 64 columns
   g.roff = 1 - g.jsd;
   g.R = njd + 2;
   g.plane = (long long)g.P * g.R;
