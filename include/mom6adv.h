@@ -137,7 +137,8 @@ long long mom6adv_device_bytes(const mom6adv_plan *plan);
 /* Options: "profile" 0/1 -- time every kernel class of advect calls with CUDA
  * events on the plan's stream (resets the accumulators); "fast" 0/1 -- 0 forces
  * the generic thread-per-cell sweeps, 1 (default) uses the streaming kernels
- * whenever no flux diagnostic is associated. */
+ * whenever no flux diagnostic is associated; "sparse" 0/1 -- 1 (default)
+ * updates only the cells next to faces with residual transport on trips >= 2. */
 int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value);
 /* Kernel classes of the per-class timers: the stand-ins for the reference's
  * (Ocean advect tracer) / (Ocean tracer halo updates) / (Ocean tracer global

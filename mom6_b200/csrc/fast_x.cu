@@ -6,8 +6,11 @@
 // ---------------------------------------------------------------------------
 #define XT_USE 120     // useful cells per 128-cell warp tile (lanes 1..30)
 
+#ifndef XMINB
+#define XMINB 4
+#endif
 template <int SCHEME>
-__global__ void __launch_bounds__(128, 4)
+__global__ void __launch_bounds__(128, XMINB)
 k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const double *__restrict__ hcv,
          const double *__restrict__ gqv, const double *__restrict__ hlstv, const double *__restrict__ ihv,
          const double *__restrict__ mmv, const int *__restrict__ entry, const int *__restrict__ domore_k, int wbase) {

@@ -42,13 +42,25 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
                  : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
   } while (!ok);
 }
+__device__ __forceinline__ void mbar_wait_sleep(unsigned bar, unsigned parity) {      // producer: back off while the ring is full
+  unsigned ok;
+  for (;;) {
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    if (ok) break;
+    __nanosleep(256);
+  }
+}
 __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned bytes, unsigned bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
+#ifndef YMINB
+#define YMINB 2
+#endif
 template <int SCHEME>
-__global__ void __launch_bounds__(32 * (YW + 1), 2)
+__global__ void __launch_bounds__(32 * (YW + 1), YMINB)
 k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const double *__restrict__ hcv,
          const double *__restrict__ gqv, const double *__restrict__ hlstv, const double *__restrict__ ihv,
          const double *__restrict__ mmv, const int *__restrict__ entry, const int *__restrict__ domore_k) {
@@ -86,7 +98,7 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
     else if (lane < 6 + nact) { src = tt.dst[m0 + lane - 6] + lev; roff = 0; }
     for (int it = 0; it < nsteps; it++) {
       const int s = it % YNS;
-      mbar_wait(smem_u32(&bar_empty[s]), ((it / YNS) & 1) ^ 1);
+      mbar_wait_sleep(smem_u32(&bar_empty[s]), ((it / YNS) & 1) ^ 1);
       const unsigned fb = smem_u32(&bar_full[s]);
       if (lane == 0) mbar_expect_tx(fb, (6 + nact) * YROWB);
       __syncwarp();

@@ -267,7 +267,8 @@ __global__ void k_mass_update(Geom g, Range rg, double *__restrict__ res, double
                               const double *__restrict__ hh, const double *__restrict__ areaT,
                               const double *__restrict__ neglect, double h_neglect,
                               const int *__restrict__ entry, const int *__restrict__ domore_k,
-                              double *__restrict__ hlst, double *__restrict__ ihnew) {
+                              double *__restrict__ hlst, double *__restrict__ ihnew,
+                              int *__restrict__ list, int *__restrict__ count, int cap) {
   int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y, k0 = blockIdx.z;
   if (ci >= g.P) return;
   const int i = ci - g.coff, j = rj - g.roff;
@@ -305,13 +306,18 @@ __global__ void k_mass_update(Geom g, Range rg, double *__restrict__ res, double
     }
   }
   hlst[q] = hl; ihnew[q] = ih;
+  if (list && ih > 0.0) {      // residual iterations: remember the cells that change (sparse.cu)
+    const int idx = atomicAdd(count, 1);
+    if (idx < cap) list[idx] = (int)q;
+  }
 }
 void launch_mass_update(cudaStream_t s, int dir, const Geom &g, Range rg, double *res, double *hprev,
                         const double *hh, const double *areaT, const double *neglect, double h_neglect,
-                        const int *entry, const int *domore_k, double *hlst, double *ihnew) {
+                        const int *entry, const int *domore_k, double *hlst, double *ihnew,
+                        int *list, int *count, int cap) {
   dim3 grid((g.P + TPB - 1) / TPB, g.R, g.nk);
-  if (dir == 0) k_mass_update<0><<<grid, TPB, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew);
-  else k_mass_update<1><<<grid, TPB, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew);
+  if (dir == 0) k_mass_update<0><<<grid, TPB, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap);
+  else k_mass_update<1><<<grid, TPB, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap);
 }
 
 // ---------------------------------------------------------------------------

@@ -20,7 +20,8 @@ void launch_mass_flux(cudaStream_t s, int dir, const Geom &g, Range rg, const do
                       double *hc, double *gq, int plm);
 void launch_mass_update(cudaStream_t s, int dir, const Geom &g, Range rg, double *res, double *hprev,
                         const double *hh, const double *areaT, const double *neglect, double h_neglect,
-                        const int *entry, const int *domore_k, double *hlst, double *ihnew);
+                        const int *entry, const int *domore_k, double *hlst, double *ihnew,
+                        int *list, int *count, int cap);
 void launch_tracer_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TracerDev *tr, int ntr,
                          int src, const double *hh, const double *cfl, const double *hlst, const double *ihnew,
                          const double *mm, const double *IareaT, const int *entry, const int *domore_k, double Idt);
@@ -43,3 +44,8 @@ void launch_x_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const Tr
 void launch_y_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
                    const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm, const int *entry,
                    const int *domore_k);
+
+// sparse.cu: list-driven tracer update of the residual iterations
+void launch_sparse_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TrTable &tt,
+                         const int *list, int cnt, int cap, const double *hh, const double *cfl, const double *hlst,
+                         const double *ihnew, const double *mm, const int *entry, double *newT);

@@ -62,6 +62,9 @@ struct mom6adv_plan {
   long long dev_bytes = 0;
   int opt_fused = 0;
   int opt_fast = 1;
+  int opt_sparse = 1;                // list-driven tracer update on residual iterations (sparse.cu)
+  int *sp_list = nullptr; double *sp_new = nullptr; int sp_cap = 0, sp_ntr = 0;
+  long long sparse_sweeps = 0, dense_sweeps = 0;
   int wbase = 0;                     // first column of the first x tile (fast.cu)
   // per-kernel-class CUDA-event timing (option "profile")
   int opt_profile = 0;
@@ -342,6 +345,8 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   int *f[] = {plan->domore_u, plan->domore_v, plan->entry_u, plan->entry_v, plan->domore_k, plan->sum_dev};
   for (int *p : f) if (p) cudaFree(p);
   if (plan->sum_host) cudaFreeHost(plan->sum_host);
+  if (plan->sp_list) cudaFree(plan->sp_list);
+  if (plan->sp_new) cudaFree(plan->sp_new);
   for (auto &s : plan->tr) free_slot(s);
   if (plan->tr_dev) cudaFree(plan->tr_dev);
   if (plan->halo_fields_dev) cudaFree(plan->halo_fields_dev);
@@ -443,7 +448,7 @@ static int group_pass(mom6adv_plan *plan) {
 
 // One directional sweep over cells [is..ie] x [js..je] (advect_x :329 / advect_y :705),
 // all levels with domore_k > 0, all tracers.
-static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme) {
+static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, int itt) {
   const Geom &g = plan->g;
   cudaStream_t s = plan->stream;
   const double min_h = 0.1 * plan->Angstrom_H;        // :401 / :773
@@ -458,15 +463,51 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme) 
     const bool x = (dir == 0);
     int *dom = x ? plan->domore_u : plan->domore_v, *ent = x ? plan->entry_u : plan->entry_v;
     double *res = x ? plan->uhr : plan->vhr;
+    // residual iterations: the cells that change are few -- collect them and update in place (sparse.cu)
+    bool sparse = plan->opt_sparse && itt >= 2;
+    if (sparse && (!plan->sp_list || plan->sp_ntr < plan->ntr)) {
+      if (plan->sp_list) { cudaFree(plan->sp_list); cudaFree(plan->sp_new); plan->sp_list = nullptr; plan->sp_new = nullptr; }
+      plan->sp_cap = (int)std::max<long long>(4096, field_elems(plan) / 64);
+      plan->sp_ntr = plan->ntr;
+      int rc = dev_alloc(plan, &plan->sp_list, plan->sp_cap); if (rc) return rc;
+      rc = dev_alloc(plan, &plan->sp_new, (long long)plan->sp_cap * plan->ntr); if (rc) return rc;
+    }
     {
       ProfScope ps(plan, MOM6ADV_KC_MASS);
+      if (sparse) CK(cudaMemsetAsync(plan->sum_dev + 1, 0, sizeof(int), s));
       launch_flags_begin(s, g, plan->domore_k, dom, ent, x ? rg.js : rg.js - 1, rg.je);
       launch_mass_flux(s, dir, g, rg, res, plan->hprev, plan->areaT, min_h, ent, dom, plan->hh, plan->cfl,
                        plan->hc, plan->gq, scheme == SCHEME_PLM);
       launch_mass_update(s, dir, g, rg, res, plan->hprev, plan->hh, plan->areaT, x ? plan->uh_neglect : plan->vh_neglect,
-                         h_neglect, ent, plan->domore_k, plan->hlst, plan->ihnew);
+                         h_neglect, ent, plan->domore_k, plan->hlst, plan->ihnew,
+                         sparse ? plan->sp_list : nullptr, plan->sum_dev + 1, plan->sp_cap);
       plan->launches += 3;
     }
+    int cnt = 0;
+    if (sparse) {
+      CK(cudaMemcpyAsync(plan->sum_host + 1, plan->sum_dev + 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+      CK(cudaStreamSynchronize(s));
+      cnt = plan->sum_host[1];
+      if (cnt > plan->sp_cap) sparse = false;      // too many active cells: take the dense kernels
+    }
+    if (sparse) {
+      ProfScope pt(plan, x ? MOM6ADV_KC_TRACER_X : MOM6ADV_KC_TRACER_Y);
+      for (int m0 = 0; m0 < plan->ntr; m0 += MOM6ADV_MAXT) {
+        TrTable tt;
+        tt.n = std::min(MOM6ADV_MAXT, plan->ntr - m0);
+        for (int m = 0; m < tt.n; m++) {
+          const TracerSlot &ts = plan->tr[m0 + m];
+          tt.src[m] = ts.buf[plan->cur]; tt.dst[m] = ts.buf[plan->cur]; tt.cu[m] = ts.conc_underflow;
+        }
+        launch_sparse_sweep(s, scheme, dir, g, rg, tt, plan->sp_list, cnt, plan->sp_cap, plan->hh, plan->cfl, plan->hlst,
+                            plan->ihnew, x ? plan->mmx : plan->mmy, ent, plan->sp_new + (long long)plan->sp_cap * m0);
+        if (cnt > 0) plan->launches += 2;
+      }
+      plan->sparse_sweeps++;
+      CK(cudaGetLastError());
+      return 0;
+    }
+    plan->dense_sweeps++;
     ProfScope pt(plan, x ? MOM6ADV_KC_TRACER_X : MOM6ADV_KC_TRACER_Y);
     for (int m0 = 0; m0 < plan->ntr; m0 += MOM6ADV_MAXT) {
       TrTable tt;
@@ -494,7 +535,7 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme) 
       launch_mass_flux(s, 0, g, rg, plan->uhr, plan->hprev, plan->areaT, min_h, plan->entry_u, plan->domore_u, plan->hh, plan->cfl,
                        nullptr, nullptr, 0);
       launch_mass_update(s, 0, g, rg, plan->uhr, plan->hprev, plan->hh, plan->areaT, plan->uh_neglect, h_neglect,
-                         plan->entry_u, plan->domore_k, plan->hlst, plan->ihnew);
+                         plan->entry_u, plan->domore_k, plan->hlst, plan->ihnew, nullptr, nullptr, 0);
     }
     ProfScope pt(plan, MOM6ADV_KC_TRACER_X);
     launch_tracer_sweep(s, scheme, 0, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->hlst,
@@ -508,7 +549,7 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme) 
       launch_mass_flux(s, 1, g, rg, plan->vhr, plan->hprev, plan->areaT, min_h, plan->entry_v, plan->domore_v, plan->hh, plan->cfl,
                        nullptr, nullptr, 0);
       launch_mass_update(s, 1, g, rg, plan->vhr, plan->hprev, plan->hh, plan->areaT, plan->vh_neglect, h_neglect,
-                         plan->entry_v, plan->domore_k, plan->hlst, plan->ihnew);
+                         plan->entry_v, plan->domore_k, plan->hlst, plan->ihnew, nullptr, nullptr, 0);
     }
     ProfScope pt(plan, MOM6ADV_KC_TRACER_Y);
     launch_tracer_sweep(s, scheme, 1, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->hlst,
@@ -587,14 +628,14 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
     if (x_first) {                                                          // :249-269
       Range rx = {isv, iev, jsv - stencil, jev + stencil};
       Range ry = {isv, iev, jsv, jev};
-      if ((rc = sweep(plan, 0, rx, Idt, scheme))) return rc;
-      if ((rc = sweep(plan, 1, ry, Idt, scheme))) return rc;
+      if ((rc = sweep(plan, 0, rx, Idt, scheme, itt))) return rc;
+      if ((rc = sweep(plan, 1, ry, Idt, scheme, itt))) return rc;
       launch_domore_k(s, g, plan->domore_k, plan->domore_u, plan->domore_v, jsv - stencil, jev + stencil, jsv - 1, jev);
     } else {                                                                // :271-290
       Range ry = {isv - stencil, iev + stencil, jsv, jev};
       Range rx = {isv, iev, jsv, jev};
-      if ((rc = sweep(plan, 1, ry, Idt, scheme))) return rc;
-      if ((rc = sweep(plan, 0, rx, Idt, scheme))) return rc;
+      if ((rc = sweep(plan, 1, ry, Idt, scheme, itt))) return rc;
+      if ((rc = sweep(plan, 0, rx, Idt, scheme, itt))) return rc;
       launch_domore_k(s, g, plan->domore_k, plan->domore_u, plan->domore_v, jsv, jev, jsv - 1, jev);
     }
     plan->launches += 1;
@@ -782,6 +823,7 @@ extern "C" int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value
   if (!plan || !key) return fail(plan, MOM6ADV_ERR_INVALID, "set_option: NULL argument");
   if (!strcmp(key, "fused")) { plan->opt_fused = value; return MOM6ADV_OK; }
   if (!strcmp(key, "fast")) { plan->opt_fast = value; return MOM6ADV_OK; }
+  if (!strcmp(key, "sparse")) { plan->opt_sparse = value; return MOM6ADV_OK; }
   if (!strcmp(key, "profile")) {
     plan->opt_profile = value;
     for (int c = 0; c < MOM6ADV_KC_COUNT; c++) { plan->prof_ms[c] = 0.0; plan->prof_n[c] = 0; }
