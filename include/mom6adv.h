@@ -89,6 +89,28 @@ int mom6adv_plan_destroy(mom6adv_plan *plan);   /* tracer_advect_end :1153 */
 const char *mom6adv_last_error(const mom6adv_plan *plan);
 const char *mom6adv_version(void);
 
+/* ---- multi-GPU: LAYOUT = npi,npj, one rank per GPU ------------------------ */
+/* The device-resident stand-in for MOM_domains' create_group_pass /
+ * do_group_pass (MOM_tracer_advect.F90:140-144,206 -> mpp_do_group_update) and
+ * sum_across_PEs(domore_k, nz) (:305 -> mpp_sum): halo strips are packed on
+ * the GPU, exchanged rank-to-rank with NCCL send/recv over NVLink and unpacked
+ * on the GPU; the convergence flags are an NCCL all-reduce.
+ * Rank r = pi + npi*pj.  One rank calls mom6adv_comm_unique_id and distributes
+ * the 128 bytes (MPI_Bcast in the Fortran model); every rank then calls
+ * mom6adv_comm_init with the global compute extents of each layout column /
+ * row (what mpp_get_compute_domains reports): ibeg/iend[npi], jbeg/jend[npj]. */
+int mom6adv_comm_unique_id(char *id128);
+int mom6adv_comm_init(mom6adv_plan *plan, const char *id128, const int *ibeg, const int *iend,
+                      const int *jbeg, const int *jend);
+/* Host-only view of the exchange plan of rank (dom->pi, dom->pj) (tests; needs
+ * no device).  what: 0 self dst, 1 self src, 2 self sign, 3 send src to `peer`,
+ * 4 send sign to `peer`, 5 recv dst from `peer`; indices are offsets into one
+ * padded plane.  Returns the list length (fills at most cap entries); geom
+ * (nullable) receives P, R, coff, roff of the padded plane. */
+int mom6adv_exchange_list(const mom6adv_grid *g, const mom6adv_domain *dom, const int *ibeg, const int *iend,
+                          const int *jbeg, const int *jend, int peer, int pos, int what, int *out, int cap,
+                          int *geom);
+
 /* ---- registry data (MOM_tracer_types.F90:9-130) -------------------------- */
 /* Declare Reg%ntr.  Tracer slots 0..ntr-1 get HBM storage. */
 int mom6adv_set_ntr(mom6adv_plan *plan, int ntr);

@@ -16,7 +16,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libmom6adv_b200.so")
-SOURCES = ["kernels.cu", "plan.cu", "fast_x.cu", "fast_y.cu", "sparse.cu"]
+SOURCES = ["kernels.cu", "plan.cu", "fast_x.cu", "fast_y.cu", "sparse.cu", "halo.cu"]
 HEADERS = ["internal.cuh", "kernels.h", "fast_common.cuh", os.path.join("..", "..", "include", "mom6adv.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-fmad=false", "-lineinfo",
@@ -46,7 +46,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not stale():
         return LIB
     extra = os.environ.get("MOM6ADV_NVCC_EXTRA", "").split()      # experiments: -DXMINB=5 ...
-    cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + sources()
+    cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + sources() + ["-lnccl"]
     env = dict(os.environ)
     # the image exports CC/CXX pointing at a wrapper without libgomp; nvcc needs the system g++
     cmd += ["-ccbin", "/usr/bin/g++"] if os.path.exists("/usr/bin/g++") else []

@@ -50,6 +50,12 @@ SYMBOLS = {
     "mom6adv_plan_destroy": (C.c_int, [_P]),
     "mom6adv_last_error": (C.c_char_p, [_P]),
     "mom6adv_version": (C.c_char_p, []),
+    "mom6adv_comm_unique_id": (C.c_int, [C.c_char_p]),
+    "mom6adv_comm_init": (C.c_int, [_P, C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                    C.POINTER(C.c_int)]),
+    "mom6adv_exchange_list": (C.c_int, [C.POINTER(mom6adv_grid), C.POINTER(mom6adv_domain), C.POINTER(C.c_int),
+                                        C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int, C.c_int,
+                                        C.c_int, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_int)]),
     "mom6adv_set_ntr": (C.c_int, [_P, C.c_int]),
     "mom6adv_bind_tracer": (C.c_int, [_P, C.c_int, _P, C.c_double, _P, _P, _P, _P, _P]),
     "mom6adv_advect": (C.c_int, [_P, _P, _P, _P, C.c_double, C.c_int, _P, C.c_int, C.c_int, _P, _P,
@@ -110,6 +116,59 @@ def ptr(a) -> Optional[int]:
     raise TypeError("unsupported array type %r" % type(a))
 
 
+def _iarr(v):
+    return (C.c_int * len(v))(*[int(x) for x in v])
+
+
+def make_structs(G, GV, CS=None):
+    """mom6adv_grid / mom6adv_config / mom6adv_domain PODs of a host grid (plus the arrays to keep alive)."""
+    keep = []
+    g = mom6adv_grid()
+    for n in ("isc", "iec", "jsc", "jec", "isd", "ied", "jsd", "jed", "IsdB", "IedB", "JsdB", "JedB"):
+        setattr(g, n, int(getattr(G, n)))
+    g.nk = int(GV.ke)
+    for n in ("areaT", "IareaT", "mask2dT", "mask2dCu", "mask2dCv"):
+        a = np.ascontiguousarray(getattr(G, n), dtype=np.float64)
+        keep.append(a)
+        setattr(g, n, a.ctypes.data_as(_dp))
+    g.Angstrom_H, g.H_subroundoff = GV.Angstrom_H, GV.H_subroundoff
+    c = mom6adv_config()
+    if CS is not None:
+        c.dt_baroclinic = CS.dt
+        c.usePPM, c.useHuynh, c.useHuynhStencilBug = int(CS.usePPM), int(CS.useHuynh), int(CS.useHuynhStencilBug)
+        c.debug = int(getattr(CS, "debug", False))
+    c.first_direction = int(G.first_direction)
+    D = G.Domain
+    d = mom6adv_domain()
+    d.nig, d.njg = D.nig, D.njg
+    d.npi, d.npj = D.layout
+    d.pi, d.pj = D.pe
+    d.ioff, d.joff = G.ioff, G.joff
+    d.cyclic_x, d.cyclic_y, d.tripolar_n = int(D.cyclic_x), int(D.cyclic_y), int(D.tripolar_n)
+    return g, c, d, keep
+
+
+def comm_unique_id() -> bytes:
+    buf = C.create_string_buffer(128)
+    rc = lib().mom6adv_comm_unique_id(buf)
+    if rc != OK:
+        raise Mom6AdvError(rc, lib().mom6adv_last_error(None).decode())
+    return buf.raw
+
+
+def exchange_list(G, GV, extents, peer: int, pos: int, what: int):
+    """Host-only: one list of the exchange plan of G's rank (see mom6adv_exchange_list).  Returns (list, geom)."""
+    g, c, d, keep = make_structs(G, GV)
+    ib, ie, jb, je = (_iarr(v) for v in extents)
+    geom = (C.c_int * 4)()
+    n = lib().mom6adv_exchange_list(C.byref(g), C.byref(d), ib, ie, jb, je, peer, pos, what, None, 0, geom)
+    if n < 0:
+        raise Mom6AdvError(ERR_INVALID, "exchange_list failed")
+    out = (C.c_int * max(n, 1))()
+    lib().mom6adv_exchange_list(C.byref(g), C.byref(d), ib, ie, jb, je, peer, pos, what, out, n, geom)
+    return np.array(out[:n], dtype=np.int64), tuple(geom)
+
+
 class Plan:
     """Thin object wrapper around mom6adv_plan*."""
 
@@ -117,27 +176,8 @@ class Plan:
         self._l = lib()
         self._h = _P()
         self._keep = []
-        g = mom6adv_grid()
-        for n in ("isc", "iec", "jsc", "jec", "isd", "ied", "jsd", "jed", "IsdB", "IedB", "JsdB", "JedB"):
-            setattr(g, n, int(getattr(G, n)))
-        g.nk = int(GV.ke)
-        for n in ("areaT", "IareaT", "mask2dT", "mask2dCu", "mask2dCv"):
-            a = np.ascontiguousarray(getattr(G, n), dtype=np.float64)
-            self._keep.append(a)
-            setattr(g, n, a.ctypes.data_as(_dp))
-        g.Angstrom_H, g.H_subroundoff = GV.Angstrom_H, GV.H_subroundoff
-        c = mom6adv_config()
-        c.dt_baroclinic = CS.dt
-        c.usePPM, c.useHuynh, c.useHuynhStencilBug = int(CS.usePPM), int(CS.useHuynh), int(CS.useHuynhStencilBug)
-        c.debug = int(getattr(CS, "debug", False))
-        c.first_direction = int(G.first_direction)
-        D = G.Domain
-        d = mom6adv_domain()
-        d.nig, d.njg = D.nig, D.njg
-        d.npi, d.npj = D.layout
-        d.pi, d.pj = D.pe
-        d.ioff, d.joff = G.ioff, G.joff
-        d.cyclic_x, d.cyclic_y, d.tripolar_n = int(D.cyclic_x), int(D.cyclic_y), int(D.tripolar_n)
+        g, c, d, keep = make_structs(G, GV, CS)
+        self._keep += keep
         rc = self._l.mom6adv_plan_create(C.byref(g), C.byref(c), C.byref(d), int(device), C.byref(self._h))
         if rc != OK:
             raise Mom6AdvError(rc, self._l.mom6adv_last_error(None).decode())
@@ -158,6 +198,12 @@ class Plan:
             self.destroy()
         except Exception:
             pass
+
+    # -- multi-GPU --------------------------------------------------------------
+    def comm_init(self, id128: Optional[bytes], extents):
+        """extents = (ibeg[npi], iend[npi], jbeg[npj], jend[npj]) global compute extents of the layout."""
+        ib, ie, jb, je = (_iarr(v) for v in extents)
+        self._ck(self._l.mom6adv_comm_init(self._h, id128, ib, ie, jb, je))
 
     # -- registry ---------------------------------------------------------------
     def set_ntr(self, ntr: int):

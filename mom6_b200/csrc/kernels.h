@@ -49,3 +49,18 @@ void launch_y_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const Tr
 void launch_sparse_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TrTable &tt,
                          const int *list, int cnt, int cap, const double *hh, const double *cfl, const double *hlst,
                          const double *ihnew, const double *mm, const int *entry, double *newT);
+
+// halo.cu: exchange planning (host side)
+#include <vector>
+struct ExchangeSpec {
+  int nig, njg, npi, npj, halo_i, halo_j;
+  int cyclic_x, cyclic_y, tripolar_n, symmetric;
+  std::vector<int> ibeg, iend, jbeg, jend;      // global compute extents of each layout column / row
+};
+struct HaloBuild { std::vector<int> dst, src; std::vector<signed char> sgn; };
+struct PeerBuild {
+  int rank = -1;
+  std::vector<int> send_src[3], recv_dst[3];      // per stagger: 0 h, 1 u, 2 v
+  std::vector<signed char> send_sgn[3];
+};
+void build_halo_exchange(const Geom &g, const ExchangeSpec &x, int me, HaloBuild local[3], std::vector<PeerBuild> &peers);

@@ -4,6 +4,8 @@
 #include "internal.cuh"
 #include "kernels.h"
 
+#include <nccl.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -26,6 +28,15 @@ struct HaloList {       // one stagger position
   int n = 0;
   int *dst = nullptr, *src = nullptr;
   signed char *sgn = nullptr;
+};
+
+struct PeerLists {        // one neighbour rank of the multi-GPU group pass
+  int rank = -1;
+  int n_send[3] = {0, 0, 0}, n_recv[3] = {0, 0, 0};
+  int *send_src[3] = {nullptr, nullptr, nullptr}, *recv_dst[3] = {nullptr, nullptr, nullptr};
+  signed char *send_sgn[3] = {nullptr, nullptr, nullptr};
+  double *sendbuf = nullptr, *recvbuf = nullptr;
+  long long send_elems = 0, recv_elems = 0;
 };
 
 struct mom6adv_plan {
@@ -62,6 +73,13 @@ struct mom6adv_plan {
   long long dev_bytes = 0;
   int opt_fused = 0;
   int opt_fast = 1;
+  // multi-GPU (LAYOUT = npi,npj): one rank per GPU, NCCL over NVLink
+  bool multi = false;
+  ncclComm_t comm = nullptr;
+  int nranks = 1, rank = 0;
+  std::vector<PeerLists> peers;
+  int peer_ntr = -1;                 // ntr the exchange buffers were sized for
+  long long halo_bytes_sent = 0;
   int opt_sparse = 1;                // list-driven tracer update on residual iterations (sparse.cu)
   int *sp_list = nullptr; double *sp_new = nullptr; int sp_cap = 0, sp_ntr = 0;
   long long sparse_sweeps = 0, dense_sweeps = 0;
@@ -97,6 +115,7 @@ static void prof_collect(mom6adv_plan *p) {   // call after the stream is synchr
 }
 
 static thread_local std::string g_err;
+static void make_geom(const mom6adv_grid *gr, Geom &g, int &wbase);
 
 #define CK(call)                                                                            \
   do {                                                                                      \
@@ -258,13 +277,144 @@ static int create_impl(mom6adv_plan *plan, const mom6adv_grid *gr) {
   plan->launches++;
   CK(cudaGetLastError());
 
-  for (int pos = 0; pos < 3; pos++) {
-    HostHalo hh;
-    build_halo_host(plan, pos, hh);
-    if ((rc = upload_halo_list(plan, hh, plan->halo[pos]))) return rc;
+  if (!plan->multi) {
+    for (int pos = 0; pos < 3; pos++) {
+      HostHalo hh;
+      build_halo_host(plan, pos, hh);
+      if ((rc = upload_halo_list(plan, hh, plan->halo[pos]))) return rc;
+    }
   }
   CK(cudaStreamSynchronize(plan->stream));
   return 0;
+}
+
+#define CKN(call)                                                                           \
+  do {                                                                                      \
+    ncclResult_t e_ = (call);                                                               \
+    if (e_ != ncclSuccess) {                                                                \
+      char b_[512];                                                                         \
+      snprintf(b_, sizeof b_, "NCCL error %s at %s:%d (%s)", ncclGetErrorString(e_), __FILE__, __LINE__, #call); \
+      if (plan) plan->err = b_; g_err = b_;                                                 \
+      return MOM6ADV_ERR_COMM;                                                              \
+    }                                                                                       \
+  } while (0)
+
+template <typename T>
+static int upload_vec(mom6adv_plan *plan, const std::vector<T> &h, T **d) {
+  *d = nullptr;
+  if (h.empty()) return 0;
+  CK(cudaMalloc((void **)d, sizeof(T) * h.size()));
+  CK(cudaMemcpy(*d, h.data(), sizeof(T) * h.size(), cudaMemcpyHostToDevice));
+  plan->dev_bytes += (long long)(sizeof(T) * h.size());
+  return 0;
+}
+
+extern "C" int mom6adv_comm_unique_id(char *id128) {
+  if (!id128) return MOM6ADV_ERR_INVALID;
+  ncclUniqueId id;
+  if (ncclGetUniqueId(&id) != ncclSuccess) return fail(nullptr, MOM6ADV_ERR_COMM, "ncclGetUniqueId failed");
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+  memcpy(id128, &id, 128);
+  return MOM6ADV_OK;
+}
+
+// Exchange lists of this rank (host side of comm_init; also what mom6adv_exchange_list reports).
+static void exchange_spec(const Geom &g, const mom6adv_domain &d, const int *ibeg, const int *iend, const int *jbeg,
+                          const int *jend, ExchangeSpec &x) {
+  x.nig = d.nig; x.njg = d.njg; x.npi = d.npi; x.npj = d.npj;
+  x.halo_i = g.isc - g.isd; x.halo_j = g.jsc - g.jsd;
+  x.cyclic_x = d.cyclic_x; x.cyclic_y = d.cyclic_y; x.tripolar_n = d.tripolar_n;
+  x.symmetric = (g.IsdB == g.isd - 1);
+  x.ibeg.assign(ibeg, ibeg + d.npi); x.iend.assign(iend, iend + d.npi);
+  x.jbeg.assign(jbeg, jbeg + d.npj); x.jend.assign(jend, jend + d.npj);
+}
+
+extern "C" int mom6adv_comm_init(mom6adv_plan *plan, const char *id128, const int *ibeg, const int *iend,
+                                 const int *jbeg, const int *jend) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "comm_init: plan not initialised");
+  if (!ibeg || !iend || !jbeg || !jend) return fail(plan, MOM6ADV_ERR_INVALID, "comm_init: NULL extents");
+  if (plan->comm || !plan->peers.empty() || plan->halo[0].n || plan->halo[1].n || plan->halo[2].n)
+    return fail(plan, MOM6ADV_ERR_INVALID, "comm_init: called twice");
+  CK(cudaSetDevice(plan->device));
+  ExchangeSpec x;
+  exchange_spec(plan->g, plan->dom, ibeg, iend, jbeg, jend, x);
+  if (x.ibeg[plan->dom.pi] != plan->g.isc + plan->dom.ioff || x.jbeg[plan->dom.pj] != plan->g.jsc + plan->dom.joff ||
+      x.iend[plan->dom.pi] != plan->g.iec + plan->dom.ioff || x.jend[plan->dom.pj] != plan->g.jec + plan->dom.joff)
+    return fail(plan, MOM6ADV_ERR_INVALID, "comm_init: extents disagree with this rank's grid");
+  HaloBuild local[3];
+  std::vector<PeerBuild> pb;
+  build_halo_exchange(plan->g, x, plan->rank, local, pb);
+  int rc;
+  for (int pos = 0; pos < 3; pos++) {
+    HostHalo hh; hh.dst = local[pos].dst; hh.src = local[pos].src; hh.sgn = local[pos].sgn;
+    if ((rc = upload_halo_list(plan, hh, plan->halo[pos]))) return rc;
+  }
+  for (const PeerBuild &b : pb) {
+    PeerLists pl;
+    pl.rank = b.rank;
+    for (int pos = 0; pos < 3; pos++) {
+      pl.n_send[pos] = (int)b.send_src[pos].size(); pl.n_recv[pos] = (int)b.recv_dst[pos].size();
+      if ((rc = upload_vec(plan, b.send_src[pos], &pl.send_src[pos]))) return rc;
+      if ((rc = upload_vec(plan, b.send_sgn[pos], &pl.send_sgn[pos]))) return rc;
+      if ((rc = upload_vec(plan, b.recv_dst[pos], &pl.recv_dst[pos]))) return rc;
+    }
+    plan->peers.push_back(pl);
+  }
+  if (id128 && plan->nranks > 1) {
+    ncclUniqueId id;
+    memcpy(&id, id128, 128);
+    CKN(ncclCommInitRank(&plan->comm, plan->nranks, id, plan->rank));
+  }
+  return MOM6ADV_OK;
+}
+
+// Host-side view of the exchange plan (tests; no device work).  what: 0 local dst, 1 local src, 2 local sign,
+// 3 send src to `peer`, 4 send sign to `peer`, 5 recv dst from `peer`.  Returns the count (<0: error);
+// fills at most cap entries.  geom (nullable) receives P, R, coff, roff of the padded layout.
+extern "C" int mom6adv_exchange_list(const mom6adv_grid *gr, const mom6adv_domain *dom, const int *ibeg,
+                                     const int *iend, const int *jbeg, const int *jend, int peer, int pos, int what,
+                                     int *out, int cap, int *geom) {
+  if (!gr || !dom || pos < 0 || pos > 2) return -1;
+  Geom g; int wbase;
+  make_geom(gr, g, wbase);
+  ExchangeSpec x;
+  exchange_spec(g, *dom, ibeg, iend, jbeg, jend, x);
+  HaloBuild local[3];
+  std::vector<PeerBuild> pb;
+  build_halo_exchange(g, x, dom->pi + dom->npi * dom->pj, local, pb);
+  if (geom) { geom[0] = g.P; geom[1] = g.R; geom[2] = g.coff; geom[3] = g.roff; }
+  std::vector<int> v;
+  if (what == 0) v = local[pos].dst;
+  else if (what == 1) v = local[pos].src;
+  else if (what == 2) v.assign(local[pos].sgn.begin(), local[pos].sgn.end());
+  else {
+    for (const PeerBuild &b : pb) if (b.rank == peer) {
+      if (what == 3) v = b.send_src[pos];
+      else if (what == 4) v.assign(b.send_sgn[pos].begin(), b.send_sgn[pos].end());
+      else if (what == 5) v = b.recv_dst[pos];
+    }
+  }
+  for (int n = 0; n < (int)v.size() && n < cap; n++) out[n] = v[n];
+  return (int)v.size();
+}
+
+// Padded HBM layout of one plane (internal.cuh) from the Fortran index bounds.
+static void make_geom(const mom6adv_grid *gr, Geom &g, int &wbase) {
+  const int hi = gr->isc - gr->isd;
+  g.isd = gr->isd; g.ied = gr->ied; g.jsd = gr->jsd; g.jed = gr->jed;
+  g.isc = gr->isc; g.iec = gr->iec; g.jsc = gr->jsc; g.jec = gr->jec;
+  g.IsdB = gr->IsdB; g.JsdB = gr->JsdB; g.nk = gr->nk;
+  const int nid = g.ied - g.isd + 1, njd = g.jed - g.jsd + 1;
+  int lead = ((hi + 1 + 15) / 16) * 16 - hi;            // column of isd; isc lands on a multiple of 16
+  if (lead < 4) lead += 16;
+  g.coff = lead - g.isd;
+  // x tiles of the streaming kernel: 128 columns from wbase + 120*n, 120 useful (lanes 1..30)
+  wbase = (lead - 4) & ~3;
+  const int ntx = (lead + nid - 1 - (wbase + 4)) / 120 + 1;
+  g.P = ((std::max(lead + nid + 1, wbase + 120 * (ntx - 1) + 128) + 63) / 64) * 64;   // y tiles are 64 columns
+  g.roff = 1 - g.jsd;
+  g.R = njd + 2;
+  g.plane = (long long)g.P * g.R;
 }
 
 extern "C" const char *mom6adv_version(void) { return MOM6ADV_VERSION; }
@@ -298,20 +448,7 @@ extern "C" int mom6adv_plan_create(const mom6adv_grid *gr, const mom6adv_config 
   plan->H_subroundoff = gr->H_subroundoff;
   plan->IedB = gr->IedB; plan->JedB = gr->JedB;
   Geom &g = plan->g;
-  g.isd = gr->isd; g.ied = gr->ied; g.jsd = gr->jsd; g.jed = gr->jed;
-  g.isc = gr->isc; g.iec = gr->iec; g.jsc = gr->jsc; g.jec = gr->jec;
-  g.IsdB = gr->IsdB; g.JsdB = gr->JsdB; g.nk = gr->nk;
-  const int nid = g.ied - g.isd + 1, njd = g.jed - g.jsd + 1;
-  int lead = ((hi + 1 + 15) / 16) * 16 - hi;            // column of isd; isc lands on a multiple of 16
-  if (lead < 4) lead += 16;
-  g.coff = lead - g.isd;
-  // x tiles of the streaming kernel: 128 columns from wbase + 120*n, 120 useful (lanes 1..30)
-  plan->wbase = (lead - 4) & ~3;
-  const int ntx = (lead + nid - 1 - (plan->wbase + 4)) / 120 + 1;
-  g.P = ((std::max(lead + nid + 1, plan->wbase + 120 * (ntx - 1) + 128) + 63) / 64) * 64;   // y tiles are 64 columns
-  g.roff = 1 - g.jsd;
-  g.R = njd + 2;
-  g.plane = (long long)g.P * g.R;
+  make_geom(gr, g, plan->wbase);
   if (dom) plan->dom = *dom;
   else {
     mom6adv_domain d = {};
@@ -319,10 +456,9 @@ extern "C" int mom6adv_plan_create(const mom6adv_grid *gr, const mom6adv_config 
     d.ioff = -(g.isc - 1); d.joff = -(g.jsc - 1);
     plan->dom = d;
   }
-  if (plan->dom.npi * plan->dom.npj != 1) {
-    delete plan;
-    return fail(nullptr, MOM6ADV_ERR_UNSUPPORTED, "plan_create: multi-block layouts go through mom6adv_halo_config");
-  }
+  plan->multi = (plan->dom.npi * plan->dom.npj != 1);     // lists and communicator come from mom6adv_comm_init
+  plan->nranks = plan->dom.npi * plan->dom.npj;
+  plan->rank = plan->dom.pi + plan->dom.npi * plan->dom.pj;
   int rc = create_impl(plan, gr);
   if (rc) { g_err = plan->err; mom6adv_plan_destroy(plan); return rc; }
   *out = plan;
@@ -345,6 +481,12 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   int *f[] = {plan->domore_u, plan->domore_v, plan->entry_u, plan->entry_v, plan->domore_k, plan->sum_dev};
   for (int *p : f) if (p) cudaFree(p);
   if (plan->sum_host) cudaFreeHost(plan->sum_host);
+  for (PeerLists &p : plan->peers) {
+    for (int pos = 0; pos < 3; pos++) { if (p.send_src[pos]) cudaFree(p.send_src[pos]); if (p.send_sgn[pos]) cudaFree(p.send_sgn[pos]); if (p.recv_dst[pos]) cudaFree(p.recv_dst[pos]); }
+    if (p.sendbuf) cudaFree(p.sendbuf);
+    if (p.recvbuf) cudaFree(p.recvbuf);
+  }
+  if (plan->comm) ncclCommDestroy(plan->comm);
   if (plan->sp_list) cudaFree(plan->sp_list);
   if (plan->sp_new) cudaFree(plan->sp_new);
   for (auto &s : plan->tr) free_slot(s);
@@ -434,15 +576,63 @@ static int group_pass(mom6adv_plan *plan) {
   cudaStream_t s = plan->stream;
   ProfScope ps(plan, MOM6ADV_KC_HALO);
   // u list -> uhr, v list -> vhr, h list -> hprev + tracers (live buffer)
+  const int nh = 1 + plan->ntr;
   double **tab = plan->halo_fields_dev + plan->cur * (3 + plan->ntr);
-  launch_halo_apply(s, g.plane, g.nk, plan->halo[1].dst, plan->halo[1].src, plan->halo[1].sgn, plan->halo[1].n,
-                    tab + 0, 1);
-  launch_halo_apply(s, g.plane, g.nk, plan->halo[2].dst, plan->halo[2].src, plan->halo[2].sgn, plan->halo[2].n,
-                    tab + 1, 1);
-  launch_halo_apply(s, g.plane, g.nk, plan->halo[0].dst, plan->halo[0].src, plan->halo[0].sgn, plan->halo[0].n,
-                    tab + 2, 1 + plan->ntr);
+  double **ftab[3] = {tab + 2, tab + 0, tab + 1};        // field tables by stagger: h, u, v
+  const int nf[3] = {nh, 1, 1};
+  // (1) halo points whose source lies in this rank's own block (cyclic wrap / fold onto itself)
+  for (int pos = 0; pos < 3; pos++)
+    launch_halo_apply(s, g.plane, g.nk, plan->halo[pos].dst, plan->halo[pos].src, plan->halo[pos].sgn, plan->halo[pos].n,
+                      ftab[pos], nf[pos]);
   plan->launches += 3;
+  if (plan->multi && !plan->peers.empty()) {
+    if (!plan->comm) return fail(plan, MOM6ADV_ERR_COMM, "advect: mom6adv_comm_init has not been called on this multi-block plan");
+    // (2) pack one message per neighbour: [h: hprev, tracers][u: uhr][v: vhr], each [field][level][point]
+    for (PeerLists &p : plan->peers) {
+      long long off = 0;
+      for (int pos = 0; pos < 3; pos++) {
+        launch_halo_pack(s, g.plane, g.nk, p.send_src[pos], p.send_sgn[pos], p.n_send[pos], ftab[pos], nf[pos], p.sendbuf + off);
+        off += (long long)nf[pos] * g.nk * p.n_send[pos];
+        plan->launches++;
+      }
+    }
+    CK(cudaGetLastError());
+    // (3) device-resident exchange over NVLink
+    CKN(ncclGroupStart());
+    for (PeerLists &p : plan->peers) {
+      if (p.send_elems) CKN(ncclSend(p.sendbuf, (size_t)p.send_elems, ncclDouble, p.rank, plan->comm, s));
+      if (p.recv_elems) CKN(ncclRecv(p.recvbuf, (size_t)p.recv_elems, ncclDouble, p.rank, plan->comm, s));
+      plan->halo_bytes_sent += 8 * p.send_elems;
+    }
+    CKN(ncclGroupEnd());
+    // (4) unpack
+    for (PeerLists &p : plan->peers) {
+      long long off = 0;
+      for (int pos = 0; pos < 3; pos++) {
+        launch_halo_unpack(s, g.plane, g.nk, p.recv_dst[pos], p.n_recv[pos], ftab[pos], nf[pos], p.recvbuf + off);
+        off += (long long)nf[pos] * g.nk * p.n_recv[pos];
+        plan->launches++;
+      }
+    }
+  }
   CK(cudaGetLastError());
+  return 0;
+}
+
+// Exchange buffers are sized by ntr; (re)allocate when the registry changed.
+static int size_peer_buffers(mom6adv_plan *plan) {
+  if (!plan->multi || plan->peer_ntr == plan->ntr) return 0;
+  const Geom &g = plan->g;
+  for (PeerLists &p : plan->peers) {
+    if (p.sendbuf) { cudaFree(p.sendbuf); p.sendbuf = nullptr; }
+    if (p.recvbuf) { cudaFree(p.recvbuf); p.recvbuf = nullptr; }
+    p.send_elems = (long long)g.nk * ((long long)(1 + plan->ntr) * p.n_send[0] + p.n_send[1] + p.n_send[2]);
+    p.recv_elems = (long long)g.nk * ((long long)(1 + plan->ntr) * p.n_recv[0] + p.n_recv[1] + p.n_recv[2]);
+    int rc;
+    if (p.send_elems && (rc = dev_alloc(plan, &p.sendbuf, p.send_elems))) return rc;
+    if (p.recv_elems && (rc = dev_alloc(plan, &p.recvbuf, p.recv_elems))) return rc;
+  }
+  plan->peer_ntr = plan->ntr;
   return 0;
 }
 
@@ -574,6 +764,7 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
   cudaStream_t s = plan->stream;
   CK(cudaSetDevice(plan->device));
   { int rc = sync_tracer_table(plan); if (rc) return rc; }
+  { int rc = size_peer_buffers(plan); if (rc) return rc; }
   const int is = g.isc, ie = g.iec, js = g.jsc, je = g.jec;
   int stencil = 2;                                                          // :118
   const bool use_PPM_stencil = plan->cfg.usePPM && !plan->cfg.useHuynhStencilBug;   // :129
@@ -641,7 +832,9 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
     plan->launches += 1;
     if (itt >= max_iter) break;                                             // :297-299
     if (isv > is - stencil) {                                               // :302
-      launch_sum_domore_k(s, plan->domore_k, g.nk, plan->sum_dev);          // :305-307 (single block: identity sum)
+      if (plan->multi && plan->comm)                                        // :305 sum_across_PEs(domore_k, nz)
+        CKN(ncclAllReduce(plan->domore_k, plan->domore_k, g.nk, ncclInt, ncclSum, plan->comm, s));
+      launch_sum_domore_k(s, plan->domore_k, g.nk, plan->sum_dev);          // :307 do_any
       plan->launches += 1;
       CK(cudaMemcpyAsync(plan->sum_host, plan->sum_dev, sizeof(int), cudaMemcpyDeviceToHost, s));
       CK(cudaStreamSynchronize(s));

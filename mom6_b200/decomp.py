@@ -58,22 +58,28 @@ def _cols(Gg, G, lo_local, n, lo_global_array):
     return gg - lo_global_array
 
 
-def cut_h(Gg: OceanGrid, G: OceanGrid, a: np.ndarray) -> np.ndarray:
+def cut_h(Gg: OceanGrid, G: OceanGrid, a, index_only: bool = False):
     """Local data-domain copy of a global h-point array (halo included)."""
     ci = np.arange(G.nid) + G.isd + G.ioff - Gg.ioff - Gg.isd
     rj = np.arange(G.njd) + G.jsd + G.joff - Gg.joff - Gg.jsd
+    if index_only:
+        return rj, ci
     return np.ascontiguousarray(a[..., rj[:, None], ci[None, :]])
 
 
-def cut_u(Gg, G, a):
+def cut_u(Gg, G, a, index_only: bool = False):
     ci = np.arange(G.nIB) + G.IsdB + G.ioff - Gg.ioff - Gg.IsdB
     rj = np.arange(G.njd) + G.jsd + G.joff - Gg.joff - Gg.jsd
+    if index_only:
+        return rj, ci
     return np.ascontiguousarray(a[..., rj[:, None], ci[None, :]])
 
 
-def cut_v(Gg, G, a):
+def cut_v(Gg, G, a, index_only: bool = False):
     ci = np.arange(G.nid) + G.isd + G.ioff - Gg.ioff - Gg.isd
     rj = np.arange(G.nJB) + G.JsdB + G.joff - Gg.joff - Gg.JsdB
+    if index_only:
+        return rj, ci
     return np.ascontiguousarray(a[..., rj[:, None], ci[None, :]])
 
 

@@ -113,6 +113,9 @@ def _ensure_plan(G, GV, CS, Reg, device: int = -1):
         plan = capi.Plan(G, GV, CS, device=device)
         for k, v in CS.gpu_options.items():
             plan.set_option(k, int(v))
+        if G.Domain.layout[0] * G.Domain.layout[1] > 1:     # LAYOUT > 1x1: exchange lists + NCCL communicator
+            from . import multi
+            multi.comm_init_plan(plan, G)
         plan._sig = None
         CS._plan = plan
     sig = _registry_signature(Reg)

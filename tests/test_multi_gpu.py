@@ -1,0 +1,76 @@
+"""N-GPU answer == 1-PE answer, bitwise (the reference's test.layout standard,
+.testing/Makefile:383,454,595): one rank per GPU, NCCL halo exchange."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _ngpu():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+def _worker(rank, world, port, layout, scheme, cfl, q):
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from mom6_b200 import synth, decomp, multi
+        from mom6_b200.types import TracerRegistry, register_tracer
+        from mom6_b200.tracer_advect import tracer_advect_init, tracer_advect_end, advect_tracer
+        from oracle import oracle
+        c = synth.make_case(96, 70, 3, 5, cfl=cfl)
+        params = {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}
+        # 1-PE oracle answer
+        CSo = tracer_advect_init(None, c.G, None, params, None, None)
+        Ro = synth.bind_registry(c)
+        h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
+        nit_o = 0
+        for _ in range(2):
+            nit_o = oracle.advect_tracer(h, u, v, None, c.dt, c.G, c.GV, None, CSo, Ro)
+        # this rank's block on its GPU
+        pe = multi.rank_to_pe(rank, layout)
+        G = decomp.local_grid(c.G, layout, pe)
+        R0 = synth.bind_registry(c)
+        Reg = TracerRegistry()
+        for tr in R0.Tr:
+            register_tracer(decomp.cut_h(c.G, G, tr.t), Reg, underflow_conc=tr.conc_underflow)
+        CS = tracer_advect_init(None, G, None, params, None, None)
+        hl, ul, vl = decomp.cut_h(c.G, G, h), decomp.cut_u(c.G, G, u), decomp.cut_v(c.G, G, v)
+        nit = 0
+        for _ in range(2):
+            nit = advect_tracer(hl, ul, vl, None, c.dt, G, c.GV, None, CS, Reg)
+        ok = (nit == nit_o)
+        for m in range(c.ntr):
+            want = decomp.cut_h(c.G, G, Ro.Tr[m].t)
+            ok = ok and np.array_equal(G.interior(want).view(np.uint64), G.interior(Reg.Tr[m].t).view(np.uint64))
+        tracer_advect_end(CS)
+        q.put((rank, bool(ok), nit, nit_o))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("layout", [(1, 2), (2, 1)])
+@pytest.mark.parametrize("scheme,cfl", [("PPM", 0.9), ("PLM", 0.5)])
+def test_two_gpu_layout_invariance(layout, scheme, cfl):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, layout, scheme, cfl, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=300) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert [r[:2] for r in res] == [(0, True), (1, True)], res
