@@ -1,0 +1,366 @@
+!> Drop-in replacement of MOM6's module MOM_tracer_advect whose work is done on an
+!! NVIDIA B200 through the C ABI of include/mom6adv.h (libmom6adv_b200.so).
+!!
+!! Same public names, dummy-argument lists and error behaviour as the reference
+!! module (src/tracer/MOM_tracer_advect.F90:25-30, :52-86, :1090, :1153), so
+!! step_MOM_tracer_dyn (src/core/MOM.F90:1438) and the offline tracer driver
+!! (src/tracer/MOM_offline_main.F90:334,515,556,940,957) call it unchanged.
+!! Build: list this file INSTEAD of src/tracer/MOM_tracer_advect.F90 (MOM6's
+!! own same-named-module convention, config_src/external/README.md) and link
+!! -lmom6adv_b200 -lcudart -lnccl.  See INTEGRATION.md.
+!!
+!! This file contains no arithmetic: it marshals G, GV, CS and the tracer
+!! registry into plain-old-data descriptors and raw pointers.
+module MOM_tracer_advect
+
+use, intrinsic :: iso_c_binding, only : c_int, c_double, c_ptr, c_char, c_null_ptr, c_null_char, c_loc, &
+                                        c_associated, c_f_pointer, c_long_long
+use MOM_coms,            only : PE_here, root_PE, num_PEs, broadcast
+use MOM_cpu_clock,       only : cpu_clock_id, cpu_clock_begin, cpu_clock_end
+use MOM_cpu_clock,       only : CLOCK_MODULE, CLOCK_ROUTINE
+use MOM_diag_mediator,   only : diag_ctrl, time_type
+use MOM_domains,         only : sum_across_PEs
+use mpp_domains_mod,     only : CYCLIC_GLOBAL_DOMAIN, FOLD_NORTH_EDGE   ! the values MOM_domain_type%X_FLAGS/Y_FLAGS hold
+use MOM_error_handler,   only : MOM_error, FATAL, WARNING
+use MOM_file_parser,     only : get_param, log_version, param_file_type
+use MOM_grid,            only : ocean_grid_type
+use MOM_open_boundary,   only : ocean_OBC_type
+use MOM_tracer_registry, only : tracer_registry_type, tracer_type
+use MOM_unit_scaling,    only : unit_scale_type
+use MOM_verticalGrid,    only : verticalGrid_type
+implicit none ; private
+
+#include <MOM_memory.h>
+
+public advect_tracer
+public tracer_advect_init
+public tracer_advect_end
+
+!> Control structure: the reference's members (:30-40) plus the GPU plan handle.
+type, public :: tracer_advect_CS ; private
+  real    :: dt                      !< The baroclinic dynamics time step [T ~> s]
+  type(diag_ctrl), pointer :: diag => NULL() !< Diagnostics control structure
+  logical :: debug                   !< If true, write verbose checksums
+  logical :: usePPM                  !< If true, use PPM instead of PLM
+  logical :: useHuynh                !< If true, use the Huynh scheme for PPM interface values
+  logical :: useHuynhStencilBug = .false. !< Legacy too-narrow stencil for PPM:H3
+  type(c_ptr) :: plan = c_null_ptr   !< mom6adv_plan* (created on the first advect_tracer call)
+  integer :: ntr_bound = -1          !< Reg%ntr the plan was last bound with
+  integer(kind=c_long_long) :: reg_hash = 0 !< hash of the registry's pointers at the last bind
+end type tracer_advect_CS
+
+integer :: id_clock_advect !< (Ocean advect tracer): the whole GPU call incl. host<->device copies
+integer :: id_clock_pass   !< (Ocean tracer halo updates): kept for clock-table compatibility
+integer :: id_clock_sync   !< (Ocean tracer global synch): kept for clock-table compatibility
+
+! ---- POD descriptors of include/mom6adv.h ---------------------------------------------
+type, bind(c) :: mom6adv_grid
+  integer(c_int) :: isc, iec, jsc, jec, isd, ied, jsd, jed, IsdB, IedB, JsdB, JedB, nk
+  type(c_ptr)    :: areaT, IareaT, mask2dT, mask2dCu, mask2dCv
+  real(c_double) :: Angstrom_H, H_subroundoff
+end type mom6adv_grid
+
+type, bind(c) :: mom6adv_config
+  real(c_double) :: dt_baroclinic
+  integer(c_int) :: usePPM, useHuynh, useHuynhStencilBug, debug, first_direction
+end type mom6adv_config
+
+type, bind(c) :: mom6adv_domain
+  integer(c_int) :: nig, njg, npi, npj, pi, pj, ioff, joff, cyclic_x, cyclic_y, tripolar_n
+end type mom6adv_domain
+
+! ---- the C entry points (style of src/framework/posix.F90:52-229) ----------------------
+interface
+  function mom6adv_plan_create(g, c, dom, device, plan) bind(c, name="mom6adv_plan_create") result(rc)
+    import :: c_int, c_ptr, mom6adv_grid, mom6adv_config, mom6adv_domain
+    type(mom6adv_grid),   intent(in)  :: g
+    type(mom6adv_config), intent(in)  :: c
+    type(mom6adv_domain), intent(in)  :: dom
+    integer(c_int), value             :: device
+    type(c_ptr),          intent(out) :: plan
+    integer(c_int) :: rc
+  end function mom6adv_plan_create
+
+  function mom6adv_plan_destroy(plan) bind(c, name="mom6adv_plan_destroy") result(rc)
+    import :: c_int, c_ptr
+    type(c_ptr), value :: plan
+    integer(c_int) :: rc
+  end function mom6adv_plan_destroy
+
+  function mom6adv_last_error(plan) bind(c, name="mom6adv_last_error") result(msg)
+    import :: c_ptr
+    type(c_ptr), value :: plan
+    type(c_ptr) :: msg
+  end function mom6adv_last_error
+
+  function mom6adv_comm_unique_id(id128) bind(c, name="mom6adv_comm_unique_id") result(rc)
+    import :: c_int, c_char
+    character(kind=c_char), intent(out) :: id128(128)
+    integer(c_int) :: rc
+  end function mom6adv_comm_unique_id
+
+  function mom6adv_comm_init(plan, id128, ibeg, iend, jbeg, jend) bind(c, name="mom6adv_comm_init") result(rc)
+    import :: c_int, c_char, c_ptr
+    type(c_ptr), value :: plan
+    character(kind=c_char), intent(in) :: id128(128)
+    integer(c_int), intent(in) :: ibeg(*), iend(*), jbeg(*), jend(*)
+    integer(c_int) :: rc
+  end function mom6adv_comm_init
+
+  function mom6adv_set_ntr(plan, ntr) bind(c, name="mom6adv_set_ntr") result(rc)
+    import :: c_int, c_ptr
+    type(c_ptr), value :: plan
+    integer(c_int), value :: ntr
+    integer(c_int) :: rc
+  end function mom6adv_set_ntr
+
+  function mom6adv_bind_tracer(plan, m, t, conc_underflow, ad_x, ad_y, ad2d_x, ad2d_y, advection_xy) &
+           bind(c, name="mom6adv_bind_tracer") result(rc)
+    import :: c_int, c_ptr, c_double
+    type(c_ptr), value :: plan
+    integer(c_int), value :: m          !< 0-based tracer index
+    type(c_ptr), value :: t, ad_x, ad_y, ad2d_x, ad2d_y, advection_xy   !< c_null_ptr == unassociated
+    real(c_double), value :: conc_underflow
+    integer(c_int) :: rc
+  end function mom6adv_bind_tracer
+
+  function mom6adv_advect(plan, h_end, uhtr, vhtr, dt, x_first, vol_prev, max_iter_in, update_vol_prev, &
+                          uhr_out, vhr_out, n_iter) bind(c, name="mom6adv_advect") result(rc)
+    import :: c_int, c_ptr, c_double
+    type(c_ptr), value :: plan, h_end, uhtr, vhtr, vol_prev, uhr_out, vhr_out
+    real(c_double), value :: dt
+    integer(c_int), value :: x_first          !< -1 absent, 0 / 1
+    integer(c_int), value :: max_iter_in      !< < 0 absent
+    integer(c_int), value :: update_vol_prev  !< -1 absent, 0 / 1
+    integer(c_int), intent(out) :: n_iter
+    integer(c_int) :: rc
+  end function mom6adv_advect
+end interface
+
+contains
+
+!> Raise MOM_error(FATAL) with the library's message when a C call failed.
+subroutine check_rc(rc, plan, where)
+  integer(c_int),   intent(in) :: rc    !< status returned by the C ABI (0 == OK)
+  type(c_ptr),      intent(in) :: plan  !< plan handle (may be null)
+  character(len=*), intent(in) :: where !< name of the caller
+  character(kind=c_char), pointer :: cmsg(:)
+  character(len=512) :: msg
+  type(c_ptr) :: p
+  integer :: n
+  if (rc == 0) return
+  msg = "" ; p = mom6adv_last_error(plan)
+  if (c_associated(p)) then
+    call c_f_pointer(p, cmsg, [512])
+    do n=1,512 ; if (cmsg(n) == c_null_char) exit ; msg(n:n) = cmsg(n) ; enddo
+  endif
+  call MOM_error(FATAL, "MOM_tracer_advect (B200), "//trim(where)//": "//trim(msg))
+end subroutine check_rc
+
+!> Create the GPU plan: grid descriptors, HBM mirrors and, with more than one PE,
+!! the halo-exchange lists and the NCCL communicator (stands in for the
+!! create_group_pass calls of the reference, :140-144).
+subroutine make_plan(G, GV, CS)
+  type(ocean_grid_type), target, intent(inout) :: G   !< ocean grid structure
+  type(verticalGrid_type),       intent(in)    :: GV  !< ocean vertical grid structure
+  type(tracer_advect_CS),        intent(inout) :: CS  !< control structure
+  type(mom6adv_grid)   :: cg
+  type(mom6adv_config) :: cc
+  type(mom6adv_domain) :: cd
+  integer, allocatable :: ext(:)
+  integer(c_int), allocatable :: ibeg(:), iend(:), jbeg(:), jend(:)
+  character(kind=c_char) :: id(128)
+  integer :: idw(32), npi, npj, rank, pi, pj, n
+  cg%isc = G%isc ; cg%iec = G%iec ; cg%jsc = G%jsc ; cg%jec = G%jec
+  cg%isd = G%isd ; cg%ied = G%ied ; cg%jsd = G%jsd ; cg%jed = G%jed
+  cg%IsdB = G%IsdB ; cg%IedB = G%IedB ; cg%JsdB = G%JsdB ; cg%JedB = G%JedB
+  cg%nk = GV%ke
+  cg%areaT = c_loc(G%areaT) ; cg%IareaT = c_loc(G%IareaT) ; cg%mask2dT = c_loc(G%mask2dT)
+  cg%mask2dCu = c_loc(G%mask2dCu) ; cg%mask2dCv = c_loc(G%mask2dCv)
+  cg%Angstrom_H = GV%Angstrom_H ; cg%H_subroundoff = GV%H_subroundoff
+  cc%dt_baroclinic = CS%dt
+  cc%usePPM = merge(1, 0, CS%usePPM) ; cc%useHuynh = merge(1, 0, CS%useHuynh)
+  cc%useHuynhStencilBug = merge(1, 0, CS%useHuynhStencilBug) ; cc%debug = merge(1, 0, CS%debug)
+  cc%first_direction = G%first_direction
+  npi = G%Domain%layout(1) ; npj = G%Domain%layout(2)
+  rank = PE_here() - root_PE()              ! FMS lays PEs out with the i-position varying fastest
+  pi = mod(rank, npi) ; pj = rank / npi
+  cd%nig = G%Domain%niglobal ; cd%njg = G%Domain%njglobal
+  cd%npi = npi ; cd%npj = npj ; cd%pi = pi ; cd%pj = pj
+  cd%ioff = G%idg_offset ; cd%joff = G%jdg_offset        ! global index = local index + offset
+  ! topology flags as create_MOM_domain stored them (config_src/infra/FMS2/MOM_domain_infra.F90:1345-1366)
+  cd%cyclic_x = merge(1, 0, G%Domain%X_FLAGS == CYCLIC_GLOBAL_DOMAIN)
+  cd%cyclic_y = merge(1, 0, G%Domain%Y_FLAGS == CYCLIC_GLOBAL_DOMAIN)
+  cd%tripolar_n = merge(1, 0, G%Domain%Y_FLAGS == FOLD_NORTH_EDGE)
+  call check_rc(mom6adv_plan_create(cg, cc, cd, -1_c_int, CS%plan), c_null_ptr, "plan_create")
+  if (npi*npj > 1) then
+    ! global compute extents of every layout column / row: each PE contributes its own, the rest are zero
+    allocate(ext(2*(npi+npj))) ; ext(:) = 0
+    if (pj == 0) then ; ext(pi+1) = G%isc + G%idg_offset ; ext(npi+pi+1) = G%iec + G%idg_offset ; endif
+    if (pi == 0) then ; ext(2*npi+pj+1) = G%jsc + G%jdg_offset ; ext(2*npi+npj+pj+1) = G%jec + G%jdg_offset ; endif
+    call sum_across_PEs(ext, 2*(npi+npj))
+    allocate(ibeg(npi), iend(npi), jbeg(npj), jend(npj))
+    ibeg(:) = ext(1:npi) ; iend(:) = ext(npi+1:2*npi)
+    jbeg(:) = ext(2*npi+1:2*npi+npj) ; jend(:) = ext(2*npi+npj+1:2*(npi+npj))
+    ! the NCCL id: drawn on the root PE, broadcast as 32 default integers
+    if (rank == 0) call check_rc(mom6adv_comm_unique_id(id), CS%plan, "comm_unique_id")
+    idw = transfer(id, idw)
+    call broadcast(idw, 32, root_PE())
+    id = transfer(idw, id)
+    call check_rc(mom6adv_comm_init(CS%plan, id, ibeg, iend, jbeg, jend), CS%plan, "comm_init")
+  endif
+end subroutine make_plan
+
+!> A cheap signature of the registry: the plan is re-bound only when ntr or any pointer changed.
+function registry_hash(Reg) result(h)
+  type(tracer_registry_type), intent(in) :: Reg !< tracer registry
+  integer(kind=c_long_long) :: h
+  integer :: m
+  h = Reg%ntr
+  do m=1,Reg%ntr
+    h = h*31 + transfer(c_loc(Reg%Tr(m)%t), h)
+    if (associated(Reg%Tr(m)%ad_x)) h = h*31 + 1
+    if (associated(Reg%Tr(m)%ad_y)) h = h*31 + 2
+    if (associated(Reg%Tr(m)%ad2d_x)) h = h*31 + 3
+    if (associated(Reg%Tr(m)%ad2d_y)) h = h*31 + 4
+    if (associated(Reg%Tr(m)%advection_xy)) h = h*31 + 5
+  enddo
+end function registry_hash
+
+!> Pointer of an optional diagnostic array, null when unassociated.
+function ptr3(a) result(p)
+  real, dimension(:,:,:), pointer :: a !< diagnostic array or null
+  type(c_ptr) :: p
+  p = c_null_ptr ; if (associated(a)) p = c_loc(a)
+end function ptr3
+function ptr2(a) result(p)
+  real, dimension(:,:), pointer :: a !< diagnostic array or null
+  type(c_ptr) :: p
+  p = c_null_ptr ; if (associated(a)) p = c_loc(a)
+end function ptr2
+
+!> Horizontal tracer advection on the GPU; argument list of the reference (:52-86).
+subroutine advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first_in, &
+                         vol_prev, max_iter_in, update_vol_prev, uhr_out, vhr_out)
+  type(ocean_grid_type), target, intent(inout) :: G     !< ocean grid structure
+  type(verticalGrid_type), intent(in)    :: GV    !< ocean vertical grid structure
+  real, dimension(SZI_(G),SZJ_(G),SZK_(GV)), target, &
+                           intent(in)    :: h_end !< layer thickness after advection [H ~> m or kg m-2]
+  real, dimension(SZIB_(G),SZJ_(G),SZK_(GV)), target, &
+                           intent(in)    :: uhtr  !< accumulated zonal volume/mass flux [H L2 ~> m3 or kg]
+  real, dimension(SZI_(G),SZJB_(G),SZK_(GV)), target, &
+                           intent(in)    :: vhtr  !< accumulated meridional volume/mass flux [H L2 ~> m3 or kg]
+  type(ocean_OBC_type),    pointer       :: OBC   !< open boundary condition data
+  real,                    intent(in)    :: dt    !< time increment [T ~> s]
+  type(unit_scale_type),   intent(in)    :: US    !< dimensional unit scaling type
+  type(tracer_advect_CS),  pointer       :: CS    !< control structure for this module
+  type(tracer_registry_type), pointer    :: Reg   !< tracer registry
+  logical,       optional, intent(in)    :: x_first_in !< override of the first direction
+  real, dimension(SZI_(G),SZJ_(G),SZK_(GV)), target, &
+                 optional, intent(inout) :: vol_prev !< cell volume before advection [H L2 ~> m3 or kg]
+  integer,       optional, intent(in)    :: max_iter_in !< maximum number of advection iterations
+  logical,       optional, intent(in)    :: update_vol_prev !< if present and true, update vol_prev
+  real, dimension(SZIB_(G),SZJ_(G),SZK_(GV)), target, &
+                 optional, intent(out)   :: uhr_out !< remaining zonal flux [H L2 ~> m3 or kg]
+  real, dimension(SZI_(G),SZJB_(G),SZK_(GV)), target, &
+                 optional, intent(out)   :: vhr_out !< remaining meridional flux [H L2 ~> m3 or kg]
+  integer(c_int) :: xf, mi, uv, nit
+  integer(kind=c_long_long) :: h
+  type(c_ptr) :: p_vol, p_uo, p_vo
+  integer :: m
+
+  if (.not. associated(CS)) call MOM_error(FATAL, "MOM_tracer_advect: "// &
+       "tracer_advect_init must be called before advect_tracer.")
+  if (.not. associated(Reg)) call MOM_error(FATAL, "MOM_tracer_advect: "// &
+       "register_tracer must be called before advect_tracer.")
+  if (Reg%ntr==0) return
+  if (associated(OBC)) then ; if (OBC%OBC_pe) call MOM_error(FATAL, "MOM_tracer_advect (B200): "// &
+       "tracer reservoirs of open boundary segments are not supported yet (mom6adv status 3).") ; endif
+  call cpu_clock_begin(id_clock_advect)
+
+  if (.not. c_associated(CS%plan)) call make_plan(G, GV, CS)
+  h = registry_hash(Reg)
+  if (Reg%ntr /= CS%ntr_bound .or. h /= CS%reg_hash) then
+    call check_rc(mom6adv_set_ntr(CS%plan, int(Reg%ntr, c_int)), CS%plan, "set_ntr")
+    do m=1,Reg%ntr
+      call check_rc(mom6adv_bind_tracer(CS%plan, int(m-1, c_int), c_loc(Reg%Tr(m)%t), &
+                      real(Reg%Tr(m)%conc_underflow, c_double), ptr3(Reg%Tr(m)%ad_x), ptr3(Reg%Tr(m)%ad_y), &
+                      ptr2(Reg%Tr(m)%ad2d_x), ptr2(Reg%Tr(m)%ad2d_y), ptr3(Reg%Tr(m)%advection_xy)), &
+                    CS%plan, "bind_tracer")
+    enddo
+    CS%ntr_bound = Reg%ntr ; CS%reg_hash = h
+  endif
+
+  xf = -1 ; if (present(x_first_in)) xf = merge(1, 0, x_first_in)
+  mi = -1 ; if (present(max_iter_in)) mi = max_iter_in
+  uv = -1 ; if (present(update_vol_prev)) uv = merge(1, 0, update_vol_prev)
+  p_vol = c_null_ptr ; if (present(vol_prev)) p_vol = c_loc(vol_prev)
+  p_uo = c_null_ptr ; if (present(uhr_out)) p_uo = c_loc(uhr_out)
+  p_vo = c_null_ptr ; if (present(vhr_out)) p_vo = c_loc(vhr_out)
+  call check_rc(mom6adv_advect(CS%plan, c_loc(h_end), c_loc(uhtr), c_loc(vhtr), real(dt, c_double), xf, p_vol, &
+                               mi, uv, p_uo, p_vo, nit), CS%plan, "advect_tracer")
+
+  call cpu_clock_end(id_clock_advect)
+end subroutine advect_tracer
+
+!> Initialise the module: same parameters, defaults and messages as the reference (:1090-1150).
+subroutine tracer_advect_init(Time, G, US, param_file, diag, CS)
+  type(time_type), target, intent(in)    :: Time        !< current model time
+  type(ocean_grid_type),   intent(in)    :: G           !< ocean grid structure
+  type(unit_scale_type),   intent(in)    :: US          !< dimensional unit scaling type
+  type(param_file_type),   intent(in)    :: param_file  !< open file to parse for model parameters
+  type(diag_ctrl), target, intent(inout) :: diag        !< regulates diagnostic output
+  type(tracer_advect_CS),  pointer       :: CS          !< module control structure
+  ! This include declares and sets the variable "version".
+# include "version_variable.h"
+  character(len=40)  :: mdl = "MOM_tracer_advect" ! This module's name.
+  character(len=256) :: mesg                      ! the advection scheme's name
+
+  if (associated(CS)) then
+    call MOM_error(WARNING, "tracer_advect_init called with associated control structure.")
+    return
+  endif
+  allocate(CS)
+  CS%diag => diag
+
+  call log_version(param_file, mdl, version, "")
+  call get_param(param_file, mdl, "DT", CS%dt, fail_if_missing=.true., &
+                 desc="The (baroclinic) dynamics time step.", units="s", scale=US%s_to_T)
+  call get_param(param_file, mdl, "DEBUG", CS%debug, default=.false.)
+  call get_param(param_file, mdl, "TRACER_ADVECTION_SCHEME", mesg, &
+                 desc="The horizontal transport scheme for tracers:\n"//&
+                      "  PLM    - Piecewise Linear Method\n"//&
+                      "  PPM:H3 - Piecewise Parabolic Method (Huyhn 3rd order)\n"//&
+                      "  PPM    - Piecewise Parabolic Method (Colella-Woodward)", default='PLM')
+  select case (trim(mesg))
+    case ("PLM")    ; CS%usePPM = .false.
+    case ("PPM:H3") ; CS%usePPM = .true.  ; CS%useHuynh = .true.
+    case ("PPM")    ; CS%usePPM = .true.  ; CS%useHuynh = .false.
+    case default
+      call MOM_error(FATAL, "MOM_tracer_advect, tracer_advect_init: "//&
+                     "Unknown TRACER_ADVECTION_SCHEME = "//trim(mesg))
+  end select
+  if (.not.CS%usePPM) CS%useHuynh = .false.
+  if (CS%useHuynh) then
+    call get_param(param_file, mdl, "USE_HUYNH_STENCIL_BUG", CS%useHuynhStencilBug, &
+                   desc="If true, use a stencil width of 2 in PPM:H3 tracer advection. This is "//&
+                        "incorrect and will produce regressions in certain configurations, but may "//&
+                        "be required to reproduce results in legacy simulations.", default=.false.)
+  endif
+
+  id_clock_advect = cpu_clock_id('(Ocean advect tracer)', grain=CLOCK_MODULE)
+  id_clock_pass = cpu_clock_id('(Ocean tracer halo updates)', grain=CLOCK_ROUTINE)
+  id_clock_sync = cpu_clock_id('(Ocean tracer global synch)', grain=CLOCK_ROUTINE)
+end subroutine tracer_advect_init
+
+!> Release the GPU plan and the control structure (:1153-1158).
+subroutine tracer_advect_end(CS)
+  type(tracer_advect_CS), pointer :: CS !< module control structure
+  integer(c_int) :: rc
+  if (associated(CS)) then
+    if (c_associated(CS%plan)) rc = mom6adv_plan_destroy(CS%plan)
+    deallocate(CS)
+  endif
+end subroutine tracer_advect_end
+
+end module MOM_tracer_advect
