@@ -294,6 +294,12 @@ def run_e2e(args, name):
     ni, nj, nk, ntr, scheme = workload_shape(name)
     c = synth.make_case(ni, nj, nk, ntr, cfl=args.cfl, device="cuda")
     CS = tracer_advect_init(None, c.G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}, None, None)
+    if args.mirror_chunk is not None:
+        CS.gpu_options["mirror_chunk"] = args.mirror_chunk
+    if args.mirror_ahead is not None:
+        CS.gpu_options["mirror_ahead"] = args.mirror_ahead
+    if args.trace:
+        CS.gpu_options["trace"] = args.trace
     Reg = TracerRegistry()
     keep = []
     for m in range(ntr):
@@ -343,11 +349,20 @@ def main():
     ap.add_argument("--e2e-warmup", type=int, default=1)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--e2e-only", action="store_true", help="print only the e2e leg (pipeline tuning)")
+    ap.add_argument("--mirror-chunk", type=int, default=None, help="tracers per pipeline stage of the MIRROR call")
+    ap.add_argument("--mirror-ahead", type=int, default=None, help="chunks uploaded in front of the running one")
+    ap.add_argument("--trace", type=int, default=0, help="library prints the MIRROR pipeline's stream times (2: per chunk)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "native":
         args.warmup = 3
     if args.impl == "reference":
         return run_reference(args)
+    if args.e2e_only:
+        import torch
+        torch.cuda.set_device(0)
+        print(json.dumps(run_e2e(args, args.workload)))
+        return 0
     return run_native(args)
 
 

@@ -160,13 +160,18 @@ long long mom6adv_device_bytes(const mom6adv_plan *plan);
  * events on the plan's stream (resets the accumulators); "fast" 0/1 -- 0 forces
  * the generic thread-per-cell sweeps, 1 (default) uses the streaming kernels
  * whenever no flux diagnostic is associated; "sparse" 0/1 -- 1 (default)
- * updates only the cells next to faces with residual transport on trips >= 2. */
+ * updates only the cells next to faces with residual transport on trips >= 2;
+ * "mirror_chunk" n -- tracers per pipeline stage of mom6adv_advect (default 4,
+ * 0 = one stage: upload everything, compute, download everything);
+ * "mirror_ahead" n -- uploads queued n chunks in front of the compute (default 2); "trace" 0/1
+ * -- mom6adv_advect prints its copy-stream and compute times to stderr. */
 int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value);
 /* Kernel classes of the per-class timers: the stand-ins for the reference's
  * (Ocean advect tracer) / (Ocean tracer halo updates) / (Ocean tracer global
  * synch) clock triple (:1146-1148), resolved per kernel family. */
 enum { MOM6ADV_KC_PROLOGUE = 0, MOM6ADV_KC_HALO = 1, MOM6ADV_KC_FLAGS = 2, MOM6ADV_KC_MASS = 3,
-       MOM6ADV_KC_TRACER_X = 4, MOM6ADV_KC_TRACER_Y = 5, MOM6ADV_KC_OTHER = 6, MOM6ADV_KC_COUNT = 7 };
+       MOM6ADV_KC_TRACER_X = 4, MOM6ADV_KC_TRACER_Y = 5, MOM6ADV_KC_OTHER = 6, MOM6ADV_KC_SPARSE = 7,
+       MOM6ADV_KC_COUNT = 8 };
 /* Accumulated device time [ms] and number of timed brackets of one class
  * since "profile" was last set. */
 int mom6adv_kernel_class_time(const mom6adv_plan *plan, int kclass, double *ms_total, long long *n);

@@ -37,21 +37,35 @@ __device__ __forceinline__ double minpos(double x, double y) {
 
 // Exact x/3 and x/6 (bit-identical to the IEEE quotient): Markstein's sequence
 // q0 = RN(x*RN(1/d)), r = x - d*q0 (exact by FMA), q = RN(q0 + r*RN(1/d)); the
-// sign is copied from x so that -0 is preserved.  Checked exhaustively-at-random
-// against true division (6e8 values over every exponent incl. denormals,
-// scripts/check_markstein.c): d = 3 never differs; d = 6 differs only on exact
-// ties of denormal quotients (|x| < 2^-1021), which take the true division.
-static __device__ __noinline__ double div_slow(double x, double d) { return x / d; }
+// sign is copied from x so that -0 is preserved.  Checked against true division
+// on 6e8 random values over every exponent incl. denormals
+// (scripts/check_markstein.c): d = 3 never differs; d = 6 differs only on exact
+// ties of denormal quotients, |x| < 2^-1021.  There the bit pattern of |x| IS
+// the integer |x| / 2^-1074, so the quotient is an integer division rounded
+// half to even (div6_int) -- no call, no FP division in the hot loops.
 template <int D>
-__device__ __forceinline__ double divc(double x) {
+__device__ __forceinline__ double divc_fast(double x) {
   const double c = (D == 3) ? 0.33333333333333331 : 0.16666666666666666;
   const double q0 = __dmul_rn(x, c);
   const double r = __fma_rn(-(double)D, q0, x);
-  double q = copysign(__fma_rn(r, c, q0), x);
-  if (D == 6) {
-    const unsigned u = (unsigned)__double2hiint(x) & 0x7fffffffu;
-    if (__builtin_expect(u < 0x00400000u && (u | (unsigned)__double2loint(x)) != 0u, 0)) q = div_slow(x, 6.0);
-  }
+  return copysign(__fma_rn(r, c, q0), x);
+}
+__device__ __forceinline__ bool div6_tiny(double x) {        // 0 < |x| < 2^-1021
+  const unsigned u = (unsigned)__double2hiint(x) & 0x7fffffffu;
+  return u < 0x00200000u && (u | (unsigned)__double2loint(x)) != 0u;
+}
+__device__ __forceinline__ double div6_int(double x) {       // exact x/6 for |x| < 2^-1021
+  const unsigned long long b = (unsigned long long)__double_as_longlong(x);
+  const unsigned long long k = b & 0x7fffffffffffffffULL;
+  unsigned long long q = k / 6ULL;
+  const unsigned long long rem = k - 6ULL * q;
+  q += (rem > 3ULL || (rem == 3ULL && (q & 1ULL))) ? 1ULL : 0ULL;
+  return __longlong_as_double((long long)((b & 0x8000000000000000ULL) | q));
+}
+template <int D>
+__device__ __forceinline__ double divc(double x) {           // general form (cold paths, PPM:H3 edges)
+  double q = divc_fast<D>(x);
+  if (D == 6 && div6_tiny(x)) q = div6_int(x);
   return q;
 }
 
@@ -66,7 +80,7 @@ __device__ __forceinline__ double slope_f(double a_hi, double a_lo, double A2_hi
 
 // CW84 edge value between cells lo and hi=lo+1 (:535-536 / :920-921)
 __device__ __forceinline__ double edge_cw(double Tlo, double Thi, double slo, double shi) {
-  return 0.5 * ((Tlo + Thi) + divc<3>(slo - shi));
+  return 0.5 * ((Tlo + Thi) + divc_fast<3>(slo - shi));
 }
 
 // PPM:H3 edge values of one cell (:530-533 / :915-918)
@@ -77,16 +91,24 @@ __device__ __forceinline__ void edges_h3(double Tm, double Tc, double Tp, double
   aR = gmax2(gmin2(Tc, Tp), aR); aR = gmin2(gmax2(Tc, Tp), aR);
 }
 
-// Monotonic limiter (:538-548 / :923-933), first half: everything the common
-// path needs.  pp = mask*mask*(Tp-Tc)*(Tc-Tm), evaluated left to right.  On
-// return aL/aR hold the PCM-selected edge values, dA = aR-aL, S = aR+aL, and
-// `fix` says whether the (rare) overshoot correction ppm_fix must still run.
-__device__ __forceinline__ bool ppm_limit1(double &aL, double &aR, double Tc, double pp, double &dA, double &S,
-                                           double &t1) {
+// Monotonic limiter (:538-548 / :923-933) in three inlined pieces so that the two rare
+// events (a denormal dA*dA, an overshoot correction) cost one branch per thread-step
+// instead of one per cell:
+//   ppm_lim_a : dA, S, t1 = dA*(Tc - 0.5*S), dd = dA*dA, t2 = dd/6 (fast form)
+//   [if div6_tiny(dd): t2 = div6_int(dd)]
+//   ppm_lim_b : PCM select (mask*(Tp-Tc)*(Tc-Tm) <= 0) and the overshoot flag |t1| > t2
+//   [if flag: ppm_fix]
+//   ppm_a6
+__device__ __forceinline__ void ppm_lim_a(double aL, double aR, double Tc, double &dA, double &S, double &t1,
+                                          double &dd, double &t2) {
   dA = aR - aL;
   S = aR + aL;
   t1 = dA * (Tc - 0.5 * S);
-  const double t2 = divc<6>(dA * dA);
+  dd = dA * dA;
+  t2 = divc_fast<6>(dd);
+}
+__device__ __forceinline__ bool ppm_lim_b(double &aL, double &aR, double Tc, double pp, double &dA, double &S,
+                                          double t1, double t2) {
   const bool pcm = (pp <= 0.);
   // |t1| > t2 (t2 >= +0): integer compare of the magnitudes
   const bool fix = !pcm && ((__double_as_longlong(t1) & 0x7fffffffffffffffLL) > __double_as_longlong(t2));
@@ -94,7 +116,7 @@ __device__ __forceinline__ bool ppm_limit1(double &aL, double &aR, double Tc, do
   dA = pcm ? 0.0 : dA; S = pcm ? Tc + Tc : S;
   return fix;
 }
-// second half, only where fix: t1 > t2 -> aL = 3Tc - 2aR (:543); t1 < -t2 -> aR = 3Tc - 2aL (:545)
+// where the flag is set: t1 > t2 -> aL = 3Tc - 2aR (:543); t1 < -t2 -> aR = 3Tc - 2aL (:545)
 __device__ __forceinline__ void ppm_fix(double &aL, double &aR, double Tc, double t1, double &dA, double &S) {
   if (__double2hiint(t1) >= 0) aL = 3. * Tc - 2. * aR;
   else aR = 3. * Tc - 2. * aL;

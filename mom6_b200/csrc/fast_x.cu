@@ -114,10 +114,16 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
 #pragma unroll
         for (int n = 0; n < 4; n++) edges_h3(T[n], T[n + 1], T[n + 2], aL[n], aR[n]);
       }
-      double S[4], t1[4];
+      double S[4], t1[4], dd[4], t2[4];
       bool fix[4];
 #pragma unroll
-      for (int n = 0; n < 4; n++) fix[n] = ppm_limit1(aL[n], aR[n], T[n + 1], mm[n] * a[n + 1] * a[n], dA[n], S[n], t1[n]);
+      for (int n = 0; n < 4; n++) ppm_lim_a(aL[n], aR[n], T[n + 1], dA[n], S[n], t1[n], dd[n], t2[n]);
+      if (div6_tiny(dd[0]) | div6_tiny(dd[1]) | div6_tiny(dd[2]) | div6_tiny(dd[3])) {      // denormal dA^2: rare
+#pragma unroll
+        for (int n = 0; n < 4; n++) if (div6_tiny(dd[n])) t2[n] = div6_int(dd[n]);
+      }
+#pragma unroll
+      for (int n = 0; n < 4; n++) fix[n] = ppm_lim_b(aL[n], aR[n], T[n + 1], mm[n] * a[n + 1] * a[n], dA[n], S[n], t1[n], t2[n]);
       if (fix[0] | fix[1] | fix[2] | fix[3]) {       // overshoot corrections are rare: one region per 4 cells
 #pragma unroll
         for (int n = 0; n < 4; n++) if (fix[n]) ppm_fix(aL[n], aR[n], T[n + 1], t1[n], dA[n], S[n]);

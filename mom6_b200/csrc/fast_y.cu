@@ -22,6 +22,11 @@
 #define YNS 8           // ring stages
 #define YCOLS 64        // columns per CTA
 #define YROWB (YCOLS * 8)
+#ifndef YUNROLL
+#define YUNROLL 3
+#endif
+#define Y_PRAGMA_(x) _Pragma(#x)
+#define Y_UNROLL(n) Y_PRAGMA_(unroll n)
 
 struct __align__(16) YStage { double mass[6][YCOLS]; double T[YW][YCOLS]; };
 
@@ -126,10 +131,12 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   double T1[2] = {0, 0}, T2[2] = {0, 0}, T3[2] = {0, 0};   // T(r-1), T(r-2), T(r-3)
   double a1[2] = {0, 0}, A21[2] = {0, 0};                  // difference across face r-2|r-1 and 2|.|
   double s2[2] = {0, 0}, e3[2] = {0, 0}, pp2[2] = {0, 0};  // slope, south edge, limiter product of cell r-2
-  double Fn3[2] = {0, 0}, flp[2] = {0, 0};                 // north outflow of cell r-3, flux through face r-4
+  double Fn3[2] = {0, 0};                                  // north outflow of cell r-3 (through face r-3)
+  double flp[2] = {0, 0};                                  // flux through face r-4
   double hh3[2] = {0, 0}, hc3[2] = {0, 0}, gq3[2] = {0, 0};   // factors of face J = r-3
   bool act3 = false;                                       // face J = r-3 is part of the sweep
-#pragma unroll 3
+  const bool do_cu = (cu > 0.0);
+  Y_UNROLL(YUNROLL)
   for (int it = 0; it < nsteps; it++) {
     const int r = r_lo + it, s = it % YNS;
     mbar_wait(smem_u32(&bar_full[s]), (it / YNS) & 1);
@@ -148,36 +155,63 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
     const double Tn[2] = {tn.x, tn.y};
     const double hh2[2] = {qhh.x, qhh.y}, hc2[2] = {qhc.x, qhc.y}, gq2[2] = {qgq.x, qgq.y};
     const double hl[2] = {qhl.x, qhl.y}, ih[2] = {qih.x, qih.y}, mm1[2] = {qmm.x, qmm.y};
+    double a0[2], A20[2], s1[2] = {0, 0};
+#pragma unroll
+    for (int n = 0; n < 2; n++) {
+      a0[n] = Tn[n] - T1[n];                               // face r-1|r
+      A20[n] = 2.0 * fabs(a0[n]);
+      if (SCHEME != SCHEME_PPM_H3) s1[n] = slope_f(a0[n], a1[n], A20[n], A21[n], Tn[n] - T2[n], mm1[n]);    // cell r-1
+    }
+    // parabola of cell r-2: xL/xR = edge values, dA, a6  (PLM: xL = xR = T, dA = 0.5*slope, a6 unused)
+    double xL[2], xR[2], dA[2], a6[2] = {0, 0};
+    if (SCHEME == SCHEME_PLM) {
+#pragma unroll
+      for (int n = 0; n < 2; n++) { xL[n] = T2[n]; xR[n] = T2[n]; dA[n] = 0.5 * s2[n]; }
+    } else {
+      double S[2], t1[2], dd[2], t2[2], e2[2] = {0, 0};
+#pragma unroll
+      for (int n = 0; n < 2; n++) {
+        if (SCHEME == SCHEME_PPM_CW) { e2[n] = edge_cw(T2[n], T1[n], s2[n], s1[n]); xL[n] = e3[n]; xR[n] = e2[n]; }
+        else edges_h3(T3[n], T2[n], T1[n], xL[n], xR[n]);
+        ppm_lim_a(xL[n], xR[n], T2[n], dA[n], S[n], t1[n], dd[n], t2[n]);
+      }
+      if (div6_tiny(dd[0]) | div6_tiny(dd[1])) {           // denormal dA^2: rare
+#pragma unroll
+        for (int n = 0; n < 2; n++) if (div6_tiny(dd[n])) t2[n] = div6_int(dd[n]);
+      }
+      bool fix[2];
+#pragma unroll
+      for (int n = 0; n < 2; n++) fix[n] = ppm_lim_b(xL[n], xR[n], T2[n], pp2[n], dA[n], S[n], t1[n], t2[n]);
+      if (fix[0] | fix[1]) {                               // overshoot correction: rare
+#pragma unroll
+        for (int n = 0; n < 2; n++) if (fix[n]) ppm_fix(xL[n], xR[n], T2[n], t1[n], dA[n], S[n]);
+      }
+#pragma unroll
+      for (int n = 0; n < 2; n++) { a6[n] = ppm_a6(T2[n], S[n]); e3[n] = e2[n]; }
+    }
     double o[2];
 #pragma unroll
     for (int n = 0; n < 2; n++) {
-      const double a0 = Tn[n] - T1[n];                     // face r-1|r
-      const double A20 = 2.0 * fabs(a0);
-      double s1 = 0.0, Fn2, Fs2 = 0.0;
-      if (SCHEME != SCHEME_PPM_H3) s1 = slope_f(a0, a1[n], A20, A21[n], Tn[n] - T2[n], mm1[n]);      // cell r-1
-      if (SCHEME == SCHEME_PLM) {
-        // cell r-2 feeds its north face r-2 (hh2 >= 0) and its south face r-3 (hh3 < 0); gq = 1-CFL
-        Fn2 = hh2[n] * (T2[n] + 0.5 * s2[n] * gq2[n]);
-        if (hh3[n] < 0.0) Fs2 = hh3[n] * (T2[n] - 0.5 * s2[n] * gq3[n]);
+      // cell r-2 feeds its north face r-2 when hh2 >= 0 (kept for the next step) and its south face r-3 when hh3 < 0
+      double Fn2, Fs2 = 0.0;
+      if (SCHEME == SCHEME_PLM) {      // hh*(T +- 0.5*slope*(1-CFL)), gq = 1-CFL (:946-961)
+        Fn2 = hh2[n] * (xR[n] + dA[n] * gq2[n]);
+        if (hh3[n] < 0.0) Fs2 = hh3[n] * (xL[n] - dA[n] * gq3[n]);
       } else {
-        double aL, aR, dA, a6, S, t1, e2 = 0.0;
-        if (SCHEME == SCHEME_PPM_CW) { e2 = edge_cw(T2[n], T1[n], s2[n], s1); aL = e3[n]; aR = e2; }
-        else edges_h3(T3[n], T2[n], T1[n], aL, aR);
-        if (ppm_limit1(aL, aR, T2[n], pp2[n], dA, S, t1)) ppm_fix(aL, aR, T2[n], t1, dA, S);
-        a6 = ppm_a6(T2[n], S);
-        Fn2 = out_hi(hh2[n], hc2[n], gq2[n], aR, dA, a6);
-        if (hh3[n] < 0.0) Fs2 = out_lo(hh3[n], hc3[n], gq3[n], aL, dA, a6);
-        e3[n] = e2;
+        Fn2 = out_hi(hh2[n], hc2[n], gq2[n], xR[n], dA[n], a6[n]);
+        if (hh3[n] < 0.0) Fs2 = out_lo(hh3[n], hc3[n], gq3[n], xL[n], dA[n], a6[n]);
       }
       // flux through face J = r-3 (between cells r-3 and r-2); +0 on rows that are not swept (:1016-1018)
-      const double fl3 = act3 ? ((hh3[n] >= 0.0) ? Fn3[n] : Fs2) : 0.0;
-      o[n] = T3[n];
-      if (ih[n] > 0.0) o[n] = (T3[n] * hl[n] - (fl3 - flp[n])) * ih[n];
-      if (cu > 0.0 && inr[n]) o[n] = underflow(o[n], cu);
-      flp[n] = fl3; Fn3[n] = Fn2;
-      pp2[n] = mm1[n] * a0 * a1[n];                        // cell r-1: mask*(Tp-Tc)*(Tc-Tm)
+      const double f = (hh3[n] >= 0.0) ? Fn3[n] : Fs2;
+      const double fl3 = act3 ? f : 0.0;
+      const double upd = (T3[n] * hl[n] - (fl3 - flp[n])) * ih[n];
+      o[n] = (__double_as_longlong(ih[n]) != 0LL) ? upd : T3[n];             // do_i: Ihnew > 0 (it is never negative)
+      if (do_cu && inr[n]) o[n] = underflow(o[n], cu);
+      flp[n] = fl3;
+      Fn3[n] = Fn2;
+      pp2[n] = mm1[n] * a0[n] * a1[n];                     // cell r-1: mask*(Tp-Tc)*(Tc-Tm)
       T3[n] = T2[n]; T2[n] = T1[n]; T1[n] = Tn[n];
-      a1[n] = a0; A21[n] = A20; s2[n] = s1;
+      a1[n] = a0[n]; A21[n] = A20[n]; s2[n] = s1[n];
       hh3[n] = hh2[n]; hc3[n] = hc2[n]; gq3[n] = gq2[n];
     }
     act3 = act2;

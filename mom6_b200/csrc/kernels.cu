@@ -524,3 +524,23 @@ void launch_fill(cudaStream_t s, double *p, long long n, double v) {
   if (n <= 0) return;
   k_fill<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p, n, v);
 }
+
+__global__ void k_fill_int(int *p, int n, int v) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) p[t] = v;
+}
+// Set on the device: a host-to-device copy here would queue behind the bulk tracer uploads of the MIRROR pipeline.
+void launch_fill_int(cudaStream_t s, int *p, int n, int v) {
+  if (n <= 0) return;
+  k_fill_int<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(p, n, v);
+}
+
+// Publish n ints to host-mapped pinned memory: the convergence word and the active-cell count reach the
+// host as posted PCIe writes, not through a copy engine busy with a chunk of tracers.
+__global__ void k_publish(volatile int *host, const int *dev, int n) {
+  if (threadIdx.x < n) host[threadIdx.x] = dev[threadIdx.x];
+  __threadfence_system();
+}
+void launch_publish(cudaStream_t s, int *host_mapped, const int *dev, int n) {
+  k_publish<<<1, 32, 0, s>>>(host_mapped, dev, n);
+}

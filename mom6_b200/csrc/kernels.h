@@ -35,6 +35,8 @@ void launch_halo_pack(cudaStream_t s, long long plane, int nk, const int *src, c
 void launch_halo_unpack(cudaStream_t s, long long plane, int nk, const int *dst, int n,
                         double *const *fields, int nfields, const double *buf);
 void launch_fill(cudaStream_t s, double *p, long long n, double v);
+void launch_fill_int(cudaStream_t s, int *p, int n, int v);
+void launch_publish(cudaStream_t s, int *host_mapped, const int *dev, int n);
 
 // fast.cu: streaming tracer sweeps
 int x_fast_tiles(const Geom &g, int wbase);

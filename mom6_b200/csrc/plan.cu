@@ -12,6 +12,7 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <chrono>
 
 #define MOM6ADV_VERSION "mom6adv-b200 0.1 (sm_100a)"
 
@@ -22,6 +23,7 @@ struct TracerSlot {
   double *diag[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
   double conc_underflow = 0.0;
   bool bound = false;
+  int cur = 0;                              // live ping-pong buffer
 };
 
 struct HaloList {       // one stagger position
@@ -39,6 +41,7 @@ struct PeerLists {        // one neighbour rank of the multi-GPU group pass
   long long send_elems = 0, recv_elems = 0;
 };
 
+#define MIRROR_CHUNK_DEFAULT 2
 struct mom6adv_plan {
   Geom g;
   mom6adv_config cfg;
@@ -56,12 +59,18 @@ struct mom6adv_plan {
   double *uhr = nullptr, *vhr = nullptr, *hprev = nullptr;
   double *hh = nullptr, *cfl = nullptr, *hlst = nullptr, *ihnew = nullptr, *hc = nullptr, *gq = nullptr;
   int *domore_u = nullptr, *domore_v = nullptr, *entry_u = nullptr, *entry_v = nullptr, *domore_k = nullptr;
-  int *sum_dev = nullptr, *sum_host = nullptr;
+  int *sum_dev = nullptr, *sum_host = nullptr, *sum_host_dev = nullptr;   // sum_host: mapped pinned; sum_host_dev: its device alias
   double *staging = nullptr;
+  double *stage_in = nullptr;        // MIRROR pipeline: ring of contiguous upload slots (slots x chunk x Fortran-layout tracer)
+  long long stage_in_elems = 0;
   long long staging_elems = 0;
   std::vector<TracerSlot> tr;
   int ntr = 0;
-  int cur = 0;                       // live ping-pong buffer of every tracer
+  int cur = 0;                       // live ping-pong buffer of the tracers of the active range
+  int m_lo = 0, m_hi = 0;            // active tracer range of the running advect call [m_lo, m_hi)
+  cudaStream_t s_in = nullptr, s_out = nullptr;      // MIRROR mode: H2D / D2H copy streams
+  std::vector<cudaEvent_t> ev_chunk;                 // per chunk c: [4c] uploaded, [4c+1] repacked, [4c+2] computed, [4c+3] downloaded
+  cudaEvent_t ev_huv = nullptr;                      // h_end/uhtr/vhtr uploaded
   TracerDev *tr_dev = nullptr;       // device copy of the tracer table
   bool tr_dirty = true;
   double **halo_fields_dev = nullptr;  // [uhr], [vhr], [hprev, T...]
@@ -80,6 +89,9 @@ struct mom6adv_plan {
   std::vector<PeerLists> peers;
   int peer_ntr = -1;                 // ntr the exchange buffers were sized for
   long long halo_bytes_sent = 0;
+  int opt_chunk = MIRROR_CHUNK_DEFAULT;  // tracers per pipeline stage of the MIRROR call
+  int opt_ahead = 2;                 // chunks whose upload is queued in front of the running one
+  int opt_trace = 0;                 // print the MIRROR pipeline's copy/compute times to stderr
   int opt_sparse = 1;                // list-driven tracer update on residual iterations (sparse.cu)
   int *sp_list = nullptr; double *sp_new = nullptr; int sp_cap = 0, sp_ntr = 0;
   long long sparse_sweeps = 0, dense_sweeps = 0;
@@ -257,7 +269,8 @@ static int create_impl(mom6adv_plan *plan, const mom6adv_grid *gr) {
   for (int **pp : pf) { int rc = dev_alloc(plan, pp, (long long)g.R * g.nk); if (rc) return rc; }
   { int rc = dev_alloc(plan, &plan->domore_k, g.nk); if (rc) return rc; }
   { int rc = dev_alloc(plan, &plan->sum_dev, 4); if (rc) return rc; }
-  CK(cudaMallocHost((void **)&plan->sum_host, sizeof(int) * 4));
+  CK(cudaHostAlloc((void **)&plan->sum_host, sizeof(int) * 4, cudaHostAllocMapped));
+  CK(cudaHostGetDevicePointer((void **)&plan->sum_host_dev, plan->sum_host, 0));
   // staging buffer: the largest Fortran-layout 3-D field (u or v stagger)
   plan->staging_elems = (long long)(g.ied - g.isd + 2) * (g.jed - g.jsd + 2) * g.nk;
   { int rc = dev_alloc(plan, &plan->staging, plan->staging_elems); if (rc) return rc; }
@@ -498,6 +511,11 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
     if (plan->halo[p].sgn) cudaFree(plan->halo[p].sgn);
   }
   for (cudaEvent_t e : plan->prof_ev) cudaEventDestroy(e);
+  for (cudaEvent_t e : plan->ev_chunk) cudaEventDestroy(e);
+  if (plan->stage_in) cudaFree(plan->stage_in);
+  if (plan->ev_huv) cudaEventDestroy(plan->ev_huv);
+  if (plan->s_in) cudaStreamDestroy(plan->s_in);
+  if (plan->s_out) cudaStreamDestroy(plan->s_out);
   if (plan->ev0) cudaEventDestroy(plan->ev0);
   if (plan->ev1) cudaEventDestroy(plan->ev1);
   if (plan->stream) cudaStreamDestroy(plan->stream);
@@ -576,23 +594,24 @@ static int group_pass(mom6adv_plan *plan) {
   cudaStream_t s = plan->stream;
   ProfScope ps(plan, MOM6ADV_KC_HALO);
   // u list -> uhr, v list -> vhr, h list -> hprev + tracers (live buffer)
-  const int nh = 1 + plan->ntr;
+  const int nact = plan->m_hi - plan->m_lo;
   double **tab = plan->halo_fields_dev + plan->cur * (3 + plan->ntr);
-  double **ftab[3] = {tab + 2, tab + 0, tab + 1};        // field tables by stagger: h, u, v
-  const int nf[3] = {nh, 1, 1};
+  // field-table segments by stagger: h = hprev + the active tracers, u = uhr, v = vhr
+  struct Seg { double **t; int n; };
+  const Seg segs[3][2] = {{{tab + 2, 1}, {tab + 3 + plan->m_lo, nact}}, {{tab + 0, 1}, {nullptr, 0}}, {{tab + 1, 1}, {nullptr, 0}}};
   // (1) halo points whose source lies in this rank's own block (cyclic wrap / fold onto itself)
-  for (int pos = 0; pos < 3; pos++)
-    launch_halo_apply(s, g.plane, g.nk, plan->halo[pos].dst, plan->halo[pos].src, plan->halo[pos].sgn, plan->halo[pos].n,
-                      ftab[pos], nf[pos]);
-  plan->launches += 3;
+  for (int pos = 0; pos < 3; pos++) for (const Seg &sg : segs[pos]) if (sg.n > 0) {
+    launch_halo_apply(s, g.plane, g.nk, plan->halo[pos].dst, plan->halo[pos].src, plan->halo[pos].sgn, plan->halo[pos].n, sg.t, sg.n);
+    plan->launches++;
+  }
   if (plan->multi && !plan->peers.empty()) {
     if (!plan->comm) return fail(plan, MOM6ADV_ERR_COMM, "advect: mom6adv_comm_init has not been called on this multi-block plan");
     // (2) pack one message per neighbour: [h: hprev, tracers][u: uhr][v: vhr], each [field][level][point]
     for (PeerLists &p : plan->peers) {
       long long off = 0;
-      for (int pos = 0; pos < 3; pos++) {
-        launch_halo_pack(s, g.plane, g.nk, p.send_src[pos], p.send_sgn[pos], p.n_send[pos], ftab[pos], nf[pos], p.sendbuf + off);
-        off += (long long)nf[pos] * g.nk * p.n_send[pos];
+      for (int pos = 0; pos < 3; pos++) for (const Seg &sg : segs[pos]) if (sg.n > 0) {
+        launch_halo_pack(s, g.plane, g.nk, p.send_src[pos], p.send_sgn[pos], p.n_send[pos], sg.t, sg.n, p.sendbuf + off);
+        off += (long long)sg.n * g.nk * p.n_send[pos];
         plan->launches++;
       }
     }
@@ -600,17 +619,19 @@ static int group_pass(mom6adv_plan *plan) {
     // (3) device-resident exchange over NVLink
     CKN(ncclGroupStart());
     for (PeerLists &p : plan->peers) {
-      if (p.send_elems) CKN(ncclSend(p.sendbuf, (size_t)p.send_elems, ncclDouble, p.rank, plan->comm, s));
-      if (p.recv_elems) CKN(ncclRecv(p.recvbuf, (size_t)p.recv_elems, ncclDouble, p.rank, plan->comm, s));
-      plan->halo_bytes_sent += 8 * p.send_elems;
+      const long long ns = (long long)g.nk * ((long long)(1 + nact) * p.n_send[0] + p.n_send[1] + p.n_send[2]);
+      const long long nr = (long long)g.nk * ((long long)(1 + nact) * p.n_recv[0] + p.n_recv[1] + p.n_recv[2]);
+      if (ns) CKN(ncclSend(p.sendbuf, (size_t)ns, ncclDouble, p.rank, plan->comm, s));
+      if (nr) CKN(ncclRecv(p.recvbuf, (size_t)nr, ncclDouble, p.rank, plan->comm, s));
+      plan->halo_bytes_sent += 8 * ns;
     }
     CKN(ncclGroupEnd());
     // (4) unpack
     for (PeerLists &p : plan->peers) {
       long long off = 0;
-      for (int pos = 0; pos < 3; pos++) {
-        launch_halo_unpack(s, g.plane, g.nk, p.recv_dst[pos], p.n_recv[pos], ftab[pos], nf[pos], p.recvbuf + off);
-        off += (long long)nf[pos] * g.nk * p.n_recv[pos];
+      for (int pos = 0; pos < 3; pos++) for (const Seg &sg : segs[pos]) if (sg.n > 0) {
+        launch_halo_unpack(s, g.plane, g.nk, p.recv_dst[pos], p.n_recv[pos], sg.t, sg.n, p.recvbuf + off);
+        off += (long long)sg.n * g.nk * p.n_recv[pos];
         plan->launches++;
       }
     }
@@ -644,7 +665,7 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
   const double min_h = 0.1 * plan->Angstrom_H;        // :401 / :773
   const double h_neglect = plan->H_subroundoff;       // :403 / :775
   bool any_ad2d = false, any_diag = false;
-  for (int m = 0; m < plan->ntr; m++) {
+  for (int m = plan->m_lo; m < plan->m_hi; m++) {
     if (plan->tr[m].diag[dir == 0 ? 2 : 3]) any_ad2d = true;
     for (int d = 0; d < 5; d++) if (plan->tr[m].diag[d]) any_diag = true;
   }
@@ -675,22 +696,22 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
     }
     int cnt = 0;
     if (sparse) {
-      CK(cudaMemcpyAsync(plan->sum_host + 1, plan->sum_dev + 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+      launch_publish(s, plan->sum_host_dev + 1, plan->sum_dev + 1, 1);
       CK(cudaStreamSynchronize(s));
       cnt = plan->sum_host[1];
       if (cnt > plan->sp_cap) sparse = false;      // too many active cells: take the dense kernels
     }
     if (sparse) {
-      ProfScope pt(plan, x ? MOM6ADV_KC_TRACER_X : MOM6ADV_KC_TRACER_Y);
-      for (int m0 = 0; m0 < plan->ntr; m0 += MOM6ADV_MAXT) {
+      ProfScope pt(plan, MOM6ADV_KC_SPARSE);
+      for (int m0 = plan->m_lo; m0 < plan->m_hi; m0 += MOM6ADV_MAXT) {
         TrTable tt;
-        tt.n = std::min(MOM6ADV_MAXT, plan->ntr - m0);
+        tt.n = std::min(MOM6ADV_MAXT, plan->m_hi - m0);
         for (int m = 0; m < tt.n; m++) {
           const TracerSlot &ts = plan->tr[m0 + m];
           tt.src[m] = ts.buf[plan->cur]; tt.dst[m] = ts.buf[plan->cur]; tt.cu[m] = ts.conc_underflow;
         }
         launch_sparse_sweep(s, scheme, dir, g, rg, tt, plan->sp_list, cnt, plan->sp_cap, plan->hh, plan->cfl, plan->hlst,
-                            plan->ihnew, x ? plan->mmx : plan->mmy, ent, plan->sp_new + (long long)plan->sp_cap * m0);
+                            plan->ihnew, x ? plan->mmx : plan->mmy, ent, plan->sp_new + (long long)plan->sp_cap * (m0 - plan->m_lo));
         if (cnt > 0) plan->launches += 2;
       }
       plan->sparse_sweeps++;
@@ -699,9 +720,9 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
     }
     plan->dense_sweeps++;
     ProfScope pt(plan, x ? MOM6ADV_KC_TRACER_X : MOM6ADV_KC_TRACER_Y);
-    for (int m0 = 0; m0 < plan->ntr; m0 += MOM6ADV_MAXT) {
+    for (int m0 = plan->m_lo; m0 < plan->m_hi; m0 += MOM6ADV_MAXT) {
       TrTable tt;
-      tt.n = std::min(MOM6ADV_MAXT, plan->ntr - m0);
+      tt.n = std::min(MOM6ADV_MAXT, plan->m_hi - m0);
       for (int m = 0; m < tt.n; m++) {
         const TracerSlot &ts = plan->tr[m0 + m];
         tt.src[m] = ts.buf[plan->cur];
@@ -728,9 +749,9 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
                          plan->entry_u, plan->domore_k, plan->hlst, plan->ihnew, nullptr, nullptr, 0);
     }
     ProfScope pt(plan, MOM6ADV_KC_TRACER_X);
-    launch_tracer_sweep(s, scheme, 0, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->hlst,
+    launch_tracer_sweep(s, scheme, 0, g, rg, plan->tr_dev + plan->m_lo, plan->m_hi - plan->m_lo, plan->cur, plan->hh, plan->cfl, plan->hlst,
                         plan->ihnew, plan->mmx, plan->IareaT, plan->entry_u, plan->domore_k, Idt);
-    if (any_ad2d) launch_ad2d(s, scheme, 0, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->ihnew,
+    if (any_ad2d) launch_ad2d(s, scheme, 0, g, rg, plan->tr_dev + plan->m_lo, plan->m_hi - plan->m_lo, plan->cur, plan->hh, plan->cfl, plan->ihnew,
                               plan->mmx, plan->entry_u, plan->domore_k, Idt);
   } else {
     {
@@ -742,9 +763,9 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
                          plan->entry_v, plan->domore_k, plan->hlst, plan->ihnew, nullptr, nullptr, 0);
     }
     ProfScope pt(plan, MOM6ADV_KC_TRACER_Y);
-    launch_tracer_sweep(s, scheme, 1, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->hlst,
+    launch_tracer_sweep(s, scheme, 1, g, rg, plan->tr_dev + plan->m_lo, plan->m_hi - plan->m_lo, plan->cur, plan->hh, plan->cfl, plan->hlst,
                         plan->ihnew, plan->mmy, plan->IareaT, plan->entry_v, plan->domore_k, Idt);
-    if (any_ad2d) launch_ad2d(s, scheme, 1, g, rg, plan->tr_dev, plan->ntr, plan->cur, plan->hh, plan->cfl, plan->ihnew,
+    if (any_ad2d) launch_ad2d(s, scheme, 1, g, rg, plan->tr_dev + plan->m_lo, plan->m_hi - plan->m_lo, plan->cur, plan->hh, plan->cfl, plan->ihnew,
                               plan->mmy, plan->entry_v, plan->domore_k, Idt);
   }
   plan->launches += 4 + (any_ad2d ? 1 : 0);
@@ -754,12 +775,18 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
 }
 
 // advect_tracer :112-320 on the resident fields.
+// The tracers [m_lo, m_hi) are advected; the tracer-independent part (uhr, vhr, hprev, flags) is the same
+// whatever the range, which is what lets MIRROR mode pipeline chunks of tracers against the PCIe copies.
 static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_iter_in, bool use_vol_prev,
-                      bool update_vol_prev, int *n_iter_out) {
+                      bool update_vol_prev, int *n_iter_out, int m_lo, int m_hi) {
   if (n_iter_out) *n_iter_out = 0;
   if (plan->ntr == 0) return MOM6ADV_OK;                                   // :124
-  for (int m = 0; m < plan->ntr; m++)
+  if (m_lo < 0 || m_hi > plan->ntr || m_lo >= m_hi) return fail(plan, MOM6ADV_ERR_INVALID, "advect: bad tracer range");
+  for (int m = m_lo; m < m_hi; m++) {
     if (!plan->tr[m].buf[0]) return fail(plan, MOM6ADV_ERR_NOT_INIT, "advect: tracer storage missing");
+    if (plan->tr[m].cur != plan->tr[m_lo].cur) return fail(plan, MOM6ADV_ERR_INVALID, "advect: tracer buffers out of step");
+  }
+  plan->m_lo = m_lo; plan->m_hi = m_hi; plan->cur = plan->tr[m_lo].cur;
   const Geom &g = plan->g;
   cudaStream_t s = plan->stream;
   CK(cudaSetDevice(plan->device));
@@ -789,13 +816,9 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
   launch_init_residuals(s, g, plan->h_end, plan->uhtr, plan->vhtr, use_vol_prev ? plan->vol_prev : nullptr,
                         plan->areaT, plan->uhr, plan->vhr, plan->hprev);    // :152-178
   }
-  {
-    std::vector<int> ones(g.nk, 1);
-    CK(cudaMemcpyAsync(plan->domore_k, ones.data(), sizeof(int) * g.nk, cudaMemcpyHostToDevice, s));
-    CK(cudaStreamSynchronize(s));   // ones goes out of scope
-  }
-  plan->launches += 1;
-  for (int m = 0; m < plan->ntr; m++)                                       // :192-198
+  launch_fill_int(s, plan->domore_k, g.nk, 1);                               // :156
+  plan->launches += 2;
+  for (int m = m_lo; m < m_hi; m++)                                         // :192-198
     for (int d = 0; d < 5; d++)
       if (plan->tr[m].diag[d])
         CK(cudaMemsetAsync(plan->tr[m].diag[d], 0, sizeof(double) * ((d == 2 || d == 3) ? g.plane : field_elems(plan)), s));
@@ -836,7 +859,7 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
         CKN(ncclAllReduce(plan->domore_k, plan->domore_k, g.nk, ncclInt, ncclSum, plan->comm, s));
       launch_sum_domore_k(s, plan->domore_k, g.nk, plan->sum_dev);          // :307 do_any
       plan->launches += 1;
-      CK(cudaMemcpyAsync(plan->sum_host, plan->sum_dev, sizeof(int), cudaMemcpyDeviceToHost, s));
+      launch_publish(s, plan->sum_host_dev, plan->sum_dev, 1);
       CK(cudaStreamSynchronize(s));
       if (plan->sum_host[0] == 0) break;                                    // :308-310
     }
@@ -849,6 +872,7 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
   float ms = 0.f;
   CK(cudaEventElapsedTime(&ms, plan->ev0, plan->ev1));
   plan->last_ms = ms;
+  for (int m = m_lo; m < m_hi; m++) plan->tr[m].cur = plan->cur;
   prof_collect(plan);
   CK(cudaGetLastError());
   return MOM6ADV_OK;
@@ -906,7 +930,7 @@ extern "C" int mom6adv_upload_tracer(mom6adv_plan *plan, int m, const double *sr
   if (m < 0 || m >= plan->ntr) return fail(plan, MOM6ADV_ERR_INVALID, "upload_tracer: tracer index out of range");
   if (!src) return fail(plan, MOM6ADV_ERR_INVALID, "upload_tracer: NULL source");
   CK(cudaSetDevice(plan->device));
-  int rc = upload(plan, plan->tr[m].buf[plan->cur], src, plan->g.isd, plan->g.jsd, plan->g.nk);
+  int rc = upload(plan, plan->tr[m].buf[plan->tr[m].cur], src, plan->g.isd, plan->g.jsd, plan->g.nk);
   if (rc) return rc;
   CK(cudaStreamSynchronize(plan->stream));
   return MOM6ADV_OK;
@@ -917,7 +941,7 @@ extern "C" int mom6adv_download_tracer(mom6adv_plan *plan, int m, double *dst) {
   if (m < 0 || m >= plan->ntr) return fail(plan, MOM6ADV_ERR_INVALID, "download_tracer: tracer index out of range");
   if (!dst) return fail(plan, MOM6ADV_ERR_INVALID, "download_tracer: NULL destination");
   CK(cudaSetDevice(plan->device));
-  int rc = download(plan, dst, plan->tr[m].buf[plan->cur], plan->g.isd, plan->g.jsd, plan->g.nk);
+  int rc = download(plan, dst, plan->tr[m].buf[plan->tr[m].cur], plan->g.isd, plan->g.jsd, plan->g.nk);
   if (rc) return rc;
   CK(cudaStreamSynchronize(plan->stream));
   return MOM6ADV_OK;
@@ -946,11 +970,47 @@ extern "C" int mom6adv_download_diag(mom6adv_plan *plan, int m, int kind, double
 extern "C" int mom6adv_advect_resident(mom6adv_plan *plan, double dt, int x_first, int max_iter_in,
                                        int use_vol_prev, int update_vol_prev, int *n_iter) {
   if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "advect: tracer_advect_init must be called before advect_tracer");
-  return run_advect(plan, dt, x_first, max_iter_in, use_vol_prev != 0, update_vol_prev > 0, n_iter);
+  return run_advect(plan, dt, x_first, max_iter_in, use_vol_prev != 0, update_vol_prev > 0, n_iter, 0, plan->ntr);
 }
 
 // ---------------------------------------------------------------------------
 // MIRROR mode: one call == one reference advect_tracer call on host arrays.
+// ---------------------------------------------------------------------------
+// Strided DMA between a Fortran-layout host array (ilo:ied, jlo:jed, nlev) and the padded HBM field:
+// no staging buffer and no repack kernel, so copy engines and SMs work at the same time.
+static int xfer3d(mom6adv_plan *plan, cudaStream_t st, double *dev, const double *host, int ilo, int jlo, int nlev,
+                  bool to_dev) {
+  const Geom &g = plan->g;
+  const size_t ni = (size_t)(g.ied - ilo + 1), nj = (size_t)(g.jed - jlo + 1);
+  cudaMemcpy3DParms p;
+  memset(&p, 0, sizeof p);
+  const cudaPitchedPtr hp = make_cudaPitchedPtr((void *)host, ni * 8, ni * 8, nj);
+  const cudaPitchedPtr dp = make_cudaPitchedPtr((void *)dev, (size_t)g.P * 8, (size_t)g.P * 8, (size_t)g.R);
+  const cudaPos dpos = make_cudaPos((size_t)(ilo + g.coff) * 8, (size_t)(jlo + g.roff), 0);
+  if (to_dev) { p.srcPtr = hp; p.dstPtr = dp; p.dstPos = dpos; p.kind = cudaMemcpyHostToDevice; }
+  else { p.srcPtr = dp; p.srcPos = dpos; p.dstPtr = hp; p.kind = cudaMemcpyDeviceToHost; }
+  p.extent = make_cudaExtent(ni * 8, nj, (size_t)nlev);
+  CK(cudaMemcpy3DAsync(&p, st));
+  return 0;
+}
+static int put(mom6adv_plan *plan, cudaStream_t st, double *dev, const double *src, int ilo, int jlo, int nlev) {
+  if (is_device_ptr(src)) return upload(plan, dev, src, ilo, jlo, nlev);      // repack kernel on the main stream
+  return xfer3d(plan, st, dev, src, ilo, jlo, nlev, true);
+}
+static int get(mom6adv_plan *plan, cudaStream_t st, double *dst, const double *dev, int ilo, int jlo, int nlev) {
+  if (is_device_ptr(dst)) return download(plan, dst, dev, ilo, jlo, nlev);
+  return xfer3d(plan, st, const_cast<double *>(dev), dst, ilo, jlo, nlev, false);
+}
+
+
+// ---------------------------------------------------------------------------
+// MIRROR mode: one call == one reference advect_tracer call on host arrays.
+// Tracers are independent of one another, so the call is pipelined in chunks:
+// H2D of chunk c+1 (stream s_in), the whole algorithm on chunk c (main stream)
+// and D2H of chunk c-1 (stream s_out) overlap, and both PCIe directions stay
+// busy.  The tracer-independent recursion (uhr, vhr, hprev, flags) is simply
+// repeated per chunk from the resident h_end/uhtr/vhtr: a few ms against the
+// ~75 ms a chunk spends on the bus.
 // ---------------------------------------------------------------------------
 extern "C" int mom6adv_advect(mom6adv_plan *plan, const double *h_end, const double *uhtr, const double *vhtr,
                               double dt, int x_first, double *vol_prev, int max_iter_in, int update_vol_prev,
@@ -959,36 +1019,132 @@ extern "C" int mom6adv_advect(mom6adv_plan *plan, const double *h_end, const dou
   if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "advect: tracer_advect_init must be called before advect_tracer");
   if (plan->ntr == 0) return MOM6ADV_OK;   // :124
   if (!h_end || !uhtr || !vhtr) return fail(plan, MOM6ADV_ERR_INVALID, "advect: NULL input array");
-  for (int m = 0; m < plan->ntr; m++)
+  bool any_dev = false, any_diag = false;
+  for (int m = 0; m < plan->ntr; m++) {
     if (!plan->tr[m].bound || !plan->tr[m].host_t)
       return fail(plan, MOM6ADV_ERR_NOT_INIT, "advect: register_tracer must be called before advect_tracer (tracer not bound)");
+    any_dev = any_dev || is_device_ptr(plan->tr[m].host_t);
+    for (int d = 0; d < 5; d++) any_diag = any_diag || plan->tr[m].diag[d];
+  }
   CK(cudaSetDevice(plan->device));
   const Geom &g = plan->g;
+  cudaStream_t s = plan->stream;
+  if (!plan->s_in) {
+    CK(cudaStreamCreateWithFlags(&plan->s_in, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&plan->s_out, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&plan->ev_huv, cudaEventDisableTiming));
+  }
+  // device-pointer registries and diagnostic runs are not pipelined (their copies are kernels on the main stream)
+  const int chunk = (any_dev || any_diag || plan->opt_chunk <= 0) ? plan->ntr : plan->opt_chunk;
+  const int nchunk = (plan->ntr + chunk - 1) / chunk;
+  while ((int)plan->ev_chunk.size() < 4 * nchunk) { cudaEvent_t e; CK(cudaEventCreate(&e)); plan->ev_chunk.push_back(e); }   // per chunk: uploaded, compute start, compute end, downloaded
   int rc;
-  if ((rc = upload(plan, plan->h_end, h_end, g.isd, g.jsd, g.nk))) return rc;
-  if ((rc = upload(plan, plan->uhtr, uhtr, g.IsdB, g.jsd, g.nk))) return rc;
-  if ((rc = upload(plan, plan->vhtr, vhtr, g.isd, g.JsdB, g.nk))) return rc;
-  if (vol_prev) {
-    if (!plan->vol_prev) { rc = dev_alloc(plan, &plan->vol_prev, field_elems(plan)); if (rc) return rc; }
-    if ((rc = upload(plan, plan->vol_prev, vol_prev, g.isd, g.jsd, g.nk))) return rc;
+  cudaEvent_t tr_ev[6] = {};
+  if (plan->opt_trace) {
+    for (auto &e : tr_ev) CK(cudaEventCreate(&e));
+    CK(cudaEventRecord(tr_ev[0], s)); CK(cudaEventRecord(tr_ev[2], plan->s_in));
   }
-  for (int m = 0; m < plan->ntr; m++)
-    if ((rc = upload(plan, plan->tr[m].buf[plan->cur], plan->tr[m].host_t, g.isd, g.jsd, g.nk))) return rc;
-  const bool upd = vol_prev && update_vol_prev > 0;
-  rc = run_advect(plan, dt, x_first, max_iter_in, vol_prev != nullptr, upd, n_iter);
-  if (rc) return rc;
-  for (int m = 0; m < plan->ntr; m++) {
-    if ((rc = download(plan, plan->tr[m].host_t, plan->tr[m].buf[plan->cur], g.isd, g.jsd, g.nk))) return rc;
-    for (int d = 0; d < 5; d++) if (plan->tr[m].diag[d] && plan->tr[m].host_diag[d]) {
-      int ilo, jlo, nlev;
-      diag_info(g, d, &ilo, &jlo, &nlev);
-      if ((rc = download(plan, plan->tr[m].host_diag[d], plan->tr[m].diag[d], ilo, jlo, nlev))) return rc;
+  // h_end, uhtr, vhtr(, vol_prev) go first on the upload stream, so that the copy engine serves them before
+  // the first tracer chunk (nothing is being downloaded yet: the strided copy is harmless here)
+  {
+    cudaStream_t su = any_dev ? s : plan->s_in;
+    if (vol_prev && !plan->vol_prev) { rc = dev_alloc(plan, &plan->vol_prev, field_elems(plan)); if (rc) return rc; CK(cudaStreamSynchronize(s)); }
+    if ((rc = put(plan, su, plan->h_end, h_end, g.isd, g.jsd, g.nk))) return rc;
+    if ((rc = put(plan, su, plan->uhtr, uhtr, g.IsdB, g.jsd, g.nk))) return rc;
+    if ((rc = put(plan, su, plan->vhtr, vhtr, g.isd, g.JsdB, g.nk))) return rc;
+    if (vol_prev && (rc = put(plan, su, plan->vol_prev, vol_prev, g.isd, g.jsd, g.nk))) return rc;
+    if (!any_dev) { CK(cudaEventRecord(plan->ev_huv, plan->s_in)); CK(cudaStreamWaitEvent(s, plan->ev_huv, 0)); }
+  }
+  // Uploads run `ahead` chunks in front of the compute, as CONTIGUOUS copies into a ring of staging slots
+  // that a repack kernel then spreads into the padded layout.  (Measured on this box, scripts/pcie_probe2.py:
+  // a row-strided H2D copy slows a concurrent D2H copy to 35 GB/s, a contiguous one leaves it at 50 GB/s;
+  // strided D2H costs nothing, so results go straight from the padded layout to the host array.)
+  const int ahead = std::max(1, plan->opt_ahead);
+  const int nslot = ahead + 1;
+  const long long telems = (long long)(g.ied - g.isd + 1) * (g.jed - g.jsd + 1) * g.nk;
+  if (!any_dev && plan->stage_in_elems < telems * chunk * nslot) {
+    if (plan->stage_in) { CK(cudaStreamSynchronize(s)); cudaFree(plan->stage_in); plan->stage_in = nullptr; plan->dev_bytes -= 8 * plan->stage_in_elems; }
+    plan->stage_in_elems = telems * chunk * nslot;
+    if ((rc = dev_alloc(plan, &plan->stage_in, plan->stage_in_elems))) return rc;
+    CK(cudaStreamSynchronize(s));     // dev_alloc clears on the main stream: must not race the first upload
+  }
+  auto t_host0 = std::chrono::steady_clock::now();
+  double host_enq_ms = 0.0;
+  auto enqueue_in = [&](int c) -> int {
+    if (c >= nchunk) return 0;
+    auto t0 = std::chrono::steady_clock::now();
+    const int m0 = c * chunk, m1 = std::min(plan->ntr, m0 + chunk);
+    if (any_dev) {
+      for (int m = m0; m < m1; m++) {
+        int r = put(plan, s, plan->tr[m].buf[plan->tr[m].cur], plan->tr[m].host_t, g.isd, g.jsd, g.nk);
+        if (r) return r;
+      }
+      CK(cudaEventRecord(plan->ev_chunk[4 * c], s));
+    } else {
+      double *slot = plan->stage_in + (long long)(c % nslot) * chunk * telems;
+      if (c >= nslot) CK(cudaStreamWaitEvent(plan->s_in, plan->ev_chunk[4 * (c - nslot) + 1], 0));   // slot repacked
+      for (int m = m0; m < m1; m++)
+        CK(cudaMemcpyAsync(slot + (long long)(m - m0) * telems, plan->tr[m].host_t, sizeof(double) * telems,
+                           cudaMemcpyHostToDevice, plan->s_in));
+      CK(cudaEventRecord(plan->ev_chunk[4 * c], plan->s_in));
+      if (plan->opt_trace && c == nchunk - 1) CK(cudaEventRecord(tr_ev[3], plan->s_in));
     }
+    host_enq_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return 0;
+  };
+  for (int c = 0; c < std::min(ahead, nchunk); c++) if ((rc = enqueue_in(c))) return rc;
+  const bool upd = vol_prev && update_vol_prev > 0;
+  double ms_total = 0.0;
+  for (int c = 0; c < nchunk; c++) {
+    const int m0 = c * chunk, m1 = std::min(plan->ntr, m0 + chunk);
+    if ((rc = enqueue_in(c + ahead))) return rc;
+    CK(cudaStreamWaitEvent(s, plan->ev_chunk[4 * c], 0));
+    if (!any_dev) {
+      const double *slot = plan->stage_in + (long long)(c % nslot) * chunk * telems;
+      for (int m = m0; m < m1; m++)
+        launch_repack_in(s, g, plan->tr[m].buf[plan->tr[m].cur], slot + (long long)(m - m0) * telems, g.isd, g.jsd, g.nk);
+      plan->launches += m1 - m0;
+    }
+    CK(cudaEventRecord(plan->ev_chunk[4 * c + 1], s));        // the slot is free again; compute starts
+    rc = run_advect(plan, dt, x_first, max_iter_in, vol_prev != nullptr, upd && c == nchunk - 1, n_iter, m0, m1);
+    if (rc) return rc;
+    ms_total += plan->last_ms;
+    cudaStream_t so = any_dev ? s : plan->s_out;
+    CK(cudaEventRecord(plan->ev_chunk[4 * c + 2], s));
+    CK(cudaStreamWaitEvent(so, plan->ev_chunk[4 * c + 2], 0));
+    if (plan->opt_trace && c == 0) CK(cudaEventRecord(tr_ev[4], so));
+    for (int m = m0; m < m1; m++) {
+      if ((rc = get(plan, so, plan->tr[m].host_t, plan->tr[m].buf[plan->tr[m].cur], g.isd, g.jsd, g.nk))) return rc;
+      for (int d = 0; d < 5; d++) if (plan->tr[m].diag[d] && plan->tr[m].host_diag[d]) {
+        int ilo, jlo, nlev;
+        diag_info(g, d, &ilo, &jlo, &nlev);
+        if ((rc = get(plan, so, plan->tr[m].host_diag[d], plan->tr[m].diag[d], ilo, jlo, nlev))) return rc;
+      }
+    }
+    if (plan->opt_trace) CK(cudaEventRecord(plan->ev_chunk[4 * c + 3], so));
   }
-  if (uhr_out && (rc = download(plan, uhr_out, plan->uhr, g.IsdB, g.jsd, g.nk))) return rc;   // :316
-  if (vhr_out && (rc = download(plan, vhr_out, plan->vhr, g.isd, g.JsdB, g.nk))) return rc;   // :317
-  if (upd && (rc = download(plan, vol_prev, plan->vol_prev, g.isd, g.jsd, g.nk))) return rc;  // :319
-  CK(cudaStreamSynchronize(plan->stream));
+  plan->last_ms = ms_total;
+  if (uhr_out && (rc = get(plan, s, uhr_out, plan->uhr, g.IsdB, g.jsd, g.nk))) return rc;   // :316
+  if (vhr_out && (rc = get(plan, s, vhr_out, plan->vhr, g.isd, g.JsdB, g.nk))) return rc;   // :317
+  if (upd && (rc = get(plan, s, vol_prev, plan->vol_prev, g.isd, g.jsd, g.nk))) return rc;  // :319
+  if (plan->opt_trace) { CK(cudaEventRecord(tr_ev[5], any_dev ? s : plan->s_out)); CK(cudaEventRecord(tr_ev[1], s)); }
+  CK(cudaStreamSynchronize(plan->s_out));
+  CK(cudaStreamSynchronize(s));
+  if (plan->opt_trace) {
+    float a = 0, b = 0, c2 = 0, d = 0, e = 0;
+    cudaEventElapsedTime(&a, tr_ev[0], tr_ev[1]); cudaEventElapsedTime(&b, tr_ev[2], tr_ev[3]);
+    cudaEventElapsedTime(&c2, tr_ev[4], tr_ev[5]); cudaEventElapsedTime(&d, tr_ev[0], tr_ev[4]); cudaEventElapsedTime(&e, tr_ev[0], tr_ev[5]);
+    fprintf(stderr, "[mom6adv trace] chunks %d x %d tracers: main %.1f ms, H2D stream %.1f ms, D2H stream %.1f ms (starts at %.1f, ends at %.1f), compute sum %.1f ms; host: %.1f ms in H2D enqueues, %.1f ms total\n",
+            nchunk, chunk, a, b, c2, d, e, ms_total, host_enq_ms,
+            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_host0).count());
+    if (plan->opt_trace > 1)
+      for (int c = 0; c < nchunk; c++) {
+        float t[4];
+        for (int q = 0; q < 4; q++) cudaEventElapsedTime(&t[q], tr_ev[0], plan->ev_chunk[4 * c + q]);
+        fprintf(stderr, "[mom6adv trace]   chunk %2d: uploaded %7.1f  compute %7.1f .. %7.1f  downloaded %7.1f ms\n", c, t[0], t[1], t[2], t[3]);
+      }
+    for (auto &ev : tr_ev) cudaEventDestroy(ev);
+  }
   return MOM6ADV_OK;
 }
 
@@ -1017,6 +1173,9 @@ extern "C" int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value
   if (!strcmp(key, "fused")) { plan->opt_fused = value; return MOM6ADV_OK; }
   if (!strcmp(key, "fast")) { plan->opt_fast = value; return MOM6ADV_OK; }
   if (!strcmp(key, "sparse")) { plan->opt_sparse = value; return MOM6ADV_OK; }
+  if (!strcmp(key, "mirror_chunk")) { plan->opt_chunk = value; return MOM6ADV_OK; }
+  if (!strcmp(key, "mirror_ahead")) { plan->opt_ahead = value; return MOM6ADV_OK; }
+  if (!strcmp(key, "trace")) { plan->opt_trace = value; return MOM6ADV_OK; }
   if (!strcmp(key, "profile")) {
     plan->opt_profile = value;
     for (int c = 0; c < MOM6ADV_KC_COUNT; c++) { plan->prof_ms[c] = 0.0; plan->prof_n[c] = 0; }

@@ -27,3 +27,4 @@ int main(){
   double z = -0.0; double q = mk(z,3.0,c3); printf("-0 -> %g signbit %d\n", q, signbit(q)!=0);
   return 0;
 }
+/* (the integer form used for |x| < 2^-1021 is checked by scripts/check_div6_int.c) */

@@ -161,3 +161,36 @@ def test_residual_iterations_dense_and_sparse(scheme, sparse, x_first):
     c, Ro, Rg, outs, nit = _run_pair(90, 41, 3, 6, scheme, cfl=1.6, x_first=x_first, sparse=sparse)
     assert nit >= 3
     _assert_bitwise(c, Ro, Rg, outs)
+
+
+@pytest.mark.parametrize("max_iter", [1, 2, None])
+@pytest.mark.parametrize("ntr", [3, 9])
+def test_offline_arguments_bitwise(max_iter, ntr):
+    """vol_prev / max_iter_in / update_vol_prev / uhr_out (offline tracer mode, :84-86,165-171,316-320).
+    ntr = 9 is three pipeline chunks of the MIRROR call: vol_prev must be written back exactly once."""
+    c = synth.make_case(70, 45, 3, ntr, cfl=1.5)
+    G, nk = c.G, c.GV.ke
+    params = {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": "PPM"}
+    h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
+    rng = np.random.default_rng(5)
+    vol0 = np.zeros(G.shape_h(nk))
+    G.interior(vol0)[...] = G.interior(G.areaT) * G.interior(h) * rng.uniform(0.8, 1.2, G.interior(h).shape)
+    res = []
+    for impl in (oracle.advect_tracer, advect_tracer):
+        CS = tracer_advect_init(None, G, None, params, None, None)
+        R = synth.bind_registry(c)
+        vol = vol0.copy()
+        uo, vo = np.zeros(G.shape_u(nk)), np.zeros(G.shape_v(nk))
+        uu, vv = u, v
+        nits = []
+        for call in range(2):      # second call continues from the residuals of the first, as the offline driver does
+            nits.append(impl(h, uu, vv, None, c.dt, G, c.GV, None, CS, R, x_first_in=(call == 0), vol_prev=vol,
+                             max_iter_in=max_iter, update_vol_prev=True, uhr_out=uo, vhr_out=vo))
+            uu, vv = uo.copy(), vo.copy()
+        if impl is advect_tracer:
+            tracer_advect_end(CS)
+        res.append((R, vol, uo, vo, nits))
+    (Ro, vol_o, uo_o, vo_o, n_o), (Rg, vol_g, uo_g, vo_g, n_g) = res
+    assert n_o == n_g
+    _assert_bitwise(c, Ro, Rg, (uo_o, vo_o, uo_g, vo_g))
+    assert np.array_equal(G.interior(vol_o).view(np.uint64), G.interior(vol_g).view(np.uint64))
