@@ -194,3 +194,11 @@ def test_offline_arguments_bitwise(max_iter, ntr):
     assert n_o == n_g
     _assert_bitwise(c, Ro, Rg, (uo_o, vo_o, uo_g, vo_g))
     assert np.array_equal(G.interior(vol_o).view(np.uint64), G.interior(vol_g).view(np.uint64))
+
+
+@pytest.mark.parametrize("scheme", ["PLM", "PPM", "PPM:H3"])
+@pytest.mark.parametrize("x_first", [True, False])
+def test_hundred_consecutive_calls_bitwise(scheme, x_first):
+    """double-gyre shape, 10 tracers, 100 consecutive calls, bitwise."""
+    c, Ro, Rg, outs, nit = _run_pair(44, 40, 2, 10, scheme, cfl=0.45, x_first=x_first, ncalls=100)
+    _assert_bitwise(c, Ro, Rg, outs)
