@@ -4,31 +4,37 @@
 // ---------------------------------------------------------------------------
 // y sweep: register pipeline marching north, fed by a shared-memory row ring.
 //
-// CTA = 64 columns x YW tracers (one consumer warp per tracer, two columns per
-// lane) + one producer warp.  For every step r the producer issues 512-byte
-// bulk copies (cp.async.bulk -> UBLKCP) of tracer row r of each tracer and of
-// the six tracer-independent rows the step needs (uhh/0.5CFL/1-2/3CFL of face
-// r-2, hlst/Ihnew of cell r-3, mask product of cell r-1) into stage r % YNS,
-// completing on that stage's `full` mbarrier; consumers release the stage on
-// its `empty` mbarrier as soon as the values are in registers.  YNS rows are
-// in flight per CTA, so HBM latency is hidden without prefetch registers, and
-// the mass rows are fetched once per CTA instead of once per tracer.
+// CTA = 32 columns x 2*YW tracers (one consumer warp per PAIR of tracers, one
+// column per lane) + one producer warp.  For every step r the producer issues
+// 256-byte bulk copies (cp.async.bulk -> UBLKCP) of tracer row r of each tracer
+// and of the six tracer-independent rows the step needs (uhh/0.5CFL/1-2/3CFL of
+// face r-2, hlst/Ihnew of cell r-3, mask product of cell r-1) into stage
+// r % YNS, completing on that stage's `full` mbarrier; consumers release the
+// stage on its `empty` mbarrier as soon as the values are in registers.  YNS
+// rows are in flight per CTA, so HBM latency is hidden without prefetch
+// registers; the mass rows are fetched once per 14 tracers, and a thread holds
+// them once for its two tracers (fewer registers and selects than two columns
+// of one tracer).
 //
 // At step r a consumer thread finishes the slope of cell r-1, the edge between
 // cells r-2 and r-1, the parabola of cell r-2, the flux through face J = r-3
 // and the update of cell r-3 (written in place: rows <= r-3 are never read again).
 // ---------------------------------------------------------------------------
-#define YW 7            // tracers (consumer warps) per CTA: 7 + 1 producer warp = 256 threads
+#ifndef YW
+#define YW 7            // consumer warps per CTA: 7 + 1 producer warp = 256 threads
+#endif
+#define YTW 2           // tracers per consumer warp
+#define YT (YW * YTW)   // tracers per CTA
 #define YNS 8           // ring stages
-#define YCOLS 64        // columns per CTA
+#define YCOLS 32        // columns per CTA
 #define YROWB (YCOLS * 8)
 #ifndef YUNROLL
-#define YUNROLL 3
+#define YUNROLL 2
 #endif
 #define Y_PRAGMA_(x) _Pragma(#x)
 #define Y_UNROLL(n) Y_PRAGMA_(unroll n)
 
-struct __align__(16) YStage { double mass[6][YCOLS]; double T[YW][YCOLS]; };
+struct __align__(16) YStage { double mass[6][YCOLS]; double T[YT][YCOLS]; };
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
@@ -76,11 +82,12 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   if (domore_k[k0] <= 0) return;                                  // CTA-uniform
   const int cbase = YCOLS * blockIdx.x;
   if (cbase + YCOLS - 1 - g.coff < rg.is || cbase - g.coff > rg.ie) return;   // no column of the tile is swept
-  const int m0 = blockIdx.y * YW;
-  const int nact = min(YW, tt.n - m0);
+  const int m0 = blockIdx.y * YT;
+  const int nact = min(YT, tt.n - m0);                            // tracers of this CTA
+  const int nwarp = (nact + YTW - 1) / YTW;                       // consumer warps with work
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < YNS; s++) { mbar_init(smem_u32(&bar_full[s]), 1); mbar_init(smem_u32(&bar_empty[s]), nact); }
+    for (int s = 0; s < YNS; s++) { mbar_init(smem_u32(&bar_full[s]), 1); mbar_init(smem_u32(&bar_empty[s]), nwarp); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -115,15 +122,18 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
     }
     return;
   }
-  if (w >= nact) return;
+  if (w >= nwarp) return;
 
-  // ---- consumer warp: tracer m0+w, columns cbase + 2*lane, +1 ----
-  const int m = m0 + w;
-  const int c = cbase + 2 * lane;
-  const int i0 = c - g.coff;
-  const bool inr[2] = {i0 >= rg.is && i0 <= rg.ie, i0 + 1 >= rg.is && i0 + 1 <= rg.ie};
-  double *__restrict__ Tt = tt.dst[m] + lev + 2 * lane;     // in place; + P*row
-  const double cu = tt.cu[m];
+  // ---- consumer warp: tracers m0+2w and m0+2w+1 (n = 0, 1), column cbase + lane ----
+  const int t0 = YTW * w;
+  const bool two = (t0 + 1 < nact);                          // the warp's second tracer exists
+  const int ts[2] = {t0, two ? t0 + 1 : t0};                 // (a lone tracer is computed twice, stored once)
+  const int i0 = cbase + lane - g.coff;
+  const bool inr = (i0 >= rg.is && i0 <= rg.ie);
+  double *__restrict__ Tt0 = tt.dst[m0 + ts[0]] + lev + lane;     // in place; + P*row
+  double *__restrict__ Tt1 = tt.dst[m0 + ts[1]] + lev + lane;
+  const double cu[2] = {tt.cu[m0 + ts[0]], tt.cu[m0 + ts[1]]};
+  const bool do_cu[2] = {cu[0] > 0.0 && inr, cu[1] > 0.0 && inr};
   const int *__restrict__ ent = entry + k0 * g.R;
   const int rf_lo = rg.js - 1 + g.roff, rf_hi = rg.je + g.roff;         // face rows of the sweep
   const int rc_lo = rg.js + g.roff;                                     // first cell row to update
@@ -133,34 +143,26 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   double s2[2] = {0, 0}, e3[2] = {0, 0}, pp2[2] = {0, 0};  // slope, south edge, limiter product of cell r-2
   double Fn3[2] = {0, 0};                                  // north outflow of cell r-3 (through face r-3)
   double flp[2] = {0, 0};                                  // flux through face r-4
-  double hh3[2] = {0, 0}, hc3[2] = {0, 0}, gq3[2] = {0, 0};   // factors of face J = r-3
+  double hh3 = 0, hc3 = 0, gq3 = 0;                        // factors of face J = r-3 (shared by both tracers)
   bool act3 = false;                                       // face J = r-3 is part of the sweep
-  const bool do_cu = (cu > 0.0);
   Y_UNROLL(YUNROLL)
   for (int it = 0; it < nsteps; it++) {
     const int r = r_lo + it, s = it % YNS;
     mbar_wait(smem_u32(&bar_full[s]), (it / YNS) & 1);
     const YStage &q = stg[s];
-    const double2 tn = *reinterpret_cast<const double2 *>(&q.T[w][2 * lane]);
-    const double2 qhh = *reinterpret_cast<const double2 *>(&q.mass[0][2 * lane]);
-    const double2 qhc = *reinterpret_cast<const double2 *>(&q.mass[1][2 * lane]);
-    const double2 qgq = *reinterpret_cast<const double2 *>(&q.mass[2][2 * lane]);
-    const double2 qhl = *reinterpret_cast<const double2 *>(&q.mass[3][2 * lane]);
-    const double2 qih = *reinterpret_cast<const double2 *>(&q.mass[4][2 * lane]);
-    const double2 qmm = *reinterpret_cast<const double2 *>(&q.mass[5][2 * lane]);
+    const double Tn[2] = {q.T[ts[0]][lane], q.T[ts[1]][lane]};
+    const double hh2 = q.mass[0][lane], hc2 = q.mass[1][lane], gq2 = q.mass[2][lane];
+    const double hl = q.mass[3][lane], ih = q.mass[4][lane], mm1 = q.mass[5][lane];
     __syncwarp();
     if (lane == 0) mbar_arrive(smem_u32(&bar_empty[s]));      // the stage may be refilled
     const bool act2 = (r - 2 >= rf_lo && r - 2 <= rf_hi) && ent[r - 2];
     const bool out_row = (r - 3 >= rc_lo);
-    const double Tn[2] = {tn.x, tn.y};
-    const double hh2[2] = {qhh.x, qhh.y}, hc2[2] = {qhc.x, qhc.y}, gq2[2] = {qgq.x, qgq.y};
-    const double hl[2] = {qhl.x, qhl.y}, ih[2] = {qih.x, qih.y}, mm1[2] = {qmm.x, qmm.y};
     double a0[2], A20[2], s1[2] = {0, 0};
 #pragma unroll
     for (int n = 0; n < 2; n++) {
       a0[n] = Tn[n] - T1[n];                               // face r-1|r
       A20[n] = 2.0 * fabs(a0[n]);
-      if (SCHEME != SCHEME_PPM_H3) s1[n] = slope_f(a0[n], a1[n], A20[n], A21[n], Tn[n] - T2[n], mm1[n]);    // cell r-1
+      if (SCHEME != SCHEME_PPM_H3) s1[n] = slope_f(a0[n], a1[n], A20[n], A21[n], Tn[n] - T2[n], mm1);    // cell r-1
     }
     // parabola of cell r-2: xL/xR = edge values, dA, a6  (PLM: xL = xR = T, dA = 0.5*slope, a6 unused)
     double xL[2], xR[2], dA[2], a6[2] = {0, 0};
@@ -189,40 +191,45 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
 #pragma unroll
       for (int n = 0; n < 2; n++) { a6[n] = ppm_a6(T2[n], S[n]); e3[n] = e2[n]; }
     }
+    // cell r-2 feeds its north face r-2 when hh2 >= 0 (kept for the next step) and its south face r-3 when hh3 < 0
+    const bool south = (hh3 < 0.0);                        // same for both tracers
+    const bool do_i = (__double_as_longlong(ih) != 0LL);   // Ihnew > 0 (it is never negative)
     double o[2];
 #pragma unroll
     for (int n = 0; n < 2; n++) {
-      // cell r-2 feeds its north face r-2 when hh2 >= 0 (kept for the next step) and its south face r-3 when hh3 < 0
       double Fn2, Fs2 = 0.0;
       if (SCHEME == SCHEME_PLM) {      // hh*(T +- 0.5*slope*(1-CFL)), gq = 1-CFL (:946-961)
-        Fn2 = hh2[n] * (xR[n] + dA[n] * gq2[n]);
-        if (hh3[n] < 0.0) Fs2 = hh3[n] * (xL[n] - dA[n] * gq3[n]);
+        Fn2 = hh2 * (xR[n] + dA[n] * gq2);
+        if (south) Fs2 = hh3 * (xL[n] - dA[n] * gq3);
       } else {
-        Fn2 = out_hi(hh2[n], hc2[n], gq2[n], xR[n], dA[n], a6[n]);
-        if (hh3[n] < 0.0) Fs2 = out_lo(hh3[n], hc3[n], gq3[n], xL[n], dA[n], a6[n]);
+        Fn2 = out_hi(hh2, hc2, gq2, xR[n], dA[n], a6[n]);
+        if (south) Fs2 = out_lo(hh3, hc3, gq3, xL[n], dA[n], a6[n]);
       }
       // flux through face J = r-3 (between cells r-3 and r-2); +0 on rows that are not swept (:1016-1018)
-      const double f = (hh3[n] >= 0.0) ? Fn3[n] : Fs2;
+      const double f = south ? Fs2 : Fn3[n];
       const double fl3 = act3 ? f : 0.0;
-      const double upd = (T3[n] * hl[n] - (fl3 - flp[n])) * ih[n];
-      o[n] = (__double_as_longlong(ih[n]) != 0LL) ? upd : T3[n];             // do_i: Ihnew > 0 (it is never negative)
-      if (do_cu && inr[n]) o[n] = underflow(o[n], cu);
+      const double upd = (T3[n] * hl - (fl3 - flp[n])) * ih;
+      o[n] = do_i ? upd : T3[n];
+      if (do_cu[n]) o[n] = underflow(o[n], cu[n]);
       flp[n] = fl3;
       Fn3[n] = Fn2;
-      pp2[n] = mm1[n] * a0[n] * a1[n];                     // cell r-1: mask*(Tp-Tc)*(Tc-Tm)
+      pp2[n] = mm1 * a0[n] * a1[n];                        // cell r-1: mask*(Tp-Tc)*(Tc-Tm)
       T3[n] = T2[n]; T2[n] = T1[n]; T1[n] = Tn[n];
       a1[n] = a0[n]; A21[n] = A20[n]; s2[n] = s1[n];
-      hh3[n] = hh2[n]; hc3[n] = hc2[n]; gq3[n] = gq2[n];
     }
+    hh3 = hh2; hc3 = hc2; gq3 = gq2;
     act3 = act2;
-    if (out_row) *reinterpret_cast<double2 *>(Tt + (long long)P * (r - 3)) = make_double2(o[0], o[1]);
+    if (out_row) {
+      Tt0[(long long)P * (r - 3)] = o[0];
+      if (two) Tt1[(long long)P * (r - 3)] = o[1];
+    }
   }
 }
 
 void launch_y_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
                    const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm,
                    const int *entry, const int *domore_k) {
-  dim3 grid(g.P / YCOLS, (tt.n + YW - 1) / YW, g.nk), block(32 * (YW + 1));
+  dim3 grid(g.P / YCOLS, (tt.n + YT - 1) / YT, g.nk), block(32 * (YW + 1));
   const size_t smem = sizeof(YStage) * YNS;
 #define YLAUNCH(S)                                                                                        \
   do {                                                                                                    \
