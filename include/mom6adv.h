@@ -104,8 +104,10 @@ int mom6adv_comm_init(mom6adv_plan *plan, const char *id128, const int *ibeg, co
                       const int *jbeg, const int *jend);
 /* Host-only view of the exchange plan of rank (dom->pi, dom->pj) (tests; needs
  * no device).  what: 0 self dst, 1 self src, 2 self sign, 3 send src to `peer`,
- * 4 send sign to `peer`, 5 recv dst from `peer`; indices are offsets into one
- * padded plane.  Returns the list length (fills at most cap entries); geom
+ * 4 send sign to `peer`, 5 recv dst from `peer`, 6 / 7 the index of those same
+ * points in `peer`'s own padded plane and their sign (the peer-pull form of the
+ * exchange: each halo value is loaded straight from the owner's field through a
+ * CUDA IPC mapping); indices are offsets into one padded plane.  Returns the list length (fills at most cap entries); geom
  * (nullable) receives P, R, coff, roff of the padded plane. */
 int mom6adv_exchange_list(const mom6adv_grid *g, const mom6adv_domain *dom, const int *ibeg, const int *iend,
                           const int *jbeg, const int *jend, int peer, int pos, int what, int *out, int cap,
@@ -164,14 +166,19 @@ long long mom6adv_device_bytes(const mom6adv_plan *plan);
  * "mirror_chunk" n -- tracers per pipeline stage of mom6adv_advect (default 4,
  * 0 = one stage: upload everything, compute, download everything);
  * "mirror_ahead" n -- uploads queued n chunks in front of the compute (default 2); "trace" 0/1
- * -- mom6adv_advect prints its copy-stream and compute times to stderr. */
+ * -- mom6adv_advect prints its copy-stream and compute times to stderr;
+ * "pull" 0/1 -- multi-block plans: 1 (default) fills halos by loading the
+ * neighbour GPU's fields directly (CUDA IPC + NVLink), 0 packs and uses NCCL
+ * send/recv; choose before the first advect call. */
 int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value);
 /* Kernel classes of the per-class timers: the stand-ins for the reference's
  * (Ocean advect tracer) / (Ocean tracer halo updates) / (Ocean tracer global
  * synch) clock triple (:1146-1148), resolved per kernel family. */
 enum { MOM6ADV_KC_PROLOGUE = 0, MOM6ADV_KC_HALO = 1, MOM6ADV_KC_FLAGS = 2, MOM6ADV_KC_MASS = 3,
        MOM6ADV_KC_TRACER_X = 4, MOM6ADV_KC_TRACER_Y = 5, MOM6ADV_KC_OTHER = 6, MOM6ADV_KC_SPARSE = 7,
-       MOM6ADV_KC_COUNT = 8 };
+       /* parts of HALO on a multi-block plan (already counted in HALO): */
+       MOM6ADV_KC_EXCH_PACK = 8, MOM6ADV_KC_EXCH_WIRE = 9, MOM6ADV_KC_EXCH_UNPACK = 10,
+       MOM6ADV_KC_COUNT = 11 };
 /* Accumulated device time [ms] and number of timed brackets of one class
  * since "profile" was last set. */
 int mom6adv_kernel_class_time(const mom6adv_plan *plan, int kclass, double *ms_total, long long *n);

@@ -18,7 +18,8 @@ LIB_PATH = os.path.join(_HERE, "libmom6adv_b200.so")
 
 OK, ERR_NOT_INIT, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_COMM = range(6)
 F_H_END, F_UHTR, F_VHTR, F_VOL_PREV, F_UHR, F_VHR, F_HPREV = range(7)
-KC_NAMES = ("prologue", "halo", "flags", "mass", "tracer_x", "tracer_y", "other", "sparse")
+KC_NAMES = ("prologue", "halo", "flags", "mass", "tracer_x", "tracer_y", "other", "sparse",
+            "exch_pack", "exch_wire", "exch_unpack")
 DIAG_KINDS = ("ad_x", "ad_y", "ad2d_x", "ad2d_y", "advection_xy")
 
 _dp = C.POINTER(C.c_double)

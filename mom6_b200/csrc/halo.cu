@@ -76,6 +76,16 @@ void build_halo_exchange(const Geom &g, const ExchangeSpec &x, int me, HaloBuild
     return peers[slot[r]];
   };
   auto pidx = [&](int i, int j) { return (i + g.coff) + g.P * (j + g.roff); };
+  // padded layouts of the other ranks (make_geom is a pure function of the index bounds)
+  std::vector<Geom> pg(nr);
+  for (int r = 0; r < nr; r++) {
+    mom6adv_grid gr = {};
+    gr.isc = geo[r].isc; gr.iec = geo[r].iec; gr.jsc = geo[r].jsc; gr.jec = geo[r].jec;
+    gr.isd = geo[r].isd; gr.ied = geo[r].ied; gr.jsd = geo[r].jsd; gr.jed = geo[r].jed;
+    gr.IsdB = geo[r].IsdB; gr.IedB = geo[r].ied; gr.JsdB = geo[r].JsdB; gr.JedB = geo[r].jed; gr.nk = g.nk;
+    int wb;
+    make_geom(&gr, pg[r], wb);
+  }
   for (int d = 0; d < nr; d++) {            // receiver
     const RankGeo &G = geo[d];
     for (int pos = 0; pos < 3; pos++) {
@@ -90,7 +100,12 @@ void build_halo_exchange(const Geom &g, const ExchangeSpec &x, int me, HaloBuild
           local[pos].dst.push_back(pidx(i, j)); local[pos].src.push_back(pidx(s.i, s.j));
           local[pos].sgn.push_back((signed char)s.sgn);
         } else if (d == me) {
-          peer(s.rank).recv_dst[pos].push_back(pidx(i, j));
+          PeerBuild &p = peer(s.rank);
+          p.recv_dst[pos].push_back(pidx(i, j));
+          const Geom &q = pg[s.rank];
+          p.recv_src[pos].push_back((s.i + q.coff) + q.P * (s.j + q.roff));
+          p.recv_sgn[pos].push_back((signed char)s.sgn);
+          p.peer_plane = q.plane;
         } else if (s.rank == me) {
           PeerBuild &p = peer(d);
           p.send_src[pos].push_back(pidx(s.i, s.j)); p.send_sgn[pos].push_back((signed char)s.sgn);

@@ -503,6 +503,23 @@ __global__ void k_halo_unpack(long long plane, int nk, const int *__restrict__ d
   const int k0 = blockIdx.y, f = blockIdx.z;
   fields[f][plane * k0 + dstv[t]] = buf[((long long)f * nk + k0) * n + t];
 }
+// Peer-pull form of pack + send + recv + unpack: every halo point is loaded straight from the owner's
+// field in the neighbouring GPU's HBM (CUDA IPC mapping, NVLink load) and stored in place.
+__global__ void k_halo_pull(long long plane, long long peer_plane, int nk, const int *__restrict__ dstv,
+                            const int *__restrict__ srcv, const signed char *__restrict__ sgn, int n,
+                            double *const *__restrict__ fields, double *const *__restrict__ peer_fields) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  const int k0 = blockIdx.y, f = blockIdx.z;
+  const double v = __ldcv(peer_fields[f] + peer_plane * k0 + srcv[t]);
+  fields[f][plane * k0 + dstv[t]] = (sgn[t] < 0) ? -v : v;
+}
+void launch_halo_pull(cudaStream_t s, long long plane, long long peer_plane, int nk, const int *dst, const int *src,
+                      const signed char *sgn, int n, double *const *fields, double *const *peer_fields, int nfields) {
+  if (n <= 0 || nfields <= 0) return;
+  dim3 grid((n + TPB - 1) / TPB, nk, nfields);
+  k_halo_pull<<<grid, TPB, 0, s>>>(plane, peer_plane, nk, dst, src, sgn, n, fields, peer_fields);
+}
 void launch_halo_pack(cudaStream_t s, long long plane, int nk, const int *src, const signed char *sgn, int n,
                       double *const *fields, int nfields, double *buf) {
   if (n <= 0 || nfields <= 0) return;

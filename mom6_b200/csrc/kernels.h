@@ -1,5 +1,6 @@
 // Host-callable launch wrappers of kernels.cu (internal).
 #pragma once
+#include "../../include/mom6adv.h"
 #include "internal.cuh"
 
 void launch_repack_in(cudaStream_t s, const Geom &g, double *dst, const double *src, int ilo, int jlo, int nlev);
@@ -32,6 +33,8 @@ void launch_halo_apply(cudaStream_t s, long long plane, int nk, const int *dst, 
                        const signed char *sgn, int n, double *const *fields, int nfields);
 void launch_halo_pack(cudaStream_t s, long long plane, int nk, const int *src, const signed char *sgn, int n,
                       double *const *fields, int nfields, double *buf);
+void launch_halo_pull(cudaStream_t s, long long plane, long long peer_plane, int nk, const int *dst, const int *src,
+                      const signed char *sgn, int n, double *const *fields, double *const *peer_fields, int nfields);
 void launch_halo_unpack(cudaStream_t s, long long plane, int nk, const int *dst, int n,
                         double *const *fields, int nfields, const double *buf);
 void launch_fill(cudaStream_t s, double *p, long long n, double v);
@@ -64,5 +67,10 @@ struct PeerBuild {
   int rank = -1;
   std::vector<int> send_src[3], recv_dst[3];      // per stagger: 0 h, 1 u, 2 v
   std::vector<signed char> send_sgn[3];
+  // peer-pull form of the same exchange: where each received point lives in the SENDER's padded layout
+  std::vector<int> recv_src[3];
+  std::vector<signed char> recv_sgn[3];
+  long long peer_plane = 0;                       // the sender's plane size (its level stride)
 };
+void make_geom(const mom6adv_grid *gr, Geom &g, int &wbase);
 void build_halo_exchange(const Geom &g, const ExchangeSpec &x, int me, HaloBuild local[3], std::vector<PeerBuild> &peers);

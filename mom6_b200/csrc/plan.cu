@@ -39,6 +39,12 @@ struct PeerLists {        // one neighbour rank of the multi-GPU group pass
   signed char *send_sgn[3] = {nullptr, nullptr, nullptr};
   double *sendbuf = nullptr, *recvbuf = nullptr;
   long long send_elems = 0, recv_elems = 0;
+  // peer-pull exchange: source indices in the neighbour's layout and its fields mapped through CUDA IPC
+  int *recv_src[3] = {nullptr, nullptr, nullptr};
+  signed char *recv_sgn[3] = {nullptr, nullptr, nullptr};
+  long long peer_plane = 0;
+  std::vector<void *> mapped;        // cudaIpcOpenMemHandle results, slot order [uhr, vhr, hprev, buf0 x ntr, buf1 x ntr]
+  double **fields_dev = nullptr;     // two tables like halo_fields_dev, of the neighbour's pointers
 };
 
 #define MIRROR_CHUNK_DEFAULT 2
@@ -91,6 +97,9 @@ struct mom6adv_plan {
   long long halo_bytes_sent = 0;
   int opt_chunk = MIRROR_CHUNK_DEFAULT;  // tracers per pipeline stage of the MIRROR call
   int opt_ahead = 2;                 // chunks whose upload is queued in front of the running one
+  int opt_pull = 1;                  // multi-GPU group pass by peer-memory loads (0: pack -> NCCL send/recv -> unpack)
+  int ipc_ntr = -1;                  // registry size the IPC mappings were made for
+  int *bar_dev = nullptr;            // scratch word of the neighbour barrier
   int opt_trace = 0;                 // print the MIRROR pipeline's copy/compute times to stderr
   int opt_sparse = 1;                // list-driven tracer update on residual iterations (sparse.cu)
   int *sp_list = nullptr; double *sp_new = nullptr; int sp_cap = 0, sp_ntr = 0;
@@ -100,8 +109,8 @@ struct mom6adv_plan {
   int opt_profile = 0;
   std::vector<cudaEvent_t> prof_ev;      // pairs: [2n] start, [2n+1] stop
   std::vector<int> prof_cls;             // class of pair n (pairs used in the current call)
-  double prof_ms[MOM6ADV_KC_COUNT] = {0, 0, 0, 0, 0, 0, 0};
-  long long prof_n[MOM6ADV_KC_COUNT] = {0, 0, 0, 0, 0, 0, 0};
+  double prof_ms[MOM6ADV_KC_COUNT] = {};
+  long long prof_n[MOM6ADV_KC_COUNT] = {};
 };
 
 // RAII bracket: records an event pair around the launches of one kernel class.
@@ -127,7 +136,7 @@ static void prof_collect(mom6adv_plan *p) {   // call after the stream is synchr
 }
 
 static thread_local std::string g_err;
-static void make_geom(const mom6adv_grid *gr, Geom &g, int &wbase);
+static void teardown_ipc(mom6adv_plan *plan, bool collective);
 
 #define CK(call)                                                                            \
   do {                                                                                      \
@@ -370,7 +379,10 @@ extern "C" int mom6adv_comm_init(mom6adv_plan *plan, const char *id128, const in
       if ((rc = upload_vec(plan, b.send_src[pos], &pl.send_src[pos]))) return rc;
       if ((rc = upload_vec(plan, b.send_sgn[pos], &pl.send_sgn[pos]))) return rc;
       if ((rc = upload_vec(plan, b.recv_dst[pos], &pl.recv_dst[pos]))) return rc;
+      if ((rc = upload_vec(plan, b.recv_src[pos], &pl.recv_src[pos]))) return rc;
+      if ((rc = upload_vec(plan, b.recv_sgn[pos], &pl.recv_sgn[pos]))) return rc;
     }
+    pl.peer_plane = b.peer_plane;
     plan->peers.push_back(pl);
   }
   if (id128 && plan->nranks > 1) {
@@ -382,7 +394,8 @@ extern "C" int mom6adv_comm_init(mom6adv_plan *plan, const char *id128, const in
 }
 
 // Host-side view of the exchange plan (tests; no device work).  what: 0 local dst, 1 local src, 2 local sign,
-// 3 send src to `peer`, 4 send sign to `peer`, 5 recv dst from `peer`.  Returns the count (<0: error);
+// 3 send src to `peer`, 4 send sign to `peer`, 5 recv dst from `peer`, 6 / 7 the same points' index in `peer`'s own
+// padded layout and their sign (peer-pull form).  Returns the count (<0: error);
 // fills at most cap entries.  geom (nullable) receives P, R, coff, roff of the padded layout.
 extern "C" int mom6adv_exchange_list(const mom6adv_grid *gr, const mom6adv_domain *dom, const int *ibeg,
                                      const int *iend, const int *jbeg, const int *jend, int peer, int pos, int what,
@@ -405,6 +418,8 @@ extern "C" int mom6adv_exchange_list(const mom6adv_grid *gr, const mom6adv_domai
       if (what == 3) v = b.send_src[pos];
       else if (what == 4) v.assign(b.send_sgn[pos].begin(), b.send_sgn[pos].end());
       else if (what == 5) v = b.recv_dst[pos];
+      else if (what == 6) v = b.recv_src[pos];
+      else if (what == 7) v.assign(b.recv_sgn[pos].begin(), b.recv_sgn[pos].end());
     }
   }
   for (int n = 0; n < (int)v.size() && n < cap; n++) out[n] = v[n];
@@ -412,7 +427,7 @@ extern "C" int mom6adv_exchange_list(const mom6adv_grid *gr, const mom6adv_domai
 }
 
 // Padded HBM layout of one plane (internal.cuh) from the Fortran index bounds.
-static void make_geom(const mom6adv_grid *gr, Geom &g, int &wbase) {
+void make_geom(const mom6adv_grid *gr, Geom &g, int &wbase) {
   const int hi = gr->isc - gr->isd;
   g.isd = gr->isd; g.ied = gr->ied; g.jsd = gr->jsd; g.jed = gr->jed;
   g.isc = gr->isc; g.iec = gr->iec; g.jsc = gr->jsc; g.jec = gr->jec;
@@ -487,6 +502,8 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   if (!plan) return MOM6ADV_OK;
   cudaSetDevice(plan->device);
   if (plan->stream) cudaStreamSynchronize(plan->stream);
+  teardown_ipc(plan, true);
+  if (plan->bar_dev) cudaFree(plan->bar_dev);
   double *d[] = {plan->areaT, plan->IareaT, plan->mCu, plan->mCv, plan->uh_neglect, plan->vh_neglect, plan->mmx,
                  plan->mmy, plan->h_end, plan->uhtr, plan->vhtr, plan->vol_prev, plan->uhr, plan->vhr, plan->hprev,
                  plan->hh, plan->cfl, plan->hlst, plan->ihnew, plan->hc, plan->gq, plan->staging};
@@ -495,7 +512,7 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   for (int *p : f) if (p) cudaFree(p);
   if (plan->sum_host) cudaFreeHost(plan->sum_host);
   for (PeerLists &p : plan->peers) {
-    for (int pos = 0; pos < 3; pos++) { if (p.send_src[pos]) cudaFree(p.send_src[pos]); if (p.send_sgn[pos]) cudaFree(p.send_sgn[pos]); if (p.recv_dst[pos]) cudaFree(p.recv_dst[pos]); }
+    for (int pos = 0; pos < 3; pos++) { if (p.send_src[pos]) cudaFree(p.send_src[pos]); if (p.send_sgn[pos]) cudaFree(p.send_sgn[pos]); if (p.recv_dst[pos]) cudaFree(p.recv_dst[pos]); if (p.recv_src[pos]) cudaFree(p.recv_src[pos]); if (p.recv_sgn[pos]) cudaFree(p.recv_sgn[pos]); }
     if (p.sendbuf) cudaFree(p.sendbuf);
     if (p.recvbuf) cudaFree(p.recvbuf);
   }
@@ -568,6 +585,7 @@ static int sync_tracer_table(mom6adv_plan *plan) {
     h[m].ad_x = s.diag[0]; h[m].ad_y = s.diag[1]; h[m].ad2d_x = s.diag[2]; h[m].ad2d_y = s.diag[3]; h[m].adv_xy = s.diag[4];
     h[m].conc_underflow = s.conc_underflow;
   }
+  if (plan->ipc_ntr >= 0) plan->ipc_ntr = -2;          // buffers may have moved: map again
   if (plan->tr_dev) { cudaFree(plan->tr_dev); plan->tr_dev = nullptr; }
   CK(cudaMalloc((void **)&plan->tr_dev, sizeof(TracerDev) * h.size()));
   CK(cudaMemcpyAsync(plan->tr_dev, h.data(), sizeof(TracerDev) * h.size(), cudaMemcpyHostToDevice, plan->stream));
@@ -589,7 +607,89 @@ static int sync_tracer_table(mom6adv_plan *plan) {
 // ---------------------------------------------------------------------------
 // do_group_pass (:206) on one device.
 // ---------------------------------------------------------------------------
-static int group_pass(mom6adv_plan *plan) {
+// ---------------------------------------------------------------------------
+// Peer-pull exchange.  Every rank exports its exchanged buffers (uhr, vhr, hprev, both buffers of every
+// tracer) as CUDA IPC handles, the handles travel in one ncclAllGather, and each rank maps its neighbours'
+// buffers.  A group pass is then a gather kernel per neighbour that loads the owner's values over NVLink
+// and stores them into the local halo -- no pack buffer, no send/recv, no unpack -- fenced by two
+// one-word all-reduces (data ready / done reading).  Falls back to the NCCL send/recv path on all ranks
+// together if any mapping fails.
+// ---------------------------------------------------------------------------
+static int exch_barrier(mom6adv_plan *plan) {
+  CKN(ncclAllReduce(plan->bar_dev, plan->bar_dev, 1, ncclInt, ncclMax, plan->comm, plan->stream));
+  return 0;
+}
+
+static void teardown_ipc(mom6adv_plan *plan, bool collective) {
+  bool any = false;
+  for (PeerLists &p : plan->peers) {
+    for (void *q : p.mapped) if (q) { cudaIpcCloseMemHandle(q); any = true; }
+    p.mapped.clear();
+    if (p.fields_dev) { cudaFree(p.fields_dev); p.fields_dev = nullptr; }
+  }
+  // nobody may free a buffer a neighbour still has mapped
+  if (any && collective && plan->comm && plan->bar_dev) {
+    ncclAllReduce(plan->bar_dev, plan->bar_dev, 1, ncclInt, ncclMax, plan->comm, plan->stream);
+    cudaStreamSynchronize(plan->stream);
+  }
+  plan->ipc_ntr = -1;
+}
+
+static int setup_ipc(mom6adv_plan *plan) {
+  if (!plan->multi || plan->peers.empty() || !plan->comm || !plan->opt_pull) return 0;
+  if (plan->ipc_ntr == plan->ntr) return 0;
+  cudaStream_t s = plan->stream;
+  if (!plan->bar_dev) { int rc = dev_alloc(plan, &plan->bar_dev, 4); if (rc) return rc; }
+  teardown_ipc(plan, true);
+  const int ntr = plan->ntr, nslot = 3 + 2 * ntr, nr = plan->nranks;
+  std::vector<cudaIpcMemHandle_t> mine(nslot), all((size_t)nslot * nr);
+  std::vector<double *> slot(nslot);
+  slot[0] = plan->uhr; slot[1] = plan->vhr; slot[2] = plan->hprev;
+  for (int m = 0; m < ntr; m++) { slot[3 + m] = plan->tr[m].buf[0]; slot[3 + ntr + m] = plan->tr[m].buf[1]; }
+  int ok = 1;
+  for (int q = 0; q < nslot; q++)
+    if (!slot[q] || cudaIpcGetMemHandle(&mine[q], slot[q]) != cudaSuccess) { cudaGetLastError(); ok = 0; memset(&mine[q], 0, sizeof mine[q]); }
+  unsigned char *d_mine = nullptr, *d_all = nullptr;
+  const size_t hb = sizeof(cudaIpcMemHandle_t) * nslot;
+  CK(cudaMalloc((void **)&d_mine, hb)); CK(cudaMalloc((void **)&d_all, hb * nr));
+  CK(cudaMemcpyAsync(d_mine, mine.data(), hb, cudaMemcpyHostToDevice, s));
+  CKN(ncclAllGather(d_mine, d_all, hb, ncclChar, plan->comm, s));
+  CK(cudaMemcpyAsync(all.data(), d_all, hb * nr, cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  cudaFree(d_mine); cudaFree(d_all);
+  for (PeerLists &p : plan->peers) {
+    p.mapped.assign(nslot, nullptr);
+    for (int q = 0; q < nslot && ok; q++)
+      if (cudaIpcOpenMemHandle(&p.mapped[q], all[(size_t)p.rank * nslot + q], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+        cudaGetLastError(); p.mapped[q] = nullptr; ok = 0;
+      }
+  }
+  // all ranks take the same path
+  CK(cudaMemcpyAsync(plan->bar_dev + 1, &ok, sizeof(int), cudaMemcpyHostToDevice, s));
+  CKN(ncclAllReduce(plan->bar_dev + 1, plan->bar_dev + 1, 1, ncclInt, ncclMin, plan->comm, s));
+  CK(cudaMemcpyAsync(&ok, plan->bar_dev + 1, sizeof(int), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  if (!ok) {
+    teardown_ipc(plan, true);
+    plan->opt_pull = 0;
+    if (plan->rank == 0) fprintf(stderr, "[mom6adv] CUDA IPC mapping of neighbour fields failed on some rank: group pass uses NCCL send/recv\n");
+    return 0;
+  }
+  const int nf = 3 + ntr;
+  for (PeerLists &p : plan->peers) {
+    std::vector<double *> hf(2 * nf);
+    for (int b = 0; b < 2; b++) {
+      hf[b * nf + 0] = (double *)p.mapped[0]; hf[b * nf + 1] = (double *)p.mapped[1]; hf[b * nf + 2] = (double *)p.mapped[2];
+      for (int m = 0; m < ntr; m++) hf[b * nf + 3 + m] = (double *)p.mapped[3 + b * ntr + m];
+    }
+    CK(cudaMalloc((void **)&p.fields_dev, sizeof(double *) * 2 * nf));
+    CK(cudaMemcpy(p.fields_dev, hf.data(), sizeof(double *) * 2 * nf, cudaMemcpyHostToDevice));
+  }
+  plan->ipc_ntr = ntr;
+  return 0;
+}
+
+static int group_pass(mom6adv_plan *plan, bool first_of_call) {
   const Geom &g = plan->g;
   cudaStream_t s = plan->stream;
   ProfScope ps(plan, MOM6ADV_KC_HALO);
@@ -606,7 +706,28 @@ static int group_pass(mom6adv_plan *plan) {
   }
   if (plan->multi && !plan->peers.empty()) {
     if (!plan->comm) return fail(plan, MOM6ADV_ERR_COMM, "advect: mom6adv_comm_init has not been called on this multi-block plan");
+    if (plan->opt_pull && plan->ipc_ntr == plan->ntr) {
+      // the neighbours' previous writes must be complete: at the first pass of a call a barrier says so, later
+      // passes follow the all-reduce of the convergence flags, which every rank enters after its sweeps
+      if (first_of_call) { int rc = exch_barrier(plan); if (rc) return rc; }
+      { ProfScope pw(plan, MOM6ADV_KC_EXCH_WIRE);
+      for (PeerLists &p : plan->peers) {
+        double **ptab = p.fields_dev + plan->cur * (3 + plan->ntr);
+        const Seg psegs[3][2] = {{{ptab + 2, 1}, {ptab + 3 + plan->m_lo, nact}}, {{ptab + 0, 1}, {nullptr, 0}}, {{ptab + 1, 1}, {nullptr, 0}}};
+        for (int pos = 0; pos < 3; pos++) for (int q = 0; q < 2; q++) if (segs[pos][q].n > 0) {
+          launch_halo_pull(s, g.plane, p.peer_plane, g.nk, p.recv_dst[pos], p.recv_src[pos], p.recv_sgn[pos], p.n_recv[pos],
+                           segs[pos][q].t, psegs[pos][q].t, segs[pos][q].n);
+          plan->launches++;
+        }
+        plan->halo_bytes_sent += 8LL * g.nk * ((long long)(1 + nact) * p.n_recv[0] + p.n_recv[1] + p.n_recv[2]);
+      }
+      }
+      CK(cudaGetLastError());
+      // nobody overwrites its rows before every neighbour has read them
+      return exch_barrier(plan);
+    }
     // (2) pack one message per neighbour: [h: hprev, tracers][u: uhr][v: vhr], each [field][level][point]
+    { ProfScope pp(plan, MOM6ADV_KC_EXCH_PACK);
     for (PeerLists &p : plan->peers) {
       long long off = 0;
       for (int pos = 0; pos < 3; pos++) for (const Seg &sg : segs[pos]) if (sg.n > 0) {
@@ -615,8 +736,10 @@ static int group_pass(mom6adv_plan *plan) {
         plan->launches++;
       }
     }
+    }
     CK(cudaGetLastError());
     // (3) device-resident exchange over NVLink
+    { ProfScope pw(plan, MOM6ADV_KC_EXCH_WIRE);
     CKN(ncclGroupStart());
     for (PeerLists &p : plan->peers) {
       const long long ns = (long long)g.nk * ((long long)(1 + nact) * p.n_send[0] + p.n_send[1] + p.n_send[2]);
@@ -626,7 +749,9 @@ static int group_pass(mom6adv_plan *plan) {
       plan->halo_bytes_sent += 8 * ns;
     }
     CKN(ncclGroupEnd());
+    }
     // (4) unpack
+    ProfScope pu(plan, MOM6ADV_KC_EXCH_UNPACK);
     for (PeerLists &p : plan->peers) {
       long long off = 0;
       for (int pos = 0; pos < 3; pos++) for (const Seg &sg : segs[pos]) if (sg.n > 0) {
@@ -643,6 +768,7 @@ static int group_pass(mom6adv_plan *plan) {
 // Exchange buffers are sized by ntr; (re)allocate when the registry changed.
 static int size_peer_buffers(mom6adv_plan *plan) {
   if (!plan->multi || plan->peer_ntr == plan->ntr) return 0;
+  if (plan->opt_pull && plan->ipc_ntr == plan->ntr) return 0;      // the pull path needs no message buffers
   const Geom &g = plan->g;
   for (PeerLists &p : plan->peers) {
     if (p.sendbuf) { cudaFree(p.sendbuf); p.sendbuf = nullptr; }
@@ -791,6 +917,7 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
   cudaStream_t s = plan->stream;
   CK(cudaSetDevice(plan->device));
   { int rc = sync_tracer_table(plan); if (rc) return rc; }
+  { int rc = setup_ipc(plan); if (rc) return rc; }
   { int rc = size_peer_buffers(plan); if (rc) return rc; }
   const int is = g.isc, ie = g.iec, js = g.jsc, je = g.jec;
   int stencil = 2;                                                          // :118
@@ -827,7 +954,7 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
   int itt;
   for (itt = 1; itt <= max_iter; itt++) {                                   // :203
     if (isv > is - stencil) {                                               // :205
-      { int rc = group_pass(plan); if (rc) return rc; }                     // :206
+      { int rc = group_pass(plan, itt == 1); if (rc) return rc; }           // :206
       const int nsten_halo = halo_min / stencil;                            // :208
       isv = is - nsten_halo * stencil; jsv = js - nsten_halo * stencil;     // :209
       iev = ie + nsten_halo * stencil; jev = je + nsten_halo * stencil;     // :210
@@ -1175,6 +1302,7 @@ extern "C" int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value
   if (!strcmp(key, "sparse")) { plan->opt_sparse = value; return MOM6ADV_OK; }
   if (!strcmp(key, "mirror_chunk")) { plan->opt_chunk = value; return MOM6ADV_OK; }
   if (!strcmp(key, "mirror_ahead")) { plan->opt_ahead = value; return MOM6ADV_OK; }
+  if (!strcmp(key, "pull")) { if (plan->ipc_ntr >= 0 && value != plan->opt_pull) return fail(plan, MOM6ADV_ERR_INVALID, "set_option: pull must be chosen before the first advect call"); plan->opt_pull = value; return MOM6ADV_OK; }
   if (!strcmp(key, "trace")) { plan->opt_trace = value; return MOM6ADV_OK; }
   if (!strcmp(key, "profile")) {
     plan->opt_profile = value;

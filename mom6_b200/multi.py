@@ -102,6 +102,7 @@ def bench_multi(args, name, world, rank, local_rank, peak, peak_src):
     G, h, u, v, cut = cut_local(c, layout, pe)
     CS = tracer_advect_init(None, G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}, None, None)
     plan = capi.Plan(G, c.GV, CS)
+    plan.set_option("pull", int(os.environ.get("MOM6ADV_PULL", "1")))     # 0: NCCL send/recv exchange (comparison runs)
     comm_init_plan(plan, G)
     plan.set_ntr(ntr)
     for m in range(ntr):
@@ -149,7 +150,7 @@ def bench_multi(args, name, world, rank, local_rank, peak, peak_src):
                "config": {"workload": name, "ni": ni, "nj": nj, "nk": nk, "ntr": ntr, "scheme": scheme, "halo": 4,
                           "cfl99": args.cfl, "iterations_per_call": nit, "layout": "%dx%d" % tuple(layout),
                           "l2": "inputs_exceed_l2 (%.1f GB resident per GPU)" % (plan.device_bytes / 1e9),
-                          "fma_contraction": "off", "halo_exchange": "GPU pack -> NCCL send/recv (NVLink) -> GPU unpack"},
+                          "fma_contraction": "off", "halo_exchange": ("peer-memory loads over NVLink (CUDA IPC), all-reduce fences" if int(os.environ.get("MOM6ADV_PULL", "1")) else "GPU pack -> NCCL send/recv (NVLink) -> GPU unpack")},
                "roofline": {"bound": "hbm", "kernel": "k_%s (rank 0 block)" % dom, "achieved": ach, "peak": peak,
                             "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
                             "avg_launch_ms": dom_avg, "alg_bytes_per_launch": alg_launch,

@@ -87,7 +87,7 @@ def _lists(G, GV, ext, nranks):
     for peer in range(nranks):
         per = []
         for pos in range(3):
-            per.append(tuple(capi.exchange_list(G, GV, ext, peer, pos, w)[0] for w in (3, 4, 5)))
+            per.append(tuple(capi.exchange_list(G, GV, ext, peer, pos, w)[0] for w in (3, 4, 5, 6, 7)))
         if any(len(x[0]) or len(x[2]) for x in per):
             L["peer"][peer] = per
     return L, geom
@@ -97,7 +97,7 @@ def _pack(L, peer, padded):
     """Message to `peer`: [h: hprev,t0,t1][u: uhr][v: vhr], each [field][level][point] (halo.cu / plan.cu order)."""
     parts = []
     for pos, fidx in ((0, (2, 3, 4)), (1, (0,)), (2, (1,))):
-        src, sgn, _ = L["peer"][peer][pos]
+        src, sgn = L["peer"][peer][pos][:2]
         for f in fidx:
             flat = padded[f].reshape(padded[f].shape[0], -1)
             parts.append((flat[:, src] * sgn[None, :]).ravel())
@@ -114,6 +114,15 @@ def _unpack(L, peer, padded, msg):
             flat[:, dst] = msg[off:off + n].reshape(flat.shape[0], len(dst))
             off += n
     assert off == msg.size
+
+
+def _pull(L, peer, padded, peer_padded):
+    """Peer-pull form (plan.cu group_pass, k_halo_pull): read the owner's padded planes directly."""
+    for f, pos in enumerate(POS_OF_FIELD):
+        dst, psrc, psgn = L["peer"][peer][pos][2:5]
+        mine = padded[f].reshape(padded[f].shape[0], -1)
+        theirs = peer_padded[f].reshape(peer_padded[f].shape[0], -1)
+        mine[:, dst] = theirs[:, psrc] * psgn[None, :]
 
 
 def _apply_self(L, padded):
@@ -163,6 +172,17 @@ def test_exchange_plan_equals_oracle_group_pass(layout, topo, symmetric):
         for f in range(5):
             got = _from_padded(G, lists[r][1], padded[r][f], POS_OF_FIELD[f], fields[r][f].shape)
             assert np.array_equal(got.view(np.uint64), want[r][f].view(np.uint64)), (r, f)
+    # the peer-pull form of the same exchange: every rank reads its neighbours' planes as they were before the pass
+    before = [[_to_padded(G, lists[r][1], a, POS_OF_FIELD[f]) for f, a in enumerate(fields[r])] for r, G in enumerate(grids)]
+    after = [[a.copy() for a in before[r]] for r in range(nr)]
+    for r in range(nr):
+        _apply_self(lists[r][0], after[r])
+        for peer in lists[r][0]["peer"]:
+            _pull(lists[r][0], peer, after[r], before[peer])
+    for r, G in enumerate(grids):
+        for f in range(5):
+            got = _from_padded(G, lists[r][1], after[r][f], POS_OF_FIELD[f], fields[r][f].shape)
+            assert np.array_equal(got.view(np.uint64), want[r][f].view(np.uint64)), ("pull", r, f)
 
 
 def _free_port():

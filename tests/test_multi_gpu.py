@@ -17,7 +17,7 @@ def _ngpu():
         return 0
 
 
-def _worker(rank, world, port, layout, scheme, cfl, q):
+def _worker(rank, world, port, layout, scheme, cfl, q, pull=1):
     import torch
     import torch.distributed as dist
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
@@ -45,6 +45,7 @@ def _worker(rank, world, port, layout, scheme, cfl, q):
         for tr in R0.Tr:
             register_tracer(decomp.cut_h(c.G, G, tr.t), Reg, underflow_conc=tr.conc_underflow)
         CS = tracer_advect_init(None, G, None, params, None, None)
+        CS.gpu_options["pull"] = pull      # 1: peer-memory loads over NVLink, 0: pack -> NCCL send/recv -> unpack
         hl, ul, vl = decomp.cut_h(c.G, G, h), decomp.cut_u(c.G, G, u), decomp.cut_v(c.G, G, v)
         nit = 0
         for _ in range(2):
@@ -59,18 +60,39 @@ def _worker(rank, world, port, layout, scheme, cfl, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("layout", [(1, 2), (2, 1)])
-@pytest.mark.parametrize("scheme,cfl", [("PPM", 0.9), ("PLM", 0.5)])
-def test_two_gpu_layout_invariance(layout, scheme, cfl):
+def _run(world, layout, scheme, cfl, pull=1):
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, layout, scheme, cfl, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, layout, scheme, cfl, q, pull)) for r in range(world)]
     for p in procs:
         p.start()
     res = sorted(q.get(timeout=300) for _ in procs)
     for p in procs:
         p.join(timeout=60)
-    assert [r[:2] for r in res] == [(0, True), (1, True)], res
+    assert [r[:2] for r in res] == [(r, True) for r in range(world)], res
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("layout", [(1, 2), (2, 1)])
+@pytest.mark.parametrize("scheme,cfl", [("PPM", 0.9), ("PLM", 0.5)])
+def test_two_gpu_layout_invariance(layout, scheme, cfl):
+    _run(2, layout, scheme, cfl)
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+def test_two_gpu_nccl_send_recv_path():
+    _run(2, (1, 2), "PPM", 0.9, pull=0)
+
+
+@pytest.mark.skipif(_ngpu() < 4, reason="needs 4 GPUs")
+@pytest.mark.parametrize("layout", [(2, 2), (1, 4)])
+def test_four_gpu_layout_invariance(layout):
+    _run(4, layout, "PPM", 1.4)
+
+
+@pytest.mark.skipif(_ngpu() < 8, reason="needs 8 GPUs")
+@pytest.mark.parametrize("layout", [(2, 4), (1, 8)])
+def test_eight_gpu_layout_invariance(layout):
+    _run(8, layout, "PPM:H3", 0.9)
