@@ -169,7 +169,9 @@ long long mom6adv_device_bytes(const mom6adv_plan *plan);
  * -- mom6adv_advect prints its copy-stream and compute times to stderr;
  * "pull" 0/1 -- multi-block plans: 1 (default) fills halos by loading the
  * neighbour GPU's fields directly (CUDA IPC + NVLink), 0 packs and uses NCCL
- * send/recv; choose before the first advect call. */
+ * send/recv; choose before the first advect call; "overlap" 0/1 -- 1 (default):
+ * on 1 x N layouts the tracer halo rows of the first pass travel under the x
+ * sweep of the interior rows. */
 int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value);
 /* Kernel classes of the per-class timers: the stand-ins for the reference's
  * (Ocean advect tracer) / (Ocean tracer halo updates) / (Ocean tracer global

@@ -1,5 +1,6 @@
 // x sweep of the streaming path (see fast_common.cuh for the design notes).
 #include "fast_common.cuh"
+#include <algorithm>
 
 // ---------------------------------------------------------------------------
 // x sweep
@@ -13,12 +14,13 @@ template <int SCHEME>
 __global__ void __launch_bounds__(128, XMINB)
 k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const double *__restrict__ hcv,
          const double *__restrict__ gqv, const double *__restrict__ hlstv, const double *__restrict__ ihv,
-         const double *__restrict__ mmv, const int *__restrict__ entry, const int *__restrict__ domore_k, int wbase) {
+         const double *__restrict__ mmv, const int *__restrict__ entry, const int *__restrict__ domore_k, int wbase,
+         int wj_lo, int wj_hi) {      // rows (Fortran j) this launch owns; the others belong to another launch of the sweep
   const unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
-  const int rj = blockIdx.y * 4 + (threadIdx.x >> 5), k0 = blockIdx.z;
+  const int rj = wj_lo + g.roff + blockIdx.y * 4 + (threadIdx.x >> 5), k0 = blockIdx.z;
   const int j = rj - g.roff;
-  if (j < g.jsd || j > g.jed) return;                        // warp-uniform
+  if (j > wj_hi) return;                                     // warp-uniform
   const int c0 = wbase + XT_USE * blockIdx.x + 4 * lane;       // first of this lane's 4 columns
   const long long q0 = (long long)c0 + (long long)g.P * rj + g.plane * k0;
   const bool lev = domore_k[k0] > 0;
@@ -159,10 +161,12 @@ int x_fast_tiles(const Geom &g, int wbase) { return (g.ied + g.coff - (wbase + 4
 
 void launch_x_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
                    const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm,
-                   const int *entry, const int *domore_k, int wbase) {
-  dim3 grid(x_fast_tiles(g, wbase), (g.R + 3) / 4, g.nk);
-  if (scheme == SCHEME_PLM) k_x_fast<SCHEME_PLM><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase);
-  else if (scheme == SCHEME_PPM_CW) k_x_fast<SCHEME_PPM_CW><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase);
-  else k_x_fast<SCHEME_PPM_H3><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase);
+                   const int *entry, const int *domore_k, int wbase, int wj_lo, int wj_hi) {
+  wj_lo = std::max(wj_lo, g.jsd); wj_hi = std::min(wj_hi, g.jed);
+  if (wj_lo > wj_hi) return;
+  dim3 grid(x_fast_tiles(g, wbase), (wj_hi - wj_lo + 1 + 3) / 4, g.nk);
+  if (scheme == SCHEME_PLM) k_x_fast<SCHEME_PLM><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi);
+  else if (scheme == SCHEME_PPM_CW) k_x_fast<SCHEME_PPM_CW><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi);
+  else k_x_fast<SCHEME_PPM_H3><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi);
 }
 

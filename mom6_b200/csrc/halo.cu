@@ -94,6 +94,7 @@ void build_halo_exchange(const Geom &g, const ExchangeSpec &x, int me, HaloBuild
       if (x.symmetric) { if (pos == 1) ic0 = G.isc - 1; if (pos == 2) jc0 = G.jsc - 1; }
       for (int j = jlo; j <= G.jed; j++) for (int i = ilo; i <= G.ied; i++) {
         if (i >= ic0 && i <= G.iec && j >= jc0 && j <= G.jec) continue;     // not a halo point
+        if (!halo_point_used(pos, i, j, G.isc, G.iec, G.jsc, G.jec, x.depth)) continue;
         Src s;
         if (!locate(x, geo, pos, i + G.ioff, j + G.joff, &s)) continue;
         if (d == me && s.rank == me) {

@@ -45,7 +45,7 @@ void launch_publish(cudaStream_t s, int *host_mapped, const int *dev, int n);
 int x_fast_tiles(const Geom &g, int wbase);
 void launch_x_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
                    const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm, const int *entry,
-                   const int *domore_k, int wbase);
+                   const int *domore_k, int wbase, int wj_lo, int wj_hi);
 void launch_y_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
                    const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm, const int *entry,
                    const int *domore_k);
@@ -60,6 +60,7 @@ void launch_sparse_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Ran
 struct ExchangeSpec {
   int nig, njg, npi, npj, halo_i, halo_j;
   int cyclic_x, cyclic_y, tripolar_n, symmetric;
+  int depth = 0;                                // halo points deeper than this are never read between two passes (0: all)
   std::vector<int> ibeg, iend, jbeg, jend;      // global compute extents of each layout column / row
 };
 struct HaloBuild { std::vector<int> dst, src; std::vector<signed char> sgn; };
@@ -73,4 +74,10 @@ struct PeerBuild {
   long long peer_plane = 0;                       // the sender's plane size (its level stride)
 };
 void make_geom(const mom6adv_grid *gr, Geom &g, int &wbase);
+// Is halo point (i,j) of stagger pos within `depth` cells of the computational domain (faces: of a cell that is)?
+inline bool halo_point_used(int pos, int i, int j, int isc, int iec, int jsc, int jec, int depth) {
+  if (depth <= 0) return true;
+  const int ilo = isc - depth - (pos == 1), jlo = jsc - depth - (pos == 2);
+  return i >= ilo && i <= iec + depth && j >= jlo && j <= jec + depth;
+}
 void build_halo_exchange(const Geom &g, const ExchangeSpec &x, int me, HaloBuild local[3], std::vector<PeerBuild> &peers);

@@ -100,6 +100,10 @@ struct mom6adv_plan {
   int opt_pull = 1;                  // multi-GPU group pass by peer-memory loads (0: pack -> NCCL send/recv -> unpack)
   int ipc_ntr = -1;                  // registry size the IPC mappings were made for
   int *bar_dev = nullptr;            // scratch word of the neighbour barrier
+  cudaStream_t s_pull = nullptr;     // tracer halos of the first pass are pulled here, under the interior x sweep
+  cudaEvent_t ev_pull_go = nullptr, ev_pull_done = nullptr;
+  bool pull_pending = false;         // the tracer halo rows are still in flight on s_pull
+  int opt_overlap = 1;
   int opt_trace = 0;                 // print the MIRROR pipeline's copy/compute times to stderr
   int opt_sparse = 1;                // list-driven tracer update on residual iterations (sparse.cu)
   int *sp_list = nullptr; double *sp_new = nullptr; int sp_cap = 0, sp_ntr = 0;
@@ -231,6 +235,15 @@ static bool locate_self(const mom6adv_plan *p, int pos, int ig, int jg, int *il,
   return false;
 }
 
+// Halo depth that can be read between two group passes: nsten_halo*stencil (:208-210).  Deeper halo points
+// (the outermost row when halo = 4 and stencil = 3) are not exchanged: the reference fills them, nothing reads them.
+static int exch_depth(const mom6adv_plan *p) {
+  const Geom &g = p->g;
+  const int stencil = (p->cfg.usePPM && !p->cfg.useHuynhStencilBug) ? 3 : 2;
+  const int halo_min = std::min(std::min(g.isc - g.isd, g.ied - g.iec), std::min(g.jsc - g.jsd, g.jed - g.jec));
+  return std::max(1, halo_min / stencil) * stencil;
+}
+
 static void build_halo_host(const mom6adv_plan *p, int pos, HostHalo &out) {
   const Geom &g = p->g;
   const bool symmetric = (g.IsdB == g.isd - 1);
@@ -239,6 +252,7 @@ static void build_halo_host(const mom6adv_plan *p, int pos, HostHalo &out) {
   if (symmetric) { if (pos == 1) ic0 = g.isc - 1; if (pos == 2) jc0 = g.jsc - 1; }
   for (int j = jlo; j <= g.jed; j++) for (int i = ilo; i <= g.ied; i++) {
     if (i >= ic0 && i <= g.iec && j >= jc0 && j <= g.jec) continue;
+    if (!halo_point_used(pos, i, j, g.isc, g.iec, g.jsc, g.jec, exch_depth(p))) continue;
     int il, jl, sg;
     if (!locate_self(p, pos, i + p->dom.ioff, j + p->dom.joff, &il, &jl, &sg)) continue;
     out.dst.push_back((i + g.coff) + g.P * (j + g.roff));
@@ -360,6 +374,7 @@ extern "C" int mom6adv_comm_init(mom6adv_plan *plan, const char *id128, const in
   CK(cudaSetDevice(plan->device));
   ExchangeSpec x;
   exchange_spec(plan->g, plan->dom, ibeg, iend, jbeg, jend, x);
+  x.depth = exch_depth(plan);
   if (x.ibeg[plan->dom.pi] != plan->g.isc + plan->dom.ioff || x.jbeg[plan->dom.pj] != plan->g.jsc + plan->dom.joff ||
       x.iend[plan->dom.pi] != plan->g.iec + plan->dom.ioff || x.jend[plan->dom.pj] != plan->g.jec + plan->dom.joff)
     return fail(plan, MOM6ADV_ERR_INVALID, "comm_init: extents disagree with this rank's grid");
@@ -531,6 +546,7 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   for (cudaEvent_t e : plan->ev_chunk) cudaEventDestroy(e);
   if (plan->stage_in) cudaFree(plan->stage_in);
   if (plan->ev_huv) cudaEventDestroy(plan->ev_huv);
+  if (plan->s_pull) { cudaStreamDestroy(plan->s_pull); cudaEventDestroy(plan->ev_pull_go); cudaEventDestroy(plan->ev_pull_done); }
   if (plan->s_in) cudaStreamDestroy(plan->s_in);
   if (plan->s_out) cudaStreamDestroy(plan->s_out);
   if (plan->ev0) cudaEventDestroy(plan->ev0);
@@ -689,7 +705,7 @@ static int setup_ipc(mom6adv_plan *plan) {
   return 0;
 }
 
-static int group_pass(mom6adv_plan *plan, bool first_of_call) {
+static int group_pass(mom6adv_plan *plan, bool first_of_call, bool defer_tracers) {
   const Geom &g = plan->g;
   cudaStream_t s = plan->stream;
   ProfScope ps(plan, MOM6ADV_KC_HALO);
@@ -710,17 +726,40 @@ static int group_pass(mom6adv_plan *plan, bool first_of_call) {
       // the neighbours' previous writes must be complete: at the first pass of a call a barrier says so, later
       // passes follow the all-reduce of the convergence flags, which every rank enters after its sweeps
       if (first_of_call) { int rc = exch_barrier(plan); if (rc) return rc; }
-      { ProfScope pw(plan, MOM6ADV_KC_EXCH_WIRE);
-      for (PeerLists &p : plan->peers) {
-        double **ptab = p.fields_dev + plan->cur * (3 + plan->ntr);
-        const Seg psegs[3][2] = {{{ptab + 2, 1}, {ptab + 3 + plan->m_lo, nact}}, {{ptab + 0, 1}, {nullptr, 0}}, {{ptab + 1, 1}, {nullptr, 0}}};
-        for (int pos = 0; pos < 3; pos++) for (int q = 0; q < 2; q++) if (segs[pos][q].n > 0) {
-          launch_halo_pull(s, g.plane, p.peer_plane, g.nk, p.recv_dst[pos], p.recv_src[pos], p.recv_sgn[pos], p.n_recv[pos],
-                           segs[pos][q].t, psegs[pos][q].t, segs[pos][q].n);
-          plan->launches++;
+      // q = 0: hprev / uhr / vhr, q = 1: the tracers.  With defer_tracers the tracer rows travel on s_pull while the
+      // x sweep of the interior rows runs (1 x N layouts: those rows need no neighbour data); the sweep of the halo
+      // rows waits for ev_pull_done (sweep()).  Tracer sources are the neighbours' live buffers, which nobody
+      // writes before the convergence all-reduce of this trip, so only the mass fields need the closing fence.
+      auto pull = [&](cudaStream_t st, int q) {
+        for (PeerLists &p : plan->peers) {
+          double **ptab = p.fields_dev + plan->cur * (3 + plan->ntr);
+          const Seg psegs[3][2] = {{{ptab + 2, 1}, {ptab + 3 + plan->m_lo, nact}}, {{ptab + 0, 1}, {nullptr, 0}}, {{ptab + 1, 1}, {nullptr, 0}}};
+          for (int pos = 0; pos < 3; pos++) if (segs[pos][q].n > 0) {
+            launch_halo_pull(st, g.plane, p.peer_plane, g.nk, p.recv_dst[pos], p.recv_src[pos], p.recv_sgn[pos], p.n_recv[pos],
+                             segs[pos][q].t, psegs[pos][q].t, segs[pos][q].n);
+            plan->launches++;
+          }
         }
+      };
+      for (PeerLists &p : plan->peers)
         plan->halo_bytes_sent += 8LL * g.nk * ((long long)(1 + nact) * p.n_recv[0] + p.n_recv[1] + p.n_recv[2]);
+      { ProfScope pw(plan, MOM6ADV_KC_EXCH_WIRE);
+        pull(s, 0);
+        if (!defer_tracers) pull(s, 1);
       }
+      if (defer_tracers) {
+        if (!plan->s_pull) {
+          int prio_lo = 0, prio_hi = 0;
+          CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+          CK(cudaStreamCreateWithPriority(&plan->s_pull, cudaStreamNonBlocking, prio_hi));   // its blocks go ahead of the sweep's
+          CK(cudaEventCreateWithFlags(&plan->ev_pull_go, cudaEventDisableTiming));
+          CK(cudaEventCreateWithFlags(&plan->ev_pull_done, cudaEventDisableTiming));
+        }
+        CK(cudaEventRecord(plan->ev_pull_go, s));
+        CK(cudaStreamWaitEvent(plan->s_pull, plan->ev_pull_go, 0));
+        pull(plan->s_pull, 1);
+        CK(cudaEventRecord(plan->ev_pull_done, plan->s_pull));
+        plan->pull_pending = true;
       }
       CK(cudaGetLastError());
       // nobody overwrites its rows before every neighbour has read them
@@ -795,6 +834,11 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
     if (plan->tr[m].diag[dir == 0 ? 2 : 3]) any_ad2d = true;
     for (int d = 0; d < 5; d++) if (plan->tr[m].diag[d]) any_diag = true;
   }
+  const bool split_rows = plan->pull_pending && dir == 0 && plan->opt_fast && !any_diag && itt == 1;
+  if (plan->pull_pending && !split_rows) {            // any other consumer needs the halo rows now
+    CK(cudaStreamWaitEvent(s, plan->ev_pull_done, 0));
+    plan->pull_pending = false;
+  }
   if (plan->opt_fast && !any_diag) {
     // streaming kernels (fast.cu): mass fields as below, then all tracers in chunks of MOM6ADV_MAXT
     const bool x = (dir == 0);
@@ -855,8 +899,18 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
         tt.dst[m] = x ? ts.buf[1 - plan->cur] : ts.buf[plan->cur];
         tt.cu[m] = ts.conc_underflow;
       }
-      if (x) launch_x_fast(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
-                           plan->domore_k, plan->wbase);
+      if (x && split_rows) {
+        // rows of the computational domain first; the halo rows once their tracer values have arrived
+        launch_x_fast(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
+                      plan->domore_k, plan->wbase, g.jsc, g.jec);
+        if (plan->pull_pending) { CK(cudaStreamWaitEvent(s, plan->ev_pull_done, 0)); plan->pull_pending = false; }
+        launch_x_fast(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
+                      plan->domore_k, plan->wbase, g.jsd, g.jsc - 1);
+        launch_x_fast(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
+                      plan->domore_k, plan->wbase, g.jec + 1, g.jed);
+        plan->launches += 2;
+      } else if (x) launch_x_fast(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
+                           plan->domore_k, plan->wbase, g.jsd, g.jed);
       else launch_y_fast(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmy, ent,
                          plan->domore_k);
       plan->launches++;
@@ -954,7 +1008,12 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
   int itt;
   for (itt = 1; itt <= max_iter; itt++) {                                   // :203
     if (isv > is - stencil) {                                               // :205
-      { int rc = group_pass(plan, itt == 1); if (rc) return rc; }           // :206
+      bool defer = false;
+      if (itt == 1 && x_first && plan->opt_overlap && plan->opt_fast && plan->dom.npi == 1) {
+        defer = true;
+        for (int m = m_lo; m < m_hi; m++) for (int d = 0; d < 5; d++) if (plan->tr[m].diag[d]) defer = false;
+      }
+      { int rc = group_pass(plan, itt == 1, defer); if (rc) return rc; }     // :206
       const int nsten_halo = halo_min / stencil;                            // :208
       isv = is - nsten_halo * stencil; jsv = js - nsten_halo * stencil;     // :209
       iev = ie + nsten_halo * stencil; jev = je + nsten_halo * stencil;     // :210
@@ -991,6 +1050,7 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
       if (plan->sum_host[0] == 0) break;                                    // :308-310
     }
   }
+  if (plan->pull_pending) { CK(cudaStreamWaitEvent(s, plan->ev_pull_done, 0)); plan->pull_pending = false; }
   if (n_iter_out) *n_iter_out = std::min(itt, max_iter);
   if (update_vol_prev && use_vol_prev)                                      // :318-320
     CK(cudaMemcpyAsync(plan->vol_prev, plan->hprev, sizeof(double) * field_elems(plan), cudaMemcpyDeviceToDevice, s));
@@ -1303,6 +1363,7 @@ extern "C" int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value
   if (!strcmp(key, "mirror_chunk")) { plan->opt_chunk = value; return MOM6ADV_OK; }
   if (!strcmp(key, "mirror_ahead")) { plan->opt_ahead = value; return MOM6ADV_OK; }
   if (!strcmp(key, "pull")) { if (plan->ipc_ntr >= 0 && value != plan->opt_pull) return fail(plan, MOM6ADV_ERR_INVALID, "set_option: pull must be chosen before the first advect call"); plan->opt_pull = value; return MOM6ADV_OK; }
+  if (!strcmp(key, "overlap")) { plan->opt_overlap = value; return MOM6ADV_OK; }
   if (!strcmp(key, "trace")) { plan->opt_trace = value; return MOM6ADV_OK; }
   if (!strcmp(key, "profile")) {
     plan->opt_profile = value;

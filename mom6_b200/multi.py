@@ -103,6 +103,7 @@ def bench_multi(args, name, world, rank, local_rank, peak, peak_src):
     CS = tracer_advect_init(None, G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}, None, None)
     plan = capi.Plan(G, c.GV, CS)
     plan.set_option("pull", int(os.environ.get("MOM6ADV_PULL", "1")))     # 0: NCCL send/recv exchange (comparison runs)
+    plan.set_option("overlap", int(os.environ.get("MOM6ADV_OVERLAP", "1")))
     comm_init_plan(plan, G)
     plan.set_ntr(ntr)
     for m in range(ntr):
