@@ -24,7 +24,7 @@ use mpp_domains_mod,     only : CYCLIC_GLOBAL_DOMAIN, FOLD_NORTH_EDGE   ! the va
 use MOM_error_handler,   only : MOM_error, FATAL, WARNING
 use MOM_file_parser,     only : get_param, log_version, param_file_type
 use MOM_grid,            only : ocean_grid_type
-use MOM_open_boundary,   only : ocean_OBC_type
+use MOM_open_boundary,   only : ocean_OBC_type, OBC_segment_type
 use MOM_tracer_registry, only : tracer_registry_type, tracer_type
 use MOM_unit_scaling,    only : unit_scale_type
 use MOM_verticalGrid,    only : verticalGrid_type
@@ -47,6 +47,7 @@ type, public :: tracer_advect_CS ; private
   type(c_ptr) :: plan = c_null_ptr   !< mom6adv_plan* (created on the first advect_tracer call)
   integer :: ntr_bound = -1          !< Reg%ntr the plan was last bound with
   integer(kind=c_long_long) :: reg_hash = 0 !< hash of the registry's pointers at the last bind
+  logical :: obc_was_set = .false.   !< an OBC table is active in the plan
 end type tracer_advect_CS
 
 integer :: id_clock_advect !< (Ocean advect tracer): the whole GPU call incl. host<->device copies
@@ -68,6 +69,23 @@ end type mom6adv_config
 type, bind(c) :: mom6adv_domain
   integer(c_int) :: nig, njg, npi, npj, pi, pj, ioff, joff, cyclic_x, cyclic_y, tripolar_n
 end type mom6adv_domain
+type, bind(c) :: mom6adv_obc_tracer
+  integer(c_int) :: ntr_index
+  type(c_ptr)    :: tres
+  real(c_double) :: OBC_inflow_conc
+end type mom6adv_obc_tracer
+type, bind(c) :: mom6adv_obc_segment
+  integer(c_int) :: is_E_or_W, is_N_or_S, direction, specified
+  integer(c_int) :: isd, ied, jsd, jed, IsdB, IedB, JsdB, JedB
+  integer(c_int) :: ntseg
+  type(c_ptr)    :: Tr
+end type mom6adv_obc_segment
+type, bind(c) :: mom6adv_obc
+  integer(c_int) :: OBC_pe, number_of_segments
+  integer(c_int) :: open_u_BCs_exist_globally, open_v_BCs_exist_globally
+  integer(c_int) :: specified_u_BCs_exist_globally, specified_v_BCs_exist_globally
+  type(c_ptr)    :: segment
+end type mom6adv_obc
 
 ! ---- the C entry points (style of src/framework/posix.F90:52-229) ----------------------
 interface
@@ -106,6 +124,13 @@ interface
     integer(c_int), intent(in) :: ibeg(*), iend(*), jbeg(*), jend(*)
     integer(c_int) :: rc
   end function mom6adv_comm_init
+
+  function mom6adv_set_obc(plan, obc) bind(c, name="mom6adv_set_obc") result(rc)
+    import :: c_int, c_ptr
+    type(c_ptr), value :: plan
+    type(c_ptr), value :: obc           !< c_loc of a mom6adv_obc, or c_null_ptr (unassociated OBC)
+    integer(c_int) :: rc
+  end function mom6adv_set_obc
 
   function mom6adv_set_ntr(plan, ntr) bind(c, name="mom6adv_set_ntr") result(rc)
     import :: c_int, c_ptr
@@ -274,8 +299,6 @@ subroutine advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first
   if (.not. associated(Reg)) call MOM_error(FATAL, "MOM_tracer_advect: "// &
        "register_tracer must be called before advect_tracer.")
   if (Reg%ntr==0) return
-  if (associated(OBC)) then ; if (OBC%OBC_pe) call MOM_error(FATAL, "MOM_tracer_advect (B200): "// &
-       "tracer reservoirs of open boundary segments are not supported yet (mom6adv status 3).") ; endif
   call cpu_clock_begin(id_clock_advect)
 
   if (.not. c_associated(CS%plan)) call make_plan(G, GV, CS)
@@ -291,6 +314,9 @@ subroutine advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first
     CS%ntr_bound = Reg%ntr ; CS%reg_hash = h
   endif
 
+  ! the OBC argument (:64): segment tables and tracer reservoirs go to the device on every call (tres evolves)
+  call pass_obc(OBC, CS)
+
   xf = -1 ; if (present(x_first_in)) xf = merge(1, 0, x_first_in)
   mi = -1 ; if (present(max_iter_in)) mi = max_iter_in
   uv = -1 ; if (present(update_vol_prev)) uv = merge(1, 0, update_vol_prev)
@@ -302,6 +328,58 @@ subroutine advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first
 
   call cpu_clock_end(id_clock_advect)
 end subroutine advect_tracer
+
+!> Marshal ocean_OBC_type into the POD tables of include/mom6adv.h and hand them to the plan.
+!! Only the members advect_x / advect_y read are passed (reference :442-478,580-628,825-862,965-1014).
+subroutine pass_obc(OBC, CS)
+  type(ocean_OBC_type),   pointer :: OBC !< open boundary condition data (may be unassociated)
+  type(tracer_advect_CS), pointer :: CS  !< control structure for this module
+  type(mom6adv_obc), target :: o
+  type(mom6adv_obc_segment), allocatable, target :: segs(:)
+  type(mom6adv_obc_tracer),  allocatable, target :: trs(:)
+  type(OBC_segment_type), pointer :: segment => NULL()
+  integer :: n, m, nt, off
+
+  if (.not. associated(OBC)) then
+    if (CS%obc_was_set) call check_rc(mom6adv_set_obc(CS%plan, c_null_ptr), CS%plan, "set_obc")
+    CS%obc_was_set = .false. ; return
+  endif
+  nt = 0
+  do n=1,OBC%number_of_segments
+    if (associated(OBC%segment(n)%tr_Reg)) nt = nt + OBC%segment(n)%tr_Reg%ntseg
+  enddo
+  allocate(segs(max(OBC%number_of_segments,1)), trs(max(nt,1)))
+  off = 0
+  do n=1,OBC%number_of_segments
+    segment => OBC%segment(n)
+    segs(n)%is_E_or_W = merge(1, 0, segment%is_E_or_W) ; segs(n)%is_N_or_S = merge(1, 0, segment%is_N_or_S)
+    segs(n)%direction = segment%direction ; segs(n)%specified = merge(1, 0, segment%specified)
+    segs(n)%isd = segment%HI%isd ; segs(n)%ied = segment%HI%ied ; segs(n)%jsd = segment%HI%jsd ; segs(n)%jed = segment%HI%jed
+    segs(n)%IsdB = segment%HI%IsdB ; segs(n)%IedB = segment%HI%IedB
+    segs(n)%JsdB = segment%HI%JsdB ; segs(n)%JedB = segment%HI%JedB
+    segs(n)%ntseg = -1 ; segs(n)%Tr = c_null_ptr
+    if (associated(segment%tr_Reg)) then
+      segs(n)%ntseg = segment%tr_Reg%ntseg
+      do m=1,segment%tr_Reg%ntseg
+        trs(off+m)%ntr_index = segment%tr_Reg%Tr(m)%ntr_index
+        trs(off+m)%OBC_inflow_conc = segment%tr_Reg%Tr(m)%OBC_inflow_conc
+        trs(off+m)%tres = c_null_ptr
+        if (allocated(segment%tr_Reg%Tr(m)%tres)) trs(off+m)%tres = c_loc(segment%tr_Reg%Tr(m)%tres)
+      enddo
+      if (segment%tr_Reg%ntseg > 0) segs(n)%Tr = c_loc(trs(off+1))
+      off = off + segment%tr_Reg%ntseg
+    endif
+  enddo
+  o%OBC_pe = merge(1, 0, OBC%OBC_pe) ; o%number_of_segments = OBC%number_of_segments
+  o%open_u_BCs_exist_globally = merge(1, 0, OBC%open_u_BCs_exist_globally)
+  o%open_v_BCs_exist_globally = merge(1, 0, OBC%open_v_BCs_exist_globally)
+  o%specified_u_BCs_exist_globally = merge(1, 0, OBC%specified_u_BCs_exist_globally)
+  o%specified_v_BCs_exist_globally = merge(1, 0, OBC%specified_v_BCs_exist_globally)
+  o%segment = c_loc(segs(1))
+  call check_rc(mom6adv_set_obc(CS%plan, c_loc(o)), CS%plan, "set_obc")
+  CS%obc_was_set = .true.
+  deallocate(segs, trs)
+end subroutine pass_obc
 
 !> Initialise the module: same parameters, defaults and messages as the reference (:1090-1150).
 subroutine tracer_advect_init(Time, G, US, param_file, diag, CS)

@@ -34,7 +34,7 @@ enum {
   MOM6ADV_OK = 0,
   MOM6ADV_ERR_NOT_INIT = 1,    /* plan NULL / tracer not bound (reference FATALs :120-123) */
   MOM6ADV_ERR_INVALID = 2,     /* bad argument */
-  MOM6ADV_ERR_UNSUPPORTED = 3, /* OBC active, halo < stencil */
+  MOM6ADV_ERR_UNSUPPORTED = 3, /* halo < stencil; OBC on a multi-block plan */
   MOM6ADV_ERR_CUDA = 4,
   MOM6ADV_ERR_COMM = 5         /* halo-exchange transport failure */
 };
@@ -112,6 +112,35 @@ int mom6adv_comm_init(mom6adv_plan *plan, const char *id128, const int *ibeg, co
 int mom6adv_exchange_list(const mom6adv_grid *g, const mom6adv_domain *dom, const int *ibeg, const int *iend,
                           const int *jbeg, const int *jend, int peer, int pos, int what, int *out, int cap,
                           int *geom);
+
+/* ---- open boundaries (ocean_OBC_type, src/core/MOM_open_boundary.F90:119-142,145-260,264-400) ----
+ * The members advect_x / advect_y read (MOM_tracer_advect.F90:442-478,580-628,825-862,965-1014).
+ * tres has the segment's own bounds, Fortran layout: E/W segments (IsdB:IedB, jsd:jed, nk), N/S segments
+ * (isd:ied, JsdB:JedB, nk); NULL == not allocated.  ntr_index is 1-based as in Fortran.  ntseg < 0 ==
+ * segment%tr_Reg unassociated.  direction: OBC_DIRECTION_N/S/E/W = 100/200/300/400 (:80-83). */
+typedef struct {
+  int ntr_index;
+  const double *tres;
+  double OBC_inflow_conc;
+} mom6adv_obc_tracer;
+typedef struct {
+  int is_E_or_W, is_N_or_S, direction, specified;
+  int isd, ied, jsd, jed, IsdB, IedB, JsdB, JedB;     /* segment%HI */
+  int ntseg;
+  const mom6adv_obc_tracer *Tr;
+} mom6adv_obc_segment;
+typedef struct {
+  int OBC_pe;
+  int number_of_segments;
+  int open_u_BCs_exist_globally, open_v_BCs_exist_globally;
+  int specified_u_BCs_exist_globally, specified_v_BCs_exist_globally;
+  const mom6adv_obc_segment *segment;
+} mom6adv_obc;
+/* The OBC argument of advect_tracer (:64): call before mom6adv_advect / mom6adv_advect_resident whenever the
+ * reservoirs changed (every step in a model with evolving tres); the tables and reservoirs are copied to the
+ * device.  NULL, or OBC_pe == 0, is the unassociated pointer.  With an active OBC the sweeps take the
+ * open-boundary kernels (obc.cu). */
+int mom6adv_set_obc(mom6adv_plan *plan, const mom6adv_obc *obc);
 
 /* ---- registry data (MOM_tracer_types.F90:9-130) -------------------------- */
 /* Declare Reg%ntr.  Tracer slots 0..ntr-1 get HBM storage. */

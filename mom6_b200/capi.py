@@ -43,6 +43,55 @@ class mom6adv_domain(C.Structure):
                                        "cyclic_x", "cyclic_y", "tripolar_n")]
 
 
+class mom6adv_obc_tracer(C.Structure):
+    _fields_ = [("ntr_index", C.c_int), ("tres", _dp), ("OBC_inflow_conc", C.c_double)]
+
+
+class mom6adv_obc_segment(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("is_E_or_W", "is_N_or_S", "direction", "specified",
+                                       "isd", "ied", "jsd", "jed", "IsdB", "IedB", "JsdB", "JedB", "ntseg")] + \
+               [("Tr", C.POINTER(mom6adv_obc_tracer))]
+
+
+class mom6adv_obc(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("OBC_pe", "number_of_segments", "open_u_BCs_exist_globally",
+                                       "open_v_BCs_exist_globally", "specified_u_BCs_exist_globally",
+                                       "specified_v_BCs_exist_globally")] + \
+               [("segment", C.POINTER(mom6adv_obc_segment))]
+
+
+def make_obc(OBC):
+    """ocean_OBC_type (mom6_b200.types.OceanOBC) -> mom6adv_obc; returns (struct, keep-alive list)."""
+    keep = []
+    segs = (mom6adv_obc_segment * max(OBC.number_of_segments, 1))()
+    for n, sg in enumerate(OBC.segment):
+        s = segs[n]
+        s.is_E_or_W, s.is_N_or_S = int(sg.is_E_or_W), int(sg.is_N_or_S)
+        s.direction, s.specified = int(sg.direction), int(sg.specified)
+        for f in ("isd", "ied", "jsd", "jed", "IsdB", "IedB", "JsdB", "JedB"):
+            setattr(s, f, int(getattr(sg.HI, f)))
+        if sg.tr_Reg is None:
+            s.ntseg = -1
+        else:
+            s.ntseg = len(sg.tr_Reg)
+            trs = (mom6adv_obc_tracer * max(len(sg.tr_Reg), 1))()
+            for m, t in enumerate(sg.tr_Reg):
+                trs[m].ntr_index, trs[m].OBC_inflow_conc = int(t.ntr_index), float(t.OBC_inflow_conc)
+                if t.tres is not None:
+                    assert t.tres.dtype == np.float64 and t.tres.flags["C_CONTIGUOUS"]
+                    trs[m].tres = t.tres.ctypes.data_as(_dp)
+            keep.append(trs)
+            s.Tr = C.cast(trs, C.POINTER(mom6adv_obc_tracer))
+    o = mom6adv_obc()
+    o.OBC_pe, o.number_of_segments = int(OBC.OBC_pe), OBC.number_of_segments
+    o.open_u_BCs_exist_globally, o.open_v_BCs_exist_globally = int(OBC.open_u_BCs_exist_globally), int(OBC.open_v_BCs_exist_globally)
+    o.specified_u_BCs_exist_globally = int(OBC.specified_u_BCs_exist_globally)
+    o.specified_v_BCs_exist_globally = int(OBC.specified_v_BCs_exist_globally)
+    o.segment = C.cast(segs, C.POINTER(mom6adv_obc_segment))
+    keep.append(segs)
+    return o, keep
+
+
 # every symbol include/mom6adv.h declares: name -> (restype, argtypes)
 _P = C.c_void_p
 SYMBOLS = {
@@ -57,6 +106,7 @@ SYMBOLS = {
     "mom6adv_exchange_list": (C.c_int, [C.POINTER(mom6adv_grid), C.POINTER(mom6adv_domain), C.POINTER(C.c_int),
                                         C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int, C.c_int,
                                         C.c_int, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_int)]),
+    "mom6adv_set_obc": (C.c_int, [_P, C.POINTER(mom6adv_obc)]),
     "mom6adv_set_ntr": (C.c_int, [_P, C.c_int]),
     "mom6adv_bind_tracer": (C.c_int, [_P, C.c_int, _P, C.c_double, _P, _P, _P, _P, _P]),
     "mom6adv_advect": (C.c_int, [_P, _P, _P, _P, C.c_double, C.c_int, _P, C.c_int, C.c_int, _P, _P,
@@ -210,6 +260,14 @@ class Plan:
     def set_ntr(self, ntr: int):
         self._ck(self._l.mom6adv_set_ntr(self._h, ntr))
         self.ntr = ntr
+
+    def set_obc(self, OBC):
+        """The OBC argument of advect_tracer: None == unassociated."""
+        if OBC is None:
+            self._ck(self._l.mom6adv_set_obc(self._h, None))
+            return
+        o, keep = make_obc(OBC)
+        self._ck(self._l.mom6adv_set_obc(self._h, C.byref(o)))
 
     def bind_tracer(self, m, t, conc_underflow=0.0, ad_x=None, ad_y=None, ad2d_x=None, ad2d_y=None,
                     advection_xy=None):

@@ -3,6 +3,7 @@
 #include "../../include/mom6adv.h"
 #include "internal.cuh"
 #include "kernels.h"
+#include "obc.cuh"
 
 #include <nccl.h>
 
@@ -104,6 +105,17 @@ struct mom6adv_plan {
   cudaEvent_t ev_pull_go = nullptr, ev_pull_done = nullptr;
   bool pull_pending = false;         // the tracer halo rows are still in flight on s_pull
   int opt_overlap = 1;
+  // open boundaries (mom6adv_set_obc)
+  bool obc_active = false;
+  int obc_flags[4] = {0, 0, 0, 0};          // open_u, open_v, specified_u, specified_v ..._BCs_exist_globally
+  std::vector<ObcSeg> obc_segs;
+  std::vector<ObcTr> obc_trs;
+  std::vector<double *> obc_tres;           // device copies of the reservoirs
+  ObcSeg *obc_segs_dev = nullptr;
+  ObcTr *obc_trs_dev = nullptr;
+  unsigned char *obc_cond = nullptr;
+  long long obc_cond_bytes = 0;
+  double *obc_ttmp = nullptr, *obc_slope = nullptr, *obc_fx = nullptr, *obc_hh2 = nullptr, *maskT = nullptr;
   int opt_trace = 0;                 // print the MIRROR pipeline's copy/compute times to stderr
   int opt_sparse = 1;                // list-driven tracer update on residual iterations (sparse.cu)
   int *sp_list = nullptr; double *sp_new = nullptr; int sp_cap = 0, sp_ntr = 0;
@@ -141,6 +153,7 @@ static void prof_collect(mom6adv_plan *p) {   // call after the stream is synchr
 
 static thread_local std::string g_err;
 static void teardown_ipc(mom6adv_plan *plan, bool collective);
+static void free_obc(mom6adv_plan *plan);
 
 #define CK(call)                                                                            \
   do {                                                                                      \
@@ -282,7 +295,7 @@ static int create_impl(mom6adv_plan *plan, const mom6adv_grid *gr) {
   CK(cudaEventCreate(&plan->ev1));
   const long long pl = g.plane;
   double **p2[] = {&plan->areaT, &plan->IareaT, &plan->mCu, &plan->mCv,
-                   &plan->uh_neglect, &plan->vh_neglect, &plan->mmx, &plan->mmy};
+                   &plan->uh_neglect, &plan->vh_neglect, &plan->mmx, &plan->mmy, &plan->maskT};
   for (double **pp : p2) { int rc = dev_alloc(plan, pp, pl); if (rc) return rc; }
   const long long fe = field_elems(plan);
   double **p3[] = {&plan->h_end, &plan->uhtr, &plan->vhtr, &plan->uhr, &plan->vhr, &plan->hprev,
@@ -304,6 +317,7 @@ static int create_impl(mom6adv_plan *plan, const mom6adv_grid *gr) {
   CK(cudaStreamSynchronize(plan->stream));
   if ((rc = upload(plan, plan->IareaT, gr->IareaT, g.isd, g.jsd, 1))) return rc;
   CK(cudaStreamSynchronize(plan->stream));
+  if (gr->mask2dT) { if ((rc = upload(plan, plan->maskT, gr->mask2dT, g.isd, g.jsd, 1))) return rc; CK(cudaStreamSynchronize(plan->stream)); }
   if ((rc = upload(plan, plan->mCu, gr->mask2dCu, g.IsdB, g.jsd, 1))) return rc;
   CK(cudaStreamSynchronize(plan->stream));
   if ((rc = upload(plan, plan->mCv, gr->mask2dCv, g.isd, g.JsdB, 1))) return rc;
@@ -518,6 +532,8 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   cudaSetDevice(plan->device);
   if (plan->stream) cudaStreamSynchronize(plan->stream);
   teardown_ipc(plan, true);
+  free_obc(plan);
+  { double *o[] = {plan->obc_ttmp, plan->obc_slope, plan->obc_fx, plan->obc_hh2, plan->maskT}; for (double *p : o) if (p) cudaFree(p); }
   if (plan->bar_dev) cudaFree(plan->bar_dev);
   double *d[] = {plan->areaT, plan->IareaT, plan->mCu, plan->mCv, plan->uh_neglect, plan->vh_neglect, plan->mmx,
                  plan->mmy, plan->h_end, plan->uhtr, plan->vhtr, plan->vol_prev, plan->uhr, plan->vhr, plan->hprev,
@@ -554,6 +570,142 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   if (plan->stream) cudaStreamDestroy(plan->stream);
   delete plan;
   return MOM6ADV_OK;
+}
+
+// ---------------------------------------------------------------------------
+// OBC argument of advect_tracer (:64).  Copies the segment tables and reservoirs to the device.
+// ---------------------------------------------------------------------------
+static void free_obc(mom6adv_plan *plan) {
+  for (double *p : plan->obc_tres) if (p) cudaFree(p);
+  plan->obc_tres.clear(); plan->obc_segs.clear(); plan->obc_trs.clear();
+  if (plan->obc_segs_dev) { cudaFree(plan->obc_segs_dev); plan->obc_segs_dev = nullptr; }
+  if (plan->obc_trs_dev) { cudaFree(plan->obc_trs_dev); plan->obc_trs_dev = nullptr; }
+  if (plan->obc_cond) { cudaFree(plan->obc_cond); plan->obc_cond = nullptr; }
+  plan->obc_cond_bytes = 0;
+  plan->obc_active = false;
+}
+
+extern "C" int mom6adv_set_obc(mom6adv_plan *plan, const mom6adv_obc *obc) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "set_obc: plan not initialised");
+  CK(cudaSetDevice(plan->device));
+  CK(cudaStreamSynchronize(plan->stream));
+  free_obc(plan);
+  if (!obc || !obc->OBC_pe) return MOM6ADV_OK;                 // unassociated / no segment on this PE (:442, :580)
+  if (plan->multi) return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "set_obc: open boundaries on a multi-block plan are not supported");
+  if (obc->number_of_segments < 0 || (obc->number_of_segments > 0 && !obc->segment))
+    return fail(plan, MOM6ADV_ERR_INVALID, "set_obc: bad segment list");
+  const Geom &g = plan->g;
+  plan->obc_flags[0] = obc->open_u_BCs_exist_globally; plan->obc_flags[1] = obc->open_v_BCs_exist_globally;
+  plan->obc_flags[2] = obc->specified_u_BCs_exist_globally; plan->obc_flags[3] = obc->specified_v_BCs_exist_globally;
+  long long cond_bytes = 0;
+  for (int n = 0; n < obc->number_of_segments; n++) {
+    const mom6adv_obc_segment &h = obc->segment[n];
+    ObcSeg sg;
+    sg.dir = h.direction; sg.is_ew = h.is_E_or_W; sg.is_ns = h.is_N_or_S; sg.specified = h.specified;
+    sg.has_reg = (h.ntseg >= 0);
+    sg.isd = h.isd; sg.ied = h.ied; sg.jsd = h.jsd; sg.jed = h.jed;
+    sg.IsdB = h.IsdB; sg.IedB = h.IedB; sg.JsdB = h.JsdB; sg.JedB = h.JedB;
+    sg.ntseg = std::max(h.ntseg, 0); sg.tr_off = (int)plan->obc_trs.size();
+    if (sg.is_ew == sg.is_ns) return fail(plan, MOM6ADV_ERR_INVALID, "set_obc: a segment must be either E/W or N/S");
+    // the faces and the cells next to them must lie inside the data domain (the reference indexes them unchecked)
+    const bool ok = sg.is_ew ? (sg.IsdB - 2 >= g.isd && sg.IsdB + 3 <= g.ied && sg.jsd >= g.jsd && sg.jed <= g.jed && sg.jsd <= sg.jed)
+                             : (sg.JsdB - 2 >= g.jsd && sg.JsdB + 3 <= g.jed && sg.isd >= g.isd && sg.ied <= g.ied && sg.isd <= sg.ied && sg.JedB >= sg.JsdB);
+    if (!ok) return fail(plan, MOM6ADV_ERR_INVALID, "set_obc: segment outside the data domain");
+    sg.cond_off = cond_bytes;
+    const long long nfaces = sg.is_ew ? (long long)(sg.jed - sg.jsd + 1) : (long long)(sg.ied - sg.isd + 1) * (sg.JedB - sg.JsdB + 1);
+    const long long ntres = sg.is_ew ? (long long)(sg.IedB - sg.IsdB + 1) * (sg.jed - sg.jsd + 1) * g.nk : nfaces * g.nk;
+    cond_bytes += nfaces * g.nk;
+    for (int e = 0; e < sg.ntseg; e++) {
+      const mom6adv_obc_tracer &t = h.Tr[e];
+      if (t.ntr_index < 1 || t.ntr_index > plan->ntr) return fail(plan, MOM6ADV_ERR_INVALID, "set_obc: ntr_index outside the registry (call set_ntr first)");
+      ObcTr d; d.m = t.ntr_index - 1; d.conc = t.OBC_inflow_conc; d.tres = nullptr;
+      if (t.tres) {
+        double *dev = nullptr;
+        CK(cudaMalloc((void **)&dev, sizeof(double) * ntres));
+        plan->obc_tres.push_back(dev);
+        if (is_device_ptr(t.tres)) CK(cudaMemcpyAsync(dev, t.tres, sizeof(double) * ntres, cudaMemcpyDeviceToDevice, plan->stream));
+        else CK(cudaMemcpyAsync(dev, t.tres, sizeof(double) * ntres, cudaMemcpyHostToDevice, plan->stream));
+        d.tres = dev;
+      }
+      plan->obc_trs.push_back(d);
+    }
+    plan->obc_segs.push_back(sg);
+  }
+  CK(cudaMalloc((void **)&plan->obc_segs_dev, sizeof(ObcSeg) * std::max<size_t>(plan->obc_segs.size(), 1)));
+  CK(cudaMalloc((void **)&plan->obc_trs_dev, sizeof(ObcTr) * std::max<size_t>(plan->obc_trs.size(), 1)));
+  if (!plan->obc_segs.empty()) CK(cudaMemcpyAsync(plan->obc_segs_dev, plan->obc_segs.data(), sizeof(ObcSeg) * plan->obc_segs.size(), cudaMemcpyHostToDevice, plan->stream));
+  if (!plan->obc_trs.empty()) CK(cudaMemcpyAsync(plan->obc_trs_dev, plan->obc_trs.data(), sizeof(ObcTr) * plan->obc_trs.size(), cudaMemcpyHostToDevice, plan->stream));
+  plan->obc_cond_bytes = std::max<long long>(cond_bytes, 1);
+  CK(cudaMalloc((void **)&plan->obc_cond, plan->obc_cond_bytes));
+  const long long fe = field_elems(plan);
+  double **scr[] = {&plan->obc_ttmp, &plan->obc_slope, &plan->obc_fx, &plan->obc_hh2};
+  for (double **pp : scr) if (!*pp) { int rc = dev_alloc(plan, pp, fe); if (rc) return rc; }
+  CK(cudaStreamSynchronize(plan->stream));
+  plan->obc_active = true;
+  return MOM6ADV_OK;
+}
+
+// One sweep with an associated OBC (obc.cu): the reference's order of operations, tracer by tracer.
+static int sweep_obc(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme) {
+  const Geom &g = plan->g;
+  cudaStream_t s = plan->stream;
+  const double min_h = 0.1 * plan->Angstrom_H, h_neglect = plan->H_subroundoff;
+  const bool x = (dir == 0);
+  int *dom = x ? plan->domore_u : plan->domore_v, *ent = x ? plan->entry_u : plan->entry_v;
+  double *res = x ? plan->uhr : plan->vhr;
+  const double *mm = x ? plan->mmx : plan->mmy;
+  const long long fe = field_elems(plan);
+  const int open_g = plan->obc_flags[x ? 0 : 1], spec_g = plan->obc_flags[x ? 2 : 3];
+  {
+    ProfScope ps(plan, MOM6ADV_KC_MASS);
+    launch_flags_begin(s, g, plan->domore_k, dom, ent, x ? rg.js : rg.js - 1, rg.je);
+    launch_mass_flux(s, dir, g, rg, res, plan->hprev, plan->areaT, min_h, ent, dom, plan->hh, plan->cfl, nullptr, nullptr, 0);
+    CK(cudaMemcpyAsync(plan->obc_hh2, plan->hh, sizeof(double) * fe, cudaMemcpyDeviceToDevice, s));
+    CK(cudaMemsetAsync(plan->obc_cond, 0, plan->obc_cond_bytes, s));
+    // :580-628 / :965-1014 -- uhh := uhr on the faces that take a prescribed inflow
+    if (spec_g || open_g)
+      for (const ObcSeg &sg : plan->obc_segs) {
+        if (!sg.has_reg || (x ? !sg.is_ew : !sg.is_ns)) continue;
+        if (!x && !sg.specified) continue;                    // the y form tests segment%specified here (:970), the x form does not
+        launch_obc_mass(s, dir, g, rg, sg, 1, res, plan->obc_hh2, plan->maskT, plan->obc_cond, ent, plan->domore_k);
+        plan->launches++;
+      }
+    if (open_g)
+      for (const ObcSeg &sg : plan->obc_segs) {
+        if (!sg.has_reg || sg.specified || (x ? !sg.is_ew : !sg.is_ns)) continue;
+        launch_obc_mass(s, dir, g, rg, sg, 2, res, plan->obc_hh2, plan->maskT, plan->obc_cond, ent, plan->domore_k);
+        plan->launches++;
+      }
+    launch_mass_update(s, dir, g, rg, res, plan->hprev, plan->obc_hh2, plan->areaT, x ? plan->uh_neglect : plan->vh_neglect,
+                       h_neglect, ent, plan->domore_k, plan->hlst, plan->ihnew, nullptr, nullptr, 0);
+    plan->launches += 3;
+  }
+  ProfScope pt(plan, x ? MOM6ADV_KC_TRACER_X : MOM6ADV_KC_TRACER_Y);
+  const int sten = (scheme == SCHEME_PPM_CW) ? 2 : 1;           // the sweeps' local stencil (:398-399 / :770-771)
+  for (int m = plan->m_lo; m < plan->m_hi; m++) {
+    const TracerSlot &ts = plan->tr[m];
+    TracerDev td;
+    td.buf[0] = ts.buf[0]; td.buf[1] = ts.buf[1];
+    td.ad_x = ts.diag[0]; td.ad_y = ts.diag[1]; td.ad2d_x = ts.diag[2]; td.ad2d_y = ts.diag[3]; td.adv_xy = ts.diag[4];
+    td.conc_underflow = ts.conc_underflow;
+    const double *T = ts.buf[plan->cur];
+    CK(cudaMemcpyAsync(plan->obc_ttmp, T, sizeof(double) * fe, cudaMemcpyDeviceToDevice, s));     // T_tmp (:436-440 / :820-822)
+    if (scheme != SCHEME_PPM_H3) launch_obc_slope(s, dir, g, rg, sten, T, mm, plan->obc_slope, plan->domore_k);
+    for (const ObcSeg &sg : plan->obc_segs) {                   // :442-478 / :825-862, in segment order
+      if (!sg.has_reg || (x ? !sg.is_ew : !sg.is_ns)) continue;
+      launch_obc_override(s, dir, g, rg, sg, plan->obc_trs_dev, m, plan->obc_ttmp, plan->obc_slope, mm, ent, plan->domore_k);
+      plan->launches++;
+    }
+    double *a2 = ts.diag[x ? 2 : 3];
+    launch_obc_flux_update(s, scheme, dir, g, rg, td, m, plan->cur, plan->obc_ttmp, plan->obc_slope, plan->hh, plan->obc_hh2,
+                           plan->cfl, plan->hlst, plan->ihnew, mm, plan->IareaT, ent, plan->domore_k, Idt,
+                           plan->obc_segs_dev, (int)plan->obc_segs.size(), plan->obc_trs_dev, plan->obc_cond, a2 ? plan->obc_fx : nullptr);
+    if (a2) { launch_obc_ad2d(s, dir, g, rg, a2, plan->obc_fx, plan->ihnew, ent, plan->domore_k, Idt); plan->launches++; }
+    plan->launches += 2;
+  }
+  plan->cur = 1 - plan->cur;
+  CK(cudaGetLastError());
+  return 0;
 }
 
 extern "C" int mom6adv_set_ntr(mom6adv_plan *plan, int ntr) {
@@ -834,6 +986,7 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
     if (plan->tr[m].diag[dir == 0 ? 2 : 3]) any_ad2d = true;
     for (int d = 0; d < 5; d++) if (plan->tr[m].diag[d]) any_diag = true;
   }
+  if (plan->obc_active) return sweep_obc(plan, dir, rg, Idt, scheme);
   const bool split_rows = plan->pull_pending && dir == 0 && plan->opt_fast && !any_diag && itt == 1;
   if (plan->pull_pending && !split_rows) {            // any other consumer needs the halo rows now
     CK(cudaStreamWaitEvent(s, plan->ev_pull_done, 0));

@@ -339,3 +339,81 @@ def bind_registry(case: SynthCase, diags: bool = False):
             tr.ad2d_y = np.full(G.shape_v(), np.nan)
             tr.advection_xy = np.full(G.shape_h(nk), np.nan)
     return Reg
+
+
+def make_obc_case(ni: int = 40, nj: int = 34, nk: int = 3, ntr: int = 5, cfl: float = 0.6, seed: int = SEED0 + 77,
+                  halo: int = 4, symmetric: bool = True):
+    """A closed rectangular basin whose outer ring of cells is masked, with one open-boundary segment on each
+    side (regional-model geometry, cf. the DOME tracers of the reference's tc3):
+
+      W  specified, tracer reservoirs tres for tracers 1..3          face I = isc,   rows jsc+2 .. jec-2
+      E  open (radiation-like), OBC_inflow_conc only, tracers 2,4    face I = iec-1, rows jsc+1 .. jec-3
+      S  specified, tres for tracer 1, inflow_conc for tracer 5      face J = jsc,   columns isc+2 .. iec-2
+      N  open, tres for tracers 1..ntr                               face J = jec-1, columns isc+3 .. iec-1
+      +  one E/W segment whose tr_Reg is unassociated (must be skipped)
+
+    Transports through the segment faces have both signs, so inflow (prescribed flux, uhh := uhr) and outflow
+    (interior scheme with the overridden exterior value) both occur.  Returns (case, OBC)."""
+    from .types import (OceanOBC, OBCSegment, OBCSegmentTracer, SegmentHI, OBC_DIRECTION_N, OBC_DIRECTION_S,
+                        OBC_DIRECTION_E, OBC_DIRECTION_W)
+    c = make_case(ni, nj, nk, ntr, halo=halo, seed=seed, cyclic_x=False, land=False, cfl=cfl, symmetric=symmetric)
+    G = c.G
+    rng = _rng(seed + 1)
+    h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
+    # masked outer ring
+    mT = G.mask2dT
+    mT[...] = 0.0
+    mT[G.pj(G.jsc + 1):G.pj(G.jec), G.pi(G.isc + 1):G.pi(G.iec)] = 1.0
+    G.mask2dCu[...] = 0.0
+    G.mask2dCv[...] = 0.0
+    for j in range(G.jsd, G.jed + 1):
+        for I in range(max(G.IsdB, G.isd), G.ied):
+            G.mask2dCu[G.pj(j), G.pI(I)] = mT[G.pj(j), G.pi(I)] * mT[G.pj(j), G.pi(I + 1)]
+    for J in range(max(G.JsdB, G.jsd), G.jed):
+        for i in range(G.isd, G.ied + 1):
+            G.mask2dCv[G.pJ(J), G.pi(i)] = mT[G.pj(J), G.pi(i)] * mT[G.pj(J + 1), G.pi(i)]
+    # exterior cells of the western side are thin (Angstrom), as masked columns are in the model: an inflow then
+    # finds an empty upwind cell, the limiter returns uhh = 0 and the OBC branch restores uhh = uhr (:592-600)
+    h[:, :, G.pi(G.isc)] = c.GV.Angstrom_H
+    u *= G.mask2dCu[None]
+    v *= G.mask2dCv[None]
+    amp_u = float(np.abs(u).max()) or 1.0
+    amp_v = float(np.abs(v).max()) or 1.0
+
+    def seg_ew(I, j0, j1, direction, specified, trs):
+        hi = SegmentHI(isd=I, ied=I + 1, jsd=j0, jed=j1, IsdB=I, IedB=I, JsdB=j0 - 1, JedB=j1)
+        G.mask2dCu[G.pj(j0):G.pj(j1) + 1, G.pI(I)] = 1.0            # the open face
+        u[:, G.pj(j0):G.pj(j1) + 1, G.pI(I)] = amp_u * rng.uniform(-1.0, 1.0, (nk, j1 - j0 + 1))
+        reg = None
+        if trs is not None:
+            reg = []
+            for (m1, use_tres, conc) in trs:
+                tres = np.ascontiguousarray(rng.uniform(0.0, 30.0, (nk, j1 - j0 + 1, 1))) if use_tres else None
+                reg.append(OBCSegmentTracer(ntr_index=m1, tres=tres, OBC_inflow_conc=conc))
+        return OBCSegment(direction=direction, is_E_or_W=True, specified=specified, HI=hi, tr_Reg=reg)
+
+    def seg_ns(J, i0, i1, direction, specified, trs):
+        hi = SegmentHI(isd=i0, ied=i1, jsd=J, jed=J + 1, IsdB=i0 - 1, IedB=i1, JsdB=J, JedB=J)
+        G.mask2dCv[G.pJ(J), G.pi(i0):G.pi(i1) + 1] = 1.0
+        v[:, G.pJ(J), G.pi(i0):G.pi(i1) + 1] = amp_v * rng.uniform(-1.0, 1.0, (nk, i1 - i0 + 1))
+        reg = []
+        for (m1, use_tres, conc) in trs:
+            tres = np.ascontiguousarray(rng.uniform(0.0, 30.0, (nk, 1, i1 - i0 + 1))) if use_tres else None
+            reg.append(OBCSegmentTracer(ntr_index=m1, tres=tres, OBC_inflow_conc=conc))
+        return OBCSegment(direction=direction, is_N_or_S=True, specified=specified, HI=hi, tr_Reg=reg)
+
+    nt = min(ntr, 3)
+    segs = [
+        seg_ew(G.isc, G.jsc + 2, G.jec - 2, OBC_DIRECTION_W, True, [(m + 1, True, 0.0) for m in range(nt)]),
+        seg_ew(G.iec - 1, G.jsc + 1, G.jec - 3, OBC_DIRECTION_E, False, [(min(2, ntr), False, 7.5), (min(4, ntr), False, -1.25)]),
+        seg_ns(G.jsc, G.isc + 2, G.iec - 2, OBC_DIRECTION_S, True, [(1, True, 0.0), (ntr, False, 3.0)]),
+        seg_ns(G.jec - 1, G.isc + 3, G.iec - 1, OBC_DIRECTION_N, False, [(m + 1, True, 0.0) for m in range(ntr)]),
+        seg_ew(G.isc + 6, G.jsc + 4, G.jsc + 8, OBC_DIRECTION_W, False, None),
+    ]
+    # the last segment is an interior dummy: undo its face edits (its tr_Reg is unassociated, it must be ignored)
+    I = G.isc + 6
+    for j in range(G.jsc + 4, G.jsc + 9):
+        G.mask2dCu[G.pj(j), G.pI(I)] = mT[G.pj(j), G.pi(I)] * mT[G.pj(j), G.pi(I + 1)]
+    OBC = OceanOBC(OBC_pe=True, segment=segs, open_u_BCs_exist_globally=True, open_v_BCs_exist_globally=True,
+                   specified_u_BCs_exist_globally=True, specified_v_BCs_exist_globally=True)
+    return c, OBC

@@ -141,11 +141,12 @@ def advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first_in=Non
         raise MOMFatalError("MOM_tracer_advect: register_tracer must be called before advect_tracer.")
     if Reg.ntr == 0:  # :124
         return 0
-    if OBC is not None and getattr(OBC, "OBC_pe", True):
-        raise MOMFatalError("MOM_tracer_advect (B200): open boundary conditions are not supported yet (status 3)")
     from . import capi
     plan = _ensure_plan(G, GV, CS, Reg)
     try:
+        if OBC is not None or getattr(plan, "_obc_set", False):    # reservoirs evolve: handed over on every call
+            plan.set_obc(OBC)
+            plan._obc_set = OBC is not None
         return plan.advect(h_end, uhtr, vhtr, dt,
                            x_first=-1 if x_first_in is None else int(bool(x_first_in)),
                            vol_prev=vol_prev,

@@ -155,3 +155,55 @@ def register_tracer(tr_ptr: np.ndarray, Reg: TracerRegistry, name: str = "",
 def lock_tracer_registry(Reg: TracerRegistry) -> None:
     """lock_tracer_registry, MOM_tracer_registry.F90:261."""
     Reg.locked = True
+
+
+# ---- open boundaries (src/core/MOM_open_boundary.F90: the members advect_x / advect_y read) --------------
+OBC_NONE, OBC_DIRECTION_N, OBC_DIRECTION_S, OBC_DIRECTION_E, OBC_DIRECTION_W = 0, 100, 200, 300, 400   # :79-83
+
+
+@dataclass
+class SegmentHI:
+    """segment%HI (hor_index_type): the segment's own index ranges."""
+    isd: int = 0
+    ied: int = 0
+    jsd: int = 0
+    jed: int = 0
+    IsdB: int = 0
+    IedB: int = 0
+    JsdB: int = 0
+    JedB: int = 0
+
+
+@dataclass
+class OBCSegmentTracer:
+    """OBC_segment_tracer_type, MOM_open_boundary.F90:119-133.  tres: [k, j, I] over (IsdB:IedB, jsd:jed, nk)
+    for E/W segments, [k, J, i] over (isd:ied, JsdB:JedB, nk) for N/S segments; None == not allocated."""
+    ntr_index: int = -1              # index in the global tracer registry, 1-based as in Fortran
+    tres: Optional[np.ndarray] = None
+    OBC_inflow_conc: float = 0.0
+
+
+@dataclass
+class OBCSegment:
+    """OBC_segment_type, MOM_open_boundary.F90:145-260 (hot-path members)."""
+    direction: int = OBC_NONE
+    is_E_or_W: bool = False
+    is_N_or_S: bool = False
+    specified: bool = False
+    HI: SegmentHI = field(default_factory=SegmentHI)
+    tr_Reg: Optional[List[OBCSegmentTracer]] = None      # None == unassociated; ntseg = len(tr_Reg)
+
+
+@dataclass
+class OceanOBC:
+    """ocean_OBC_type, MOM_open_boundary.F90:264-400 (hot-path members)."""
+    OBC_pe: bool = True
+    segment: List[OBCSegment] = field(default_factory=list)
+    open_u_BCs_exist_globally: bool = False
+    open_v_BCs_exist_globally: bool = False
+    specified_u_BCs_exist_globally: bool = False
+    specified_v_BCs_exist_globally: bool = False
+
+    @property
+    def number_of_segments(self) -> int:
+        return len(self.segment)

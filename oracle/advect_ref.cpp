@@ -10,8 +10,8 @@
 //   * SIGN(a,b) is copysign(a,b);
 //   * parentheses honoured, same-precedence chains left to right;
 //   * no FMA contraction: build with -ffp-contract=off (oracle/Makefile).
-// The OBC branches (:442-478,580-628,825-862,965-1014) are not restated: the
-// oracle corresponds to a call with OBC unassociated.
+// The OBC branches (:442-478,580-628,825-862,965-1014) are restated too; OBC == NULL is the
+// unassociated pointer.
 //
 // Uninitialised reads in the reference (SURVEY.md hazard 7): do_i outside the
 // range written by the sweep is treated as .false. here.
@@ -70,6 +70,7 @@ struct Flags2 {  // logical (jlo:jhi, 1:nk)
 
 struct Ctx {
   const ora_grid &G;
+  const ora_obc *OBC = nullptr;      // NULL == unassociated
   V2 areaT, IareaT, mask2dT, mask2dCu, mask2dCv;
   explicit Ctx(const ora_grid &g)
       : G(g), areaT(g.areaT, g.isd, g.ied, g.jsd), IareaT(g.IareaT, g.isd, g.ied, g.jsd),
@@ -143,7 +144,35 @@ void advect_x(const Ctx &C, ora_tracer *Tr, int ntr, V3 &hprev, V3 &uhr, V2 &uh_
       V3 t(Tr[m].t, isd, ied, jsd, jed);
       for (int i = isd; i <= ied; i++) T_tmp(i, m) = t(i, j, k);
     }
-    // OBC overrides :442-478 not restated (OBC unassociated).
+    // loop through open boundaries and recalculate flux terms :442-478
+    if (C.OBC) { if (C.OBC->OBC_pe) {
+      for (int n = 0; n < C.OBC->number_of_segments; n++) {
+        const ora_obc_segment *segment = &C.OBC->segment[n];
+        if (segment->ntseg < 0) continue;                // .not. associated(segment%tr_Reg)
+        if (segment->is_E_or_W) {
+          if (j >= segment->jsd && j <= segment->jed) {
+            const int I = segment->IsdB;                 // Fortran: I and i are one variable
+            for (int m = 0; m < segment->ntseg; m++) {   // replace tracers with OBC values
+              const int ntr_id = segment->Tr[m].ntr_index - 1;
+              if (segment->Tr[m].tres) {
+                V3 tres(segment->Tr[m].tres, segment->IsdB, segment->IedB, segment->jsd, segment->jed);
+                if (segment->direction == ORA_OBC_DIRECTION_W) T_tmp(I, ntr_id) = tres(I, j, k);
+                else T_tmp(I + 1, ntr_id) = tres(I, j, k);
+              } else {
+                if (segment->direction == ORA_OBC_DIRECTION_W) T_tmp(I, ntr_id) = segment->Tr[m].OBC_inflow_conc;
+                else T_tmp(I + 1, ntr_id) = segment->Tr[m].OBC_inflow_conc;
+              }
+            }
+            for (int m = 0; m < ntr; m++) {              // Apply update tracer values for slope calculation
+              for (int i = segment->IsdB - 1; i <= segment->IsdB + 1; i++) {
+                double Tp = T_tmp(i + 1, m), Tc = T_tmp(i, m), Tm = T_tmp(i - 1, m);
+                slope_x(i, m) = plm_slope(Tp, Tc, Tm, C.mask2dCu(i, j), C.mask2dCu(i - 1, j));
+              }
+            }
+          }
+        }
+      }
+    } }
 
     for (int I = is - 1; I <= ie; I++) {                 // :485-514
       const int i = I;
@@ -218,7 +247,53 @@ void advect_x(const Ctx &C, ora_tracer *Tr, int ntr, V3 &hprev, V3 &uhr, V2 &uh_
         }
       }
     }
-    // OBC flux overrides :580-628 not restated.
+    if (C.OBC) { if (C.OBC->OBC_pe) {                     // :580-628
+      if (C.OBC->specified_u_BCs_exist_globally || C.OBC->open_u_BCs_exist_globally) {
+        for (int n = 0; n < C.OBC->number_of_segments; n++) {
+          const ora_obc_segment *segment = &C.OBC->segment[n];
+          if (segment->ntseg < 0) continue;
+          if (segment->is_E_or_W) {
+            if (j >= segment->jsd && j <= segment->jed) {
+              const int I = segment->IsdB;
+              // Tracer fluxes are set to prescribed values ... Now changing to simply fixed inflows.
+              if (((uhr(I, j, k) > 0.0) && (segment->direction == ORA_OBC_DIRECTION_W)) ||
+                  ((uhr(I, j, k) < 0.0) && (segment->direction == ORA_OBC_DIRECTION_E))) {
+                uhh(I) = uhr(I, j, k);
+                for (int m = 0; m < segment->ntseg; m++) {
+                  const int ntr_id = segment->Tr[m].ntr_index - 1;
+                  if (segment->Tr[m].tres) {
+                    V3 tres(segment->Tr[m].tres, segment->IsdB, segment->IedB, segment->jsd, segment->jed);
+                    flux_x(I, j, ntr_id) = uhh(I) * tres(I, j, k);
+                  } else { flux_x(I, j, ntr_id) = uhh(I) * segment->Tr[m].OBC_inflow_conc; }
+                }
+              }
+            }
+          }
+        }
+      }
+      if (C.OBC->open_u_BCs_exist_globally) {
+        for (int n = 0; n < C.OBC->number_of_segments; n++) {
+          const ora_obc_segment *segment = &C.OBC->segment[n];
+          const int I = segment->IsdB, i = I;
+          if (segment->is_E_or_W && (j >= segment->jsd && j <= segment->jed)) {
+            if (segment->specified) continue;
+            if (segment->ntseg < 0) continue;
+            // Tracer fluxes are set to prescribed values only for inflows from masked areas.
+            if (((uhr(I, j, k) > 0.0) && (C.mask2dT(i, j) < 0.5)) ||
+                ((uhr(I, j, k) < 0.0) && (C.mask2dT(i + 1, j) < 0.5))) {
+              uhh(I) = uhr(I, j, k);
+              for (int m = 0; m < segment->ntseg; m++) {
+                const int ntr_id = segment->Tr[m].ntr_index - 1;
+                if (segment->Tr[m].tres) {
+                  V3 tres(segment->Tr[m].tres, segment->IsdB, segment->IedB, segment->jsd, segment->jed);
+                  flux_x(I, j, ntr_id) = uhh(I) * tres(I, j, k);
+                } else { flux_x(I, j, ntr_id) = uhh(I) * segment->Tr[m].OBC_inflow_conc; }
+              }
+            }
+          }
+        }
+      }
+    } }
 
     for (int I = is - 1; I <= ie; I++) {                 // :632-635
       uhr(I, j, k) = uhr(I, j, k) - uhh(I);
@@ -349,7 +424,37 @@ void advect_y(const Ctx &C, ora_tracer *Tr, int ntr, V3 &hprev, V3 &vhr, V2 &vh_
     V3 t(Tr[m].t, isd, ied, jsd, jed);
     for (int i = isd; i <= ied; i++) T_tmp(i, m, j) = t(i, j, k);
   }
-  // OBC overrides :825-862 not restated.
+  // loop through open boundaries and recalculate flux terms :825-862
+  if (C.OBC) { if (C.OBC->OBC_pe) {
+    for (int n = 0; n < C.OBC->number_of_segments; n++) {
+      const ora_obc_segment *segment = &C.OBC->segment[n];
+      if (segment->ntseg < 0) continue;
+      for (int i = is; i <= ie; i++) {
+        if (segment->is_N_or_S) {
+          if (i >= segment->isd && i <= segment->ied) {
+            const int J = segment->JsdB;                 // Fortran: J and j are one variable
+            for (int m = 0; m < segment->ntseg; m++) {   // replace tracers with OBC values
+              const int ntr_id = segment->Tr[m].ntr_index - 1;
+              if (segment->Tr[m].tres) {
+                V3 tres(segment->Tr[m].tres, segment->isd, segment->ied, segment->JsdB, segment->JedB);
+                if (segment->direction == ORA_OBC_DIRECTION_S) T_tmp(i, ntr_id, J) = tres(i, J, k);
+                else T_tmp(i, ntr_id, J + 1) = tres(i, J, k);
+              } else {
+                if (segment->direction == ORA_OBC_DIRECTION_S) T_tmp(i, ntr_id, J) = segment->Tr[m].OBC_inflow_conc;
+                else T_tmp(i, ntr_id, J + 1) = segment->Tr[m].OBC_inflow_conc;
+              }
+            }
+            for (int m = 0; m < ntr; m++) {              // Apply update tracer values for slope calculation
+              for (int j = segment->JsdB - 1; j <= segment->JsdB + 1; j++) {
+                double Tp = T_tmp(i, m, j + 1), Tc = T_tmp(i, m, j), Tm = T_tmp(i, m, j - 1);
+                slope_y(i, m, j) = plm_slope(Tp, Tc, Tm, C.mask2dCv(i, j), C.mask2dCv(i, j - 1));
+              }
+            }
+          }
+        }
+      }
+    }
+  } }
 
   for (int J = js - 1; J <= je; J++) {
     const int j = J;
@@ -425,7 +530,55 @@ void advect_y(const Ctx &C, ora_tracer *Tr, int ntr, V3 &hprev, V3 &vhr, V2 &vh_
           }
         }
       }
-      // OBC flux overrides :965-1014 not restated.
+      if (C.OBC) { if (C.OBC->OBC_pe) {                 // :965-1014
+        if (C.OBC->specified_v_BCs_exist_globally || C.OBC->open_v_BCs_exist_globally) {
+          for (int n = 0; n < C.OBC->number_of_segments; n++) {
+            const ora_obc_segment *segment = &C.OBC->segment[n];
+            if (!segment->specified) continue;
+            if (segment->ntseg < 0) continue;
+            if (segment->is_N_or_S) {
+              if (J >= segment->JsdB && J <= segment->JedB) {
+                for (int i = segment->isd; i <= segment->ied; i++) {
+                  if (((vhr(i, J, k) > 0.0) && (segment->direction == ORA_OBC_DIRECTION_S)) ||
+                      ((vhr(i, J, k) < 0.0) && (segment->direction == ORA_OBC_DIRECTION_N))) {
+                    vhh(i, J) = vhr(i, J, k);
+                    for (int m = 0; m < segment->ntseg; m++) {
+                      const int ntr_id = segment->Tr[m].ntr_index - 1;
+                      if (segment->Tr[m].tres) {
+                        V3 tres(segment->Tr[m].tres, segment->isd, segment->ied, segment->JsdB, segment->JedB);
+                        flux_y(i, ntr_id, J) = vhh(i, J) * tres(i, J, k);
+                      } else { flux_y(i, ntr_id, J) = vhh(i, J) * segment->Tr[m].OBC_inflow_conc; }
+                    }
+                  }
+                }
+              }
+            }
+          }
+        }
+        if (C.OBC->open_v_BCs_exist_globally) {
+          for (int n = 0; n < C.OBC->number_of_segments; n++) {
+            const ora_obc_segment *segment = &C.OBC->segment[n];
+            if (segment->specified) continue;
+            if (segment->ntseg < 0) continue;
+            if (segment->is_N_or_S && (J >= segment->JsdB && J <= segment->JedB)) {
+              for (int i = segment->isd; i <= segment->ied; i++) {
+                // Tracer fluxes are set to prescribed values only for inflows from masked areas.
+                if (((vhr(i, J, k) > 0.0) && (C.mask2dT(i, j) < 0.5)) ||
+                    ((vhr(i, J, k) < 0.0) && (C.mask2dT(i, j + 1) < 0.5))) {
+                  vhh(i, J) = vhr(i, J, k);
+                  for (int m = 0; m < segment->ntseg; m++) {
+                    const int ntr_id = segment->Tr[m].ntr_index - 1;
+                    if (segment->Tr[m].tres) {
+                      V3 tres(segment->Tr[m].tres, segment->isd, segment->ied, segment->JsdB, segment->JedB);
+                      flux_y(i, ntr_id, J) = vhh(i, J) * tres(i, J, k);
+                    } else { flux_y(i, ntr_id, J) = vhh(i, J) * segment->Tr[m].OBC_inflow_conc; }
+                  }
+                }
+              }
+            }
+          }
+        }
+      } }
     } else {                                          // :1016-1018
       for (int i = is; i <= ie; i++) vhh(i, J) = 0.0;
       for (int m = 0; m < ntr; m++) for (int i = is; i <= ie; i++) flux_y(i, m, J) = 0.0;
@@ -663,12 +816,23 @@ extern "C" int ora_advect_tracer(const ora_grid *Gp, const ora_cs *CS, ora_trace
                                  int update_vol_prev, double *uhr_out, double *vhr_out,
                                  const ora_domain *dom, ora_pass_fn pass, ora_sum_fn sum,
                                  void *ctx, int *n_iter_out, int nthreads) {
+  return ora_advect_tracer_obc(Gp, CS, Tr, ntr, h_end_, uhtr_, vhtr_, dt, x_first_in, vol_prev_, max_iter_in,
+                               update_vol_prev, uhr_out, vhr_out, dom, pass, sum, ctx, n_iter_out, nthreads, nullptr);
+}
+
+extern "C" int ora_advect_tracer_obc(const ora_grid *Gp, const ora_cs *CS, ora_tracer *Tr, int ntr,
+                                     const double *h_end_, const double *uhtr_, const double *vhtr_,
+                                     double dt, int x_first_in, double *vol_prev_, int max_iter_in,
+                                     int update_vol_prev, double *uhr_out, double *vhr_out,
+                                     const ora_domain *dom, ora_pass_fn pass, ora_sum_fn sum,
+                                     void *ctx, int *n_iter_out, int nthreads, const ora_obc *OBC) {
   if (n_iter_out) *n_iter_out = 0;
   if (!CS || !Gp) return 1;               // :120-121
   if (!Tr && ntr != 0) return 1;          // :122-123
   if (ntr == 0) return 0;                 // :124
   const ora_grid &G = *Gp;
   Ctx C(G);
+  C.OBC = OBC;
   (void)nthreads;
 #ifdef _OPENMP
   if (nthreads > 0) omp_set_num_threads(nthreads);

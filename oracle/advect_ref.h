@@ -63,6 +63,31 @@ typedef struct {
   double conc_underflow;
 } ora_tracer;
 
+/* ocean_OBC_type / OBC_segment_type / segment tracer registry members read by the path
+ * (MOM_tracer_advect.F90:442-478,580-628,825-862,965-1014; src/core/MOM_open_boundary.F90:119-142,254,333).
+ * tres has the segment's own bounds: E/W segments (IsdB:IedB, jsd:jed, nk), N/S (isd:ied, JsdB:JedB, nk);
+ * NULL == not allocated.  ntr_index is 1-based as in Fortran.  ntseg < 0 == tr_Reg unassociated. */
+enum { ORA_OBC_NONE = 0, ORA_OBC_DIRECTION_N = 100, ORA_OBC_DIRECTION_S = 200, ORA_OBC_DIRECTION_E = 300,
+       ORA_OBC_DIRECTION_W = 400 };
+typedef struct {
+  int ntr_index;
+  const double *tres;
+  double OBC_inflow_conc;
+} ora_obc_tracer;
+typedef struct {
+  int is_E_or_W, is_N_or_S, direction, specified;
+  int isd, ied, jsd, jed, IsdB, IedB, JsdB, JedB;   /* segment%HI */
+  int ntseg;
+  const ora_obc_tracer *Tr;
+} ora_obc_segment;
+typedef struct {
+  int OBC_pe;
+  int number_of_segments;
+  int open_u_BCs_exist_globally, open_v_BCs_exist_globally;
+  int specified_u_BCs_exist_globally, specified_v_BCs_exist_globally;
+  const ora_obc_segment *segment;
+} ora_obc;
+
 /* Stand-ins for do_group_pass (MOM_tracer_advect.F90:206) and
  * sum_across_PEs (:305).  ctx is passed through untouched. */
 typedef void (*ora_pass_fn)(void *ctx, double *uhr, double *vhr, double *hprev,
@@ -100,6 +125,14 @@ int ora_advect_tracer(const ora_grid *G, const ora_cs *CS, ora_tracer *Tr, int n
                       int update_vol_prev, double *uhr_out, double *vhr_out,
                       const ora_domain *dom, ora_pass_fn pass, ora_sum_fn sum,
                       void *ctx, int *n_iter_out, int nthreads);
+
+/* The same with an associated OBC (NULL == unassociated). */
+int ora_advect_tracer_obc(const ora_grid *G, const ora_cs *CS, ora_tracer *Tr, int ntr,
+                          const double *h_end, const double *uhtr, const double *vhtr,
+                          double dt, int x_first_in, double *vol_prev, int max_iter_in,
+                          int update_vol_prev, double *uhr_out, double *vhr_out,
+                          const ora_domain *dom, ora_pass_fn pass, ora_sum_fn sum,
+                          void *ctx, int *n_iter_out, int nthreads, const ora_obc *OBC);
 
 /* Emulated multi-PE run: all ranks advance in lock step (one thread each),
  * exchanging halos through the emulated group pass.  Same optional-argument

@@ -51,6 +51,23 @@ class ora_rank(C.Structure):
                 ("n_iter", C.c_int)]
 
 
+class ora_obc_tracer(C.Structure):
+    _fields_ = [("ntr_index", C.c_int), ("tres", _dp), ("OBC_inflow_conc", C.c_double)]
+
+
+class ora_obc_segment(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("is_E_or_W", "is_N_or_S", "direction", "specified",
+                                       "isd", "ied", "jsd", "jed", "IsdB", "IedB", "JsdB", "JedB", "ntseg")] + \
+               [("Tr", C.POINTER(ora_obc_tracer))]
+
+
+class ora_obc(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("OBC_pe", "number_of_segments", "open_u_BCs_exist_globally",
+                                       "open_v_BCs_exist_globally", "specified_u_BCs_exist_globally",
+                                       "specified_v_BCs_exist_globally")] + \
+               [("segment", C.POINTER(ora_obc_segment))]
+
+
 PASS_FN = C.CFUNCTYPE(None, C.c_void_p, _dp, _dp, _dp, C.POINTER(ora_tracer), C.c_int)
 SUM_FN = C.CFUNCTYPE(None, C.c_void_p, C.POINTER(C.c_int), C.c_int)
 
@@ -73,6 +90,8 @@ def lib():
             C.POINTER(ora_grid), C.POINTER(ora_cs), C.POINTER(ora_tracer), C.c_int,
             _dp, _dp, _dp, C.c_double, C.c_int, _dp, C.c_int, C.c_int, _dp, _dp,
             C.POINTER(ora_domain), C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.c_int]
+        _lib.ora_advect_tracer_obc.restype = C.c_int
+        _lib.ora_advect_tracer_obc.argtypes = _lib.ora_advect_tracer.argtypes + [C.POINTER(ora_obc)]
         _lib.ora_advect_tracer_multi.restype = C.c_int
         _lib.ora_advect_tracer_multi.argtypes = [
             C.c_int, C.POINTER(ora_rank), C.POINTER(ora_domain), C.POINTER(ora_cs),
@@ -131,6 +150,36 @@ def make_tracers(Reg):
     return arr
 
 
+def make_obc(OBC):
+    """ocean_OBC_type -> ora_obc (returns the struct and the objects that must stay alive)."""
+    if OBC is None:
+        return None, []
+    keep = []
+    segs = (ora_obc_segment * max(OBC.number_of_segments, 1))()
+    for n, sg in enumerate(OBC.segment):
+        s = segs[n]
+        s.is_E_or_W, s.is_N_or_S, s.direction, s.specified = int(sg.is_E_or_W), int(sg.is_N_or_S), int(sg.direction), int(sg.specified)
+        for f in ("isd", "ied", "jsd", "jed", "IsdB", "IedB", "JsdB", "JedB"):
+            setattr(s, f, int(getattr(sg.HI, f)))
+        if sg.tr_Reg is None:
+            s.ntseg = -1
+        else:
+            s.ntseg = len(sg.tr_Reg)
+            trs = (ora_obc_tracer * max(len(sg.tr_Reg), 1))()
+            for m, t in enumerate(sg.tr_Reg):
+                trs[m].ntr_index, trs[m].tres, trs[m].OBC_inflow_conc = int(t.ntr_index), _p(t.tres), float(t.OBC_inflow_conc)
+            keep.append(trs)
+            s.Tr = C.cast(trs, C.POINTER(ora_obc_tracer))
+    o = ora_obc()
+    o.OBC_pe, o.number_of_segments = int(OBC.OBC_pe), OBC.number_of_segments
+    o.open_u_BCs_exist_globally, o.open_v_BCs_exist_globally = int(OBC.open_u_BCs_exist_globally), int(OBC.open_v_BCs_exist_globally)
+    o.specified_u_BCs_exist_globally = int(OBC.specified_u_BCs_exist_globally)
+    o.specified_v_BCs_exist_globally = int(OBC.specified_v_BCs_exist_globally)
+    o.segment = C.cast(segs, C.POINTER(ora_obc_segment))
+    keep.append(segs)
+    return o, keep
+
+
 def _opt_flag(v):
     return -1 if v is None else int(bool(v))
 
@@ -141,7 +190,6 @@ def advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first_in=Non
     """Oracle advect_tracer with the reference's argument list
     (MOM_tracer_advect.F90:52-53).  Updates Reg.Tr[m].t in place.  Returns the
     number of iterations taken."""
-    assert OBC is None, "the oracle restates the OBC-unassociated path only"
     if CS is None:
         raise RuntimeError("MOM_tracer_advect: tracer_advect_init must be called before advect_tracer.")
     if Reg is None:
@@ -151,11 +199,12 @@ def advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first_in=Non
     nit = C.c_int(0)
     pf = C.cast(pass_fn, C.c_void_p) if pass_fn is not None else None
     sf = C.cast(sum_fn, C.c_void_p) if sum_fn is not None else None
-    rc = lib().ora_advect_tracer(
+    obc, _keep = make_obc(OBC)
+    rc = lib().ora_advect_tracer_obc(
         C.byref(g), C.byref(cs), tr, Reg.ntr, _p(h_end), _p(uhtr), _p(vhtr), float(dt),
         _opt_flag(x_first_in), _p(vol_prev), -1 if max_iter_in is None else int(max_iter_in),
         _opt_flag(update_vol_prev), _p(uhr_out), _p(vhr_out), C.byref(dom), pf, sf, None,
-        C.byref(nit), int(nthreads))
+        C.byref(nit), int(nthreads), C.byref(obc) if obc is not None else None)
     if rc != 0:
         raise RuntimeError("oracle advect_tracer failed: %d" % rc)
     return nit.value

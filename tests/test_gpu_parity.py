@@ -202,3 +202,31 @@ def test_hundred_consecutive_calls_bitwise(scheme, x_first):
     """double-gyre shape, 10 tracers, 100 consecutive calls, bitwise."""
     c, Ro, Rg, outs, nit = _run_pair(44, 40, 2, 10, scheme, cfl=0.45, x_first=x_first, ncalls=100)
     _assert_bitwise(c, Ro, Rg, outs)
+
+
+@pytest.mark.parametrize("scheme", ["PLM", "PPM", "PPM:H3"])
+@pytest.mark.parametrize("x_first", [True, False])
+def test_open_boundaries_bitwise(scheme, x_first):
+    """Associated OBC (:442-478,580-628,825-862,965-1014): specified and open segments on all four sides,
+    tracer reservoirs and OBC_inflow_conc, inflow and outflow faces, an unassociated segment registry."""
+    c, OBC = synth.make_obc_case()
+    params = {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}
+    h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
+    nk = c.GV.ke
+    res = []
+    for impl in (oracle.advect_tracer, advect_tracer):
+        CS = tracer_advect_init(None, c.G, None, params, None, None)
+        R = synth.bind_registry(c, diags=True)
+        uo, vo = np.zeros(c.G.shape_u(nk)), np.zeros(c.G.shape_v(nk))
+        nits = [impl(h, u, v, OBC, c.dt, c.G, c.GV, None, CS, R, x_first_in=x_first, uhr_out=uo, vhr_out=vo) for _ in range(2)]
+        if impl is advect_tracer:
+            tracer_advect_end(CS)
+        res.append((R, uo, vo, nits))
+    (Ro, uo_o, vo_o, n_o), (Rg, uo_g, vo_g, n_g) = res
+    assert n_o == n_g
+    # the OBC must matter: the same call without it gives another answer
+    CS = tracer_advect_init(None, c.G, None, params, None, None)
+    Rn = synth.bind_registry(c)
+    oracle.advect_tracer(h, u, v, None, c.dt, c.G, c.GV, None, CS, Rn, x_first_in=x_first)
+    assert any(not np.array_equal(c.G.interior(a.t), c.G.interior(b.t)) for a, b in zip(Rn.Tr, Ro.Tr))
+    _assert_bitwise(c, Ro, Rg, (uo_o, vo_o, uo_g, vo_g), diags=True)
