@@ -34,15 +34,34 @@ CASES = {
     "dg_ppm_diags":   (44, 40, 2, 4, "PPM", 0.9, None, 1, True, False, {}),
     "dg_ppm_offline": (44, 40, 2, 4, "PPM", 1.5, None, 2, False, True, {}),
     "closed_nonsym":  (37, 29, 3, 3, "PPM", 0.8, None, 1, False, False, {"symmetric": False, "cyclic_x": False}),
+    # open boundaries on all four sides (synth.make_obc_case): kwargs marked "obc" build the OBC as well
+    "obc_ppm":        (40, 34, 3, 5, "PPM", 0.6, None, 2, True, False, {"obc": True}),
+    "obc_plm_yfirst": (40, 34, 3, 5, "PLM", 0.6, False, 1, False, False, {"obc": True}),
 }
 GRID_FIELDS = ("areaT", "IareaT", "mask2dT", "mask2dCu", "mask2dCv")
 
 
 def build_case(spec):
     ni, nj, nk, ntr, scheme, cfl, x_first, ncalls, diags, offline, kw = spec
-    c = synth.make_case(ni, nj, nk, ntr, cfl=cfl, **kw)
+    if kw.get("obc"):
+        c, OBC = synth.make_obc_case(ni, nj, nk, ntr, cfl=cfl)
+        c.OBC = OBC
+    else:
+        c = synth.make_case(ni, nj, nk, ntr, cfl=cfl, **kw)
+        c.OBC = None
     Reg = synth.bind_registry(c, diags=diags)
     return c, Reg
+
+
+def obc_reservoirs(OBC):
+    """(key, array) of every allocated tres, in segment / entry order."""
+    out = []
+    if OBC is not None:
+        for n, sg in enumerate(OBC.segment):
+            for e, t in enumerate(sg.tr_Reg or []):
+                if t.tres is not None:
+                    out.append(("obc_tres_%d_%d" % (n, e), t.tres))
+    return out
 
 
 def run_oracle(c, Reg, spec, inputs=None):
@@ -55,7 +74,7 @@ def run_oracle(c, Reg, spec, inputs=None):
     vol = inputs["vol_prev"].copy() if (inputs and offline) else (offline_volume(c, h) if offline else None)
     nits = []
     for call in range(ncalls):
-        nits.append(oracle.advect_tracer(h, u, v, None, c.dt, G, c.GV, None, CS, Reg, x_first_in=x_first,
+        nits.append(oracle.advect_tracer(h, u, v, c.OBC, c.dt, G, c.GV, None, CS, Reg, x_first_in=x_first,
                                          vol_prev=vol, max_iter_in=2 if offline else None,
                                          update_vol_prev=True if offline else None, uhr_out=uo, vhr_out=vo))
     out = {"n_iter": np.array(nits), "uhr_out": uo, "vhr_out": vo}
@@ -90,6 +109,8 @@ def main():
             data["t_in_%02d" % m] = tr.t.copy()
         if spec[9]:
             data["vol_prev"] = offline_volume(c, data["h_end"])
+        for key, a in obc_reservoirs(c.OBC):
+            data[key] = a.copy()
         data.update(run_oracle(c, Reg, spec))
         path = os.path.join(HERE, name + ".npz")
         np.savez_compressed(path, **data)

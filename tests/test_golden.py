@@ -26,6 +26,8 @@ def _load(name):
     for m, tr in enumerate(Reg.Tr):
         tr.t[...] = z["t_in_%02d" % m]
         assert tr.conc_underflow == z["conc_underflow"][m]
+    for key, a in mg.obc_reservoirs(c.OBC):
+        a[...] = z[key]
     return spec, z, c, Reg
 
 
@@ -65,7 +67,7 @@ def test_cuda_reproduces_golden(name):
     vol = z["vol_prev"].copy() if offline else None
     nits = []
     for call in range(ncalls):
-        nits.append(advect_tracer(z["h_end"], z["uhtr"], z["vhtr"], None, c.dt, G, c.GV, None, CS, Reg, x_first_in=x_first,
+        nits.append(advect_tracer(z["h_end"], z["uhtr"], z["vhtr"], c.OBC, c.dt, G, c.GV, None, CS, Reg, x_first_in=x_first,
                                   vol_prev=vol, max_iter_in=2 if offline else None,
                                   update_vol_prev=True if offline else None, uhr_out=uo, vhr_out=vo))
     tracer_advect_end(CS)
