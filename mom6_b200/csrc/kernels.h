@@ -74,10 +74,12 @@ struct PeerBuild {
   long long peer_plane = 0;                       // the sender's plane size (its level stride)
 };
 void make_geom(const mom6adv_grid *gr, Geom &g, int &wbase);
-// Is halo point (i,j) of stagger pos within `depth` cells of the computational domain (faces: of a cell that is)?
+// Is halo point (i,j) of stagger pos within `depth` ROWS of the computational domain (v faces: of a row that is)?
+// Only whole rows are dropped: trimming columns would turn the 32-byte E/W halo pieces into partial-sector writes.
 inline bool halo_point_used(int pos, int i, int j, int isc, int iec, int jsc, int jec, int depth) {
+  (void)i; (void)isc; (void)iec;
   if (depth <= 0) return true;
-  const int ilo = isc - depth - (pos == 1), jlo = jsc - depth - (pos == 2);
-  return i >= ilo && i <= iec + depth && j >= jlo && j <= jec + depth;
+  const int jlo = jsc - depth - (pos == 2);
+  return j >= jlo && j <= jec + depth;
 }
 void build_halo_exchange(const Geom &g, const ExchangeSpec &x, int me, HaloBuild local[3], std::vector<PeerBuild> &peers);
