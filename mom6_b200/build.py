@@ -30,6 +30,23 @@ def _nvcc() -> str:
     raise RuntimeError("nvcc not found")
 
 
+def _nccl_flags():
+    """Link against the NCCL that PyTorch ships (site-packages/nvidia/nccl), with an rpath to it: the host
+    mirror and torch.distributed then share ONE libnccl.so.2 whichever is loaded first (the system 2.27 loaded
+    first would leave torch's libtorch_cuda.so without its 2.28 symbols).  A pure Fortran host links the system
+    library instead: falls back to -lnccl when the bundled copy is absent."""
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        base = list(spec.submodule_search_locations)[0] if spec and spec.submodule_search_locations else None
+    except Exception:
+        base = None
+    if base and os.path.exists(os.path.join(base, "lib", "libnccl.so.2")) and not os.environ.get("MOM6ADV_SYSTEM_NCCL"):
+        lib = os.path.join(base, "lib")
+        return ["-I" + os.path.join(base, "include"), "-L" + lib, "-l:libnccl.so.2", "-Xlinker", "-rpath=" + lib]
+    return ["-lnccl"]
+
+
 def sources():
     return [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
 
@@ -46,7 +63,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not stale():
         return LIB
     extra = os.environ.get("MOM6ADV_NVCC_EXTRA", "").split()      # experiments: -DXMINB=5 ...
-    cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + sources() + ["-lnccl"]
+    cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + sources() + _nccl_flags()
     env = dict(os.environ)
     # the image exports CC/CXX pointing at a wrapper without libgomp; nvcc needs the system g++
     cmd += ["-ccbin", "/usr/bin/g++"] if os.path.exists("/usr/bin/g++") else []
