@@ -203,21 +203,17 @@ void launch_flags_begin(cudaStream_t s, const Geom &g, const int *domore_k, int 
 // Written for every point of the padded array (0 where the face is not part of
 // the sweep) so that the kernels that follow need no flag logic of their own.
 // ---------------------------------------------------------------------------
+// Limited transport through one face and its CFL number (:485-514 / :871-900); ur = residual transport of the
+// face if its row is swept, else 0.  Writes hh, cfl and the per-face factors of the flux formulas.
 template <int DIR>
-__global__ void k_mass_flux(Geom g, Range rg, const double *__restrict__ res, const double *__restrict__ hprev,
-                            const double *__restrict__ areaT, double min_h, const int *__restrict__ entry,
-                            int *__restrict__ domore, double *__restrict__ hh, double *__restrict__ cfl,
-                            double *__restrict__ hcv, double *__restrict__ gv, int plm) {
-  int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y, k0 = blockIdx.z;
-  if (ci >= g.P) return;
-  const int i = ci - g.coff, j = rj - g.roff;
-  const long long q = gidx(g, ci, rj, k0), q2 = gidx(g, ci, rj, 0);
+__device__ __forceinline__ void mass_flux_face(const Geom &g, long long q, long long q2, int fl, bool swept, double ur,
+                                               const double *__restrict__ res, const double *__restrict__ hprev,
+                                               const double *__restrict__ areaT, double min_h, int *__restrict__ domore,
+                                               double *__restrict__ hh, double *__restrict__ cfl,
+                                               double *__restrict__ hcv, double *__restrict__ gv, int plm) {
   const int st = (DIR == 0) ? 1 : g.P;
-  bool face_ok = (DIR == 0) ? (i >= rg.is - 1 && i <= rg.ie && j >= rg.js && j <= rg.je)
-                            : (i >= rg.is && i <= rg.ie && j >= rg.js - 1 && j <= rg.je);
   double uh = 0.0, cf = 0.0;
-  if (face_ok && entry[k0 * g.R + rj]) {
-    const double ur = res[q];
+  if (swept) {
     const double hm = hprev[q], hp = hprev[q + st];   // cells on the low / high side of the face
     const double tiny_h = DBL_MIN;
     if ((ur == 0.0) || ((ur < 0.0) && (hp <= tiny_h)) || ((ur > 0.0) && (hm <= tiny_h))) {
@@ -227,7 +223,7 @@ __global__ void k_mass_flux(Geom g, Range rg, const double *__restrict__ res, co
       double hlos = gmax2(0.0, res[q + st]);
       if ((((hup - hlos) + ur) < 0.0) && ((0.5 * hup + ur) < 0.0)) {
         uh = gmin3(-0.5 * hup, -hup + hlos, 0.0);
-        domore[k0 * g.R + rj] = 1;
+        domore[fl] = 1;
       } else {
         uh = ur;
       }
@@ -237,7 +233,7 @@ __global__ void k_mass_flux(Geom g, Range rg, const double *__restrict__ res, co
       double hlos = gmax2(0.0, -res[q - st]);
       if ((((hup - hlos) - ur) < 0.0) && ((0.5 * hup - ur) < 0.0)) {
         uh = gmax3(0.5 * hup, hup - hlos, 0.0);
-        domore[k0 * g.R + rj] = 1;
+        domore[fl] = 1;
       } else {
         uh = ur;
       }
@@ -250,6 +246,107 @@ __global__ void k_mass_flux(Geom g, Range rg, const double *__restrict__ res, co
     gv[q] = plm ? (1. - cf) : (1. - (2. / 3.) * cf);     // 1-CFL (:565,569) or 1-2/3*CFL
   }
 }
+template <int DIR>
+__device__ __forceinline__ bool mass_face_ok(const Range &rg, int i, int j) {
+  return (DIR == 0) ? (i >= rg.is - 1 && i <= rg.ie && j >= rg.js && j <= rg.je)
+                    : (i >= rg.is && i <= rg.ie && j >= rg.js - 1 && j <= rg.je);
+}
+
+// dense form: one thread per face of the padded plane
+template <int DIR>
+__global__ void k_mass_flux(Geom g, Range rg, const double *__restrict__ res, const double *__restrict__ hprev,
+                            const double *__restrict__ areaT, double min_h, const int *__restrict__ entry,
+                            int *__restrict__ domore, double *__restrict__ hh, double *__restrict__ cfl,
+                            double *__restrict__ hcv, double *__restrict__ gv, int plm) {
+  const int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y, k0 = blockIdx.z;
+  if (ci >= g.P) return;
+  const int i = ci - g.coff, j = rj - g.roff;
+  const long long q = gidx(g, ci, rj, k0), q2 = gidx(g, ci, rj, 0);
+  const bool swept = mass_face_ok<DIR>(rg, i, j) && entry[k0 * g.R + rj];
+  mass_flux_face<DIR>(g, q, q2, k0 * g.R + rj, swept, swept ? res[q] : 0.0, res, hprev, areaT, min_h, domore, hh, cfl, hcv, gv, plm);
+}
+
+// Residual trips: uhr / vhr are zero almost everywhere, so a 32-face tile (one warp) whose faces -- and the one
+// face on either side in the sweep direction -- carry no residual transport has only neutral outputs
+// (uhh = CFL = 0) that nothing reads: the list-driven tracer update (sparse.cu) touches only cells next to a
+// non-zero face.  A persistent grid scans uhr / vhr, writes the outputs of the active tiles only, records per tile
+// bit 0 "outputs written" and bit 1 "a cell of this tile may change" (a residual on the tile's own faces or on the
+// face before them) and appends the tiles with bit 1 to tlist, which is all k_mass_update_list visits.  If the
+// active-cell list overflows, k_fill_skipped completes the fields for the dense tracer kernels.
+#define SCAN_UNROLL 4
+template <int DIR>
+__global__ void __launch_bounds__(256)
+k_mass_flux_scan(Geom g, Range rg, const double *__restrict__ res, const double *__restrict__ hprev,
+                 const double *__restrict__ areaT, double min_h, const int *__restrict__ entry,
+                 int *__restrict__ domore, double *__restrict__ hh, double *__restrict__ cfl,
+                 double *__restrict__ hcv, double *__restrict__ gv, int plm, int *__restrict__ tflags,
+                 int *__restrict__ tlist, int *__restrict__ tcount) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int W = g.P >> 5;                                // warp tiles per row (P is a multiple of 64)
+  const int nrow = g.R * g.nk;
+  const int nwarp = gridDim.x * (blockDim.x >> 5);
+  const int st = (DIR == 0) ? 1 : g.P;
+  // one warp per row of a level at a time: the row's flags and ranges are decoded once, its tiles are streamed
+  for (int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < nrow; row += nwarp) {
+    const int k0 = row / g.R, rj = row - k0 * g.R, j = rj - g.roff;
+    const bool row_ok = ((DIR == 0) ? (j >= rg.js && j <= rg.je) : (j >= rg.js - 1 && j <= rg.je)) && entry[row];
+    bool lo_ok = false, hi_ok = false;                   // y: the face rows south / north of this one
+    if (DIR == 1) {
+      lo_ok = rj > 0 && (j - 1 >= rg.js - 1 && j - 1 <= rg.je) && entry[row - 1];
+      hi_ok = rj + 1 < g.R && (j + 1 >= rg.js - 1 && j + 1 <= rg.je) && entry[row + 1];
+    }
+    const int t0 = row * W;
+    if (!row_ok && !lo_ok && !hi_ok) {                   // nothing swept near this row: every tile is clean
+      for (int wx = lane; wx < W; wx += 32) tflags[t0 + wx] = 0;
+      continue;
+    }
+    const long long qrow = (long long)g.P * rj + g.plane * k0;
+    const int i_lo = (DIR == 0) ? rg.is - 1 : rg.is;     // face columns of the sweep
+    for (int wb = 0; wb < W; wb += SCAN_UNROLL) {
+      double ur[SCAN_UNROLL], lo[SCAN_UNROLL], hi[SCAN_UNROLL];
+#pragma unroll
+      for (int u = 0; u < SCAN_UNROLL; u++) {            // the loads of the batch first
+        ur[u] = 0.0; lo[u] = 0.0; hi[u] = 0.0;
+        const int wx = wb + u;
+        if (wx >= W) continue;
+        const int ci = wx * 32 + lane, i = ci - g.coff;
+        const long long q = qrow + ci;
+        const bool col_ok = (i >= i_lo && i <= rg.ie);
+        if (row_ok && col_ok) ur[u] = res[q];
+        if (DIR == 0) {
+          if (row_ok && lane == 0 && ci > 0 && i - 1 >= i_lo && i - 1 <= rg.ie) lo[u] = res[q - 1];
+          if (row_ok && lane == 31 && ci + 1 < g.P && i + 1 >= i_lo && i + 1 <= rg.ie) hi[u] = res[q + 1];
+        } else {
+          if (lo_ok && col_ok) lo[u] = res[q - st];
+          if (hi_ok && col_ok) hi[u] = res[q + st];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < SCAN_UNROLL; u++) {
+        const int wx = wb + u;
+        if (wx >= W) continue;                           // warp-uniform
+        const bool nz = (ur[u] != 0.0), nz_lo = (lo[u] != 0.0), nz_hi = (hi[u] != 0.0);
+        const int any_flux = __any_sync(FULL, nz || nz_lo || nz_hi);
+        const int any_cell = __any_sync(FULL, nz || nz_lo);
+        if (lane == 0) {
+          tflags[t0 + wx] = (any_flux ? 1 : 0) | (any_cell ? 2 : 0);
+          if (any_cell) tlist[atomicAdd(tcount, 1)] = t0 + wx;
+        }
+        if (!any_flux) continue;
+        const int ci = wx * 32 + lane, i = ci - g.coff;
+        const long long q = qrow + ci, q2 = (long long)g.P * rj + ci;
+        if (DIR == 0 && lane == 0 && ci > 0 && !nz_lo) {
+          // the face before the tile may belong to a skipped tile: its neutral values are read by this tile's first cell
+          hh[q - 1] = 0.0; cfl[q - 1] = 0.0;
+          if (hcv) { hcv[q - 1] = 0.0; gv[q - 1] = 1.0; }
+        }
+        const bool swept = row_ok && (i >= i_lo && i <= rg.ie);
+        mass_flux_face<DIR>(g, q, q2, row, swept, ur[u], res, hprev, areaT, min_h, domore, hh, cfl, hcv, gv, plm);
+      }
+    }
+  }
+}
 void launch_mass_flux(cudaStream_t s, int dir, const Geom &g, Range rg, const double *res, const double *hprev,
                       const double *areaT, double min_h, const int *entry, int *domore, double *hh, double *cfl,
                       double *hc, double *gq, int plm) {
@@ -257,20 +354,46 @@ void launch_mass_flux(cudaStream_t s, int dir, const Geom &g, Range rg, const do
   if (dir == 0) k_mass_flux<0><<<grid, TPB, 0, s>>>(g, rg, res, hprev, areaT, min_h, entry, domore, hh, cfl, hc, gq, plm);
   else k_mass_flux<1><<<grid, TPB, 0, s>>>(g, rg, res, hprev, areaT, min_h, entry, domore, hh, cfl, hc, gq, plm);
 }
+long long mass_tile_count(const Geom &g) { return (long long)(g.P / 32) * g.R * g.nk; }
+// residual-trip form; tcount must be zero on entry
+void launch_mass_flux_scan(cudaStream_t s, int dir, const Geom &g, Range rg, const double *res, const double *hprev,
+                           const double *areaT, double min_h, const int *entry, int *domore, double *hh, double *cfl,
+                           double *hc, double *gq, int plm, int *tflags, int *tlist, int *tcount, int nsm) {
+  const int grid = nsm * 8;
+  if (dir == 0) k_mass_flux_scan<0><<<grid, 256, 0, s>>>(g, rg, res, hprev, areaT, min_h, entry, domore, hh, cfl, hc, gq, plm, tflags, tlist, tcount);
+  else k_mass_flux_scan<1><<<grid, 256, 0, s>>>(g, rg, res, hprev, areaT, min_h, entry, domore, hh, cfl, hc, gq, plm, tflags, tlist, tcount);
+}
+
+// After a list overflow in a residual trip: give the skipped tiles the neutral values a dense pass would have
+// written, so that the dense tracer kernels can run.
+__global__ void k_fill_skipped(Geom g, const int *__restrict__ tflags, double *__restrict__ hh, double *__restrict__ cfl,
+                               double *__restrict__ hcv, double *__restrict__ gv, double *__restrict__ hlst,
+                               double *__restrict__ ihnew) {
+  const int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y, k0 = blockIdx.z;
+  if (ci >= g.P) return;
+  const int f = tflags[((long long)k0 * g.R + rj) * (g.P >> 5) + (ci >> 5)];
+  const long long q = gidx(g, ci, rj, k0);
+  if (!(f & 1)) { hh[q] = 0.0; cfl[q] = 0.0; if (hcv) { hcv[q] = 0.0; gv[q] = 1.0; } }
+  if (!(f & 2)) { hlst[q] = 0.0; ihnew[q] = 0.0; }
+}
+void launch_fill_skipped(cudaStream_t s, const Geom &g, const int *tflags, double *hh, double *cfl, double *hc,
+                         double *gq, double *hlst, double *ihnew) {
+  dim3 grid((g.P + TPB - 1) / TPB, g.R, g.nk);
+  k_fill_skipped<<<grid, TPB, 0, s>>>(g, tflags, hh, cfl, hc, gq, hlst, ihnew);
+}
 
 // ---------------------------------------------------------------------------
 // Residual transport and cell volume update (:632-649 for x, :1021-1040 for y).
 // ihnew == 0 encodes do_i == .false. (a true Ihnew is always > 0).
 // ---------------------------------------------------------------------------
 template <int DIR>
-__global__ void k_mass_update(Geom g, Range rg, double *__restrict__ res, double *__restrict__ hprev,
-                              const double *__restrict__ hh, const double *__restrict__ areaT,
-                              const double *__restrict__ neglect, double h_neglect,
-                              const int *__restrict__ entry, const int *__restrict__ domore_k,
-                              double *__restrict__ hlst, double *__restrict__ ihnew,
-                              int *__restrict__ list, int *__restrict__ count, int cap) {
-  int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y, k0 = blockIdx.z;
-  if (ci >= g.P) return;
+__device__ __forceinline__ void mass_update_cell(const Geom &g, const Range &rg, int ci, int rj, int k0,
+                                                 double *__restrict__ res, double *__restrict__ hprev,
+                                                 const double *__restrict__ hh, const double *__restrict__ areaT,
+                                                 const double *__restrict__ neglect, double h_neglect,
+                                                 const int *__restrict__ entry, const int *__restrict__ domore_k,
+                                                 double *__restrict__ hlst, double *__restrict__ ihnew,
+                                                 int *__restrict__ list, int *__restrict__ count, int cap) {
   const int i = ci - g.coff, j = rj - g.roff;
   const long long q = gidx(g, ci, rj, k0), q2 = gidx(g, ci, rj, 0);
   const int st = (DIR == 0) ? 1 : g.P;
@@ -311,6 +434,37 @@ __global__ void k_mass_update(Geom g, Range rg, double *__restrict__ res, double
     if (idx < cap) list[idx] = (int)q;
   }
 }
+template <int DIR>
+__global__ void k_mass_update(Geom g, Range rg, double *__restrict__ res, double *__restrict__ hprev,
+                              const double *__restrict__ hh, const double *__restrict__ areaT,
+                              const double *__restrict__ neglect, double h_neglect,
+                              const int *__restrict__ entry, const int *__restrict__ domore_k,
+                              double *__restrict__ hlst, double *__restrict__ ihnew,
+                              int *__restrict__ list, int *__restrict__ count, int cap) {
+  const int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y, k0 = blockIdx.z;
+  if (ci >= g.P) return;
+  mass_update_cell<DIR>(g, rg, ci, rj, k0, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap);
+}
+// residual trips: only the tiles k_mass_flux_scan listed (nothing changes in the others)
+template <int DIR>
+__global__ void __launch_bounds__(256)
+k_mass_update_list(Geom g, Range rg, double *__restrict__ res, double *__restrict__ hprev,
+                   const double *__restrict__ hh, const double *__restrict__ areaT,
+                   const double *__restrict__ neglect, double h_neglect,
+                   const int *__restrict__ entry, const int *__restrict__ domore_k,
+                   double *__restrict__ hlst, double *__restrict__ ihnew,
+                   int *__restrict__ list, int *__restrict__ count, int cap,
+                   const int *__restrict__ tlist, const int *__restrict__ tcount) {
+  const int lane = threadIdx.x & 31;
+  const int W = g.P >> 5;
+  const int n = *tcount;
+  const int nwarp = gridDim.x * (blockDim.x >> 5);
+  for (int e = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); e < n; e += nwarp) {
+    const int t = tlist[e];
+    const int wx = t % W, rk = t / W, rj = rk % g.R, k0 = rk / g.R;
+    mass_update_cell<DIR>(g, rg, wx * 32 + lane, rj, k0, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap);
+  }
+}
 void launch_mass_update(cudaStream_t s, int dir, const Geom &g, Range rg, double *res, double *hprev,
                         const double *hh, const double *areaT, const double *neglect, double h_neglect,
                         const int *entry, const int *domore_k, double *hlst, double *ihnew,
@@ -318,6 +472,14 @@ void launch_mass_update(cudaStream_t s, int dir, const Geom &g, Range rg, double
   dim3 grid((g.P + TPB - 1) / TPB, g.R, g.nk);
   if (dir == 0) k_mass_update<0><<<grid, TPB, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap);
   else k_mass_update<1><<<grid, TPB, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap);
+}
+void launch_mass_update_list(cudaStream_t s, int dir, const Geom &g, Range rg, double *res, double *hprev,
+                             const double *hh, const double *areaT, const double *neglect, double h_neglect,
+                             const int *entry, const int *domore_k, double *hlst, double *ihnew,
+                             int *list, int *count, int cap, const int *tlist, const int *tcount, int nsm) {
+  const int grid = nsm * 4;
+  if (dir == 0) k_mass_update_list<0><<<grid, 256, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap, tlist, tcount);
+  else k_mass_update_list<1><<<grid, 256, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap, tlist, tcount);
 }
 
 // ---------------------------------------------------------------------------

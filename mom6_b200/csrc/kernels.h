@@ -38,6 +38,16 @@ void launch_halo_pull(cudaStream_t s, long long plane, long long peer_plane, int
 void launch_halo_unpack(cudaStream_t s, long long plane, int nk, const int *dst, int n,
                         double *const *fields, int nfields, const double *buf);
 void launch_fill(cudaStream_t s, double *p, long long n, double v);
+long long mass_tile_count(const Geom &g);
+void launch_mass_flux_scan(cudaStream_t s, int dir, const Geom &g, Range rg, const double *res, const double *hprev,
+                           const double *areaT, double min_h, const int *entry, int *domore, double *hh, double *cfl,
+                           double *hc, double *gq, int plm, int *tflags, int *tlist, int *tcount, int nsm);
+void launch_mass_update_list(cudaStream_t s, int dir, const Geom &g, Range rg, double *res, double *hprev,
+                             const double *hh, const double *areaT, const double *neglect, double h_neglect,
+                             const int *entry, const int *domore_k, double *hlst, double *ihnew,
+                             int *list, int *count, int cap, const int *tlist, const int *tcount, int nsm);
+void launch_fill_skipped(cudaStream_t s, const Geom &g, const int *tflags, double *hh, double *cfl, double *hc,
+                         double *gq, double *hlst, double *ihnew);
 void launch_fill_int(cudaStream_t s, int *p, int n, int v);
 void launch_publish(cudaStream_t s, int *host_mapped, const int *dev, int n);
 

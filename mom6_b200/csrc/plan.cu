@@ -101,10 +101,13 @@ struct mom6adv_plan {
   int opt_pull = 1;                  // multi-GPU group pass by peer-memory loads (0: pack -> NCCL send/recv -> unpack)
   int ipc_ntr = -1;                  // registry size the IPC mappings were made for
   int *bar_dev = nullptr;            // scratch word of the neighbour barrier
+  int *tflags = nullptr, *tlist = nullptr;   // per 32-face tile: outputs written / cells may change; tiles to update (residual trips)
+  int nsm = 148;
   cudaStream_t s_pull = nullptr;     // tracer halos of the first pass are pulled here, under the interior x sweep
   cudaEvent_t ev_pull_go = nullptr, ev_pull_done = nullptr;
   bool pull_pending = false;         // the tracer halo rows are still in flight on s_pull
   int opt_overlap = 1;
+  int opt_sp_cap = 0;                // list capacity of the residual trips (0: cells/64); tests force overflows with it
   // open boundaries (mom6adv_set_obc)
   bool obc_active = false;
   int obc_flags[4] = {0, 0, 0, 0};          // open_u, open_v, specified_u, specified_v ..._BCs_exist_globally
@@ -535,6 +538,8 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   free_obc(plan);
   { double *o[] = {plan->obc_ttmp, plan->obc_slope, plan->obc_fx, plan->obc_hh2, plan->maskT}; for (double *p : o) if (p) cudaFree(p); }
   if (plan->bar_dev) cudaFree(plan->bar_dev);
+  if (plan->tflags) cudaFree(plan->tflags);
+  if (plan->tlist) cudaFree(plan->tlist);
   double *d[] = {plan->areaT, plan->IareaT, plan->mCu, plan->mCv, plan->uh_neglect, plan->vh_neglect, plan->mmx,
                  plan->mmy, plan->h_end, plan->uhtr, plan->vhtr, plan->vol_prev, plan->uhr, plan->vhr, plan->hprev,
                  plan->hh, plan->cfl, plan->hlst, plan->ihnew, plan->hc, plan->gq, plan->staging};
@@ -1001,7 +1006,7 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
     bool sparse = plan->opt_sparse && itt >= 2;
     if (sparse && (!plan->sp_list || plan->sp_ntr < plan->ntr)) {
       if (plan->sp_list) { cudaFree(plan->sp_list); cudaFree(plan->sp_new); plan->sp_list = nullptr; plan->sp_new = nullptr; }
-      plan->sp_cap = (int)std::max<long long>(4096, field_elems(plan) / 64);
+      plan->sp_cap = plan->opt_sp_cap > 0 ? plan->opt_sp_cap : (int)std::max<long long>(4096, field_elems(plan) / 64);
       plan->sp_ntr = plan->ntr;
       int rc = dev_alloc(plan, &plan->sp_list, plan->sp_cap); if (rc) return rc;
       rc = dev_alloc(plan, &plan->sp_new, (long long)plan->sp_cap * plan->ntr); if (rc) return rc;
@@ -1010,11 +1015,25 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
       ProfScope ps(plan, MOM6ADV_KC_MASS);
       if (sparse) CK(cudaMemsetAsync(plan->sum_dev + 1, 0, sizeof(int), s));
       launch_flags_begin(s, g, plan->domore_k, dom, ent, x ? rg.js : rg.js - 1, rg.je);
-      launch_mass_flux(s, dir, g, rg, res, plan->hprev, plan->areaT, min_h, ent, dom, plan->hh, plan->cfl,
-                       plan->hc, plan->gq, scheme == SCHEME_PLM);
-      launch_mass_update(s, dir, g, rg, res, plan->hprev, plan->hh, plan->areaT, x ? plan->uh_neglect : plan->vh_neglect,
-                         h_neglect, ent, plan->domore_k, plan->hlst, plan->ihnew,
-                         sparse ? plan->sp_list : nullptr, plan->sum_dev + 1, plan->sp_cap);
+      if (sparse && !plan->tflags) {
+        int rc = dev_alloc(plan, &plan->tflags, mass_tile_count(g)); if (rc) return rc;
+        rc = dev_alloc(plan, &plan->tlist, mass_tile_count(g)); if (rc) return rc;
+        CK(cudaDeviceGetAttribute(&plan->nsm, cudaDevAttrMultiProcessorCount, plan->device));
+      }
+      if (sparse) {
+        // residual trips: a persistent scan of uhr / vhr computes the few active tiles, the update visits only those
+        CK(cudaMemsetAsync(plan->sum_dev + 2, 0, sizeof(int), s));
+        launch_mass_flux_scan(s, dir, g, rg, res, plan->hprev, plan->areaT, min_h, ent, dom, plan->hh, plan->cfl,
+                              plan->hc, plan->gq, scheme == SCHEME_PLM, plan->tflags, plan->tlist, plan->sum_dev + 2, plan->nsm);
+        launch_mass_update_list(s, dir, g, rg, res, plan->hprev, plan->hh, plan->areaT, x ? plan->uh_neglect : plan->vh_neglect,
+                                h_neglect, ent, plan->domore_k, plan->hlst, plan->ihnew, plan->sp_list, plan->sum_dev + 1,
+                                plan->sp_cap, plan->tlist, plan->sum_dev + 2, plan->nsm);
+      } else {
+        launch_mass_flux(s, dir, g, rg, res, plan->hprev, plan->areaT, min_h, ent, dom, plan->hh, plan->cfl,
+                         plan->hc, plan->gq, scheme == SCHEME_PLM);
+        launch_mass_update(s, dir, g, rg, res, plan->hprev, plan->hh, plan->areaT, x ? plan->uh_neglect : plan->vh_neglect,
+                           h_neglect, ent, plan->domore_k, plan->hlst, plan->ihnew, nullptr, plan->sum_dev + 1, plan->sp_cap);
+      }
       plan->launches += 3;
     }
     int cnt = 0;
@@ -1022,7 +1041,11 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
       launch_publish(s, plan->sum_host_dev + 1, plan->sum_dev + 1, 1);
       CK(cudaStreamSynchronize(s));
       cnt = plan->sum_host[1];
-      if (cnt > plan->sp_cap) sparse = false;      // too many active cells: take the dense kernels
+      if (cnt > plan->sp_cap) {                    // too many active cells: take the dense kernels,
+        sparse = false;                            // which need the fields of the skipped tiles as well
+        launch_fill_skipped(s, g, plan->tflags, plan->hh, plan->cfl, plan->hc, plan->gq, plan->hlst, plan->ihnew);
+        plan->launches++;
+      }
     }
     if (sparse) {
       ProfScope pt(plan, MOM6ADV_KC_SPARSE);
@@ -1516,6 +1539,7 @@ extern "C" int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value
   if (!strcmp(key, "mirror_chunk")) { plan->opt_chunk = value; return MOM6ADV_OK; }
   if (!strcmp(key, "mirror_ahead")) { plan->opt_ahead = value; return MOM6ADV_OK; }
   if (!strcmp(key, "pull")) { if (plan->ipc_ntr >= 0 && value != plan->opt_pull) return fail(plan, MOM6ADV_ERR_INVALID, "set_option: pull must be chosen before the first advect call"); plan->opt_pull = value; return MOM6ADV_OK; }
+  if (!strcmp(key, "sparse_cap")) { plan->opt_sp_cap = value; return MOM6ADV_OK; }
   if (!strcmp(key, "overlap")) { plan->opt_overlap = value; return MOM6ADV_OK; }
   if (!strcmp(key, "trace")) { plan->opt_trace = value; return MOM6ADV_OK; }
   if (!strcmp(key, "profile")) {

@@ -10,13 +10,14 @@ pytestmark = pytest.mark.gpu
 
 
 def _run_pair(ni, nj, nk, ntr, scheme, cfl=0.3, x_first=None, diags=False, ncalls=1, symmetric=True,
-              cyclic_x=True, halo=4, bug=False, fast=1, sparse=1, **kw):
+              cyclic_x=True, halo=4, bug=False, fast=1, sparse=1, sparse_cap=0, **kw):
     c = synth.make_case(ni, nj, nk, ntr, cfl=cfl, symmetric=symmetric, cyclic_x=cyclic_x, halo=halo, **kw)
     params = {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme, "USE_HUYNH_STENCIL_BUG": bug}
     CSo = tracer_advect_init(None, c.G, None, params, None, None)
     CSg = tracer_advect_init(None, c.G, None, params, None, None)
     CSg.gpu_options["fast"] = fast
     CSg.gpu_options["sparse"] = sparse
+    CSg.gpu_options["sparse_cap"] = sparse_cap
     Ro = synth.bind_registry(c, diags=diags)
     Rg = synth.bind_registry(c, diags=diags)
     h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
@@ -230,3 +231,23 @@ def test_open_boundaries_bitwise(scheme, x_first):
     oracle.advect_tracer(h, u, v, None, c.dt, c.G, c.GV, None, CS, Rn, x_first_in=x_first)
     assert any(not np.array_equal(c.G.interior(a.t), c.G.interior(b.t)) for a, b in zip(Rn.Tr, Ro.Tr))
     _assert_bitwise(c, Ro, Rg, (uo_o, vo_o, uo_g, vo_g), diags=True)
+
+
+@pytest.mark.parametrize("scheme", ["PLM", "PPM"])
+@pytest.mark.parametrize("x_first", [True, False])
+@pytest.mark.parametrize("cap", [8, 300])
+def test_residual_list_overflow_falls_back_to_dense(scheme, x_first, cap):
+    """Residual trips skip the mass-field tiles without residual transport; when the active-cell list overflows
+    (forced here by a tiny capacity) the skipped tiles are completed and the dense kernels take over."""
+    c, Ro, Rg, outs, nit = _run_pair(300, 41, 3, 6, scheme, cfl=1.6, x_first=x_first, sparse_cap=cap)
+    assert nit >= 3
+    _assert_bitwise(c, Ro, Rg, outs)
+
+
+def test_sparse_trips_wide_grid_many_tiles():
+    # 700 columns = 23 warp tiles of the mass kernels per row: residual faces on tile edges, skipped tiles in between
+    c, Ro, Rg, outs, nit = _run_pair(700, 37, 2, 4, "PPM", cfl=0.9)
+    assert nit >= 2
+    _assert_bitwise(c, Ro, Rg, outs)
+    c, Ro, Rg, outs, nit = _run_pair(700, 37, 2, 4, "PPM", cfl=0.9, x_first=False, cyclic_x=False)
+    _assert_bitwise(c, Ro, Rg, outs)
