@@ -196,6 +196,8 @@ def run_native(args):
     CS = tracer_advect_init(None, c.G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}, None, None)
     plan = capi.Plan(c.G, c.GV, CS)
     plan.set_ntr(ntr)
+    if args.fast is not None:
+        plan.set_option("fast", args.fast)      # A/B runs: 1 = the round-1 streaming kernels
     for m in range(ntr):
         t = c.tracer(m)
         plan.upload_tracer(m, t)
@@ -352,6 +354,7 @@ def main():
     ap.add_argument("--e2e-only", action="store_true", help="print only the e2e leg (pipeline tuning)")
     ap.add_argument("--mirror-chunk", type=int, default=None, help="tracers per pipeline stage of the MIRROR call")
     ap.add_argument("--mirror-ahead", type=int, default=None, help="chunks uploaded in front of the running one")
+    ap.add_argument("--fast", type=int, default=None, help="library option 'fast' (kernel generation; A/B timing)")
     ap.add_argument("--trace", type=int, default=0, help="library prints the MIRROR pipeline's stream times (2: per chunk)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "native":

@@ -43,15 +43,25 @@ __device__ __forceinline__ double minpos(double x, double y) {
 // ties of denormal quotients, |x| < 2^-1021.  There the bit pattern of |x| IS
 // the integer |x| / 2^-1074, so the quotient is an integer division rounded
 // half to even (div6_int) -- no call, no FP division in the hot loops.
+static __constant__ double k_recip[2] = {0.33333333333333331, 0.16666666666666666};
 template <int D>
 __device__ __forceinline__ double divc_fast(double x) {
-  const double c = (D == 3) ? 0.33333333333333331 : 0.16666666666666666;
+  // The remainder is formed with the opposite sign, rn = d*q0 - x (exact), and subtracted: q = q0 - rn*c.
+  // Same value as q0 + r*c, and the zero cases come out with the sign of x without a copysign:
+  // x = -0: q0 = -0, rn = +0, q = -0 - (+0)*c = -0;  x = +0: q = +0 - (+0)*c = +0.
+  // RN(1/3), RN(1/6) come from the constant bank: an FP64 instruction takes a c[][] operand directly, whereas a
+  // literal whose low word is not zero has to be rebuilt in a register pair (two moves per use under register pressure)
+  const double c = (D == 3) ? k_recip[0] : k_recip[1];
   const double q0 = __dmul_rn(x, c);
-  const double r = __fma_rn(-(double)D, q0, x);
-  return copysign(__fma_rn(r, c, q0), x);
+  const double rn = __fma_rn((double)D, q0, -x);
+  return __fma_rn(-rn, c, q0);
 }
 __device__ __forceinline__ bool div6_tiny(double x) {        // 0 < |x| < 2^-1021
   const unsigned u = (unsigned)__double2hiint(x) & 0x7fffffffu;
+  return u < 0x00200000u && (u | (unsigned)__double2loint(x)) != 0u;
+}
+__device__ __forceinline__ bool div6_tiny_pos(double x) {    // same for x >= +0 (a square): no sign mask
+  const unsigned u = (unsigned)__double2hiint(x);
   return u < 0x00200000u && (u | (unsigned)__double2loint(x)) != 0u;
 }
 __device__ __forceinline__ double div6_int(double x) {       // exact x/6 for |x| < 2^-1021
@@ -71,10 +81,13 @@ __device__ __forceinline__ double divc(double x) {           // general form (co
 
 // PLM slope of a cell (:427-431 / :809-813) from the face differences
 // a_hi = Tp-Tc, a_lo = Tc-Tm, their doubled magnitudes A2 = 2|a|, and d = Tp-Tm.
+// Branch-free: when a_hi and a_lo differ in sign the candidate 0.5|d| is formed as |d|*0 = +0,
+// whose bit pattern is the integer minimum, so the magnitude comes out +0 with no select.
 __device__ __forceinline__ double slope_f(double a_hi, double a_lo, double A2_hi, double A2_lo, double d, double mm) {
-  double mag = 0.0;
   // same sign bit (a difference of two finite numbers is never -0)
-  if ((__double2hiint(a_hi) ^ __double2hiint(a_lo)) >= 0) mag = minpos(minpos(0.5 * fabs(d), A2_hi), A2_lo);
+  const int same = ((__double2hiint(a_hi) ^ __double2hiint(a_lo)) >= 0) ? 0x3fe00000 : 0;
+  const double hd = fabs(d) * __hiloint2double(same, 0);
+  const double mag = minpos(minpos(hd, A2_hi), A2_lo);
   return mm * copysign(mag, d);
 }
 
@@ -91,14 +104,20 @@ __device__ __forceinline__ void edges_h3(double Tm, double Tc, double Tp, double
   aR = gmax2(gmin2(Tc, Tp), aR); aR = gmin2(gmax2(Tc, Tp), aR);
 }
 
-// Monotonic limiter (:538-548 / :923-933) in three inlined pieces so that the two rare
-// events (a denormal dA*dA, an overshoot correction) cost one branch per thread-step
-// instead of one per cell:
+// Monotonic limiter (:538-548 / :923-933).  The PCM case (mask*(Tp-Tc)*(Tc-Tm) <= 0) is applied to
+// the edge values FIRST: with aL = aR = Tc the reference's post-limiter quantities follow from the
+// same arithmetic (aR-aL = +0, aR+aL = Tc+Tc, 6Tc-3(Tc+Tc) = +0) and the overshoot tests see
+// t1 = +0*(Tc-Tc) = +0 and t2 = +0, i.e. neither fires, exactly as the elseif chain demands.
+//   ppm_pcm   : aL, aR := Tc where pp <= 0
 //   ppm_lim_a : dA, S, t1 = dA*(Tc - 0.5*S), dd = dA*dA, t2 = dd/6 (fast form)
-//   [if div6_tiny(dd): t2 = div6_int(dd)]
-//   ppm_lim_b : PCM select (mask*(Tp-Tc)*(Tc-Tm) <= 0) and the overshoot flag |t1| > t2
-//   [if flag: ppm_fix]
+//   [if div6_tiny_pos(dd): t2 = div6_int(dd)]      (rare: one branch per thread-step)
+//   ppm_over  : |t1| > t2
+//   [if flag: ppm_fix]                              (rare)
 //   ppm_a6
+__device__ __forceinline__ void ppm_pcm(double &aL, double &aR, double Tc, double pp) {
+  const bool pcm = (pp <= 0.);
+  aL = pcm ? Tc : aL; aR = pcm ? Tc : aR;
+}
 __device__ __forceinline__ void ppm_lim_a(double aL, double aR, double Tc, double &dA, double &S, double &t1,
                                           double &dd, double &t2) {
   dA = aR - aL;
@@ -107,15 +126,7 @@ __device__ __forceinline__ void ppm_lim_a(double aL, double aR, double Tc, doubl
   dd = dA * dA;
   t2 = divc_fast<6>(dd);
 }
-__device__ __forceinline__ bool ppm_lim_b(double &aL, double &aR, double Tc, double pp, double &dA, double &S,
-                                          double t1, double t2) {
-  const bool pcm = (pp <= 0.);
-  // |t1| > t2 (t2 >= +0): integer compare of the magnitudes
-  const bool fix = !pcm && ((__double_as_longlong(t1) & 0x7fffffffffffffffLL) > __double_as_longlong(t2));
-  aL = pcm ? Tc : aL; aR = pcm ? Tc : aR;       // PCM: aR-aL = +0 and aR+aL = Tc+Tc
-  dA = pcm ? 0.0 : dA; S = pcm ? Tc + Tc : S;
-  return fix;
-}
+__device__ __forceinline__ bool ppm_over(double t1, double t2) { return fabs(t1) > t2; }
 // where the flag is set: t1 > t2 -> aL = 3Tc - 2aR (:543); t1 < -t2 -> aR = 3Tc - 2aL (:545)
 __device__ __forceinline__ void ppm_fix(double &aL, double &aR, double Tc, double t1, double &dA, double &S) {
   if (__double2hiint(t1) >= 0) aL = 3. * Tc - 2. * aR;
@@ -126,19 +137,18 @@ __device__ __forceinline__ double ppm_a6(double Tc, double S) { return 6. * Tc -
 
 // Flux through one face (:550-556 / :935-943) from the parabola of its upstream
 // cell: the low-side cell (aR, dA, a6) when hh >= 0, else the high-side cell
-// (aL, dA, a6).  hc = 0.5*CFL, gq = 1 - 2/3*CFL.  x - y == x + (-y) exactly, so
-// one evaluation with selected operands and flipped signs serves both forms:
+// (aL, dA, a6).  hc = 0.5*CFL, gq = 1 - 2/3*CFL.  x - y == x + (-y) and (-x)*y == -(x*y)
+// exactly, so with the tracer-independent factors signed once per face,
+//   hcs = hh >= 0 ? -hc : hc,   gqs = hh >= 0 ? -gq : gq,
+// both forms are the one expression hh*(X + hcs*(D + A6*gqs)):
 //   hh >= 0:  hh*(aR - hc*(dA - a6*gq))      hh < 0:  hh*(aL + hc*(dA + a6*gq))
-__device__ __forceinline__ double flip(double x, int sgn) {      // sgn = 0 or 0x80000000
-  return __hiloint2double(__double2hiint(x) ^ sgn, __double2loint(x));
+__device__ __forceinline__ double neg_if(double x, bool p) {
+  return __hiloint2double(__double2hiint(x) ^ (p ? (int)0x80000000 : 0), __double2loint(x));
 }
-__device__ __forceinline__ double face_flux_sel(double hh, double hc, double gq, bool up_lo, double aR_lo,
+__device__ __forceinline__ double face_flux_sgn(double hh, double hcs, double gqs, bool up_lo, double aR_lo,
                                                 double dA_lo, double a6_lo, double aL_hi, double dA_hi, double a6_hi) {
   const double X = up_lo ? aR_lo : aL_hi, D = up_lo ? dA_lo : dA_hi, A6 = up_lo ? a6_lo : a6_hi;
-  const int sg = up_lo ? (int)0x80000000 : 0;
-  const double u = A6 * gq;
-  const double w = hc * (D + flip(u, sg));
-  return hh * (X + flip(w, sg));
+  return hh * (X + hcs * (D + A6 * gqs));
 }
 // the two one-sided forms (y march, where the two sides are evaluated on different steps)
 __device__ __forceinline__ double out_hi(double hh, double hc, double gq, double aR, double dA, double a6) {

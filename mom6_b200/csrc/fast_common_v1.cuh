@@ -1,0 +1,155 @@
+// Streaming tracer-sweep kernels (the production path when no flux diagnostic
+// is associated).  Same arithmetic as kernels.cu / the reference
+// (/root/reference/src/tracer/MOM_tracer_advect.F90:517-577,652-662 for x,
+// :902-963,1043-1047 for y), restructured so that every slope, edge value,
+// parabola and face flux is computed exactly ONCE per cell / face:
+//
+//   k_x_fast  one warp = 128 consecutive cells of one row (4 per lane, LDG.128),
+//             all tracers looped in-thread with the tracer-independent mass
+//             quantities (uhh, CFL, hlst, Ihnew, mask product) held in
+//             registers; neighbour slopes / edges / outflows cross lanes by
+//             warp shuffle.  Out of place (buf[src] -> buf[1-src]); tiles
+//             overlap by 8 columns (120 useful of 128).
+//   k_y_fast  one thread = two adjacent columns of one tracer, marching in j
+//             with the whole stencil pipeline in registers (no shared memory,
+//             no recomputation, in place); the warps of a CTA are different
+//             tracers of the same columns, so the mass rows are L1 hits for
+//             all but the first warp.
+//
+// Exact-by-construction rewrites used:
+//   * max(Tp,Tc,Tm)-Tc and Tc-min(Tp,Tc,Tm) are obtained from the face
+//     differences a_hi = Tp-Tc and a_lo = Tc-Tm (rounding is monotone and
+//     sign-symmetric), so the PLM slope magnitude is
+//     min(0.5|Tp-Tm|, 2|a_hi|, 2|a_lo|) when a_hi and a_lo have the same sign
+//     and 0 otherwise; its sign is overwritten by sign(.., Tp-Tm) in the
+//     reference, so zero signs cannot differ.
+//   * min over non-negative doubles is an integer compare of the bit patterns.
+//   * the CW84 edge value aR(i) and aL(i+1) are the same expression.
+//   * a face's flux is evaluated by its upstream cell only.
+#pragma once
+#include "internal.cuh"
+#include "kernels.h"
+
+// min of two non-negative (sign bit clear) doubles: integer compare of the bit patterns
+__device__ __forceinline__ double minpos(double x, double y) {
+  return (__double_as_longlong(y) < __double_as_longlong(x)) ? y : x;
+}
+
+// Exact x/3 and x/6 (bit-identical to the IEEE quotient): Markstein's sequence
+// q0 = RN(x*RN(1/d)), r = x - d*q0 (exact by FMA), q = RN(q0 + r*RN(1/d)); the
+// sign is copied from x so that -0 is preserved.  Checked against true division
+// on 6e8 random values over every exponent incl. denormals
+// (scripts/check_markstein.c): d = 3 never differs; d = 6 differs only on exact
+// ties of denormal quotients, |x| < 2^-1021.  There the bit pattern of |x| IS
+// the integer |x| / 2^-1074, so the quotient is an integer division rounded
+// half to even (div6_int) -- no call, no FP division in the hot loops.
+template <int D>
+__device__ __forceinline__ double divc_fast(double x) {
+  const double c = (D == 3) ? 0.33333333333333331 : 0.16666666666666666;
+  const double q0 = __dmul_rn(x, c);
+  const double r = __fma_rn(-(double)D, q0, x);
+  return copysign(__fma_rn(r, c, q0), x);
+}
+__device__ __forceinline__ bool div6_tiny(double x) {        // 0 < |x| < 2^-1021
+  const unsigned u = (unsigned)__double2hiint(x) & 0x7fffffffu;
+  return u < 0x00200000u && (u | (unsigned)__double2loint(x)) != 0u;
+}
+__device__ __forceinline__ double div6_int(double x) {       // exact x/6 for |x| < 2^-1021
+  const unsigned long long b = (unsigned long long)__double_as_longlong(x);
+  const unsigned long long k = b & 0x7fffffffffffffffULL;
+  unsigned long long q = k / 6ULL;
+  const unsigned long long rem = k - 6ULL * q;
+  q += (rem > 3ULL || (rem == 3ULL && (q & 1ULL))) ? 1ULL : 0ULL;
+  return __longlong_as_double((long long)((b & 0x8000000000000000ULL) | q));
+}
+template <int D>
+__device__ __forceinline__ double divc(double x) {           // general form (cold paths, PPM:H3 edges)
+  double q = divc_fast<D>(x);
+  if (D == 6 && div6_tiny(x)) q = div6_int(x);
+  return q;
+}
+
+// PLM slope of a cell (:427-431 / :809-813) from the face differences
+// a_hi = Tp-Tc, a_lo = Tc-Tm, their doubled magnitudes A2 = 2|a|, and d = Tp-Tm.
+__device__ __forceinline__ double slope_f(double a_hi, double a_lo, double A2_hi, double A2_lo, double d, double mm) {
+  double mag = 0.0;
+  // same sign bit (a difference of two finite numbers is never -0)
+  if ((__double2hiint(a_hi) ^ __double2hiint(a_lo)) >= 0) mag = minpos(minpos(0.5 * fabs(d), A2_hi), A2_lo);
+  return mm * copysign(mag, d);
+}
+
+// CW84 edge value between cells lo and hi=lo+1 (:535-536 / :920-921)
+__device__ __forceinline__ double edge_cw(double Tlo, double Thi, double slo, double shi) {
+  return 0.5 * ((Tlo + Thi) + divc_fast<3>(slo - shi));
+}
+
+// PPM:H3 edge values of one cell (:530-533 / :915-918)
+__device__ __forceinline__ void edges_h3(double Tm, double Tc, double Tp, double &aL, double &aR) {
+  aL = divc<6>(5. * Tc + (2. * Tm - Tp));
+  aL = gmax2(gmin2(Tc, Tm), aL); aL = gmin2(gmax2(Tc, Tm), aL);
+  aR = divc<6>(5. * Tc + (2. * Tp - Tm));
+  aR = gmax2(gmin2(Tc, Tp), aR); aR = gmin2(gmax2(Tc, Tp), aR);
+}
+
+// Monotonic limiter (:538-548 / :923-933) in three inlined pieces so that the two rare
+// events (a denormal dA*dA, an overshoot correction) cost one branch per thread-step
+// instead of one per cell:
+//   ppm_lim_a : dA, S, t1 = dA*(Tc - 0.5*S), dd = dA*dA, t2 = dd/6 (fast form)
+//   [if div6_tiny(dd): t2 = div6_int(dd)]
+//   ppm_lim_b : PCM select (mask*(Tp-Tc)*(Tc-Tm) <= 0) and the overshoot flag |t1| > t2
+//   [if flag: ppm_fix]
+//   ppm_a6
+__device__ __forceinline__ void ppm_lim_a(double aL, double aR, double Tc, double &dA, double &S, double &t1,
+                                          double &dd, double &t2) {
+  dA = aR - aL;
+  S = aR + aL;
+  t1 = dA * (Tc - 0.5 * S);
+  dd = dA * dA;
+  t2 = divc_fast<6>(dd);
+}
+__device__ __forceinline__ bool ppm_lim_b(double &aL, double &aR, double Tc, double pp, double &dA, double &S,
+                                          double t1, double t2) {
+  const bool pcm = (pp <= 0.);
+  // |t1| > t2 (t2 >= +0): integer compare of the magnitudes
+  const bool fix = !pcm && ((__double_as_longlong(t1) & 0x7fffffffffffffffLL) > __double_as_longlong(t2));
+  aL = pcm ? Tc : aL; aR = pcm ? Tc : aR;       // PCM: aR-aL = +0 and aR+aL = Tc+Tc
+  dA = pcm ? 0.0 : dA; S = pcm ? Tc + Tc : S;
+  return fix;
+}
+// where the flag is set: t1 > t2 -> aL = 3Tc - 2aR (:543); t1 < -t2 -> aR = 3Tc - 2aL (:545)
+__device__ __forceinline__ void ppm_fix(double &aL, double &aR, double Tc, double t1, double &dA, double &S) {
+  if (__double2hiint(t1) >= 0) aL = 3. * Tc - 2. * aR;
+  else aR = 3. * Tc - 2. * aL;
+  dA = aR - aL; S = aR + aL;
+}
+__device__ __forceinline__ double ppm_a6(double Tc, double S) { return 6. * Tc - 3. * S; }   // :548 / :933
+
+// Flux through one face (:550-556 / :935-943) from the parabola of its upstream
+// cell: the low-side cell (aR, dA, a6) when hh >= 0, else the high-side cell
+// (aL, dA, a6).  hc = 0.5*CFL, gq = 1 - 2/3*CFL.  x - y == x + (-y) exactly, so
+// one evaluation with selected operands and flipped signs serves both forms:
+//   hh >= 0:  hh*(aR - hc*(dA - a6*gq))      hh < 0:  hh*(aL + hc*(dA + a6*gq))
+__device__ __forceinline__ double flip(double x, int sgn) {      // sgn = 0 or 0x80000000
+  return __hiloint2double(__double2hiint(x) ^ sgn, __double2loint(x));
+}
+__device__ __forceinline__ double face_flux_sel(double hh, double hc, double gq, bool up_lo, double aR_lo,
+                                                double dA_lo, double a6_lo, double aL_hi, double dA_hi, double a6_hi) {
+  const double X = up_lo ? aR_lo : aL_hi, D = up_lo ? dA_lo : dA_hi, A6 = up_lo ? a6_lo : a6_hi;
+  const int sg = up_lo ? (int)0x80000000 : 0;
+  const double u = A6 * gq;
+  const double w = hc * (D + flip(u, sg));
+  return hh * (X + flip(w, sg));
+}
+// the two one-sided forms (y march, where the two sides are evaluated on different steps)
+__device__ __forceinline__ double out_hi(double hh, double hc, double gq, double aR, double dA, double a6) {
+  return hh * (aR - hc * (dA - a6 * gq));
+}
+__device__ __forceinline__ double out_lo(double hh, double hc, double gq, double aL, double dA, double a6) {
+  return hh * (aL + hc * (dA + a6 * gq));
+}
+
+__device__ __forceinline__ double underflow(double o, double cu) {
+  // abs(o) < cu with both magnitudes as integers (cu > 0)
+  return ((__double_as_longlong(o) & 0x7fffffffffffffffLL) < __double_as_longlong(cu)) ? 0.0 : o;
+}
+

@@ -68,11 +68,23 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
     hc[0] = __shfl_up_sync(FULL, hc[4], 1);
     gq[0] = __shfl_up_sync(FULL, gq[4], 1);
   }
-  bool uplo[5], upd[4];      // face fed by its low-side cell (:519 uhh >= 0); cell is updated (:657 do_i, Ihnew > 0)
+  // per-lane flags, tracer-independent, packed so that they cost one register instead of 13 predicates:
+  // bit n (0..4): face n is fed by its low-side cell (:519 uhh >= 0); bit 5+n: cell n is updated (:657 do_i,
+  // Ihnew > 0); bit 9+n: cell n is inside the sweep's own range (underflow test, :683-687)
+  unsigned flg = 0;
 #pragma unroll
-  for (int n = 0; n < 5; n++) uplo[n] = (hh[n] >= 0.0);
+  for (int n = 0; n < 5; n++) flg |= (hh[n] >= 0.0) ? (1u << n) : 0u;
 #pragma unroll
-  for (int n = 0; n < 4; n++) upd[n] = (ih[n] > 0.0);
+  for (int n = 0; n < 4; n++) flg |= ((ih[n] > 0.0) ? (32u << n) : 0u) | (inr[n] ? (512u << n) : 0u);
+  asm volatile("" : "+r"(flg));      // opaque: keeps the compiler from re-deriving the bits with FP64 compares per tracer
+  // signed flux factors (face_flux_sgn): PPM wants -hc, -gq on faces fed from the low side, PLM +gq there
+  double hcs[5], gqs[5];
+#pragma unroll
+  for (int n = 0; n < 5; n++) {
+    const bool lo = (flg >> n) & 1u;
+    hcs[n] = neg_if(hc[n], lo);
+    gqs[n] = neg_if(gq[n], SCHEME == SCHEME_PLM ? !lo : lo);
+  }
 
   double2 n0 = *reinterpret_cast<const double2 *>(tt.src[0] + q0);
   double2 n1 = *reinterpret_cast<const double2 *>(tt.src[0] + q0 + 2);
@@ -99,8 +111,9 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
       const double s_e = __shfl_down_sync(FULL, s[0], 1);
 #pragma unroll
       for (int n = 1; n < 5; n++) {
-        const double sup = (n < 4) ? s[n] : s_e, Tup = T[n + 1];
-        fl[n] = uplo[n] ? hh[n] * (T[n] + 0.5 * s[n - 1] * gq[n]) : hh[n] * (Tup - 0.5 * sup * gq[n]);
+        const bool lo = (flg >> n) & 1u;
+        const double sup = lo ? s[n - 1] : ((n < 4) ? s[n] : s_e), Tup = lo ? T[n] : T[n + 1];
+        fl[n] = hh[n] * (Tup + 0.5 * sup * gqs[n]);
       }
     } else {
       double aL[4], aR[4], dA[4], a6[4];
@@ -117,18 +130,25 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
         for (int n = 0; n < 4; n++) edges_h3(T[n], T[n + 1], T[n + 2], aL[n], aR[n]);
       }
       double S[4], t1[4], dd[4], t2[4];
-      bool fix[4];
 #pragma unroll
-      for (int n = 0; n < 4; n++) ppm_lim_a(aL[n], aR[n], T[n + 1], dA[n], S[n], t1[n], dd[n], t2[n]);
-      if (div6_tiny(dd[0]) | div6_tiny(dd[1]) | div6_tiny(dd[2]) | div6_tiny(dd[3])) {      // denormal dA^2: rare
-#pragma unroll
-        for (int n = 0; n < 4; n++) if (div6_tiny(dd[n])) t2[n] = div6_int(dd[n]);
+      for (int n = 0; n < 4; n++) {
+        ppm_pcm(aL[n], aR[n], T[n + 1], mm[n] * a[n + 1] * a[n]);
+        ppm_lim_a(aL[n], aR[n], T[n + 1], dA[n], S[n], t1[n], dd[n], t2[n]);
       }
+      if (div6_tiny_pos(dd[0]) | div6_tiny_pos(dd[1]) | div6_tiny_pos(dd[2]) | div6_tiny_pos(dd[3])) {   // denormal dA^2: rare
 #pragma unroll
-      for (int n = 0; n < 4; n++) fix[n] = ppm_lim_b(aL[n], aR[n], T[n + 1], mm[n] * a[n + 1] * a[n], dA[n], S[n], t1[n], t2[n]);
-      if (fix[0] | fix[1] | fix[2] | fix[3]) {       // overshoot corrections are rare: one region per 4 cells
+        for (int n = 0; n < 4; n++) if (div6_tiny_pos(dd[n])) t2[n] = div6_int(dd[n]);
+      }
+      bool anyfix = ppm_over(t1[0], t2[0]);
 #pragma unroll
-        for (int n = 0; n < 4; n++) if (fix[n]) ppm_fix(aL[n], aR[n], T[n + 1], t1[n], dA[n], S[n]);
+      for (int n = 1; n < 4; n++) anyfix |= ppm_over(t1[n], t2[n]);
+      if (anyfix) {       // overshoot corrections are rare: one region per 4 cells
+#pragma unroll
+        for (int n = 0; n < 4; n++) {
+          double u = t1[n];
+          asm volatile("" : "+d"(u));      // re-test here instead of carrying four predicates through the hot path
+          if (ppm_over(u, t2[n])) ppm_fix(aL[n], aR[n], T[n + 1], u, dA[n], S[n]);
+        }
       }
 #pragma unroll
       for (int n = 0; n < 4; n++) a6[n] = ppm_a6(T[n + 1], S[n]);
@@ -138,17 +158,20 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
 #pragma unroll
       for (int n = 1; n < 5; n++) {
         const double xL = (n < 4) ? aL[n] : aL_e, xD = (n < 4) ? dA[n] : dA_e, x6 = (n < 4) ? a6[n] : a6_e;
-        fl[n] = face_flux_sel(hh[n], hc[n], gq[n], uplo[n], aR[n - 1], dA[n - 1], a6[n - 1], xL, xD, x6);
+        fl[n] = face_flux_sgn(hh[n], hcs[n], gqs[n], (flg >> n) & 1u, aR[n - 1], dA[n - 1], a6[n - 1], xL, xD, x6);
       }
     }
     fl[0] = __shfl_up_sync(FULL, fl[4], 1);
-    const double cu = tt.cu[m];
     double o[4];
 #pragma unroll
     for (int n = 0; n < 4; n++) {
-      o[n] = T[n + 1];
-      if (upd[n]) o[n] = (T[n + 1] * hl[n] - (fl[n + 1] - fl[n])) * ih[n];
-      if (cu > 0.0 && inr[n]) o[n] = underflow(o[n], cu);
+      const double upd = (T[n + 1] * hl[n] - (fl[n + 1] - fl[n])) * ih[n];
+      o[n] = ((flg >> (5 + n)) & 1u) ? upd : T[n + 1];
+    }
+    const double cu = tt.cu[m];
+    if (cu > 0.0) {      // warp-uniform: most tracers carry no underflow threshold
+#pragma unroll
+      for (int n = 0; n < 4; n++) if ((flg >> (9 + n)) & 1u) o[n] = underflow(o[n], cu);
     }
     if (st) {
       *reinterpret_cast<double2 *>(tt.dst[m] + q0) = make_double2(o[0], o[1]);

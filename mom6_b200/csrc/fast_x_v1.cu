@@ -1,0 +1,172 @@
+// x sweep of the streaming path (see fast_common_v1.cuh for the design notes).
+#include "fast_common_v1.cuh"
+#include <algorithm>
+
+// ---------------------------------------------------------------------------
+// x sweep
+// ---------------------------------------------------------------------------
+#define XT_USE 120     // useful cells per 128-cell warp tile (lanes 1..30)
+
+#ifndef XMINB
+#define XMINB 4
+#endif
+template <int SCHEME>
+__global__ void __launch_bounds__(128, XMINB)
+k_x_fast_v1(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const double *__restrict__ hcv,
+         const double *__restrict__ gqv, const double *__restrict__ hlstv, const double *__restrict__ ihv,
+         const double *__restrict__ mmv, const int *__restrict__ entry, const int *__restrict__ domore_k, int wbase,
+         int wj_lo, int wj_hi) {      // rows (Fortran j) this launch owns; the others belong to another launch of the sweep
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int rj = wj_lo + g.roff + blockIdx.y * 4 + (threadIdx.x >> 5), k0 = blockIdx.z;
+  const int j = rj - g.roff;
+  if (j > wj_hi) return;                                     // warp-uniform
+  const int c0 = wbase + XT_USE * blockIdx.x + 4 * lane;       // first of this lane's 4 columns
+  const long long q0 = (long long)c0 + (long long)g.P * rj + g.plane * k0;
+  const bool lev = domore_k[k0] > 0;
+  const bool in_j = (j >= rg.js && j <= rg.je);
+  const bool active = lev && in_j && entry[k0 * g.R + rj];
+  const bool st = (lane >= 1 && lane <= 30) && (c0 + 3 >= g.isd + g.coff) && (c0 <= g.ied + g.coff);
+  bool inr[4];
+#pragma unroll
+  for (int n = 0; n < 4; n++) { const int i = c0 + n - g.coff; inr[n] = lev && in_j && i >= rg.is && i <= rg.ie; }
+
+  if (!active) {     // copy through (+ underflow on the sweep's own range, :683-687)
+    if (!st) return;
+    for (int m = 0; m < tt.n; m++) {
+      const double2 v0 = *reinterpret_cast<const double2 *>(tt.src[m] + q0);
+      const double2 v1 = *reinterpret_cast<const double2 *>(tt.src[m] + q0 + 2);
+      double o[4] = {v0.x, v0.y, v1.x, v1.y};
+      const double cu = tt.cu[m];
+      if (cu > 0.0) {
+#pragma unroll
+        for (int n = 0; n < 4; n++) if (inr[n]) o[n] = underflow(o[n], cu);
+      }
+      *reinterpret_cast<double2 *>(tt.dst[m] + q0) = make_double2(o[0], o[1]);
+      *reinterpret_cast<double2 *>(tt.dst[m] + q0 + 2) = make_double2(o[2], o[3]);
+    }
+    return;
+  }
+
+  // tracer-independent quantities of this lane's 4 cells and their 5 faces
+  double hh[5], hc[5], gq[5], hl[4], ih[4], mm[4];     // faces: [0] = west face of cell 0, [n+1] = east face of cell n
+  {
+    const double2 a0 = *reinterpret_cast<const double2 *>(hhv + q0), a1 = *reinterpret_cast<const double2 *>(hhv + q0 + 2);
+    const double2 b0 = *reinterpret_cast<const double2 *>(hcv + q0), b1 = *reinterpret_cast<const double2 *>(hcv + q0 + 2);
+    const double2 c0v = *reinterpret_cast<const double2 *>(gqv + q0), c1v = *reinterpret_cast<const double2 *>(gqv + q0 + 2);
+    const double2 h0 = *reinterpret_cast<const double2 *>(hlstv + q0), h1 = *reinterpret_cast<const double2 *>(hlstv + q0 + 2);
+    const double2 i0 = *reinterpret_cast<const double2 *>(ihv + q0), i1 = *reinterpret_cast<const double2 *>(ihv + q0 + 2);
+    const long long q2 = (long long)c0 + (long long)g.P * rj;
+    const double2 m0 = *reinterpret_cast<const double2 *>(mmv + q2), m1 = *reinterpret_cast<const double2 *>(mmv + q2 + 2);
+    hh[1] = a0.x; hh[2] = a0.y; hh[3] = a1.x; hh[4] = a1.y;
+    hc[1] = b0.x; hc[2] = b0.y; hc[3] = b1.x; hc[4] = b1.y;
+    gq[1] = c0v.x; gq[2] = c0v.y; gq[3] = c1v.x; gq[4] = c1v.y;
+    hl[0] = h0.x; hl[1] = h0.y; hl[2] = h1.x; hl[3] = h1.y;
+    ih[0] = i0.x; ih[1] = i0.y; ih[2] = i1.x; ih[3] = i1.y;
+    mm[0] = m0.x; mm[1] = m0.y; mm[2] = m1.x; mm[3] = m1.y;
+    hh[0] = __shfl_up_sync(FULL, hh[4], 1);
+    hc[0] = __shfl_up_sync(FULL, hc[4], 1);
+    gq[0] = __shfl_up_sync(FULL, gq[4], 1);
+  }
+  bool uplo[5], upd[4];      // face fed by its low-side cell (:519 uhh >= 0); cell is updated (:657 do_i, Ihnew > 0)
+#pragma unroll
+  for (int n = 0; n < 5; n++) uplo[n] = (hh[n] >= 0.0);
+#pragma unroll
+  for (int n = 0; n < 4; n++) upd[n] = (ih[n] > 0.0);
+
+  double2 n0 = *reinterpret_cast<const double2 *>(tt.src[0] + q0);
+  double2 n1 = *reinterpret_cast<const double2 *>(tt.src[0] + q0 + 2);
+  for (int m = 0; m < tt.n; m++) {
+    double T[6];      // T[0] = west neighbour, T[1..4] own cells, T[5] = east neighbour
+    T[1] = n0.x; T[2] = n0.y; T[3] = n1.x; T[4] = n1.y;
+    if (m + 1 < tt.n) {       // prefetch the next tracer
+      n0 = *reinterpret_cast<const double2 *>(tt.src[m + 1] + q0);
+      n1 = *reinterpret_cast<const double2 *>(tt.src[m + 1] + q0 + 2);
+    }
+    T[0] = __shfl_up_sync(FULL, T[4], 1);
+    T[5] = __shfl_down_sync(FULL, T[1], 1);
+    double a[5], A2[5];       // a[n] = T[n+1]-T[n]: difference across face n (same numbering as hh)
+#pragma unroll
+    for (int n = 0; n < 5; n++) { a[n] = T[n + 1] - T[n]; A2[n] = 2.0 * fabs(a[n]); }
+    double s[4];
+    if (SCHEME != SCHEME_PPM_H3) {
+#pragma unroll
+      for (int n = 0; n < 4; n++) s[n] = slope_f(a[n + 1], a[n], A2[n + 1], A2[n], T[n + 2] - T[n], mm[n]);
+    }
+    double fl[5];      // flux through face n
+    if (SCHEME == SCHEME_PLM) {
+      // face n is fed by cell n-1 (hh >= 0) or cell n (hh < 0); own cells are 0..3, cell 4 is the east neighbour's
+      const double s_e = __shfl_down_sync(FULL, s[0], 1);
+#pragma unroll
+      for (int n = 1; n < 5; n++) {
+        const double sup = (n < 4) ? s[n] : s_e, Tup = T[n + 1];
+        fl[n] = uplo[n] ? hh[n] * (T[n] + 0.5 * s[n - 1] * gq[n]) : hh[n] * (Tup - 0.5 * sup * gq[n]);
+      }
+    } else {
+      double aL[4], aR[4], dA[4], a6[4];
+      if (SCHEME == SCHEME_PPM_CW) {
+        const double s_e = __shfl_down_sync(FULL, s[0], 1);
+        double e[5];     // e[n+1] = edge value at the east face of cell n
+#pragma unroll
+        for (int n = 0; n < 4; n++) e[n + 1] = edge_cw(T[n + 1], T[n + 2], s[n], (n < 3) ? s[n + 1] : s_e);
+        e[0] = __shfl_up_sync(FULL, e[4], 1);
+#pragma unroll
+        for (int n = 0; n < 4; n++) { aL[n] = e[n]; aR[n] = e[n + 1]; }
+      } else {
+#pragma unroll
+        for (int n = 0; n < 4; n++) edges_h3(T[n], T[n + 1], T[n + 2], aL[n], aR[n]);
+      }
+      double S[4], t1[4], dd[4], t2[4];
+      bool fix[4];
+#pragma unroll
+      for (int n = 0; n < 4; n++) ppm_lim_a(aL[n], aR[n], T[n + 1], dA[n], S[n], t1[n], dd[n], t2[n]);
+      if (div6_tiny(dd[0]) | div6_tiny(dd[1]) | div6_tiny(dd[2]) | div6_tiny(dd[3])) {      // denormal dA^2: rare
+#pragma unroll
+        for (int n = 0; n < 4; n++) if (div6_tiny(dd[n])) t2[n] = div6_int(dd[n]);
+      }
+#pragma unroll
+      for (int n = 0; n < 4; n++) fix[n] = ppm_lim_b(aL[n], aR[n], T[n + 1], mm[n] * a[n + 1] * a[n], dA[n], S[n], t1[n], t2[n]);
+      if (fix[0] | fix[1] | fix[2] | fix[3]) {       // overshoot corrections are rare: one region per 4 cells
+#pragma unroll
+        for (int n = 0; n < 4; n++) if (fix[n]) ppm_fix(aL[n], aR[n], T[n + 1], t1[n], dA[n], S[n]);
+      }
+#pragma unroll
+      for (int n = 0; n < 4; n++) a6[n] = ppm_a6(T[n + 1], S[n]);
+      // the east neighbour's first cell feeds face 4 when hh[4] < 0
+      const double aL_e = __shfl_down_sync(FULL, aL[0], 1), dA_e = __shfl_down_sync(FULL, dA[0], 1),
+                   a6_e = __shfl_down_sync(FULL, a6[0], 1);
+#pragma unroll
+      for (int n = 1; n < 5; n++) {
+        const double xL = (n < 4) ? aL[n] : aL_e, xD = (n < 4) ? dA[n] : dA_e, x6 = (n < 4) ? a6[n] : a6_e;
+        fl[n] = face_flux_sel(hh[n], hc[n], gq[n], uplo[n], aR[n - 1], dA[n - 1], a6[n - 1], xL, xD, x6);
+      }
+    }
+    fl[0] = __shfl_up_sync(FULL, fl[4], 1);
+    const double cu = tt.cu[m];
+    double o[4];
+#pragma unroll
+    for (int n = 0; n < 4; n++) {
+      o[n] = T[n + 1];
+      if (upd[n]) o[n] = (T[n + 1] * hl[n] - (fl[n + 1] - fl[n])) * ih[n];
+      if (cu > 0.0 && inr[n]) o[n] = underflow(o[n], cu);
+    }
+    if (st) {
+      *reinterpret_cast<double2 *>(tt.dst[m] + q0) = make_double2(o[0], o[1]);
+      *reinterpret_cast<double2 *>(tt.dst[m] + q0 + 2) = make_double2(o[2], o[3]);
+    }
+  }
+}
+
+int x_fast_tiles_v1(const Geom &g, int wbase) { return (g.ied + g.coff - (wbase + 4)) / XT_USE + 1; }
+
+void launch_x_fast_v1(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
+                   const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm,
+                   const int *entry, const int *domore_k, int wbase, int wj_lo, int wj_hi) {
+  wj_lo = std::max(wj_lo, g.jsd); wj_hi = std::min(wj_hi, g.jed);
+  if (wj_lo > wj_hi) return;
+  dim3 grid(x_fast_tiles_v1(g, wbase), (wj_hi - wj_lo + 1 + 3) / 4, g.nk);
+  if (scheme == SCHEME_PLM) k_x_fast_v1<SCHEME_PLM><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi);
+  else if (scheme == SCHEME_PPM_CW) k_x_fast_v1<SCHEME_PPM_CW><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi);
+  else k_x_fast_v1<SCHEME_PPM_H3><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi);
+}
+

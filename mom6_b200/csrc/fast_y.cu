@@ -67,6 +67,12 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
                ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
+__device__ __forceinline__ double lds_f64(unsigned addr) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr) : "memory");
+  return v;
+}
+
 #ifndef YMINB
 #define YMINB 2
 #endif
@@ -76,7 +82,7 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
          const double *__restrict__ gqv, const double *__restrict__ hlstv, const double *__restrict__ ihv,
          const double *__restrict__ mmv, const int *__restrict__ entry, const int *__restrict__ domore_k) {
   extern __shared__ __align__(128) unsigned char y_smem[];
-  YStage *stg = reinterpret_cast<YStage *>(y_smem);
+  YStage *stg = reinterpret_cast<YStage *>(y_smem);      // (used by the producer; consumers address the ring by offset)
   __shared__ __align__(8) unsigned long long bar_full[YNS], bar_empty[YNS];
   const int k0 = blockIdx.z;
   if (domore_k[k0] <= 0) return;                                  // CTA-uniform
@@ -91,10 +97,21 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
-  __syncthreads();
   const int P = g.P;
   const int r_lo = rg.js - 3 + g.roff, r_hi = rg.je + 3 + g.roff;       // padded rows of the march
   const int nsteps = r_hi - r_lo + 1;
+  // act_s[it]: the face row J = r-2 met at step it is part of the sweep (:868-869 domore_v, via `entry`); one
+  // byte per step, filled once per CTA, so that the march reads it with a single LDS instead of a global load
+  unsigned char *act_s = y_smem + sizeof(YStage) * YNS;
+  {
+    const int *__restrict__ ent = entry + k0 * g.R;
+    const int rf_lo = rg.js - 1 + g.roff, rf_hi = rg.je + g.roff;       // face rows of the sweep
+    for (int it = threadIdx.x; it < nsteps; it += blockDim.x) {
+      const int rf = r_lo + it - 2;
+      act_s[it] = (rf >= rf_lo && rf <= rf_hi && ent[rf]) ? 1 : 0;
+    }
+  }
+  __syncthreads();
   const long long lev = g.plane * k0 + cbase;
 
   if (w == YW) {
@@ -133,9 +150,8 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   double *__restrict__ Tt0 = tt.dst[m0 + ts[0]] + lev + lane;     // in place; + P*row
   double *__restrict__ Tt1 = tt.dst[m0 + ts[1]] + lev + lane;
   const double cu[2] = {tt.cu[m0 + ts[0]], tt.cu[m0 + ts[1]]};
-  const bool do_cu[2] = {cu[0] > 0.0 && inr, cu[1] > 0.0 && inr};
-  const int *__restrict__ ent = entry + k0 * g.R;
-  const int rf_lo = rg.js - 1 + g.roff, rf_hi = rg.je + g.roff;         // face rows of the sweep
+  const unsigned sb = smem_u32(y_smem) + lane * 8;                      // this lane's column in stage 0, row 0
+  const unsigned oT0 = (6 + ts[0]) * YROWB, dT = (ts[1] - ts[0]) * YROWB;
   const int rc_lo = rg.js + g.roff;                                     // first cell row to update
 
   double T1[2] = {0, 0}, T2[2] = {0, 0}, T3[2] = {0, 0};   // T(r-1), T(r-2), T(r-3)
@@ -149,13 +165,13 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   for (int it = 0; it < nsteps; it++) {
     const int r = r_lo + it, s = it % YNS;
     mbar_wait(smem_u32(&bar_full[s]), (it / YNS) & 1);
-    const YStage &q = stg[s];
-    const double Tn[2] = {q.T[ts[0]][lane], q.T[ts[1]][lane]};
-    const double hh2 = q.mass[0][lane], hc2 = q.mass[1][lane], gq2 = q.mass[2][lane];
-    const double hl = q.mass[3][lane], ih = q.mass[4][lane], mm1 = q.mass[5][lane];
+    const unsigned qa = sb + s * (unsigned)sizeof(YStage);
+    const double Tn[2] = {lds_f64(qa + oT0), lds_f64(qa + oT0 + dT)};
+    const double hh2 = lds_f64(qa), hc2 = lds_f64(qa + YROWB), gq2 = lds_f64(qa + 2 * YROWB);
+    const double hl = lds_f64(qa + 3 * YROWB), ih = lds_f64(qa + 4 * YROWB), mm1 = lds_f64(qa + 5 * YROWB);
     __syncwarp();
     if (lane == 0) mbar_arrive(smem_u32(&bar_empty[s]));      // the stage may be refilled
-    const bool act2 = (r - 2 >= rf_lo && r - 2 <= rf_hi) && ent[r - 2];
+    const bool act2 = act_s[it] != 0;
     const bool out_row = (r - 3 >= rc_lo);
     double a0[2], A20[2], s1[2] = {0, 0};
 #pragma unroll
@@ -175,18 +191,20 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
       for (int n = 0; n < 2; n++) {
         if (SCHEME == SCHEME_PPM_CW) { e2[n] = edge_cw(T2[n], T1[n], s2[n], s1[n]); xL[n] = e3[n]; xR[n] = e2[n]; }
         else edges_h3(T3[n], T2[n], T1[n], xL[n], xR[n]);
+        ppm_pcm(xL[n], xR[n], T2[n], pp2[n]);
         ppm_lim_a(xL[n], xR[n], T2[n], dA[n], S[n], t1[n], dd[n], t2[n]);
       }
-      if (div6_tiny(dd[0]) | div6_tiny(dd[1])) {           // denormal dA^2: rare
+      if (div6_tiny_pos(dd[0]) | div6_tiny_pos(dd[1])) {   // denormal dA^2: rare
 #pragma unroll
-        for (int n = 0; n < 2; n++) if (div6_tiny(dd[n])) t2[n] = div6_int(dd[n]);
+        for (int n = 0; n < 2; n++) if (div6_tiny_pos(dd[n])) t2[n] = div6_int(dd[n]);
       }
-      bool fix[2];
+      if (ppm_over(t1[0], t2[0]) | ppm_over(t1[1], t2[1])) {      // overshoot correction: rare
 #pragma unroll
-      for (int n = 0; n < 2; n++) fix[n] = ppm_lim_b(xL[n], xR[n], T2[n], pp2[n], dA[n], S[n], t1[n], t2[n]);
-      if (fix[0] | fix[1]) {                               // overshoot correction: rare
-#pragma unroll
-        for (int n = 0; n < 2; n++) if (fix[n]) ppm_fix(xL[n], xR[n], T2[n], t1[n], dA[n], S[n]);
+        for (int n = 0; n < 2; n++) {
+          double u = t1[n];
+          asm volatile("" : "+d"(u));      // re-test here instead of carrying predicates through the hot path
+          if (ppm_over(u, t2[n])) ppm_fix(xL[n], xR[n], T2[n], u, dA[n], S[n]);
+        }
       }
 #pragma unroll
       for (int n = 0; n < 2; n++) { a6[n] = ppm_a6(T2[n], S[n]); e3[n] = e2[n]; }
@@ -210,7 +228,9 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
       const double fl3 = act3 ? f : 0.0;
       const double upd = (T3[n] * hl - (fl3 - flp[n])) * ih;
       o[n] = do_i ? upd : T3[n];
-      if (do_cu[n]) o[n] = underflow(o[n], cu[n]);
+      if (cu[n] > 0.0) {      // warp-uniform: most tracers carry no underflow threshold
+        if (inr) o[n] = underflow(o[n], cu[n]);
+      }
       flp[n] = fl3;
       Fn3[n] = Fn2;
       pp2[n] = mm1 * a0[n] * a1[n];                        // cell r-1: mask*(Tp-Tc)*(Tc-Tm)
@@ -230,11 +250,11 @@ void launch_y_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const Tr
                    const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm,
                    const int *entry, const int *domore_k) {
   dim3 grid(g.P / YCOLS, (tt.n + YT - 1) / YT, g.nk), block(32 * (YW + 1));
-  const size_t smem = sizeof(YStage) * YNS;
+  const size_t smem = sizeof(YStage) * YNS + ((g.R + 6 + 15) / 16) * 16;      // stages + one activity byte per step
 #define YLAUNCH(S)                                                                                        \
   do {                                                                                                    \
-    static bool attr_set = false;                                                                         \
-    if (!attr_set) { cudaFuncSetAttribute(k_y_ring<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr_set = true; } \
+    static size_t attr_smem = 0;      /* grows with the tallest plan seen (the activity bytes scale with the rows) */ \
+    if (smem > attr_smem) { cudaFuncSetAttribute(k_y_ring<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr_smem = smem; } \
     k_y_ring<S><<<grid, block, smem, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k);       \
   } while (0)
   if (scheme == SCHEME_PLM) YLAUNCH(SCHEME_PLM);

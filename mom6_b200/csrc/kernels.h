@@ -60,6 +60,14 @@ void launch_y_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const Tr
                    const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm, const int *entry,
                    const int *domore_k);
 
+// fast_x_v1.cu / fast_y_v1.cu: the round-1 streaming kernels, selectable with option "fast" = 1 for A/B timing
+void launch_x_fast_v1(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
+                      const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm, const int *entry,
+                      const int *domore_k, int wbase, int wj_lo, int wj_hi);
+void launch_y_fast_v1(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
+                      const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm, const int *entry,
+                      const int *domore_k);
+
 // sparse.cu: list-driven tracer update of the residual iterations
 void launch_sparse_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TrTable &tt,
                          const int *list, int cnt, int cap, const double *hh, const double *cfl, const double *hlst,

@@ -88,7 +88,7 @@ struct mom6adv_plan {
   long long launches = 0;
   long long dev_bytes = 0;
   int opt_fused = 0;
-  int opt_fast = 1;
+  int opt_fast = 2;      // 0 generic kernels, 1 round-1 streaming kernels (kept for A/B timing), 2 current streaming kernels
   // multi-GPU (LAYOUT = npi,npj): one rank per GPU, NCCL over NVLink
   bool multi = false;
   ncclComm_t comm = nullptr;
@@ -1075,19 +1075,21 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
         tt.dst[m] = x ? ts.buf[1 - plan->cur] : ts.buf[plan->cur];
         tt.cu[m] = ts.conc_underflow;
       }
+      auto xf = (plan->opt_fast == 1) ? launch_x_fast_v1 : launch_x_fast;
+      auto yf = (plan->opt_fast == 1) ? launch_y_fast_v1 : launch_y_fast;
       if (x && split_rows) {
         // rows of the computational domain first; the halo rows once their tracer values have arrived
-        launch_x_fast(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
+        xf(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
                       plan->domore_k, plan->wbase, g.jsc, g.jec);
         if (plan->pull_pending) { CK(cudaStreamWaitEvent(s, plan->ev_pull_done, 0)); plan->pull_pending = false; }
-        launch_x_fast(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
+        xf(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
                       plan->domore_k, plan->wbase, g.jsd, g.jsc - 1);
-        launch_x_fast(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
+        xf(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
                       plan->domore_k, plan->wbase, g.jec + 1, g.jed);
         plan->launches += 2;
-      } else if (x) launch_x_fast(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
+      } else if (x) xf(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
                            plan->domore_k, plan->wbase, g.jsd, g.jed);
-      else launch_y_fast(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmy, ent,
+      else yf(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmy, ent,
                          plan->domore_k);
       plan->launches++;
     }

@@ -101,7 +101,7 @@ def test_om4_1_slice_bitwise():
 
 # ---- streaming (fast) kernels vs generic kernels vs oracle -------------------------------------
 @pytest.mark.parametrize("scheme", ["PLM", "PPM", "PPM:H3"])
-@pytest.mark.parametrize("fast", [0, 1])
+@pytest.mark.parametrize("fast", [0, 1, 2])
 def test_generic_and_streaming_kernels_both_bitwise(scheme, fast):
     c, Ro, Rg, outs, nit = _run_pair(44, 40, 2, 10, scheme, cfl=0.9, fast=fast)
     _assert_bitwise(c, Ro, Rg, outs)
