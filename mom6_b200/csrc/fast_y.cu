@@ -67,6 +67,11 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
                ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
+__device__ __forceinline__ bool elect_one() {
+  unsigned p;
+  asm volatile("{\n .reg .pred q;\n elect.sync _|q, 0xffffffff;\n selp.u32 %0, 1, 0, q;\n}" : "=r"(p));
+  return p != 0;
+}
 __device__ __forceinline__ double lds_f64(unsigned addr) {
   double v;
   asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr) : "memory");
@@ -115,27 +120,25 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   const long long lev = g.plane * k0 + cbase;
 
   if (w == YW) {
-    // ---- producer warp: lane l < 6 owns mass row l, lane 6+t the tracer row of tracer m0+t ----
-    const double *src = nullptr;
-    int roff = 0;                   // row of the array this lane copies at step r is max(r - roff, 0)
-    if (lane == 0) { src = hhv + lev; roff = 2; }
-    else if (lane == 1) { src = hcv + lev; roff = 2; }
-    else if (lane == 2) { src = gqv + lev; roff = 2; }
-    else if (lane == 3) { src = hlstv + lev; roff = 3; }
-    else if (lane == 4) { src = ihv + lev; roff = 3; }
-    else if (lane == 5) { src = mmv + cbase; roff = 1; }
-    else if (lane < 6 + nact) { src = tt.dst[m0 + lane - 6] + lev; roff = 0; }
+    // ---- producer warp.  Everything it computes is warp-uniform (block indices, kernel parameters, the step
+    // counter), and ONE elected lane issues the step's 6 + nact bulk copies back to back, so the addresses stay
+    // in uniform registers: no per-lane serialisation loop (ELECT / R2UR / BRA.ANY per copy) in front of UBLKCP.
+    const double *const msrc[6] = {hhv + lev, hcv + lev, gqv + lev, hlstv + lev, ihv + lev, mmv + cbase};
+    const int mroff[6] = {2, 2, 2, 3, 3, 1};      // face r-2, cell r-3, mask product of cell r-1
     for (int it = 0; it < nsteps; it++) {
       const int s = it % YNS;
       mbar_wait_sleep(smem_u32(&bar_empty[s]), ((it / YNS) & 1) ^ 1);
-      const unsigned fb = smem_u32(&bar_full[s]);
-      if (lane == 0) mbar_expect_tx(fb, (6 + nact) * YROWB);
-      __syncwarp();
-      if (lane < 6 + nact) {
-        const int row = max(r_lo + it - roff, 0);
-        const unsigned dst = smem_u32(lane < 6 ? &stg[s].mass[lane][0] : &stg[s].T[lane - 6][0]);
-        bulk_g2s(dst, src + (long long)P * row, YROWB, fb);
+      if (elect_one()) {
+        const unsigned fb = smem_u32(&bar_full[s]);
+        mbar_expect_tx(fb, (6 + nact) * YROWB);
+        const unsigned sbase = smem_u32(&stg[s]);
+        const int r = r_lo + it;
+#pragma unroll
+        for (int t = 0; t < 6; t++) bulk_g2s(sbase + t * YROWB, msrc[t] + (long long)P * max(r - mroff[t], 0), YROWB, fb);
+        for (int t = 0; t < nact; t++)
+          bulk_g2s(sbase + (6 + t) * YROWB, tt.dst[m0 + t] + lev + (long long)P * max(r, 0), YROWB, fb);
       }
+      __syncwarp();
     }
     return;
   }
