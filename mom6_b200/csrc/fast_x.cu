@@ -7,6 +7,24 @@
 // ---------------------------------------------------------------------------
 #define XT_USE 120     // useful cells per 128-cell warp tile (lanes 1..30)
 
+// Rows or warp tiles in which no cell is updated (:636-649 do_i false everywhere: land, vanished transports):
+// copy through, with the underflow test on the sweep's own range (:683-687).
+__device__ __forceinline__ void x_copy_through(const TrTable &tt, long long q0, bool st, const bool (&inr)[4]) {
+  if (!st) return;
+  for (int m = 0; m < tt.n; m++) {
+    const double2 v0 = *reinterpret_cast<const double2 *>(tt.src[m] + q0);
+    const double2 v1 = *reinterpret_cast<const double2 *>(tt.src[m] + q0 + 2);
+    double o[4] = {v0.x, v0.y, v1.x, v1.y};
+    const double cu = tt.cu[m];
+    if (cu > 0.0) {
+#pragma unroll
+      for (int n = 0; n < 4; n++) if (inr[n]) o[n] = underflow(o[n], cu);
+    }
+    *reinterpret_cast<double2 *>(tt.dst[m] + q0) = make_double2(o[0], o[1]);
+    *reinterpret_cast<double2 *>(tt.dst[m] + q0 + 2) = make_double2(o[2], o[3]);
+  }
+}
+
 #ifndef XMINB
 #define XMINB 4
 #endif
@@ -31,22 +49,7 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
 #pragma unroll
   for (int n = 0; n < 4; n++) { const int i = c0 + n - g.coff; inr[n] = lev && in_j && i >= rg.is && i <= rg.ie; }
 
-  if (!active) {     // copy through (+ underflow on the sweep's own range, :683-687)
-    if (!st) return;
-    for (int m = 0; m < tt.n; m++) {
-      const double2 v0 = *reinterpret_cast<const double2 *>(tt.src[m] + q0);
-      const double2 v1 = *reinterpret_cast<const double2 *>(tt.src[m] + q0 + 2);
-      double o[4] = {v0.x, v0.y, v1.x, v1.y};
-      const double cu = tt.cu[m];
-      if (cu > 0.0) {
-#pragma unroll
-        for (int n = 0; n < 4; n++) if (inr[n]) o[n] = underflow(o[n], cu);
-      }
-      *reinterpret_cast<double2 *>(tt.dst[m] + q0) = make_double2(o[0], o[1]);
-      *reinterpret_cast<double2 *>(tt.dst[m] + q0 + 2) = make_double2(o[2], o[3]);
-    }
-    return;
-  }
+  if (!active) { x_copy_through(tt, q0, st, inr); return; }
 
   // tracer-independent quantities of this lane's 4 cells and their 5 faces
   double hh[5], hc[5], gq[5], hl[4], ih[4], mm[4];     // faces: [0] = west face of cell 0, [n+1] = east face of cell n
@@ -76,6 +79,9 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   for (int n = 0; n < 5; n++) flg |= (hh[n] >= 0.0) ? (1u << n) : 0u;
 #pragma unroll
   for (int n = 0; n < 4; n++) flg |= ((ih[n] > 0.0) ? (32u << n) : 0u) | (inr[n] ? (512u << n) : 0u);
+  // no stored cell of this warp's 128 columns is updated (land, or no transport left on any of their faces):
+  // every output equals its input whatever the fluxes are, so the tile is copied through
+  if (!__any_sync(FULL, st && (flg & 0x1e0u) != 0u)) { x_copy_through(tt, q0, st, inr); return; }
   asm volatile("" : "+r"(flg));      // opaque: keeps the compiler from re-deriving the bits with FP64 compares per tracer
   // signed flux factors (face_flux_sgn): PPM wants -hc, -gq on faces fed from the low side, PLM +gq there
   double hcs[5], gqs[5];
