@@ -78,6 +78,10 @@ __device__ __forceinline__ double lds_f64(unsigned addr) {
   return v;
 }
 
+// conc_underflow test kept out of line: tracers with a threshold are the exception, and an inlined test is
+// if-converted into ~10 predicated instructions that every step of every tracer would issue
+__device__ __noinline__ double underflow_rare(double o, double cu, bool inr) { return inr ? underflow(o, cu) : o; }
+
 #ifndef YMINB
 #define YMINB 2
 #endif
@@ -150,9 +154,13 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   const int ts[2] = {t0, two ? t0 + 1 : t0};                 // (a lone tracer is computed twice, stored once)
   const int i0 = cbase + lane - g.coff;
   const bool inr = (i0 >= rg.is && i0 <= rg.ie);
-  double *__restrict__ Tt0 = tt.dst[m0 + ts[0]] + lev + lane;     // in place; + P*row
-  double *__restrict__ Tt1 = tt.dst[m0 + ts[1]] + lev + lane;
+  // in place: the store of step it goes to row r_lo + it - 3; one running pointer, the second tracer at a fixed distance
+  double *wp = tt.dst[m0 + ts[0]] + lev + lane + (long long)P * (r_lo - 3);
+  const long long wd = tt.dst[m0 + ts[1]] - tt.dst[m0 + ts[0]];
   const double cu[2] = {tt.cu[m0 + ts[0]], tt.cu[m0 + ts[1]]};
+  const bool any_cu = (cu[0] > 0.0) || (cu[1] > 0.0);
+  unsigned bfull0 = smem_u32(&bar_full[0]), bempty0 = smem_u32(&bar_empty[0]);
+  asm volatile("" : "+r"(bfull0), "+r"(bempty0));      // computed once (the conversion reads a special register)
   const unsigned sb = smem_u32(y_smem) + lane * 8;                      // this lane's column in stage 0, row 0
   const unsigned oT0 = (6 + ts[0]) * YROWB, dT = (ts[1] - ts[0]) * YROWB;
   const int rc_lo = rg.js + g.roff;                                     // first cell row to update
@@ -167,13 +175,13 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   Y_UNROLL(YUNROLL)
   for (int it = 0; it < nsteps; it++) {
     const int r = r_lo + it, s = it % YNS;
-    mbar_wait(smem_u32(&bar_full[s]), (it / YNS) & 1);
+    mbar_wait(bfull0 + 8u * s, (it / YNS) & 1);
     const unsigned qa = sb + s * (unsigned)sizeof(YStage);
     const double Tn[2] = {lds_f64(qa + oT0), lds_f64(qa + oT0 + dT)};
     const double hh2 = lds_f64(qa), hc2 = lds_f64(qa + YROWB), gq2 = lds_f64(qa + 2 * YROWB);
     const double hl = lds_f64(qa + 3 * YROWB), ih = lds_f64(qa + 4 * YROWB), mm1 = lds_f64(qa + 5 * YROWB);
     __syncwarp();
-    if (lane == 0) mbar_arrive(smem_u32(&bar_empty[s]));      // the stage may be refilled
+    if (lane == 0) mbar_arrive(bempty0 + 8u * s);      // the stage may be refilled
     const bool act2 = act_s[it] != 0;
     const bool out_row = (r - 3 >= rc_lo);
     double a0[2], A20[2], s1[2] = {0, 0};
@@ -231,21 +239,23 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
       const double fl3 = act3 ? f : 0.0;
       const double upd = (T3[n] * hl - (fl3 - flp[n])) * ih;
       o[n] = do_i ? upd : T3[n];
-      if (cu[n] > 0.0) {      // warp-uniform: most tracers carry no underflow threshold
-        if (inr) o[n] = underflow(o[n], cu[n]);
-      }
       flp[n] = fl3;
       Fn3[n] = Fn2;
       pp2[n] = mm1 * a0[n] * a1[n];                        // cell r-1: mask*(Tp-Tc)*(Tc-Tm)
       T3[n] = T2[n]; T2[n] = T1[n]; T1[n] = Tn[n];
       a1[n] = a0[n]; A21[n] = A20[n]; s2[n] = s1[n];
     }
+    if (any_cu) {      // warp-uniform and rare: a real branch (and one for both tracers), not predication
+      if (cu[0] > 0.0) o[0] = underflow_rare(o[0], cu[0], inr);
+      if (cu[1] > 0.0) o[1] = underflow_rare(o[1], cu[1], inr);
+    }
     hh3 = hh2; hc3 = hc2; gq3 = gq2;
     act3 = act2;
     if (out_row) {
-      Tt0[(long long)P * (r - 3)] = o[0];
-      if (two) Tt1[(long long)P * (r - 3)] = o[1];
+      wp[0] = o[0];
+      if (two) wp[wd] = o[1];
     }
+    wp += P;
   }
 }
 

@@ -84,6 +84,9 @@ def hot_trace(lib, name, keep=()):
     `if (rare) {...}`, compiled to `@!P BRA skip`), except those whose address is listed in keep."""
     fn, ins = sass(lib, name)
     lo, hi = find_loop(ins)
+    if "--range" in sys.argv:
+        k = sys.argv.index("--range")
+        lo, hi = int(sys.argv[k + 1], 16), int(sys.argv[k + 2], 16)
     idx = {a: n for n, (a, _) in enumerate(ins)}
     h = collections.Counter()
     pc = idx[lo]
@@ -94,7 +97,7 @@ def hot_trace(lib, name, keep=()):
         m = re.search(r"^(@!?U?P\d+\s+)?BRA(\.U)?\s.*?0x([0-9a-f]+)", t)
         if m and "BRA.DIV" not in t:
             tgt = int(m.group(3), 16)
-            if tgt <= a and not m.group(1):
+            if tgt <= a and (not m.group(1) or a == hi):
                 break                      # the loop's back edge
             if tgt > a and tgt <= hi + 0x10 and a not in keep:
                 taken.append((a, tgt, bool(m.group(1))))
@@ -112,7 +115,10 @@ def hot_trace(lib, name, keep=()):
 
 
 if "--hot" in sys.argv:
-    keep = tuple(int(x, 16) for x in sys.argv[sys.argv.index("--hot") + 1:] if re.fullmatch(r"[0-9a-f]+", x))
+    args = sys.argv[sys.argv.index("--hot") + 1:]
+    if "--range" in args:
+        args = args[:args.index("--range")]
+    keep = tuple(int(x, 16) for x in args if re.fullmatch(r"[0-9a-f]+", x))
     hot_trace(sys.argv[1], sys.argv[2], keep)
 
 if __name__ == "__main__" and "--hot" not in sys.argv:
