@@ -163,3 +163,93 @@ __device__ __forceinline__ double underflow(double o, double cu) {
   return ((__double_as_longlong(o) & 0x7fffffffffffffffLL) < __double_as_longlong(cu)) ? 0.0 : o;
 }
 
+// ---------------------------------------------------------------------------
+// One tracer, the 4 consecutive cells of this lane along the sweep direction (:411-433,517-577,652-662 for x,
+// :794-822,902-963,1021-1047 for y), shared by the x sweep (cells = 4 columns) and the transposed y sweep (cells =
+// 4 rows).  The 32 lanes of the warp hold 128 consecutive cells; neighbour values cross lanes by shuffle, so all
+// 32 lanes must call together.  T[1..4] in; T[0], T[5] are fetched here.  Faces: [0] = low face of cell 0,
+// [n+1] = high face of cell n.  flg: bit n (0..4) face n fed by its low-side cell; bit 5+n cell n updated;
+// bit 13+n (FACEACT only) face n belongs to a swept row, else its flux is +0 (:1016-1018).
+// ---------------------------------------------------------------------------
+template <int SCHEME, bool FACEACT>
+__device__ __forceinline__ void sweep4(double (&T)[6], const double (&hh)[5], const double (&hcs)[5], const double (&gqs)[5],
+                                       const double (&hl)[4], const double (&ih)[4], const double (&mm)[4],
+                                       const unsigned flg, double (&o)[4]) {
+  const unsigned FULL = 0xffffffffu;
+    T[0] = __shfl_up_sync(FULL, T[4], 1);
+    T[5] = __shfl_down_sync(FULL, T[1], 1);
+    double a[5], A2[5];       // a[n] = T[n+1]-T[n]: difference across face n (same numbering as hh)
+#pragma unroll
+    for (int n = 0; n < 5; n++) { a[n] = T[n + 1] - T[n]; A2[n] = 2.0 * fabs(a[n]); }
+    double s[4];
+    if (SCHEME != SCHEME_PPM_H3) {
+#pragma unroll
+      for (int n = 0; n < 4; n++) s[n] = slope_f(a[n + 1], a[n], A2[n + 1], A2[n], T[n + 2] - T[n], mm[n]);
+    }
+    double fl[5];      // flux through face n
+    if (SCHEME == SCHEME_PLM) {
+      // face n is fed by cell n-1 (hh >= 0) or cell n (hh < 0); own cells are 0..3, cell 4 is the east neighbour's
+      const double s_e = __shfl_down_sync(FULL, s[0], 1);
+#pragma unroll
+      for (int n = 1; n < 5; n++) {
+        const bool lo = (flg >> n) & 1u;
+        const double sup = lo ? s[n - 1] : ((n < 4) ? s[n] : s_e), Tup = lo ? T[n] : T[n + 1];
+        fl[n] = hh[n] * (Tup + 0.5 * sup * gqs[n]);
+      }
+    } else {
+      double aL[4], aR[4], dA[4], a6[4];
+      if (SCHEME == SCHEME_PPM_CW) {
+        const double s_e = __shfl_down_sync(FULL, s[0], 1);
+        double e[5];     // e[n+1] = edge value at the east face of cell n
+#pragma unroll
+        for (int n = 0; n < 4; n++) e[n + 1] = edge_cw(T[n + 1], T[n + 2], s[n], (n < 3) ? s[n + 1] : s_e);
+        e[0] = __shfl_up_sync(FULL, e[4], 1);
+#pragma unroll
+        for (int n = 0; n < 4; n++) { aL[n] = e[n]; aR[n] = e[n + 1]; }
+      } else {
+#pragma unroll
+        for (int n = 0; n < 4; n++) edges_h3(T[n], T[n + 1], T[n + 2], aL[n], aR[n]);
+      }
+      double S[4], t1[4], dd[4], t2[4];
+#pragma unroll
+      for (int n = 0; n < 4; n++) {
+        ppm_pcm(aL[n], aR[n], T[n + 1], mm[n] * a[n + 1] * a[n]);
+        ppm_lim_a(aL[n], aR[n], T[n + 1], dA[n], S[n], t1[n], dd[n], t2[n]);
+      }
+      if (div6_tiny_pos(dd[0]) | div6_tiny_pos(dd[1]) | div6_tiny_pos(dd[2]) | div6_tiny_pos(dd[3])) {   // denormal dA^2: rare
+#pragma unroll
+        for (int n = 0; n < 4; n++) if (div6_tiny_pos(dd[n])) t2[n] = div6_int(dd[n]);
+      }
+      bool anyfix = ppm_over(t1[0], t2[0]);
+#pragma unroll
+      for (int n = 1; n < 4; n++) anyfix |= ppm_over(t1[n], t2[n]);
+      if (anyfix) {       // overshoot corrections are rare: one region per 4 cells
+#pragma unroll
+        for (int n = 0; n < 4; n++) {
+          double u = t1[n];
+          asm volatile("" : "+d"(u));      // re-test here instead of carrying four predicates through the hot path
+          if (ppm_over(u, t2[n])) ppm_fix(aL[n], aR[n], T[n + 1], u, dA[n], S[n]);
+        }
+      }
+#pragma unroll
+      for (int n = 0; n < 4; n++) a6[n] = ppm_a6(T[n + 1], S[n]);
+      // the east neighbour's first cell feeds face 4 when hh[4] < 0
+      const double aL_e = __shfl_down_sync(FULL, aL[0], 1), dA_e = __shfl_down_sync(FULL, dA[0], 1),
+                   a6_e = __shfl_down_sync(FULL, a6[0], 1);
+#pragma unroll
+      for (int n = 1; n < 5; n++) {
+        const double xL = (n < 4) ? aL[n] : aL_e, xD = (n < 4) ? dA[n] : dA_e, x6 = (n < 4) ? a6[n] : a6_e;
+        fl[n] = face_flux_sgn(hh[n], hcs[n], gqs[n], (flg >> n) & 1u, aR[n - 1], dA[n - 1], a6[n - 1], xL, xD, x6);
+      }
+    }
+    if (FACEACT) {
+#pragma unroll
+      for (int n = 1; n < 5; n++) fl[n] = ((flg >> (13 + n)) & 1u) ? fl[n] : 0.0;
+    }
+    fl[0] = __shfl_up_sync(FULL, fl[4], 1);
+#pragma unroll
+    for (int n = 0; n < 4; n++) {
+      const double upd = (T[n + 1] * hl[n] - (fl[n + 1] - fl[n])) * ih[n];
+      o[n] = ((flg >> (5 + n)) & 1u) ? upd : T[n + 1];
+    }
+}

@@ -112,86 +112,15 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   double2 p0 = *reinterpret_cast<const double2 *>(tt.src[m1] + q0);
   double2 p1 = *reinterpret_cast<const double2 *>(tt.src[m1] + q0 + 2);
   for (int m = 0; m < tt.n; m++) {
-    double T[6];      // T[0] = west neighbour, T[1..4] own cells, T[5] = east neighbour
+    double T[6];      // T[1..4] own cells (sweep4 fetches the neighbours T[0], T[5] from the adjacent lanes)
     T[1] = n0.x; T[2] = n0.y; T[3] = n1.x; T[4] = n1.y;
     n0 = p0; n1 = p1;
     if (m + 2 < tt.n) {       // prefetch the tracer after the next
       p0 = *reinterpret_cast<const double2 *>(tt.src[m + 2] + q0);
       p1 = *reinterpret_cast<const double2 *>(tt.src[m + 2] + q0 + 2);
     }
-    T[0] = __shfl_up_sync(FULL, T[4], 1);
-    T[5] = __shfl_down_sync(FULL, T[1], 1);
-    double a[5], A2[5];       // a[n] = T[n+1]-T[n]: difference across face n (same numbering as hh)
-#pragma unroll
-    for (int n = 0; n < 5; n++) { a[n] = T[n + 1] - T[n]; A2[n] = 2.0 * fabs(a[n]); }
-    double s[4];
-    if (SCHEME != SCHEME_PPM_H3) {
-#pragma unroll
-      for (int n = 0; n < 4; n++) s[n] = slope_f(a[n + 1], a[n], A2[n + 1], A2[n], T[n + 2] - T[n], mm[n]);
-    }
-    double fl[5];      // flux through face n
-    if (SCHEME == SCHEME_PLM) {
-      // face n is fed by cell n-1 (hh >= 0) or cell n (hh < 0); own cells are 0..3, cell 4 is the east neighbour's
-      const double s_e = __shfl_down_sync(FULL, s[0], 1);
-#pragma unroll
-      for (int n = 1; n < 5; n++) {
-        const bool lo = (flg >> n) & 1u;
-        const double sup = lo ? s[n - 1] : ((n < 4) ? s[n] : s_e), Tup = lo ? T[n] : T[n + 1];
-        fl[n] = hh[n] * (Tup + 0.5 * sup * gqs[n]);
-      }
-    } else {
-      double aL[4], aR[4], dA[4], a6[4];
-      if (SCHEME == SCHEME_PPM_CW) {
-        const double s_e = __shfl_down_sync(FULL, s[0], 1);
-        double e[5];     // e[n+1] = edge value at the east face of cell n
-#pragma unroll
-        for (int n = 0; n < 4; n++) e[n + 1] = edge_cw(T[n + 1], T[n + 2], s[n], (n < 3) ? s[n + 1] : s_e);
-        e[0] = __shfl_up_sync(FULL, e[4], 1);
-#pragma unroll
-        for (int n = 0; n < 4; n++) { aL[n] = e[n]; aR[n] = e[n + 1]; }
-      } else {
-#pragma unroll
-        for (int n = 0; n < 4; n++) edges_h3(T[n], T[n + 1], T[n + 2], aL[n], aR[n]);
-      }
-      double S[4], t1[4], dd[4], t2[4];
-#pragma unroll
-      for (int n = 0; n < 4; n++) {
-        ppm_pcm(aL[n], aR[n], T[n + 1], mm[n] * a[n + 1] * a[n]);
-        ppm_lim_a(aL[n], aR[n], T[n + 1], dA[n], S[n], t1[n], dd[n], t2[n]);
-      }
-      if (div6_tiny_pos(dd[0]) | div6_tiny_pos(dd[1]) | div6_tiny_pos(dd[2]) | div6_tiny_pos(dd[3])) {   // denormal dA^2: rare
-#pragma unroll
-        for (int n = 0; n < 4; n++) if (div6_tiny_pos(dd[n])) t2[n] = div6_int(dd[n]);
-      }
-      bool anyfix = ppm_over(t1[0], t2[0]);
-#pragma unroll
-      for (int n = 1; n < 4; n++) anyfix |= ppm_over(t1[n], t2[n]);
-      if (anyfix) {       // overshoot corrections are rare: one region per 4 cells
-#pragma unroll
-        for (int n = 0; n < 4; n++) {
-          double u = t1[n];
-          asm volatile("" : "+d"(u));      // re-test here instead of carrying four predicates through the hot path
-          if (ppm_over(u, t2[n])) ppm_fix(aL[n], aR[n], T[n + 1], u, dA[n], S[n]);
-        }
-      }
-#pragma unroll
-      for (int n = 0; n < 4; n++) a6[n] = ppm_a6(T[n + 1], S[n]);
-      // the east neighbour's first cell feeds face 4 when hh[4] < 0
-      const double aL_e = __shfl_down_sync(FULL, aL[0], 1), dA_e = __shfl_down_sync(FULL, dA[0], 1),
-                   a6_e = __shfl_down_sync(FULL, a6[0], 1);
-#pragma unroll
-      for (int n = 1; n < 5; n++) {
-        const double xL = (n < 4) ? aL[n] : aL_e, xD = (n < 4) ? dA[n] : dA_e, x6 = (n < 4) ? a6[n] : a6_e;
-        fl[n] = face_flux_sgn(hh[n], hcs[n], gqs[n], (flg >> n) & 1u, aR[n - 1], dA[n - 1], a6[n - 1], xL, xD, x6);
-      }
-    }
-    fl[0] = __shfl_up_sync(FULL, fl[4], 1);
     double o[4];
-#pragma unroll
-    for (int n = 0; n < 4; n++) {
-      const double upd = (T[n + 1] * hl[n] - (fl[n + 1] - fl[n])) * ih[n];
-      o[n] = ((flg >> (5 + n)) & 1u) ? upd : T[n + 1];
-    }
+    sweep4<SCHEME, false>(T, hh, hcs, gqs, hl, ih, mm, flg, o);
     const double cu = tt.cu[m];
     if (cu > 0.0) {      // warp-uniform: most tracers carry no underflow threshold
 #pragma unroll

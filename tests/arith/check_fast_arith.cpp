@@ -33,6 +33,8 @@ static inline long long __double_as_longlong(double x) { long long b; memcpy(&b,
 static inline double __longlong_as_double(long long b) { double x; memcpy(&x, &b, 8); return x; }
 static inline double __dmul_rn(double a, double b) { return a * b; }
 static inline double __fma_rn(double a, double b, double c) { return std::fma(a, b, c); }
+static inline double __shfl_up_sync(unsigned, double x, int) { return x; }      // (sweep4 is not instantiated here)
+static inline double __shfl_down_sync(unsigned, double x, int) { return x; }
 using std::copysign; using std::fabs;
 #include "fast_common.cuh"
 
