@@ -25,7 +25,9 @@
 #endif
 #define YTW 2           // tracers per consumer warp
 #define YT (YW * YTW)   // tracers per CTA
+#ifndef YNS
 #define YNS 8           // ring stages
+#endif
 #define YCOLS 32        // columns per CTA
 #define YROWB (YCOLS * 8)
 #ifndef YUNROLL
