@@ -179,6 +179,20 @@ int mom6adv_advect_resident(mom6adv_plan *plan, double dt, int x_first, int max_
                             int use_vol_prev, int update_vol_prev, int *n_iter);
 int mom6adv_sync(mom6adv_plan *plan);
 
+/* ---- either side of advect_tracer: what keeps its inputs and outputs off PCIe ------------
+ * mom6adv_accumulate_transports replaces the loop of step_MOM_dyn_split_RK2
+ *   uhtr(I,j,k) = uhtr(I,j,k) + uh(I,j,k)*dt   (j=js-2,je+2 ; I=Isq-2,Ieq+2)   and the same for vhtr
+ * (src/core/MOM_dynamics_split_RK2.F90:1045-1052) on the resident UHTR / VHTR fields; uh, vh are Fortran-layout u- and
+ * v-point arrays (host or device).  mom6adv_zero_transports replaces CS%uhtr(:,:,:) = 0.0 ; CS%vhtr(:,:,:) = 0.0
+ * (src/core/MOM.F90:1465-1466).  mom6adv_column_diag replaces the vertical sums of post_tracer_transport_diagnostics
+ * (src/tracer/MOM_tracer_registry.F90:725-815) for resident tracer m: kind ADV_XY_2D (:786-791, needs advection_xy
+ * associated, h_diag ignored), ZINT (:796-802), ZINT_100M (:745-766,805-811); out2d is an (isd:ied, jsd:jed) array,
+ * zero outside the computational domain like the reference's work2d. */
+int mom6adv_accumulate_transports(mom6adv_plan *plan, const double *uh, const double *vh, double dt);
+int mom6adv_zero_transports(mom6adv_plan *plan);
+enum { MOM6ADV_CD_ADV_XY_2D = 0, MOM6ADV_CD_ZINT = 1, MOM6ADV_CD_ZINT_100M = 2 };
+int mom6adv_column_diag(mom6adv_plan *plan, int m, int kind, const double *h_diag, double H_to_m, double *out2d);
+
 /* ---- observability ------------------------------------------------------- */
 /* Device time [ms] of the last advect call, CUDA-event timed on the plan's
  * stream; the stand-in for the (Ocean advect tracer) clock (:1146). */
@@ -188,9 +202,9 @@ long long mom6adv_kernel_launches(const mom6adv_plan *plan);
 /* Bytes of HBM held by the plan. */
 long long mom6adv_device_bytes(const mom6adv_plan *plan);
 /* Options: "profile" 0/1 -- time every kernel class of advect calls with CUDA
- * events on the plan's stream (resets the accumulators); "fast" 0/1 -- 0 forces
- * the generic thread-per-cell sweeps, 1 (default) uses the streaming kernels
- * whenever no flux diagnostic is associated; "sparse" 0/1 -- 1 (default)
+ * events on the plan's stream (resets the accumulators); "fast" 0/1/2 -- 0 forces
+ * the generic thread-per-cell sweeps, 2 (default) uses the streaming kernels
+ * whenever no flux diagnostic is associated, 1 their first generation (kept for A/B timing); "sparse" 0/1 -- 1 (default)
  * updates only the cells next to faces with residual transport on trips >= 2;
  * "mirror_chunk" n -- tracers per pipeline stage of mom6adv_advect (default 4,
  * 0 = one stage: upload everything, compute, download everything);

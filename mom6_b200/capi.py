@@ -18,6 +18,7 @@ LIB_PATH = os.path.join(_HERE, "libmom6adv_b200.so")
 
 OK, ERR_NOT_INIT, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_COMM = range(6)
 F_H_END, F_UHTR, F_VHTR, F_VOL_PREV, F_UHR, F_VHR, F_HPREV = range(7)
+CD_ADV_XY_2D, CD_ZINT, CD_ZINT_100M = range(3)
 KC_NAMES = ("prologue", "halo", "flags", "mass", "tracer_x", "tracer_y", "other", "sparse",
             "exch_pack", "exch_wire", "exch_unpack")
 DIAG_KINDS = ("ad_x", "ad_y", "ad2d_x", "ad2d_y", "advection_xy")
@@ -119,6 +120,9 @@ SYMBOLS = {
     "mom6adv_advect_resident": (C.c_int, [_P, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int,
                                           C.POINTER(C.c_int)]),
     "mom6adv_sync": (C.c_int, [_P]),
+    "mom6adv_accumulate_transports": (C.c_int, [_P, _P, _P, C.c_double]),
+    "mom6adv_zero_transports": (C.c_int, [_P]),
+    "mom6adv_column_diag": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_double, _P]),
     "mom6adv_last_advect_ms": (C.c_double, [_P]),
     "mom6adv_kernel_launches": (C.c_longlong, [_P]),
     "mom6adv_device_bytes": (C.c_longlong, [_P]),
@@ -297,6 +301,19 @@ class Plan:
         return n.value
 
     def sync(self): self._ck(self._l.mom6adv_sync(self._h))
+
+    # -- either side of advect_tracer --------------------------
+    def accumulate_transports(self, uh, vh, dt):
+        """uhtr += uh*dt ; vhtr += vh*dt on the resident fields (MOM_dynamics_split_RK2.F90:1045-1052)."""
+        self._ck(self._l.mom6adv_accumulate_transports(self._h, ptr(uh), ptr(vh), float(dt)))
+
+    def zero_transports(self):
+        """CS%uhtr(:,:,:) = 0.0 ; CS%vhtr(:,:,:) = 0.0 (MOM.F90:1465-1466)."""
+        self._ck(self._l.mom6adv_zero_transports(self._h))
+
+    def column_diag(self, m, kind, h_diag, H_to_m, out2d):
+        """Vertical sums of post_tracer_transport_diagnostics (MOM_tracer_registry.F90:725-815) for resident tracer m."""
+        self._ck(self._l.mom6adv_column_diag(self._h, int(m), int(kind), ptr(h_diag), float(H_to_m), ptr(out2d)))
     def set_option(self, key: str, value: int): self._ck(self._l.mom6adv_set_option(self._h, key.encode(), value))
 
     def kernel_class_time(self, kclass: int):

@@ -4,19 +4,23 @@
 // :902-963,1043-1047 for y), restructured so that every slope, edge value,
 // parabola and face flux is computed exactly ONCE per cell / face:
 //
-//   k_x_fast  one warp = 128 consecutive cells of one row (4 per lane, LDG.128),
+//   k_x_fast  (fast_x.cu) one warp = 128 consecutive cells of one row (4 per lane, LDG.128),
 //             all tracers looped in-thread with the tracer-independent mass
-//             quantities (uhh, CFL, hlst, Ihnew, mask product) held in
-//             registers; neighbour slopes / edges / outflows cross lanes by
-//             warp shuffle.  Out of place (buf[src] -> buf[1-src]); tiles
-//             overlap by 8 columns (120 useful of 128).
-//   k_y_fast  one thread = two adjacent columns of one tracer, marching in j
-//             with the whole stencil pipeline in registers (no shared memory,
-//             no recomputation, in place); the warps of a CTA are different
-//             tracers of the same columns, so the mass rows are L1 hits for
-//             all but the first warp.
+//             quantities (uhh, signed 0.5CFL and 1-2/3CFL, hlst, Ihnew, mask product)
+//             and one register of per-cell / per-face flags held in registers;
+//             the per-tracer arithmetic is sweep4 below: neighbour slopes / edges /
+//             outflows cross lanes by warp shuffle.  Out of place (buf[src] ->
+//             buf[1-src]); tiles overlap by 8 columns (120 useful of 128).
+//   k_y_ring  (fast_y.cu) one thread = one column x two tracers, marching in j with the
+//             whole stencil pipeline in registers, fed by a shared-memory ring of rows
+//             that a producer warp fills with bulk copies; in place.
 //
-// Exact-by-construction rewrites used:
+// The cost model these kernels were shaped by: an FP64 instruction holds its scheduler's
+// issue port for two cycles, so a sweep costs (non-FP64 instructions) + 2 x (FP64 instructions); the FP64 count
+// is fixed by the reference's formulas, the rest is what the rewrites below remove.
+//
+// Exact-by-construction rewrites used (each is checked bit for bit against the literal
+// formulas of internal.cuh on the CPU by tests/arith/check_fast_arith.cpp):
 //   * max(Tp,Tc,Tm)-Tc and Tc-min(Tp,Tc,Tm) are obtained from the face
 //     differences a_hi = Tp-Tc and a_lo = Tc-Tm (rounding is monotone and
 //     sign-symmetric), so the PLM slope magnitude is
@@ -25,7 +29,9 @@
 //     reference, so zero signs cannot differ.
 //   * min over non-negative doubles is an integer compare of the bit patterns.
 //   * the CW84 edge value aR(i) and aL(i+1) are the same expression.
-//   * a face's flux is evaluated by its upstream cell only.
+//   * a face's flux is evaluated by its upstream cell only, with the factors signed once per face.
+//   * PCM is applied to the edge values before the limiter; the slope is branch-free; /3 and /6 are exact
+//     without copysign (see the helpers).
 #pragma once
 #include "internal.cuh"
 #include "kernels.h"

@@ -6,6 +6,7 @@
 //
 // CTA = 32 columns x 2*YW tracers (one consumer warp per PAIR of tracers, one
 // column per lane) + one producer warp.  For every step r the producer issues
+// (ONE elected lane, addresses in uniform registers: no per-lane serialisation in front of UBLKCP)
 // 256-byte bulk copies (cp.async.bulk -> UBLKCP) of tracer row r of each tracer
 // and of the six tracer-independent rows the step needs (uhh/0.5CFL/1-2/3CFL of
 // face r-2, hlst/Ihnew of cell r-3, mask product of cell r-1) into stage
@@ -19,6 +20,10 @@
 // At step r a consumer thread finishes the slope of cell r-1, the edge between
 // cells r-2 and r-1, the parabola of cell r-2, the flux through face J = r-3
 // and the update of cell r-3 (written in place: rows <= r-3 are never read again).
+// Consumers address the ring by byte offset (ld.shared from a stage base), read the per-step "face row is swept"
+// flag from a shared-memory byte filled once per CTA, and keep conc_underflow out of line.  Measured and dropped:
+// two rows per stage, 12 stages, 6 consumer warps, an early poll of the next stage, a row-window skip of inactive
+// stretches, a transposed (sweep4 on columns) kernel -- profiles/r01_final_ncu.md.
 // ---------------------------------------------------------------------------
 #ifndef YW
 #define YW 7            // consumer warps per CTA: 7 + 1 producer warp = 256 threads

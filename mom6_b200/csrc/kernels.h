@@ -73,6 +73,14 @@ void launch_sparse_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Ran
                          const int *list, int cnt, int cap, const double *hh, const double *cfl, const double *hlst,
                          const double *ihnew, const double *mm, const int *entry, double *newT);
 
+// step.cu: transport accumulation and column diagnostics either side of advect_tracer
+void launch_accumulate(cudaStream_t s, const Geom &g, double *acc, const double *add, double dt, int ilo, int ihi,
+                       int jlo, int jhi);
+void launch_col_sum(cudaStream_t s, const Geom &g, const double *a, double *out);
+void launch_col_zint(cudaStream_t s, const Geom &g, const double *h, const double *t, double H_to_m, double *out);
+void launch_col_zint100(cudaStream_t s, const Geom &g, const double *h, const double *t, double H_to_m, int *khi,
+                        double *out);
+
 // halo.cu: exchange planning (host side)
 #include <vector>
 struct ExchangeSpec {

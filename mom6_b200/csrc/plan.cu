@@ -1332,6 +1332,71 @@ extern "C" int mom6adv_download_diag(mom6adv_plan *plan, int m, int kind, double
   return MOM6ADV_OK;
 }
 
+// ---------------------------------------------------------------------------
+// Either side of advect_tracer: with these on the device the accumulated transports never
+// exist on the host and a column diagnostic costs one 2-D field of D2H.  Scratch: the mass fields of the sweeps
+// (hh, cfl, hc), which are dead between two advect calls.
+// ---------------------------------------------------------------------------
+extern "C" int mom6adv_accumulate_transports(mom6adv_plan *plan, const double *uh, const double *vh, double dt) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "accumulate_transports: plan not initialised");
+  if (!uh || !vh) return fail(plan, MOM6ADV_ERR_INVALID, "accumulate_transports: NULL transport");
+  CK(cudaSetDevice(plan->device));
+  const Geom &g = plan->g;
+  // MOM_hor_index.F90:87-96: IscB = isc-1 in symmetric memory (IsdB = isd-1), isc otherwise; Isq = IscB (RK2:409)
+  const int IscB = (g.IsdB == g.isd - 1) ? g.isc - 1 : g.isc, JscB = (g.JsdB == g.jsd - 1) ? g.jsc - 1 : g.jsc;
+  // MOM_dynamics_split_RK2.F90:1045-1052: j=js-2,je+2 ; I=Isq-2,Ieq+2   and   J=Jsq-2,Jeq+2 ; i=is-2,ie+2
+  // (clipped to the data domain: the reference's declared bounds)
+  int rc = upload(plan, plan->hh, uh, g.IsdB, g.jsd, g.nk);
+  if (rc) return rc;
+  launch_accumulate(plan->stream, g, plan->uhtr, plan->hh, dt, std::max(IscB - 2, g.IsdB), std::min(g.iec + 2, g.ied),
+                    std::max(g.jsc - 2, g.jsd), std::min(g.jec + 2, g.jed));
+  rc = upload(plan, plan->cfl, vh, g.isd, g.JsdB, g.nk);     // (a second scratch: the first copy may still be in flight)
+  if (rc) return rc;
+  launch_accumulate(plan->stream, g, plan->vhtr, plan->cfl, dt, std::max(g.isc - 2, g.isd), std::min(g.iec + 2, g.ied),
+                    std::max(JscB - 2, g.JsdB), std::min(g.jec + 2, g.jed));
+  plan->launches += 2;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(plan->stream));
+  return MOM6ADV_OK;
+}
+
+extern "C" int mom6adv_zero_transports(mom6adv_plan *plan) {      // MOM.F90:1465-1466
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "zero_transports: plan not initialised");
+  CK(cudaSetDevice(plan->device));
+  CK(cudaMemsetAsync(plan->uhtr, 0, sizeof(double) * field_elems(plan), plan->stream));
+  CK(cudaMemsetAsync(plan->vhtr, 0, sizeof(double) * field_elems(plan), plan->stream));
+  CK(cudaStreamSynchronize(plan->stream));
+  return MOM6ADV_OK;
+}
+
+extern "C" int mom6adv_column_diag(mom6adv_plan *plan, int m, int kind, const double *h_diag, double H_to_m,
+                                   double *out2d) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "column_diag: plan not initialised");
+  if (m < 0 || m >= plan->ntr || kind < 0 || kind > 2) return fail(plan, MOM6ADV_ERR_INVALID, "column_diag: bad index");
+  if (!out2d) return fail(plan, MOM6ADV_ERR_INVALID, "column_diag: NULL destination");
+  CK(cudaSetDevice(plan->device));
+  const Geom &g = plan->g;
+  const TracerSlot &ts = plan->tr[m];
+  double *out = plan->hc;                                  // one plane of scratch
+  if (kind == MOM6ADV_CD_ADV_XY_2D) {
+    if (!ts.diag[4]) return fail(plan, MOM6ADV_ERR_INVALID, "column_diag: advection_xy is not associated");
+    launch_col_sum(plan->stream, g, ts.diag[4], out);     // MOM_tracer_registry.F90:786-791
+  } else {
+    if (!h_diag) return fail(plan, MOM6ADV_ERR_INVALID, "column_diag: NULL h_diag");
+    if (!ts.buf[ts.cur]) return fail(plan, MOM6ADV_ERR_INVALID, "column_diag: tracer is not resident");
+    int rc = upload(plan, plan->cfl, h_diag, g.isd, g.jsd, g.nk);
+    if (rc) return rc;
+    if (kind == MOM6ADV_CD_ZINT) launch_col_zint(plan->stream, g, plan->cfl, ts.buf[ts.cur], H_to_m, out);      // :796-802
+    else launch_col_zint100(plan->stream, g, plan->cfl, ts.buf[ts.cur], H_to_m, plan->sum_dev + 3, out);        // :745-766,805-811
+  }
+  plan->launches += (kind == MOM6ADV_CD_ZINT_100M) ? 2 : 1;
+  CK(cudaGetLastError());
+  int rc = download(plan, out2d, out, g.isd, g.jsd, 1);
+  if (rc) return rc;
+  CK(cudaStreamSynchronize(plan->stream));
+  return MOM6ADV_OK;
+}
+
 extern "C" int mom6adv_advect_resident(mom6adv_plan *plan, double dt, int x_first, int max_iter_in,
                                        int use_vol_prev, int update_vol_prev, int *n_iter) {
   if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "advect: tracer_advect_init must be called before advect_tracer");

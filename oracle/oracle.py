@@ -248,3 +248,51 @@ def efp_sum(a: np.ndarray):
     limbs = (C.c_longlong * 6)()
     lib().ora_efp_sum(_p(a), a.size, limbs)
     return tuple(limbs), float(lib().ora_efp_to_real(limbs))
+
+
+# ---------------------------------------------------------------------------
+# Either side of advect_tracer, restated with numpy.  Arrays are [k, j, i] views of the
+# Fortran arrays (i fastest), indices are the grid's 1-based values mapped through G.pi / G.pj / G.pI / G.pJ.  Every
+# sum runs over k in the reference's order, element-wise over (i, j): the same IEEE operations as the Fortran loops.
+# ---------------------------------------------------------------------------
+def accumulate_transports(uhtr, vhtr, uh, vh, dt, G):
+    """uhtr(I,j,k) = uhtr(I,j,k) + uh(I,j,k)*dt  (j=js-2,je+2 ; I=Isq-2,Ieq+2) and the same for vhtr
+    (/root/reference/src/core/MOM_dynamics_split_RK2.F90:1045-1052; Isq = G%IscB, :409), clipped to the declared bounds."""
+    IscB = G.isc - 1 if G.symmetric else G.isc
+    JscB = G.jsc - 1 if G.symmetric else G.jsc
+    I0, I1 = max(IscB - 2, G.IsdB), min(G.iec + 2, G.ied)
+    j0, j1 = max(G.jsc - 2, G.jsd), min(G.jec + 2, G.jed)
+    su = (slice(None), slice(G.pj(j0), G.pj(j1) + 1), slice(G.pI(I0), G.pI(I1) + 1))
+    uhtr[su] = uhtr[su] + uh[su] * dt
+    i0, i1 = max(G.isc - 2, G.isd), min(G.iec + 2, G.ied)
+    J0, J1 = max(JscB - 2, G.JsdB), min(G.jec + 2, G.jed)
+    sv = (slice(None), slice(G.pJ(J0), G.pJ(J1) + 1), slice(G.pi(i0), G.pi(i1) + 1))
+    vhtr[sv] = vhtr[sv] + vh[sv] * dt
+
+
+def column_diag(kind, G, nz, t=None, h_diag=None, H_to_m=1.0, advection_xy=None):
+    """work2d of post_tracer_transport_diagnostics (/root/reference/src/tracer/MOM_tracer_registry.F90:725-815):
+    kind 0 adv_xy_2d (:786-791), 1 zint (:796-802), 2 zint_100m (:745-766,805-811).  Returns (jsd:jed, isd:ied)."""
+    work = np.zeros((G.jed - G.jsd + 1, G.ied - G.isd + 1))
+    sl = (slice(G.pj(G.jsc), G.pj(G.jec) + 1), slice(G.pi(G.isc), G.pi(G.iec) + 1))
+    if kind == 0:
+        for k in range(nz):
+            work[sl] = work[sl] + advection_xy[k][sl]
+    elif kind == 1:
+        for k in range(nz):
+            work[sl] = work[sl] + (h_diag[k][sl] * H_to_m) * t[k][sl]
+    else:
+        frac = np.zeros((nz,) + work[sl].shape)
+        zbot = np.zeros(work[sl].shape)
+        khi = 0
+        for k in range(nz):
+            ztop = zbot
+            zbot = ztop + h_diag[k][sl] * H_to_m
+            with np.errstate(divide="ignore", invalid="ignore"):
+                part = (100.0 - ztop) / (zbot - ztop)
+            frac[k] = np.where(zbot <= 100.0, 1.0, np.where(ztop < 100.0, part, 0.0))
+            if np.any(frac[k] > 0):
+                khi = k + 1
+        for k in range(khi):
+            work[sl] = work[sl] + frac[k] * ((h_diag[k][sl] * H_to_m) * t[k][sl])
+    return work

@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 
 
 def _run_pair(ni, nj, nk, ntr, scheme, cfl=0.3, x_first=None, diags=False, ncalls=1, symmetric=True,
-              cyclic_x=True, halo=4, bug=False, fast=1, sparse=1, sparse_cap=0, **kw):
+              cyclic_x=True, halo=4, bug=False, fast=2, sparse=1, sparse_cap=0, **kw):
     c = synth.make_case(ni, nj, nk, ntr, cfl=cfl, symmetric=symmetric, cyclic_x=cyclic_x, halo=halo, **kw)
     params = {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme, "USE_HUYNH_STENCIL_BUG": bug}
     CSo = tracer_advect_init(None, c.G, None, params, None, None)
@@ -251,3 +251,65 @@ def test_sparse_trips_wide_grid_many_tiles():
     _assert_bitwise(c, Ro, Rg, outs)
     c, Ro, Rg, outs, nit = _run_pair(700, 37, 2, 4, "PPM", cfl=0.9, x_first=False, cyclic_x=False)
     _assert_bitwise(c, Ro, Rg, outs)
+
+
+# ---- either side of advect_tracer: transport accumulation and column diagnostics on the device ----
+@pytest.mark.parametrize("symmetric", [True, False])
+def test_transport_accumulation_and_column_diagnostics_bitwise(symmetric):
+    """mom6adv_accumulate_transports / zero_transports / column_diag against the numpy restatement of
+    MOM_dynamics_split_RK2.F90:1045-1052, MOM.F90:1465-1466 and MOM_tracer_registry.F90:725-815; then an advect
+    call fed by the device-accumulated transports against the oracle fed by the host-accumulated ones."""
+    from mom6_b200 import capi
+    c = synth.make_case(60, 44, 6, 4, cfl=0.6, symmetric=symmetric)
+    G, nz = c.G, c.GV.ke
+    params = {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": "PPM"}
+    CS = tracer_advect_init(None, G, None, params, None, None)
+    p = capi.Plan(G, c.GV, CS)
+    p.set_ntr(c.ntr)
+    Rg = synth.bind_registry(c)
+    adv_xy = [np.zeros(G.shape_h(nz)) for _ in range(c.ntr)]
+    for m in range(c.ntr):
+        p.upload_tracer(m, Rg.Tr[m].t)
+        p.bind_tracer(m, None, c.conc_underflow(m), advection_xy=adv_xy[m] if m == 1 else None)
+    h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
+    # three dynamics steps of transports that add up to (roughly) the case's uhtr / vhtr
+    rng = np.random.default_rng(7)
+    dts = [300.0, 450.0, 150.0]
+    uhs = [u / 900.0 * (1.0 + 0.1 * rng.standard_normal(u.shape)) for _ in dts]
+    vhs = [v / 900.0 * (1.0 + 0.1 * rng.standard_normal(v.shape)) for _ in dts]
+    uacc, vacc = np.zeros_like(u), np.zeros_like(v)
+    p.upload_field(capi.F_H_END, h)
+    p.upload_field(capi.F_UHTR, u); p.upload_field(capi.F_VHTR, v)      # something non-zero to be zeroed
+    p.zero_transports()
+    for uh, vh, dt in zip(uhs, vhs, dts):
+        oracle.accumulate_transports(uacc, vacc, uh, vh, dt, G)
+        p.accumulate_transports(uh, vh, dt)
+    ug, vg = np.full_like(u, 9.0), np.full_like(v, 9.0)
+    p.download_field(capi.F_UHTR, ug); p.download_field(capi.F_VHTR, vg)
+    assert np.array_equal(ug.view(np.uint64), uacc.view(np.uint64))
+    assert np.array_equal(vg.view(np.uint64), vacc.view(np.uint64))
+    # advect with the accumulated transports on both sides
+    CSo = tracer_advect_init(None, G, None, params, None, None)
+    Ro = synth.bind_registry(c, diags=False)
+    Ro.Tr[1].advection_xy = np.zeros(G.shape_h(nz))
+    oracle.advect_tracer(h, uacc, vacc, None, c.dt, G, c.GV, None, CSo, Ro)
+    p.advect_resident(c.dt)
+    for m in range(c.ntr):
+        out = np.zeros_like(Rg.Tr[m].t)
+        p.download_tracer(m, out)
+        assert np.array_equal(G.interior(out).view(np.uint64), G.interior(Ro.Tr[m].t).view(np.uint64)), m
+    # column diagnostics of the advected state
+    h_diag = h * (1.0 + 0.05 * rng.standard_normal(h.shape))
+    H_to_m = 0.5
+    for m in range(c.ntr):
+        for kind in (capi.CD_ZINT, capi.CD_ZINT_100M):
+            ref = oracle.column_diag(kind, G, nz, t=Ro.Tr[m].t, h_diag=h_diag, H_to_m=H_to_m)
+            out = np.full(G.shape_h(), 7.0)
+            p.column_diag(m, kind, h_diag, H_to_m, out)
+            assert np.array_equal(out.view(np.uint64), ref.view(np.uint64)), (m, kind, np.abs(out - ref).max())
+    ref = oracle.column_diag(capi.CD_ADV_XY_2D, G, nz, advection_xy=Ro.Tr[1].advection_xy)
+    out = np.full(G.shape_h(), 7.0)
+    p.column_diag(1, capi.CD_ADV_XY_2D, None, 1.0, out)
+    assert np.array_equal(out.view(np.uint64), ref.view(np.uint64))
+    assert np.abs(ref).max() > 0.0
+    p.destroy()

@@ -255,3 +255,61 @@ def test_obc_uniform_tracer_with_matching_reservoir_stays_uniform():
     wet = c.G.interior(c.G.mask2dT) > 0
     for tr in Reg.Tr:
         assert np.allclose(c.G.interior(tr.t)[:, wet], 7.0, rtol=1e-9)
+
+
+def test_side_loops_numpy_restatement_matches_literal_loops():
+    """oracle.accumulate_transports / column_diag (vectorised over i, j) against literal triple loops written from
+    MOM_dynamics_split_RK2.F90:1045-1052 and MOM_tracer_registry.F90:745-811 on a tiny grid."""
+    from mom6_b200 import synth
+    c = synth.make_case(9, 7, 5, 2, cfl=0.5)
+    G, nz = c.G, c.GV.ke
+    rng = np.random.default_rng(3)
+    uh, vh = rng.standard_normal(G.shape_u(nz)), rng.standard_normal(G.shape_v(nz))
+    u0, v0 = rng.standard_normal(G.shape_u(nz)), rng.standard_normal(G.shape_v(nz))
+    ua, va = u0.copy(), v0.copy()
+    oracle.accumulate_transports(ua, va, uh, vh, 37.5, G)
+    ub, vb = u0.copy(), v0.copy()
+    Isq, Ieq, Jsq, Jeq = G.isc - 1, G.iec, G.jsc - 1, G.jec
+    for k in range(nz):
+        for j in range(G.jsc - 2, G.jec + 3):
+            for I in range(Isq - 2, Ieq + 3):
+                ub[k, G.pj(j), G.pI(I)] = ub[k, G.pj(j), G.pI(I)] + uh[k, G.pj(j), G.pI(I)] * 37.5
+        for J in range(Jsq - 2, Jeq + 3):
+            for i in range(G.isc - 2, G.iec + 3):
+                vb[k, G.pJ(J), G.pi(i)] = vb[k, G.pJ(J), G.pi(i)] + vh[k, G.pJ(J), G.pi(i)] * 37.5
+    assert np.array_equal(ua.view(np.uint64), ub.view(np.uint64)) and np.array_equal(va.view(np.uint64), vb.view(np.uint64))
+    t = rng.standard_normal(G.shape_h(nz))
+    h = 40.0 * rng.random(G.shape_h(nz))
+    h[:, G.pj(G.jsc), G.pi(G.isc)] = 0.0            # a vanished column and
+    h[0, G.pj(G.jsc + 1), G.pi(G.isc + 1)] = 500.0  # one whose first layer already crosses 100 m
+    H_to_m = 0.75
+    w1 = np.zeros(G.shape_h()); w2 = np.zeros(G.shape_h())
+    frac = np.zeros(G.shape_h(nz)); khi = 0
+    zbot = np.zeros(G.shape_h())
+    for k in range(nz):
+        anyp = False
+        for j in range(G.jsc, G.jec + 1):
+            for i in range(G.isc, G.iec + 1):
+                pj, pi = G.pj(j), G.pi(i)
+                ztop = zbot[pj, pi]
+                zbot[pj, pi] = ztop + h[k, pj, pi] * H_to_m
+                if zbot[pj, pi] <= 100.0:
+                    frac[k, pj, pi] = 1.0
+                elif ztop < 100.0:
+                    frac[k, pj, pi] = (100.0 - ztop) / (zbot[pj, pi] - ztop)
+                else:
+                    frac[k, pj, pi] = 0.0
+                anyp = anyp or frac[k, pj, pi] > 0
+        if anyp:
+            khi = k + 1
+    for k in range(nz):
+        for j in range(G.jsc, G.jec + 1):
+            for i in range(G.isc, G.iec + 1):
+                pj, pi = G.pj(j), G.pi(i)
+                w1[pj, pi] = w1[pj, pi] + (h[k, pj, pi] * H_to_m) * t[k, pj, pi]
+                if k < khi:
+                    w2[pj, pi] = w2[pj, pi] + frac[k, pj, pi] * ((h[k, pj, pi] * H_to_m) * t[k, pj, pi])
+    a1 = oracle.column_diag(1, G, nz, t=t, h_diag=h, H_to_m=H_to_m)
+    a2 = oracle.column_diag(2, G, nz, t=t, h_diag=h, H_to_m=H_to_m)
+    assert np.array_equal(a1.view(np.uint64), w1.view(np.uint64))
+    assert np.array_equal(a2.view(np.uint64), w2.view(np.uint64))
