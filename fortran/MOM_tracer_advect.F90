@@ -160,6 +160,31 @@ interface
     integer(c_int), intent(out) :: n_iter
     integer(c_int) :: rc
   end function mom6adv_advect
+
+  !> uhtr += uh*dt ; vhtr += vh*dt on the resident fields (replaces MOM_dynamics_split_RK2.F90:1045-1052)
+  function mom6adv_accumulate_transports(plan, uh, vh, dt) bind(c, name="mom6adv_accumulate_transports") result(rc)
+    import :: c_int, c_ptr, c_double
+    type(c_ptr), value :: plan, uh, vh
+    real(c_double), value :: dt
+    integer(c_int) :: rc
+  end function mom6adv_accumulate_transports
+
+  !> CS%uhtr(:,:,:) = 0.0 ; CS%vhtr(:,:,:) = 0.0 on the resident fields (replaces MOM.F90:1465-1466)
+  function mom6adv_zero_transports(plan) bind(c, name="mom6adv_zero_transports") result(rc)
+    import :: c_int, c_ptr
+    type(c_ptr), value :: plan
+    integer(c_int) :: rc
+  end function mom6adv_zero_transports
+
+  !> work2d of id_adv_xy_2d (kind 0), id_zint (1), id_zint_100m (2) for resident tracer m (0-based)
+  !! (replaces the vertical sums of post_tracer_transport_diagnostics, MOM_tracer_registry.F90:745-811)
+  function mom6adv_column_diag(plan, m, kind, h_diag, H_to_m, out2d) bind(c, name="mom6adv_column_diag") result(rc)
+    import :: c_int, c_ptr, c_double
+    type(c_ptr), value :: plan, h_diag, out2d
+    integer(c_int), value :: m, kind
+    real(c_double), value :: H_to_m
+    integer(c_int) :: rc
+  end function mom6adv_column_diag
 end interface
 
 contains
