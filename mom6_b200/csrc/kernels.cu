@@ -240,7 +240,8 @@ __device__ __forceinline__ void mass_flux_face(const Geom &g, long long q, long 
       cf = uh / hm;
     }
   }
-  hh[q] = uh; cfl[q] = cf;
+  hh[q] = uh;
+  if (cfl) cfl[q] = cf;      // (the streaming sweeps read 0.5*CFL and 1-2/3*CFL instead: the dense first trip skips this array)
   if (hcv) {      // per-face factors of the flux formulas, shared by every tracer (streaming kernels)
     hcv[q] = 0.5 * cf;                                   // 0.5*CFL          (:551,554 / :937,941)
     gv[q] = plm ? (1. - cf) : (1. - (2. / 3.) * cf);     // 1-CFL (:565,569) or 1-2/3*CFL

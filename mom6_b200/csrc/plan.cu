@@ -1029,7 +1029,8 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
                                 h_neglect, ent, plan->domore_k, plan->hlst, plan->ihnew, plan->sp_list, plan->sum_dev + 1,
                                 plan->sp_cap, plan->tlist, plan->sum_dev + 2, plan->nsm);
       } else {
-        launch_mass_flux(s, dir, g, rg, res, plan->hprev, plan->areaT, min_h, ent, dom, plan->hh, plan->cfl,
+        // dense trip of the streaming path: nothing reads CFL itself (k_x_fast / k_y_ring take hc, gq), so it is not written
+        launch_mass_flux(s, dir, g, rg, res, plan->hprev, plan->areaT, min_h, ent, dom, plan->hh, nullptr,
                          plan->hc, plan->gq, scheme == SCHEME_PLM);
         launch_mass_update(s, dir, g, rg, res, plan->hprev, plan->hh, plan->areaT, x ? plan->uh_neglect : plan->vh_neglect,
                            h_neglect, ent, plan->domore_k, plan->hlst, plan->ihnew, nullptr, plan->sum_dev + 1, plan->sp_cap);
