@@ -48,7 +48,8 @@ __global__ void __launch_bounds__(128, XMINB)
 k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const double *__restrict__ hcv,
          const double *__restrict__ gqv, const double *__restrict__ hlstv, const double *__restrict__ ihv,
          const double *__restrict__ mmv, const int *__restrict__ entry, const int *__restrict__ domore_k, int wbase,
-         int wj_lo, int wj_hi) {      // rows (Fortran j) this launch owns; the others belong to another launch of the sweep
+         int wj_lo, int wj_hi,        // rows (Fortran j) this launch owns; the others belong to another launch of the sweep
+         int edge_store) {            // tiles aligned on the sweep's own range: the outermost halo lanes copy the columns beside it
   const unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const int rj = wj_lo + g.roff + blockIdx.y * 4 + (threadIdx.x >> 5), k0 = blockIdx.z;
@@ -59,7 +60,10 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   const bool lev = domore_k[k0] > 0;
   const bool in_j = (j >= rg.js && j <= rg.je);
   const bool active = lev && in_j && entry[k0 * g.R + rj];
-  const bool st = (lane >= 1 && lane <= 30) && (c0 + 3 >= g.isd + g.coff) && (c0 <= g.ied + g.coff);
+  // lanes 1..30 own their cells; with edge_store lane 0 of the first tile and lane 31 of the last one also store theirs:
+  // those columns lie outside the sweep's range (never updated, output == input), so no further tile is spent on them
+  const bool edge = edge_store && ((lane == 0 && blockIdx.x == 0) || (lane == 31 && blockIdx.x == gridDim.x - 1));
+  const bool st = ((lane >= 1 && lane <= 30) || edge) && (c0 + 3 >= g.isd + g.coff) && (c0 <= g.ied + g.coff);
   bool inr[4];
 #pragma unroll
   for (int n = 0; n < 4; n++) { const int i = c0 + n - g.coff; inr[n] = lev && in_j && i >= rg.is && i <= rg.ie; }
@@ -97,6 +101,7 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   // no stored cell of this warp's 128 columns is updated (land, or no transport left on any of their faces):
   // every output equals its input whatever the fluxes are, so the tile is copied through
   if (!__any_sync(FULL, st && (flg & 0x1e0u) != 0u)) { x_copy_through(tt, q0, st, inr); return; }
+  const bool st_ok = st && !(edge && (flg & 0x1e0u) != 0u);      // (an edge lane never holds an updated cell; if it did, its value would need a neighbour it lacks)
   asm volatile("" : "+r"(flg));      // opaque: keeps the compiler from re-deriving the bits with FP64 compares per tracer
   // signed flux factors (face_flux_sgn): PPM wants -hc, -gq on faces fed from the low side, PLM +gq there
   double hcs[5], gqs[5];
@@ -133,7 +138,7 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
 #pragma unroll
       for (int n = 0; n < 4; n++) if ((flg >> (9 + n)) & 1u) o[n] = underflow(o[n], cu);
     }
-    if (st) {
+    if (st_ok) {
       *reinterpret_cast<double2 *>(tt.dst[m] + q0) = make_double2(o[0], o[1]);
       *reinterpret_cast<double2 *>(tt.dst[m] + q0 + 2) = make_double2(o[2], o[3]);
     }
@@ -147,9 +152,19 @@ void launch_x_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const Tr
                    const int *entry, const int *domore_k, int wbase, int wj_lo, int wj_hi) {
   wj_lo = std::max(wj_lo, g.jsd); wj_hi = std::min(wj_hi, g.jed);
   if (wj_lo > wj_hi) return;
-  dim3 grid(x_fast_tiles(g, wbase), (wj_hi - wj_lo + 1 + 3) / 4, g.nk);
-  if (scheme == SCHEME_PLM) k_x_fast<SCHEME_PLM><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi);
-  else if (scheme == SCHEME_PPM_CW) k_x_fast<SCHEME_PPM_CW><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi);
-  else k_x_fast<SCHEME_PPM_H3><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi);
+  int ntx = x_fast_tiles(g, wbase), edge = 0;
+  {
+    // Tiles aligned on the sweep's own columns [rg.is, rg.ie] instead of the data domain: with halo 4 and one stencil
+    // application per pass the sweep computes isc..iec only, the 4 + 4 halo columns are copied by the two outermost
+    // halo lanes, and OM4_025's 1440 columns take 12 tiles instead of 13 (the 13th computed 4 cells).
+    const int cs = rg.is + g.coff, ce = rg.ie + g.coff;
+    const int wb2 = (cs & ~3) - 4;
+    const int nt2 = (ce >= cs) ? (ce - (wb2 + 4)) / XT_USE + 1 : ntx;
+    if (ce >= cs && wb2 >= 0 && nt2 < ntx && g.isd + g.coff >= wb2 && g.ied + g.coff <= wb2 + XT_USE * nt2 + 7 &&
+        wb2 + XT_USE * (nt2 - 1) + 128 <= g.P) { wbase = wb2; ntx = nt2; edge = 1; }
+  }
+  dim3 grid(ntx, (wj_hi - wj_lo + 1 + 3) / 4, g.nk);
+  if (scheme == SCHEME_PLM) k_x_fast<SCHEME_PLM><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi, edge);
+  else if (scheme == SCHEME_PPM_CW) k_x_fast<SCHEME_PPM_CW><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi, edge);
+  else k_x_fast<SCHEME_PPM_H3><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi, edge);
 }
-
