@@ -465,8 +465,10 @@ void make_geom(const mom6adv_grid *gr, Geom &g, int &wbase) {
   g.isc = gr->isc; g.iec = gr->iec; g.jsc = gr->jsc; g.jec = gr->jec;
   g.IsdB = gr->IsdB; g.JsdB = gr->JsdB; g.nk = gr->nk;
   const int nid = g.ied - g.isd + 1, njd = g.jed - g.jsd + 1;
-  int lead = ((hi + 1 + 15) / 16) * 16 - hi;            // column of isd; isc lands on a multiple of 16
-  if (lead < 4) lead += 16;
+  // column of isd; isc lands on a multiple of 32 = the y sweep's column tile, so that a sweep over isc..iec does not
+  // spend a half-used tile at either end (OM4_025: 45 tiles instead of 46)
+  int lead = ((hi + 1 + 31) / 32) * 32 - hi;
+  if (lead < 4) lead += 32;
   g.coff = lead - g.isd;
   // x tiles of the streaming kernel: 128 columns from wbase + 120*n, 120 useful (lanes 1..30)
   wbase = (lead - 4) & ~3;
