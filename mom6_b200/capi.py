@@ -14,7 +14,8 @@ from typing import Optional
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmom6adv_b200.so")
+# MOM6ADV_LIB selects a differently-flagged build of the same sources (kernel A/B timing, scripts/variants.py)
+LIB_PATH = os.environ.get("MOM6ADV_LIB") or os.path.join(_HERE, "libmom6adv_b200.so")
 
 OK, ERR_NOT_INIT, ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_COMM = range(6)
 F_H_END, F_UHTR, F_VHTR, F_VOL_PREV, F_UHR, F_VHR, F_HPREV = range(7)

@@ -28,7 +28,9 @@
 #ifndef YW
 #define YW 7            // consumer warps per CTA: 7 + 1 producer warp = 256 threads
 #endif
+#ifndef YTW
 #define YTW 2           // tracers per consumer warp
+#endif
 #define YT (YW * YTW)   // tracers per CTA
 #ifndef YNS
 #define YNS 8           // ring stages
@@ -102,9 +104,18 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   __shared__ __align__(8) unsigned long long bar_full[YNS], bar_empty[YNS];
   const int k0 = blockIdx.z;
   if (domore_k[k0] <= 0) return;                                  // CTA-uniform
+#ifdef YSWAP
+  // tracer groups of one column tile are adjacent in launch order: they march together and share the mass rows in L2
+  const int cbase = YCOLS * blockIdx.y;
+#else
   const int cbase = YCOLS * blockIdx.x;
+#endif
   if (cbase + YCOLS - 1 - g.coff < rg.is || cbase - g.coff > rg.ie) return;   // no column of the tile is swept
+#ifdef YSWAP
+  const int m0 = blockIdx.x * YT;
+#else
   const int m0 = blockIdx.y * YT;
+#endif
   const int nact = min(YT, tt.n - m0);                            // tracers of this CTA
   const int nwarp = (nact + YTW - 1) / YTW;                       // consumer warps with work
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -157,7 +168,7 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
 
   // ---- consumer warp: tracers m0+2w and m0+2w+1 (n = 0, 1), column cbase + lane ----
   const int t0 = YTW * w;
-  const bool two = (t0 + 1 < nact);                          // the warp's second tracer exists
+  const bool two = (YTW > 1) && (t0 + 1 < nact);                          // the warp's second tracer exists
   const int ts[2] = {t0, two ? t0 + 1 : t0};                 // (a lone tracer is computed twice, stored once)
   const int i0 = cbase + lane - g.coff;
   const bool inr = (i0 >= rg.is && i0 <= rg.ie);
@@ -165,7 +176,7 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   double *wp = tt.dst[m0 + ts[0]] + lev + lane + (long long)P * (r_lo - 3);
   const long long wd = tt.dst[m0 + ts[1]] - tt.dst[m0 + ts[0]];
   const double cu[2] = {tt.cu[m0 + ts[0]], tt.cu[m0 + ts[1]]};
-  const bool any_cu = (cu[0] > 0.0) || (cu[1] > 0.0);
+  const bool any_cu = (cu[0] > 0.0) || (YTW > 1 && cu[1] > 0.0);
   unsigned bfull0 = smem_u32(&bar_full[0]), bempty0 = smem_u32(&bar_empty[0]);
   asm volatile("" : "+r"(bfull0), "+r"(bempty0));      // computed once (the conversion reads a special register)
   const unsigned sb = smem_u32(y_smem) + lane * 8;                      // this lane's column in stage 0, row 0
@@ -184,7 +195,7 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
     const int r = r_lo + it, s = it % YNS;
     mbar_wait(bfull0 + 8u * s, (it / YNS) & 1);
     const unsigned qa = sb + s * (unsigned)sizeof(YStage);
-    const double Tn[2] = {lds_f64(qa + oT0), lds_f64(qa + oT0 + dT)};
+    const double Tn[2] = {lds_f64(qa + oT0), (YTW > 1) ? lds_f64(qa + oT0 + dT) : 0.0};
     const double hh2 = lds_f64(qa), hc2 = lds_f64(qa + YROWB), gq2 = lds_f64(qa + 2 * YROWB);
     const double hl = lds_f64(qa + 3 * YROWB), ih = lds_f64(qa + 4 * YROWB), mm1 = lds_f64(qa + 5 * YROWB);
     __syncwarp();
@@ -193,7 +204,7 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
     const bool out_row = (r - 3 >= rc_lo);
     double a0[2], A20[2], s1[2] = {0, 0};
 #pragma unroll
-    for (int n = 0; n < 2; n++) {
+    for (int n = 0; n < YTW; n++) {
       a0[n] = Tn[n] - T1[n];                               // face r-1|r
       A20[n] = 2.0 * fabs(a0[n]);
       if (SCHEME != SCHEME_PPM_H3) s1[n] = slope_f(a0[n], a1[n], A20[n], A21[n], Tn[n] - T2[n], mm1);    // cell r-1
@@ -202,37 +213,37 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
     double xL[2], xR[2], dA[2], a6[2] = {0, 0};
     if (SCHEME == SCHEME_PLM) {
 #pragma unroll
-      for (int n = 0; n < 2; n++) { xL[n] = T2[n]; xR[n] = T2[n]; dA[n] = 0.5 * s2[n]; }
+      for (int n = 0; n < YTW; n++) { xL[n] = T2[n]; xR[n] = T2[n]; dA[n] = 0.5 * s2[n]; }
     } else {
       double S[2], t1[2], dd[2], t2[2], e2[2] = {0, 0};
 #pragma unroll
-      for (int n = 0; n < 2; n++) {
+      for (int n = 0; n < YTW; n++) {
         if (SCHEME == SCHEME_PPM_CW) { e2[n] = edge_cw(T2[n], T1[n], s2[n], s1[n]); xL[n] = e3[n]; xR[n] = e2[n]; }
         else edges_h3(T3[n], T2[n], T1[n], xL[n], xR[n]);
         ppm_pcm(xL[n], xR[n], T2[n], pp2[n]);
         ppm_lim_a(xL[n], xR[n], T2[n], dA[n], S[n], t1[n], dd[n], t2[n]);
       }
-      if (div6_tiny_pos(dd[0]) | div6_tiny_pos(dd[1])) {   // denormal dA^2: rare
+      if (div6_tiny_pos(dd[0]) | (YTW > 1 && div6_tiny_pos(dd[YTW - 1]))) {   // denormal dA^2: rare
 #pragma unroll
-        for (int n = 0; n < 2; n++) if (div6_tiny_pos(dd[n])) t2[n] = div6_int(dd[n]);
+        for (int n = 0; n < YTW; n++) if (div6_tiny_pos(dd[n])) t2[n] = div6_int(dd[n]);
       }
-      if (ppm_over(t1[0], t2[0]) | ppm_over(t1[1], t2[1])) {      // overshoot correction: rare
+      if (ppm_over(t1[0], t2[0]) | (YTW > 1 && ppm_over(t1[YTW - 1], t2[YTW - 1]))) {      // overshoot correction: rare
 #pragma unroll
-        for (int n = 0; n < 2; n++) {
+        for (int n = 0; n < YTW; n++) {
           double u = t1[n];
           asm volatile("" : "+d"(u));      // re-test here instead of carrying predicates through the hot path
           if (ppm_over(u, t2[n])) ppm_fix(xL[n], xR[n], T2[n], u, dA[n], S[n]);
         }
       }
 #pragma unroll
-      for (int n = 0; n < 2; n++) { a6[n] = ppm_a6(T2[n], S[n]); e3[n] = e2[n]; }
+      for (int n = 0; n < YTW; n++) { a6[n] = ppm_a6(T2[n], S[n]); e3[n] = e2[n]; }
     }
     // cell r-2 feeds its north face r-2 when hh2 >= 0 (kept for the next step) and its south face r-3 when hh3 < 0
     const bool south = (hh3 < 0.0);                        // same for both tracers
     const bool do_i = (__double_as_longlong(ih) != 0LL);   // Ihnew > 0 (it is never negative)
     double o[2];
 #pragma unroll
-    for (int n = 0; n < 2; n++) {
+    for (int n = 0; n < YTW; n++) {
       double Fn2, Fs2 = 0.0;
       if (SCHEME == SCHEME_PLM) {      // hh*(T +- 0.5*slope*(1-CFL)), gq = 1-CFL (:946-961)
         Fn2 = hh2 * (xR[n] + dA[n] * gq2);
@@ -254,13 +265,13 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
     }
     if (any_cu) {      // warp-uniform and rare: a real branch (and one for both tracers), not predication
       if (cu[0] > 0.0) o[0] = underflow_rare(o[0], cu[0], inr);
-      if (cu[1] > 0.0) o[1] = underflow_rare(o[1], cu[1], inr);
+      if (YTW > 1 && cu[1] > 0.0) o[YTW - 1] = underflow_rare(o[YTW - 1], cu[1], inr);
     }
     hh3 = hh2; hc3 = hc2; gq3 = gq2;
     act3 = act2;
     if (out_row) {
       wp[0] = o[0];
-      if (two) wp[wd] = o[1];
+      if (YTW > 1 && two) wp[wd] = o[YTW - 1];
     }
     wp += P;
   }
@@ -269,7 +280,11 @@ k_y_ring(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
 void launch_y_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
                    const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm,
                    const int *entry, const int *domore_k) {
+#ifdef YSWAP
+  dim3 grid((tt.n + YT - 1) / YT, g.P / YCOLS, g.nk), block(32 * (YW + 1));
+#else
   dim3 grid(g.P / YCOLS, (tt.n + YT - 1) / YT, g.nk), block(32 * (YW + 1));
+#endif
   const size_t smem = sizeof(YStage) * YNS + ((g.R + 6 + 15) / 16) * 16;      // stages + one activity byte per step
 #define YLAUNCH(S)                                                                                        \
   do {                                                                                                    \
