@@ -1,4 +1,4 @@
-// TEST INFRASTRUCTURE ONLY -- CPU oracle for MOM6 advect_tracer.  PARITY UNPINNED
+// TEST INFRASTRUCTURE ONLY -- CPU oracle for MOM6 advect_tracer.  Pinned bit for bit against a mechanical translation of the unmodified reference file (oracle/f2c, tests/test_f2c_reference.py); see advect_ref.h
 // (see advect_ref.h).  Never linked, loaded or called by the product path.
 //
 // Statement-by-statement restatement of

@@ -6,12 +6,17 @@
  * and bench.py's cpu_baseline / --impl reference legs may load this library;
  * the product path (mom6_b200/) never does.
  *
- * PARITY UNPINNED: the reference ships no golden vectors for this path and
- * no Fortran compiler exists in the build container, so this restatement has
- * not been checked against an execution of the reference itself.  Its
- * fidelity rests on statement-by-statement review plus the reference's own
- * relational standards (layout / rotation / rescaling / threading invariance,
- * SURVEY.md section 4), which tests/ checks on the oracle itself.
+ * PARITY PIN: the reference ships no golden vectors for this path and no Fortran
+ * compiler exists in the build container.  What pins this restatement is the
+ * reference file itself: oracle/f2c/f2cpp.py translates the UNMODIFIED
+ * MOM_tracer_advect.F90 statement by statement into C++ (oracle/_ref/, built
+ * where /root/reference exists) and tests/test_f2c_reference.py requires this
+ * restatement, the committed goldens and (on the GPU box) the CUDA path to equal
+ * it bit for bit, whole arrays, all schemes / diagnostics / optional arguments /
+ * open boundaries.  Not pinned by that: what a gfortran BINARY does where the
+ * source leaves it open (MIN/MAX on +0/-0 ties, unassigned stack logicals) --
+ * both are run both ways and change no compared output -- and the FMS group
+ * pass, which is not in the reference tree (emulated here, see ora_group_pass).
  *
  * All arrays use the reference's Fortran layout (column major, i fastest):
  *   h-point  (isd:ied,   jsd:jed,   nk)

@@ -180,7 +180,9 @@ static int id_clock_advect = 1, id_clock_pass = 2, id_clock_sync = 3;
 
 inline void cpu_clock_begin(int) {}
 inline void cpu_clock_end(int) {}
-inline void f_mom_error(int level, const char *msg) {
+inline std::string f_concat(const std::string &a, const std::string &b) { return a + b; }
+inline void f_mom_error(int level, const std::string &m) {
+  const char *msg = m.c_str();
   fprintf(stderr, "f2c MOM_error(%s): %s\n", level == fatal ? "FATAL" : "WARNING", msg);
   if (level == fatal) throw std::string(msg);
 }

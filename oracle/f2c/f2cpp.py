@@ -36,7 +36,8 @@ INTRINSICS = {"max": "f_max", "min": "f_min", "abs": "f_abs", "sign": "f_sign", 
               "ceiling": "f_ceiling", "tiny": "f_tiny", "present": "f_present", "associated": "f_associated",
               "allocated": "f_allocated", "sqrt": "f_sqrt", "epsilon": "f_epsilon", "real": "f_real"}
 # names whose Fortran declaration is `pointer` to a derived type: member access is ->
-POINTER_NAMES = {"cs", "reg", "obc", "segment", "tr_reg"}
+POINTER_NAMES = {"cs", "reg", "obc", "segment"}      # local / dummy pointers to derived types
+POINTER_MEMBERS = {"tr_reg"}                          # pointer-valued components
 CXX_RESERVED = {"int", "double", "float", "long", "short", "char", "bool", "new", "delete", "this", "class", "struct",
                 "union", "enum", "template", "typename", "namespace", "using", "public", "private", "protected",
                 "virtual", "operator", "and", "or", "not", "xor", "auto", "register", "static", "const", "volatile",
@@ -262,7 +263,7 @@ class Parser:
             a = Un(op, a) if op == "-" else a
         else:
             a = self.p_mul()
-        while self.peek()[1] in ("+", "-"):
+        while self.peek()[1] in ("+", "-", "//"):
             op = self.next()[1]
             a = Bin(op, a, self.p_mul())
         return a
@@ -418,7 +419,7 @@ class Emitter:
             else:
                 out += txt
             if k + 1 < len(r.parts):
-                out += "->" if name in POINTER_NAMES else "."
+                out += "->" if (name in POINTER_NAMES if first else name in POINTER_MEMBERS) else "."
         return out
 
     def is_whole_array_target(self, n: Node) -> bool:
@@ -468,7 +469,7 @@ class Decl:
     # base: "double" | "int" | "lbool" | ("type", tname);  dims: list of (lo, hi) strings or None
 
 
-DECL_RE = re.compile(r"^(real|integer|logical|character|type\s*\(\s*\w+\s*\))\b(.*)$")
+DECL_RE = re.compile(r"^(real|integer|logical|character|type\s*\(\s*\w+\s*\))(?![a-z0-9_])(.*)$")
 
 
 def parse_decl(st: str):
@@ -683,7 +684,7 @@ def translate_sub(sub: Sub, all_subs, src_name: str) -> str:
                 r = parse_expr(name + m.group(2))
                 args = r.parts[0][1]
             if name == "mom_error":
-                put("f_mom_error(%s);" % ", ".join(em.e(a) if not isinstance(a, Bin) else '""' for a in args[:1] + args[1:]), ln)
+                put("f_mom_error(%s);" % ", ".join(em.e(a) for a in args), ln)
                 return
             a_txt = []
             for a in args:
@@ -703,7 +704,18 @@ def translate_sub(sub: Sub, all_subs, src_name: str) -> str:
         if eq < 0:
             raise F2CError("line %s: cannot classify statement %r" % (ln, st))
         lhs, rhs = parse_expr(st[:eq]), parse_expr(st[eq + 1:])
-        if em.is_whole_array_target(lhs):
+        if em.is_whole_array_target(lhs) and isinstance(rhs, Ref) and rhs.parts[-1][1] and not em.whole(rhs.parts[-1][1]) \
+                and sum(isinstance(a, Section) for a in rhs.parts[-1][1]) == 1:
+            # rank-1 section of a higher-rank array, e.g. a(:) = b(:,k): element loop over the one sectioned dimension
+            args = rhs.parts[-1][1]
+            d = [isinstance(a, Section) for a in args].index(True)
+            if args[d].lo is not None or args[d].hi is not None:
+                raise F2CError("line %s: only full ':' sections are supported" % ln)
+            base = Ref(rhs.parts[:-1] + [(rhs.parts[-1][0], None)])
+            L, B = em.ref(lhs), em.ref(base)
+            idx = ["(s__ - %s.lo[0] + %s.lo[%d])" % (L, B, d) if k == d else em.e(a) for k, a in enumerate(args)]
+            put("for (int s__ = %s.lo[0]; s__ <= %s.hi[0]; s__++) %s(s__) = %s(%s);" % (L, L, L, B, ", ".join(idx)), ln)
+        elif em.is_whole_array_target(lhs):
             r = em.ref(rhs) if isinstance(rhs, Ref) and em.is_whole_array_target(rhs) else em.e(rhs)
             put("f_assign(%s, %s);" % (em.ref(lhs), r), ln)
         else:

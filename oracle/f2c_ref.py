@@ -1,0 +1,75 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes wrapper around oracle/_ref/libref_f2c*.so: the UNMODIFIED reference file
+/root/reference/src/tracer/MOM_tracer_advect.F90 translated statement by statement to C++ by oracle/f2c/f2cpp.py
+(there is no Fortran compiler in the image) and compiled with g++ -O2 -ffp-contract=off.
+
+build() runs the translator only where /root/reference exists (the build container); the GPU box uses the prebuilt
+libraries that travel with the snapshot (oracle/_ref/ is git-ignored, not gpurun-ignored).  Nothing of the reference
+is stored in the repository.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+from . import oracle as ora
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_REF_DIR = os.path.join(_HERE, "_ref")
+_SRC = "/root/reference/src/tracer/MOM_tracer_advect.F90"
+_libs = {}
+
+VARIANTS = {"": "libref_f2c.so", "lt": "libref_f2c_lt.so", "mm": "libref_f2c_mm.so", "chk": "libref_f2c_chk.so"}
+
+
+def available() -> bool:
+    return os.path.exists(os.path.join(_REF_DIR, VARIANTS[""])) or os.path.exists(_SRC)
+
+
+def build(force: bool = False) -> bool:
+    """Translate + compile when the reference source is present; returns whether the libraries exist."""
+    ora.build()
+    have = all(os.path.exists(os.path.join(_REF_DIR, v)) for v in VARIANTS.values())
+    if os.path.exists(_SRC) and (force or not have):
+        if force:
+            subprocess.run(["make", "-C", os.path.join(_HERE, "f2c"), "clean"], check=True, capture_output=True)
+        subprocess.run(["make", "-C", os.path.join(_HERE, "f2c")], check=True, capture_output=True)
+        have = True
+    elif os.path.exists(_SRC):
+        subprocess.run(["make", "-C", os.path.join(_HERE, "f2c")], check=True, capture_output=True)     # up to date?
+    return have
+
+
+def lib(variant: str = ""):
+    if variant not in _libs:
+        if not build():
+            raise RuntimeError("oracle/_ref/libref_f2c*.so missing and /root/reference absent: cannot build the translated reference")
+        ora.lib()      # liboracle_advect.so (group-pass emulation) first: the rpath of the ref library points at it
+        l = C.CDLL(os.path.join(_REF_DIR, VARIANTS[variant]))
+        l.ref_advect_tracer_obc.restype = C.c_int
+        l.ref_advect_tracer_obc.argtypes = [
+            C.POINTER(ora.ora_grid), C.POINTER(ora.ora_cs), C.POINTER(ora.ora_tracer), C.c_int,
+            ora._dp, ora._dp, ora._dp, C.c_double, C.c_int, ora._dp, C.c_int, C.c_int, ora._dp, ora._dp,
+            C.POINTER(ora.ora_domain), C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_int), C.POINTER(ora.ora_obc)]
+        _libs[variant] = l
+    return _libs[variant]
+
+
+def advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first_in=None, vol_prev=None, max_iter_in=None,
+                  update_vol_prev=None, uhr_out=None, vhr_out=None, variant: str = "", pass_fn=None, sum_fn=None) -> int:
+    """The translated reference's advect_tracer (same argument list as oracle.advect_tracer).  Returns the number of
+    group passes it made (the reference does not report its iteration count)."""
+    g, cs, dom = ora.make_grid(G, GV), ora.make_cs(CS), ora.make_domain(G.Domain)
+    tr = ora.make_tracers(Reg)
+    npass = C.c_int(0)
+    pf = C.cast(pass_fn, C.c_void_p) if pass_fn is not None else None
+    sf = C.cast(sum_fn, C.c_void_p) if sum_fn is not None else None
+    obc, _keep = ora.make_obc(OBC)
+    rc = lib(variant).ref_advect_tracer_obc(
+        C.byref(g), C.byref(cs), tr, Reg.ntr, ora._p(h_end), ora._p(uhtr), ora._p(vhtr), float(dt),
+        ora._opt_flag(x_first_in), ora._p(vol_prev), -1 if max_iter_in is None else int(max_iter_in),
+        ora._opt_flag(update_vol_prev), ora._p(uhr_out), ora._p(vhr_out), C.byref(dom), pf, sf, None,
+        C.byref(npass), C.byref(obc) if obc is not None else None)
+    if rc != 0:
+        raise RuntimeError("translated reference advect_tracer failed (FATAL): %d" % rc)
+    return npass.value

@@ -1,6 +1,7 @@
 """TEST INFRASTRUCTURE ONLY -- ctypes wrapper around the CPU oracle
 (oracle/advect_ref.cpp, a restatement of
-/root/reference/src/tracer/MOM_tracer_advect.F90:52-1087).  PARITY UNPINNED.
+/root/reference/src/tracer/MOM_tracer_advect.F90:52-1087).  Pinned bit for bit against a mechanical translation of
+the unmodified reference file (oracle/f2c, tests/test_f2c_reference.py); no gfortran binary has been available.
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
 --impl reference legs may import this module.

@@ -2,11 +2,11 @@
 """Generate tests/golden/*.npz: complete inputs AND oracle outputs of small advect_tracer cases.
 
 The reference (MOM6) ships no golden vector for MOM_tracer_advect.F90 and cannot
-be built in this image (no Fortran compiler, un-vendored FMS), so these files
-pin the ORACLE (oracle/advect_ref.cpp) against itself across rebuilds and pin
-the CUDA path against a stored answer -- they are not MOM6 output.  If a Fortran
-box ever runs oracle/fortran_stub_harness on the same inputs, its output goes
-here and parity becomes pinned.
+be built in this image (no Fortran compiler, un-vendored FMS).  The files are
+written from the oracle (oracle/advect_ref.cpp); tests/test_f2c_reference.py then
+requires the UNMODIFIED reference file, translated mechanically to C++
+(oracle/f2c), to reproduce every one of them bit for bit -- so they are the
+reference's answers as far as its source defines them, not only the oracle's.
 
   python tests/golden/make_golden.py      (re)writes every file listed in CASES
 """
