@@ -106,7 +106,7 @@ void build_halo_exchange(const Geom &g, const ExchangeSpec &x, int me, HaloBuild
           const Geom &q = pg[s.rank];
           p.recv_src[pos].push_back((s.i + q.coff) + q.P * (s.j + q.roff));
           p.recv_sgn[pos].push_back((signed char)s.sgn);
-          p.peer_plane = q.plane;
+          p.peer_plane = q.plane; p.peer_P = q.P; p.peer_R = q.R;
         } else if (s.rank == me) {
           PeerBuild &p = peer(d);
           p.send_src[pos].push_back(pidx(s.i, s.j)); p.send_sgn[pos].push_back((signed char)s.sgn);

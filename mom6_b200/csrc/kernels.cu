@@ -272,8 +272,7 @@ __global__ void k_mass_flux(Geom g, Range rg, const double *__restrict__ res, co
 // (uhh = CFL = 0) that nothing reads: the list-driven tracer update (sparse.cu) touches only cells next to a
 // non-zero face.  A persistent grid scans uhr / vhr, writes the outputs of the active tiles only, records per tile
 // bit 0 "outputs written" and bit 1 "a cell of this tile may change" (a residual on the tile's own faces or on the
-// face before them) and appends the tiles with bit 1 to tlist, which is all k_mass_update_list visits.  If the
-// active-cell list overflows, k_fill_skipped completes the fields for the dense tracer kernels.
+// face before them) and appends the tiles with bit 1 to tlist, which is all k_mass_update_list visits.
 #define SCAN_UNROLL 4
 template <int DIR>
 __global__ void __launch_bounds__(256)
@@ -365,24 +364,6 @@ void launch_mass_flux_scan(cudaStream_t s, int dir, const Geom &g, Range rg, con
   else k_mass_flux_scan<1><<<grid, 256, 0, s>>>(g, rg, res, hprev, areaT, min_h, entry, domore, hh, cfl, hc, gq, plm, tflags, tlist, tcount);
 }
 
-// After a list overflow in a residual trip: give the skipped tiles the neutral values a dense pass would have
-// written, so that the dense tracer kernels can run.
-__global__ void k_fill_skipped(Geom g, const int *__restrict__ tflags, double *__restrict__ hh, double *__restrict__ cfl,
-                               double *__restrict__ hcv, double *__restrict__ gv, double *__restrict__ hlst,
-                               double *__restrict__ ihnew) {
-  const int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y, k0 = blockIdx.z;
-  if (ci >= g.P) return;
-  const int f = tflags[((long long)k0 * g.R + rj) * (g.P >> 5) + (ci >> 5)];
-  const long long q = gidx(g, ci, rj, k0);
-  if (!(f & 1)) { hh[q] = 0.0; cfl[q] = 0.0; if (hcv) { hcv[q] = 0.0; gv[q] = 1.0; } }
-  if (!(f & 2)) { hlst[q] = 0.0; ihnew[q] = 0.0; }
-}
-void launch_fill_skipped(cudaStream_t s, const Geom &g, const int *tflags, double *hh, double *cfl, double *hc,
-                         double *gq, double *hlst, double *ihnew) {
-  dim3 grid((g.P + TPB - 1) / TPB, g.R, g.nk);
-  k_fill_skipped<<<grid, TPB, 0, s>>>(g, tflags, hh, cfl, hc, gq, hlst, ihnew);
-}
-
 // ---------------------------------------------------------------------------
 // Residual transport and cell volume update (:632-649 for x, :1021-1040 for y).
 // ihnew == 0 encodes do_i == .false. (a true Ihnew is always > 0).
@@ -394,7 +375,8 @@ __device__ __forceinline__ void mass_update_cell(const Geom &g, const Range &rg,
                                                  const double *__restrict__ neglect, double h_neglect,
                                                  const int *__restrict__ entry, const int *__restrict__ domore_k,
                                                  double *__restrict__ hlst, double *__restrict__ ihnew,
-                                                 int *__restrict__ list, int *__restrict__ count, int cap) {
+                                                 int *__restrict__ list, int *__restrict__ count, int cap,
+                                                 int *__restrict__ nz = nullptr) {
   const int i = ci - g.coff, j = rj - g.roff;
   const long long q = gidx(g, ci, rj, k0), q2 = gidx(g, ci, rj, 0);
   const int st = (DIR == 0) ? 1 : g.P;
@@ -414,6 +396,9 @@ __device__ __forceinline__ void mass_update_cell(const Geom &g, const Range &rg,
     double r = res[q] - uh;
     if (fabs(r) < neglect[q2]) r = 0.0;
     res[q] = r;
+    // dense trip: count the faces that keep a residual -- twice that number estimates the cells the next trip lists
+    // (the host only uses it to choose between the list-driven and the dense kernels: a hint, never a bound)
+    if (nz && r != 0.0) atomicAdd(nz, 1);
   }
   double hl = 0.0, ih = 0.0;
   if (cell_ok) {
@@ -441,10 +426,10 @@ __global__ void k_mass_update(Geom g, Range rg, double *__restrict__ res, double
                               const double *__restrict__ neglect, double h_neglect,
                               const int *__restrict__ entry, const int *__restrict__ domore_k,
                               double *__restrict__ hlst, double *__restrict__ ihnew,
-                              int *__restrict__ list, int *__restrict__ count, int cap) {
+                              int *__restrict__ list, int *__restrict__ count, int cap, int *__restrict__ nz) {
   const int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y, k0 = blockIdx.z;
   if (ci >= g.P) return;
-  mass_update_cell<DIR>(g, rg, ci, rj, k0, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap);
+  mass_update_cell<DIR>(g, rg, ci, rj, k0, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap, nz);
 }
 // residual trips: only the tiles k_mass_flux_scan listed (nothing changes in the others)
 template <int DIR>
@@ -469,10 +454,10 @@ k_mass_update_list(Geom g, Range rg, double *__restrict__ res, double *__restric
 void launch_mass_update(cudaStream_t s, int dir, const Geom &g, Range rg, double *res, double *hprev,
                         const double *hh, const double *areaT, const double *neglect, double h_neglect,
                         const int *entry, const int *domore_k, double *hlst, double *ihnew,
-                        int *list, int *count, int cap) {
+                        int *list, int *count, int cap, int *nz) {
   dim3 grid((g.P + TPB - 1) / TPB, g.R, g.nk);
-  if (dir == 0) k_mass_update<0><<<grid, TPB, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap);
-  else k_mass_update<1><<<grid, TPB, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap);
+  if (dir == 0) k_mass_update<0><<<grid, TPB, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap, nz);
+  else k_mass_update<1><<<grid, TPB, 0, s>>>(g, rg, res, hprev, hh, areaT, neglect, h_neglect, entry, domore_k, hlst, ihnew, list, count, cap, nz);
 }
 void launch_mass_update_list(cudaStream_t s, int dir, const Geom &g, Range rg, double *res, double *hprev,
                              const double *hh, const double *areaT, const double *neglect, double h_neglect,
@@ -682,6 +667,60 @@ void launch_halo_pull(cudaStream_t s, long long plane, long long peer_plane, int
   if (n <= 0 || nfields <= 0) return;
   dim3 grid((n + TPB - 1) / TPB, nk, nfields);
   k_halo_pull<<<grid, TPB, 0, s>>>(plane, peer_plane, nk, dst, src, sgn, n, fields, peer_fields);
+}
+// Pair-list form: entry t moves the two consecutive points dst2[t], dst2[t]+1 <- src2[t], src2[t]+1 (both even: 16-byte
+// aligned) of four levels per thread, all loads issued before the first store: 64 bytes in flight per thread over NVLink.
+// tile2[t] = the source points' 32-column tile in the OWNER's plane; the map (fetched into local memory first, so that
+// the pull makes one NVLink round trip) says whether any cell of that tile changed since the last pass: after a
+// list-driven residual trip nearly all of the strip is skipped.
+#define PULL_LEV 4
+__global__ void __launch_bounds__(128)
+k_halo_pull2(long long plane, long long peer_plane, int nk, const int *__restrict__ dst2, const int *__restrict__ src2,
+             const signed char *__restrict__ sgn2, const int *__restrict__ tile2, int n2,
+             double *const *__restrict__ fields, double *const *__restrict__ peer_fields,
+             const unsigned char *__restrict__ dirty, int tiles_plane) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n2) return;
+  const int f = blockIdx.z, kb = blockIdx.y * PULL_LEV;
+  const int d = dst2[t], sidx = src2[t];
+  const bool neg = sgn2[t] < 0;
+  bool need[PULL_LEV];
+#pragma unroll
+  for (int u = 0; u < PULL_LEV; u++) need[u] = (kb + u < nk);
+  if (dirty && dirty[(long long)tiles_plane * nk] == 0) {
+    const int tl = tile2[t];
+#pragma unroll
+    for (int u = 0; u < PULL_LEV; u++) if (need[u]) need[u] = dirty[(long long)tiles_plane * (kb + u) + tl] != 0;
+  }
+  const double *pf = peer_fields[f];
+  double2 v[PULL_LEV];
+#pragma unroll
+  for (int u = 0; u < PULL_LEV; u++)
+    if (need[u]) v[u] = __ldcv(reinterpret_cast<const double2 *>(pf + peer_plane * (kb + u) + sidx));
+  double *mf = fields[f];
+#pragma unroll
+  for (int u = 0; u < PULL_LEV; u++)
+    if (need[u]) {
+      double2 w = v[u];
+      if (neg) { w.x = -w.x; w.y = -w.y; }
+      *reinterpret_cast<double2 *>(mf + plane * (kb + u) + d) = w;
+    }
+}
+void launch_halo_pull2(cudaStream_t s, long long plane, long long peer_plane, int nk, const int *dst2, const int *src2,
+                       const signed char *sgn2, const int *tile2, int n2, double *const *fields,
+                       double *const *peer_fields, int nfields, const unsigned char *dirty, int peer_tiles_plane) {
+  if (n2 <= 0 || nfields <= 0) return;
+  dim3 grid((n2 + 127) / 128, (nk + PULL_LEV - 1) / PULL_LEV, nfields);
+  k_halo_pull2<<<grid, 128, 0, s>>>(plane, peer_plane, nk, dst2, src2, sgn2, tile2, n2, fields, peer_fields, dirty, peer_tiles_plane);
+}
+__global__ void k_fetch_bytes(unsigned char *__restrict__ dst, const unsigned char *__restrict__ src, long long n16) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n16) reinterpret_cast<int4 *>(dst)[t] = __ldcv(reinterpret_cast<const int4 *>(src) + t);
+}
+void launch_fetch_bytes(cudaStream_t s, unsigned char *dst, const unsigned char *src, long long bytes) {
+  const long long n16 = bytes / 16;      // (the maps are padded to a multiple of 16 bytes)
+  if (n16 <= 0) return;
+  k_fetch_bytes<<<(unsigned)((n16 + 255) / 256), 256, 0, s>>>(dst, src, n16);
 }
 void launch_halo_pack(cudaStream_t s, long long plane, int nk, const int *src, const signed char *sgn, int n,
                       double *const *fields, int nfields, double *buf) {

@@ -22,7 +22,7 @@ void launch_mass_flux(cudaStream_t s, int dir, const Geom &g, Range rg, const do
 void launch_mass_update(cudaStream_t s, int dir, const Geom &g, Range rg, double *res, double *hprev,
                         const double *hh, const double *areaT, const double *neglect, double h_neglect,
                         const int *entry, const int *domore_k, double *hlst, double *ihnew,
-                        int *list, int *count, int cap);
+                        int *list, int *count, int cap, int *nz = nullptr);
 void launch_tracer_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TracerDev *tr, int ntr,
                          int src, const double *hh, const double *cfl, const double *hlst, const double *ihnew,
                          const double *mm, const double *IareaT, const int *entry, const int *domore_k, double Idt);
@@ -35,6 +35,13 @@ void launch_halo_pack(cudaStream_t s, long long plane, int nk, const int *src, c
                       double *const *fields, int nfields, double *buf);
 void launch_halo_pull(cudaStream_t s, long long plane, long long peer_plane, int nk, const int *dst, const int *src,
                       const signed char *sgn, int n, double *const *fields, double *const *peer_fields, int nfields);
+// the same exchange, 16 bytes per load and four levels in flight per thread (pair list: dst2/src2 address two
+// consecutive points), skipping points whose source tile the owner has not changed since the last pass
+// (dirty: a LOCAL copy of the owner's per-level tile map + its "everything changed" byte; nullptr: pull everything)
+void launch_halo_pull2(cudaStream_t s, long long plane, long long peer_plane, int nk, const int *dst2, const int *src2,
+                       const signed char *sgn2, const int *tile2, int n2, double *const *fields,
+                       double *const *peer_fields, int nfields, const unsigned char *dirty, int peer_tiles_plane);
+void launch_fetch_bytes(cudaStream_t s, unsigned char *dst, const unsigned char *src, long long bytes);
 void launch_halo_unpack(cudaStream_t s, long long plane, int nk, const int *dst, int n,
                         double *const *fields, int nfields, const double *buf);
 void launch_fill(cudaStream_t s, double *p, long long n, double v);
@@ -46,8 +53,6 @@ void launch_mass_update_list(cudaStream_t s, int dir, const Geom &g, Range rg, d
                              const double *hh, const double *areaT, const double *neglect, double h_neglect,
                              const int *entry, const int *domore_k, double *hlst, double *ihnew,
                              int *list, int *count, int cap, const int *tlist, const int *tcount, int nsm);
-void launch_fill_skipped(cudaStream_t s, const Geom &g, const int *tflags, double *hh, double *cfl, double *hc,
-                         double *gq, double *hlst, double *ihnew);
 void launch_fill_int(cudaStream_t s, int *p, int n, int v);
 void launch_publish(cudaStream_t s, int *host_mapped, const int *dev, int n);
 
@@ -70,8 +75,9 @@ void launch_y_fast_v1(cudaStream_t s, int scheme, const Geom &g, Range rg, const
 
 // sparse.cu: list-driven tracer update of the residual iterations
 void launch_sparse_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TrTable &tt,
-                         const int *list, int cnt, int cap, const double *hh, const double *cfl, const double *hlst,
-                         const double *ihnew, const double *mm, const int *entry, double *newT);
+                         const int *list, const int *cnt_dev, int nsm, const double *hh, const double *cfl,
+                         const double *hlst, const double *ihnew, const double *mm, const int *entry,
+                         unsigned char *dirty);
 
 // step.cu: transport accumulation and column diagnostics either side of advect_tracer
 void launch_accumulate(cudaStream_t s, const Geom &g, double *acc, const double *add, double dt, int ilo, int ihi,
@@ -98,6 +104,7 @@ struct PeerBuild {
   std::vector<int> recv_src[3];
   std::vector<signed char> recv_sgn[3];
   long long peer_plane = 0;                       // the sender's plane size (its level stride)
+  int peer_P = 0, peer_R = 0;                     // the sender's pitch and rows (dirty-tile map of its tracers)
 };
 void make_geom(const mom6adv_grid *gr, Geom &g, int &wbase);
 // Is halo point (i,j) of stagger pos within `depth` ROWS of the computational domain (v faces: of a row that is)?

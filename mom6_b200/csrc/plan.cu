@@ -44,7 +44,17 @@ struct PeerLists {        // one neighbour rank of the multi-GPU group pass
   int *recv_src[3] = {nullptr, nullptr, nullptr};
   signed char *recv_sgn[3] = {nullptr, nullptr, nullptr};
   long long peer_plane = 0;
-  std::vector<void *> mapped;        // cudaIpcOpenMemHandle results, slot order [uhr, vhr, hprev, buf0 x ntr, buf1 x ntr]
+  // the same receive lists as 16-byte moves (two consecutive points per entry) + the leftover single points; tile = the
+  // source's 32-column tile in the owner's plane (dirty-tile skip of the tracer pulls after a list-driven trip)
+  int n_pair[3] = {0, 0, 0}, n_single[3] = {0, 0, 0};
+  int *pair_dst[3] = {nullptr, nullptr, nullptr}, *pair_src[3] = {nullptr, nullptr, nullptr}, *pair_tile[3] = {nullptr, nullptr, nullptr};
+  signed char *pair_sgn[3] = {nullptr, nullptr, nullptr};
+  int *single_dst[3] = {nullptr, nullptr, nullptr}, *single_src[3] = {nullptr, nullptr, nullptr};
+  signed char *single_sgn[3] = {nullptr, nullptr, nullptr};
+  int peer_tiles_plane = 0;
+  unsigned char *dirty_local = nullptr;      // this pass's copy of the owner's dirty map
+  long long dirty_local_bytes = 0;
+  std::vector<void *> mapped;        // cudaIpcOpenMemHandle results, slot order [uhr, vhr, hprev, buf0 x ntr, buf1 x ntr, dirty map]
   double **fields_dev = nullptr;     // two tables like halo_fields_dev, of the neighbour's pointers
 };
 
@@ -107,7 +117,9 @@ struct mom6adv_plan {
   cudaEvent_t ev_pull_go = nullptr, ev_pull_done = nullptr;
   bool pull_pending = false;         // the tracer halo rows are still in flight on s_pull
   int opt_overlap = 1;
-  int opt_sp_cap = 0;                // list capacity of the residual trips (0: cells/64); tests force overflows with it
+  int opt_pull2 = 1;                 // 16-byte pair-list pull kernel (0: one point per thread)
+  int opt_dirty = 1;                 // tracer pulls skip tiles the owner has not changed since the last pass
+  int opt_sp_cap = 0;                // estimated list length above which a residual trip takes the dense kernels (0: cells/16)
   // open boundaries (mom6adv_set_obc)
   bool obc_active = false;
   int obc_flags[4] = {0, 0, 0, 0};          // open_u, open_v, specified_u, specified_v ..._BCs_exist_globally
@@ -121,7 +133,11 @@ struct mom6adv_plan {
   double *obc_ttmp = nullptr, *obc_slope = nullptr, *obc_fx = nullptr, *obc_hh2 = nullptr, *maskT = nullptr;
   int opt_trace = 0;                 // print the MIRROR pipeline's copy/compute times to stderr
   int opt_sparse = 1;                // list-driven tracer update on residual iterations (sparse.cu)
-  int *sp_list = nullptr; double *sp_new = nullptr; int sp_cap = 0, sp_ntr = 0;
+  int *sp_list = nullptr; int sp_cap = 0;      // cells the residual trip updates (capacity: every cell, it cannot overflow)
+  long long est_cells[2] = {-1, -1};      // host's estimate of the next trip's list length per direction (-1: unknown)
+  bool est_dense[2] = {true, true};       // the count behind it is a dense trip's residual-face count (x2) / a list length
+  unsigned char *dirty = nullptr;         // multi-GPU: per level and 32-column tile 'a tracer cell changed since the last pass' + one 'everything' byte
+  long long dirty_bytes = 0;
   long long sparse_sweeps = 0, dense_sweeps = 0;
   int wbase = 0;                     // first column of the first x tile (fast.cu)
   // per-kernel-class CUDA-event timing (option "profile")
@@ -307,8 +323,8 @@ static int create_impl(mom6adv_plan *plan, const mom6adv_grid *gr) {
   int **pf[] = {&plan->domore_u, &plan->domore_v, &plan->entry_u, &plan->entry_v};
   for (int **pp : pf) { int rc = dev_alloc(plan, pp, (long long)g.R * g.nk); if (rc) return rc; }
   { int rc = dev_alloc(plan, &plan->domore_k, g.nk); if (rc) return rc; }
-  { int rc = dev_alloc(plan, &plan->sum_dev, 4); if (rc) return rc; }
-  CK(cudaHostAlloc((void **)&plan->sum_host, sizeof(int) * 4, cudaHostAllocMapped));
+  { int rc = dev_alloc(plan, &plan->sum_dev, 8); if (rc) return rc; }
+  CK(cudaHostAlloc((void **)&plan->sum_host, sizeof(int) * 8, cudaHostAllocMapped));
   CK(cudaHostGetDevicePointer((void **)&plan->sum_host_dev, plan->sum_host, 0));
   // staging buffer: the largest Fortran-layout 3-D field (u or v stagger)
   plan->staging_elems = (long long)(g.ied - g.isd + 2) * (g.jed - g.jsd + 2) * g.nk;
@@ -415,6 +431,29 @@ extern "C" int mom6adv_comm_init(mom6adv_plan *plan, const char *id128, const in
       if ((rc = upload_vec(plan, b.recv_sgn[pos], &pl.recv_sgn[pos]))) return rc;
     }
     pl.peer_plane = b.peer_plane;
+    pl.peer_tiles_plane = (b.peer_P >> 5) * b.peer_R;
+    for (int pos = 0; pos < 3; pos++) {
+      std::vector<int> pd, ps, pt, sd, ss; std::vector<signed char> pg, sg;
+      const std::vector<int> &D = b.recv_dst[pos], &S = b.recv_src[pos];
+      const std::vector<signed char> &G = b.recv_sgn[pos];
+      for (size_t t = 0; t < D.size();) {
+        const bool pair = t + 1 < D.size() && D[t + 1] == D[t] + 1 && S[t + 1] == S[t] + 1 && G[t + 1] == G[t] &&
+                          (D[t] & 1) == 0 && (S[t] & 1) == 0 && b.peer_P > 0;
+        if (pair) {
+          const int rj = S[t] / b.peer_P, ci = S[t] - rj * b.peer_P;
+          pd.push_back(D[t]); ps.push_back(S[t]); pg.push_back(G[t]); pt.push_back(rj * (b.peer_P >> 5) + (ci >> 5));
+          t += 2;
+        } else { sd.push_back(D[t]); ss.push_back(S[t]); sg.push_back(G[t]); t += 1; }
+      }
+      pl.n_pair[pos] = (int)pd.size(); pl.n_single[pos] = (int)sd.size();
+      if ((rc = upload_vec(plan, pd, &pl.pair_dst[pos]))) return rc;
+      if ((rc = upload_vec(plan, ps, &pl.pair_src[pos]))) return rc;
+      if ((rc = upload_vec(plan, pg, &pl.pair_sgn[pos]))) return rc;
+      if ((rc = upload_vec(plan, pt, &pl.pair_tile[pos]))) return rc;
+      if ((rc = upload_vec(plan, sd, &pl.single_dst[pos]))) return rc;
+      if ((rc = upload_vec(plan, ss, &pl.single_src[pos]))) return rc;
+      if ((rc = upload_vec(plan, sg, &pl.single_sgn[pos]))) return rc;
+    }
     plan->peers.push_back(pl);
   }
   if (id128 && plan->nranks > 1) {
@@ -551,12 +590,17 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   if (plan->sum_host) cudaFreeHost(plan->sum_host);
   for (PeerLists &p : plan->peers) {
     for (int pos = 0; pos < 3; pos++) { if (p.send_src[pos]) cudaFree(p.send_src[pos]); if (p.send_sgn[pos]) cudaFree(p.send_sgn[pos]); if (p.recv_dst[pos]) cudaFree(p.recv_dst[pos]); if (p.recv_src[pos]) cudaFree(p.recv_src[pos]); if (p.recv_sgn[pos]) cudaFree(p.recv_sgn[pos]); }
+    for (int pos = 0; pos < 3; pos++) {
+      void *q[] = {p.pair_dst[pos], p.pair_src[pos], p.pair_tile[pos], p.pair_sgn[pos], p.single_dst[pos], p.single_src[pos], p.single_sgn[pos]};
+      for (void *x : q) if (x) cudaFree(x);
+    }
+    if (p.dirty_local) cudaFree(p.dirty_local);
     if (p.sendbuf) cudaFree(p.sendbuf);
     if (p.recvbuf) cudaFree(p.recvbuf);
   }
   if (plan->comm) ncclCommDestroy(plan->comm);
   if (plan->sp_list) cudaFree(plan->sp_list);
-  if (plan->sp_new) cudaFree(plan->sp_new);
+  if (plan->dirty) cudaFree(plan->dirty);
   for (auto &s : plan->tr) free_slot(s);
   if (plan->tr_dev) cudaFree(plan->tr_dev);
   if (plan->halo_fields_dev) cudaFree(plan->halo_fields_dev);
@@ -816,11 +860,16 @@ static int setup_ipc(mom6adv_plan *plan) {
   cudaStream_t s = plan->stream;
   if (!plan->bar_dev) { int rc = dev_alloc(plan, &plan->bar_dev, 4); if (rc) return rc; }
   teardown_ipc(plan, true);
-  const int ntr = plan->ntr, nslot = 3 + 2 * ntr, nr = plan->nranks;
+  const int ntr = plan->ntr, nslot = 3 + 2 * ntr + 1, nr = plan->nranks;
+  if (!plan->dirty) {      // tile map + the "everything" byte, padded so that readers fetch whole 16-byte words
+    plan->dirty_bytes = (((plan->g.plane >> 5) * plan->g.nk + 16 + 15) / 16) * 16 + 16;
+    int rc = dev_alloc(plan, &plan->dirty, plan->dirty_bytes); if (rc) return rc;
+  }
   std::vector<cudaIpcMemHandle_t> mine(nslot), all((size_t)nslot * nr);
-  std::vector<double *> slot(nslot);
+  std::vector<void *> slot(nslot);
   slot[0] = plan->uhr; slot[1] = plan->vhr; slot[2] = plan->hprev;
   for (int m = 0; m < ntr; m++) { slot[3 + m] = plan->tr[m].buf[0]; slot[3 + ntr + m] = plan->tr[m].buf[1]; }
+  slot[3 + 2 * ntr] = plan->dirty;
   int ok = 1;
   for (int q = 0; q < nslot; q++)
     if (!slot[q] || cudaIpcGetMemHandle(&mine[q], slot[q]) != cudaSuccess) { cudaGetLastError(); ok = 0; memset(&mine[q], 0, sizeof mine[q]); }
@@ -889,14 +938,36 @@ static int group_pass(mom6adv_plan *plan, bool first_of_call, bool defer_tracers
       // x sweep of the interior rows runs (1 x N layouts: those rows need no neighbour data); the sweep of the halo
       // rows waits for ev_pull_done (sweep()).  Tracer sources are the neighbours' live buffers, which nobody
       // writes before the convergence all-reduce of this trip, so only the mass fields need the closing fence.
+      const bool use_dirty = !first_of_call && !defer_tracers && plan->opt_dirty && plan->opt_pull2 && plan->dirty;
       auto pull = [&](cudaStream_t st, int q) {
         for (PeerLists &p : plan->peers) {
           double **ptab = p.fields_dev + plan->cur * (3 + plan->ntr);
           const Seg psegs[3][2] = {{{ptab + 2, 1}, {ptab + 3 + plan->m_lo, nact}}, {{ptab + 0, 1}, {nullptr, 0}}, {{ptab + 1, 1}, {nullptr, 0}}};
-          for (int pos = 0; pos < 3; pos++) if (segs[pos][q].n > 0) {
+          // the tracers' pull skips tiles the owner has not touched since the last pass (after a list-driven trip:
+          // nearly all of the strip); the first pass of a call and the mass fields (3 of 55) are pulled whole
+          const unsigned char *pd = nullptr;
+          if (q == 1 && use_dirty) {
+            if (!p.dirty_local) {
+              p.dirty_local_bytes = (((long long)p.peer_tiles_plane * g.nk + 16 + 15) / 16) * 16;
+              if (cudaMalloc((void **)&p.dirty_local, (size_t)p.dirty_local_bytes) != cudaSuccess) { cudaGetLastError(); p.dirty_local = nullptr; }
+            }
+            if (p.dirty_local) {
+              launch_fetch_bytes(st, p.dirty_local, (const unsigned char *)p.mapped[3 + 2 * plan->ntr], p.dirty_local_bytes);
+              pd = p.dirty_local;
+              plan->launches++;
+            }
+          }
+          for (int pos = 0; pos < 3; pos++) if (segs[pos][q].n > 0 && !plan->opt_pull2) {
             launch_halo_pull(st, g.plane, p.peer_plane, g.nk, p.recv_dst[pos], p.recv_src[pos], p.recv_sgn[pos], p.n_recv[pos],
                              segs[pos][q].t, psegs[pos][q].t, segs[pos][q].n);
             plan->launches++;
+          }
+          for (int pos = 0; pos < 3; pos++) if (segs[pos][q].n > 0 && plan->opt_pull2) {
+            launch_halo_pull2(st, g.plane, p.peer_plane, g.nk, p.pair_dst[pos], p.pair_src[pos], p.pair_sgn[pos], p.pair_tile[pos],
+                              p.n_pair[pos], segs[pos][q].t, psegs[pos][q].t, segs[pos][q].n, pd, p.peer_tiles_plane);
+            launch_halo_pull(st, g.plane, p.peer_plane, g.nk, p.single_dst[pos], p.single_src[pos], p.single_sgn[pos], p.n_single[pos],
+                             segs[pos][q].t, psegs[pos][q].t, segs[pos][q].n);
+            plan->launches += 2;
           }
         }
       };
@@ -922,7 +993,10 @@ static int group_pass(mom6adv_plan *plan, bool first_of_call, bool defer_tracers
       }
       CK(cudaGetLastError());
       // nobody overwrites its rows before every neighbour has read them
-      return exch_barrier(plan);
+      { int rc = exch_barrier(plan); if (rc) return rc; }
+      // every neighbour has read this rank's dirty map: start the next interval clean
+      if (plan->dirty) CK(cudaMemsetAsync(plan->dirty, 0, (size_t)plan->dirty_bytes, s));
+      return 0;
     }
     // (2) pack one message per neighbour: [h: hprev, tracers][u: uhr][v: vhr], each [field][level][point]
     { ProfScope pp(plan, MOM6ADV_KC_EXCH_PACK);
@@ -983,7 +1057,17 @@ static int size_peer_buffers(mom6adv_plan *plan) {
 
 // One directional sweep over cells [is..ie] x [js..je] (advect_x :329 / advect_y :705),
 // all levels with domore_k > 0, all tracers.
+static int sweep_impl(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, int itt);
 static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, int itt) {
+  const long long sp0 = plan->sparse_sweeps;
+  const int rc = sweep_impl(plan, dir, rg, Idt, scheme, itt);
+  // a dense sweep (any kernel family) may have changed every tracer cell: the neighbours' next pull takes everything
+  // (a list-driven sweep marked its tiles itself, k_sparse_scatter)
+  if (!rc && plan->dirty && plan->sparse_sweeps == sp0)
+    CK(cudaMemsetAsync(plan->dirty + (plan->g.plane >> 5) * plan->g.nk, 1, 1, plan->stream));
+  return rc;
+}
+static int sweep_impl(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, int itt) {
   const Geom &g = plan->g;
   cudaStream_t s = plan->stream;
   const double min_h = 0.1 * plan->Angstrom_H;        // :401 / :773
@@ -1004,18 +1088,21 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
     const bool x = (dir == 0);
     int *dom = x ? plan->domore_u : plan->domore_v, *ent = x ? plan->entry_u : plan->entry_v;
     double *res = x ? plan->uhr : plan->vhr;
-    // residual iterations: the cells that change are few -- collect them and update in place (sparse.cu)
-    bool sparse = plan->opt_sparse && itt >= 2;
-    if (sparse && (!plan->sp_list || plan->sp_ntr < plan->ntr)) {
-      if (plan->sp_list) { cudaFree(plan->sp_list); cudaFree(plan->sp_new); plan->sp_list = nullptr; plan->sp_new = nullptr; }
-      plan->sp_cap = plan->opt_sp_cap > 0 ? plan->opt_sp_cap : (int)std::max<long long>(4096, field_elems(plan) / 64);
-      plan->sp_ntr = plan->ntr;
+    // residual iterations: the cells that change are few -- collect them and update in place (sparse.cu).  The list
+    // length stays on the device (the kernels stride over it), the staging space is the tracers' idle ping-pong
+    // buffers, so the list cannot overflow and the host never waits inside a sweep.  Whether a trip is worth the
+    // list-driven kernels is a host-side HINT from the previous trip's counts (either choice gives the same bits).
+    const long long dense_above = plan->opt_sp_cap > 0 ? plan->opt_sp_cap : std::max<long long>(4096, field_elems(plan) / 16);
+    bool sparse = plan->opt_sparse && itt >= 2 && field_elems(plan) < (1LL << 31) &&
+                  (plan->est_cells[dir] < 0 || plan->est_cells[dir] <= dense_above);
+    plan->est_dense[dir] = !sparse;
+    if (sparse && !plan->sp_list) {
+      plan->sp_cap = (int)field_elems(plan);
       int rc = dev_alloc(plan, &plan->sp_list, plan->sp_cap); if (rc) return rc;
-      rc = dev_alloc(plan, &plan->sp_new, (long long)plan->sp_cap * plan->ntr); if (rc) return rc;
     }
     {
       ProfScope ps(plan, MOM6ADV_KC_MASS);
-      if (sparse) CK(cudaMemsetAsync(plan->sum_dev + 1, 0, sizeof(int), s));
+      CK(cudaMemsetAsync(plan->sum_dev + 1, 0, 2 * sizeof(int), s));      // [1] cells listed, [2] tiles listed
       launch_flags_begin(s, g, plan->domore_k, dom, ent, x ? rg.js : rg.js - 1, rg.je);
       if (sparse && !plan->tflags) {
         int rc = dev_alloc(plan, &plan->tflags, mass_tile_count(g)); if (rc) return rc;
@@ -1024,31 +1111,22 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
       }
       if (sparse) {
         // residual trips: a persistent scan of uhr / vhr computes the few active tiles, the update visits only those
-        CK(cudaMemsetAsync(plan->sum_dev + 2, 0, sizeof(int), s));
         launch_mass_flux_scan(s, dir, g, rg, res, plan->hprev, plan->areaT, min_h, ent, dom, plan->hh, plan->cfl,
                               plan->hc, plan->gq, scheme == SCHEME_PLM, plan->tflags, plan->tlist, plan->sum_dev + 2, plan->nsm);
         launch_mass_update_list(s, dir, g, rg, res, plan->hprev, plan->hh, plan->areaT, x ? plan->uh_neglect : plan->vh_neglect,
                                 h_neglect, ent, plan->domore_k, plan->hlst, plan->ihnew, plan->sp_list, plan->sum_dev + 1,
                                 plan->sp_cap, plan->tlist, plan->sum_dev + 2, plan->nsm);
+        // this trip's list length is the estimate for the next one (read with the convergence word, once per trip)
+        CK(cudaMemcpyAsync(plan->sum_dev + 4 + dir, plan->sum_dev + 1, sizeof(int), cudaMemcpyDeviceToDevice, s));
       } else {
         // dense trip of the streaming path: nothing reads CFL itself (k_x_fast / k_y_ring take hc, gq), so it is not written
+        CK(cudaMemsetAsync(plan->sum_dev + 4 + dir, 0, sizeof(int), s));
         launch_mass_flux(s, dir, g, rg, res, plan->hprev, plan->areaT, min_h, ent, dom, plan->hh, nullptr,
                          plan->hc, plan->gq, scheme == SCHEME_PLM);
         launch_mass_update(s, dir, g, rg, res, plan->hprev, plan->hh, plan->areaT, x ? plan->uh_neglect : plan->vh_neglect,
-                           h_neglect, ent, plan->domore_k, plan->hlst, plan->ihnew, nullptr, plan->sum_dev + 1, plan->sp_cap);
+                           h_neglect, ent, plan->domore_k, plan->hlst, plan->ihnew, nullptr, nullptr, 0, plan->sum_dev + 4 + dir);
       }
       plan->launches += 3;
-    }
-    int cnt = 0;
-    if (sparse) {
-      launch_publish(s, plan->sum_host_dev + 1, plan->sum_dev + 1, 1);
-      CK(cudaStreamSynchronize(s));
-      cnt = plan->sum_host[1];
-      if (cnt > plan->sp_cap) {                    // too many active cells: take the dense kernels,
-        sparse = false;                            // which need the fields of the skipped tiles as well
-        launch_fill_skipped(s, g, plan->tflags, plan->hh, plan->cfl, plan->hc, plan->gq, plan->hlst, plan->ihnew);
-        plan->launches++;
-      }
     }
     if (sparse) {
       ProfScope pt(plan, MOM6ADV_KC_SPARSE);
@@ -1057,11 +1135,11 @@ static int sweep(mom6adv_plan *plan, int dir, Range rg, double Idt, int scheme, 
         tt.n = std::min(MOM6ADV_MAXT, plan->m_hi - m0);
         for (int m = 0; m < tt.n; m++) {
           const TracerSlot &ts = plan->tr[m0 + m];
-          tt.src[m] = ts.buf[plan->cur]; tt.dst[m] = ts.buf[plan->cur]; tt.cu[m] = ts.conc_underflow;
+          tt.src[m] = ts.buf[plan->cur]; tt.dst[m] = ts.buf[1 - plan->cur]; tt.cu[m] = ts.conc_underflow;
         }
-        launch_sparse_sweep(s, scheme, dir, g, rg, tt, plan->sp_list, cnt, plan->sp_cap, plan->hh, plan->cfl, plan->hlst,
-                            plan->ihnew, x ? plan->mmx : plan->mmy, ent, plan->sp_new + (long long)plan->sp_cap * (m0 - plan->m_lo));
-        if (cnt > 0) plan->launches += 2;
+        launch_sparse_sweep(s, scheme, dir, g, rg, tt, plan->sp_list, plan->sum_dev + 1, plan->nsm, plan->hh, plan->cfl,
+                            plan->hlst, plan->ihnew, x ? plan->mmx : plan->mmy, ent, plan->dirty);
+        plan->launches += 2;
       }
       plan->sparse_sweeps++;
       CK(cudaGetLastError());
@@ -1185,6 +1263,7 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
       if (plan->tr[m].diag[d])
         CK(cudaMemsetAsync(plan->tr[m].diag[d], 0, sizeof(double) * ((d == 2 || d == 3) ? g.plane : field_elems(plan)), s));
 
+  plan->est_cells[0] = plan->est_cells[1] = -1;
   int isv = is, iev = ie, jsv = js, jev = je;                               // :201
   int itt;
   for (itt = 1; itt <= max_iter; itt++) {                                   // :203
@@ -1221,14 +1300,21 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
     }
     plan->launches += 1;
     if (itt >= max_iter) break;                                             // :297-299
-    if (isv > is - stencil) {                                               // :302
+    const bool test = (isv > is - stencil);                                 // :302
+    // ONE host readback per trip: the convergence word and, with it, the two counts that hint whether the next trip's
+    // sweeps are worth the list-driven kernels.  (PLM with halo 4 has no test after the first trip: read the counts alone.)
+    const bool want_est = plan->opt_fast && plan->opt_sparse && !plan->obc_active && (test || itt == 1);
+    if (test) {
       if (plan->multi && plan->comm)                                        // :305 sum_across_PEs(domore_k, nz)
         CKN(ncclAllReduce(plan->domore_k, plan->domore_k, g.nk, ncclInt, ncclSum, plan->comm, s));
       launch_sum_domore_k(s, plan->domore_k, g.nk, plan->sum_dev);          // :307 do_any
       plan->launches += 1;
-      launch_publish(s, plan->sum_host_dev, plan->sum_dev, 1);
+    }
+    if (test || want_est) {
+      launch_publish(s, plan->sum_host_dev, plan->sum_dev, 6);
       CK(cudaStreamSynchronize(s));
-      if (plan->sum_host[0] == 0) break;                                    // :308-310
+      for (int d = 0; d < 2; d++) plan->est_cells[d] = plan->est_dense[d] ? 2LL * plan->sum_host[4 + d] : plan->sum_host[4 + d];
+      if (test && plan->sum_host[0] == 0) break;                            // :308-310
     }
   }
   if (plan->pull_pending) { CK(cudaStreamWaitEvent(s, plan->ev_pull_done, 0)); plan->pull_pending = false; }
@@ -1605,6 +1691,8 @@ extern "C" int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value
   if (!plan || !key) return fail(plan, MOM6ADV_ERR_INVALID, "set_option: NULL argument");
   if (!strcmp(key, "fused")) { plan->opt_fused = value; return MOM6ADV_OK; }
   if (!strcmp(key, "fast")) { plan->opt_fast = value; return MOM6ADV_OK; }
+  if (!strcmp(key, "dirty")) { plan->opt_dirty = value; return MOM6ADV_OK; }
+  if (!strcmp(key, "pull2")) { plan->opt_pull2 = value; return MOM6ADV_OK; }
   if (!strcmp(key, "sparse")) { plan->opt_sparse = value; return MOM6ADV_OK; }
   if (!strcmp(key, "mirror_chunk")) { plan->opt_chunk = value; return MOM6ADV_OK; }
   if (!strcmp(key, "mirror_ahead")) { plan->opt_ahead = value; return MOM6ADV_OK; }

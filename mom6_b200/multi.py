@@ -104,6 +104,8 @@ def bench_multi(args, name, world, rank, local_rank, peak, peak_src):
     plan = capi.Plan(G, c.GV, CS)
     plan.set_option("pull", int(os.environ.get("MOM6ADV_PULL", "1")))     # 0: NCCL send/recv exchange (comparison runs)
     plan.set_option("overlap", int(os.environ.get("MOM6ADV_OVERLAP", "1")))
+    plan.set_option("dirty", int(os.environ.get("MOM6ADV_DIRTY", "1")))
+    plan.set_option("pull2", int(os.environ.get("MOM6ADV_PULL2", "1")))
     comm_init_plan(plan, G)
     plan.set_ntr(ntr)
     for m in range(ntr):
@@ -135,6 +137,14 @@ def bench_multi(args, name, world, rank, local_rank, peak, peak_src):
     ms_step = float(ms.item())
     kc = {capi.KC_NAMES[k]: plan.kernel_class_time(k) for k in range(len(capi.KC_NAMES))}
     launches = plan.kernel_launches - l0
+    # per-rank class times (strips carry different amounts of land: the slowest rank sets the pace)
+    kc_t = torch.tensor([plan.kernel_class_time(k)[0] / args.steps for k in range(len(capi.KC_NAMES))] + [e0.elapsed_time(e1) / args.steps],
+                        device="cuda", dtype=torch.float64)
+    kc_all = [torch.zeros_like(kc_t) for _ in range(world)]
+    dist.all_gather(kc_all, kc_t)
+    by_rank = {capi.KC_NAMES[k]: [round(float(t[k]), 3) for t in kc_all] for k in range(len(capi.KC_NAMES))
+               if any(float(t[k]) > 0 for t in kc_all)}
+    by_rank["total"] = [round(float(t[-1]), 3) for t in kc_all]
     N = ni * nj * nk
     Nl = G.ni * G.nj * nk
     units = N * ntr
@@ -159,6 +169,7 @@ def bench_multi(args, name, world, rank, local_rank, peak, peak_src):
                                      "frac": b_alg / (ms_step * 1e-3) / 1e9 / (peak * world),
                                      "note": "whole call, all GPUs: B_alg over ms_per_step over N x peak"},
                             "class_ms_per_step": {k: v[0] / args.steps for k, v in kc.items()},
+                            "class_ms_per_step_by_rank": by_rank,
                             "halo_ms_per_step": halo_ms},
                "gpu_launches": int(launches), "clocks": clocks,
                "e2e": None, "cpu_baseline": None}
