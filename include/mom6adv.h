@@ -193,6 +193,22 @@ int mom6adv_zero_transports(mom6adv_plan *plan);
 enum { MOM6ADV_CD_ADV_XY_2D = 0, MOM6ADV_CD_ZINT = 1, MOM6ADV_CD_ZINT_100M = 2 };
 int mom6adv_column_diag(mom6adv_plan *plan, int m, int kind, const double *h_diag, double H_to_m, double *out2d);
 
+/* ---- no-allocation variant of the 100 m column integral ------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arithmetic as
+ * mom6adv_column_diag(kind = ZINT_100M) (src/tracer/MOM_tracer_registry.F90:745-766,805-811) without a plan:
+ *   h_diag, t : DEVICE arrays (ni, nj, nk), Fortran order (i fastest), of the columns to integrate (the caller passes
+ *               the computational domain); out2d : DEVICE array (ni, nj); stream : a cudaStream_t (NULL = default).
+ * Calls no cudaMalloc / cudaFree / allocating routine: its scratch (per-CTA maxima and the layer bound khi) is a fixed
+ * file-scope device array of 256 KiB + 256 B that every GPU loading the library holds until exit, which limits
+ * ni*nj to MOM6ADV_NOALLOC_MAX_COLUMNS (beyond it: MOM6ADV_ERR_UNSUPPORTED and a message in errbuf).  Asynchronous on
+ * `stream`.  All calls share the scratch: calls that overlap on the GPU race -- serialise them.  The first call on a
+ * device resolves the scratch's device address (make it before starting a capture).  errbuf (nullable) receives the
+ * error text. */
+#define MOM6ADV_NOALLOC_MAX_COLUMNS 8388608LL
+int mom6adv_zint100_noalloc(const double *h_diag, const double *t, int ni, int nj, int nk, double H_to_m,
+                            double *out2d, void *stream, char *errbuf, int errbuf_len);
+
 /* ---- observability ------------------------------------------------------- */
 /* Device time [ms] of the last advect call, CUDA-event timed on the plan's
  * stream; the stand-in for the (Ocean advect tracer) clock (:1146). */

@@ -124,6 +124,7 @@ SYMBOLS = {
     "mom6adv_accumulate_transports": (C.c_int, [_P, _P, _P, C.c_double]),
     "mom6adv_zero_transports": (C.c_int, [_P]),
     "mom6adv_column_diag": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_double, _P]),
+    "mom6adv_zint100_noalloc": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_double, _P, _P, C.c_char_p, C.c_int]),
     "mom6adv_last_advect_ms": (C.c_double, [_P]),
     "mom6adv_kernel_launches": (C.c_longlong, [_P]),
     "mom6adv_device_bytes": (C.c_longlong, [_P]),
@@ -331,3 +332,16 @@ class Plan:
     def kernel_launches(self) -> int: return int(self._l.mom6adv_kernel_launches(self._h))
     @property
     def device_bytes(self) -> int: return int(self._l.mom6adv_device_bytes(self._h))
+
+
+NOALLOC_MAX_COLUMNS = 8388608
+
+
+def zint100_noalloc(h_diag, t, ni: int, nj: int, nk: int, H_to_m: float, out2d, stream: int = 0) -> None:
+    """mom6adv_zint100_noalloc: the 100 m column integral on the caller's DEVICE arrays (ni, nj, nk) -> (ni, nj), with
+    the library's fixed scratch and no allocation (no counterpart in the reference; see include/mom6adv.h)."""
+    buf = C.create_string_buffer(256)
+    rc = lib().mom6adv_zint100_noalloc(ptr(h_diag), ptr(t), int(ni), int(nj), int(nk), float(H_to_m), ptr(out2d),
+                                       stream or None, buf, 256)
+    if rc != 0:
+        raise Mom6AdvError(rc, buf.value.decode() or "mom6adv_zint100_noalloc failed")
