@@ -99,6 +99,56 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def apply_env_options(plan):
+    """MOM6ADV_OPTS="key=value,..." -> mom6adv_set_option (debugging / A-B runs; the default run sets nothing)."""
+    for kv in os.environ.get("MOM6ADV_OPTS", "").split(","):
+        if "=" in kv:
+            k, v = kv.split("=", 1)
+            plan.set_option(k.strip(), int(v))
+
+
+def shared_config(name, ni, nj, nk, ntr, scheme, cfl, layout="1x1"):
+    """The workload description both arms print: identical keys and values for the same workload."""
+    return {"workload": name, "ni": ni, "nj": nj, "nk": nk, "ntr": ntr, "scheme": scheme, "halo": 4, "cfl99": cfl,
+            "layout": layout, "l2": "inputs_exceed_l2", "fma_contraction": "off"}
+
+
+def bitcount_chksum_device(t):
+    """MOM's bitcount checksum of a device tensor (src/framework/MOM_checksums.F90:1396-1404,2407-2414):
+    sum of popcnt(transfer(abs(x), 1_8)), before the modulus.  Integer tensor ops only (torch has no popcount)."""
+    import torch
+    x = t.abs().contiguous().view(torch.int64)
+    x = x - ((x >> 1) & 0x5555555555555555)
+    x = (x & 0x3333333333333333) + ((x >> 2) & 0x3333333333333333)
+    x = (x + (x >> 4)) & 0x0F0F0F0F0F0F0F0F
+    x = (x * 0x0101010101010101) >> 56
+    return int((x & 0xFF).sum().item())
+
+
+BC_MODULUS = 1000000000      # MOM_checksums.F90:95
+
+
+def tracer_checksums(plan, G, nk, ntr):
+    """Per-tracer bitcount sums over the computational domain of the resident tracers (before the modulus, so that
+    the sums of the ranks of a multi-GPU run add up to the 1-GPU value)."""
+    import torch
+    buf = torch.empty(G.shape_h(nk), dtype=torch.float64, device="cuda")
+    out = []
+    for m in range(ntr):
+        plan.download_tracer(m, buf)
+        out.append(bitcount_chksum_device(buf[:, G.pj(G.jsc):G.pj(G.jec) + 1, G.pi(G.isc):G.pi(G.iec) + 1]))
+    del buf
+    return out
+
+
+def fold_checksums(sums):
+    """One number for the JSON line: MOM's per-field checksums (mod bc_modulus) folded position-dependently."""
+    acc = 0
+    for m, v in enumerate(sums):
+        acc = (acc * 31 + (v % BC_MODULUS) + m) % (1 << 61)
+    return acc
+
+
 def workload_shape(name: str):
     from mom6_b200 import synth
     if "," in name:          # ad-hoc "ni,nj,nk,ntr[,scheme]" (profiling runs)
@@ -116,7 +166,9 @@ def cpu_sample_setup(name: str, cfl: float, nk_sample: int):
     from mom6_b200 import synth
     from mom6_b200.tracer_advect import tracer_advect_init
     ni, nj, nk, ntr, scheme = workload_shape(name)
-    nks = min(nk, nk_sample if nk_sample > 0 else max(4, min(16, os.cpu_count() or 1)))
+    # one level per host thread (the oracle threads over k like the reference, :147,247), at least 16, at most nk:
+    # every core of the box is used and the sample stays a few seconds per call
+    nks = min(nk, nk_sample if nk_sample > 0 else max(16, os.cpu_count() or 1))
     c = synth.make_case(ni, nj, nks, ntr, cfl=cfl)
     CS = tracer_advect_init(None, c.G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}, None, None)
     Reg = synth.bind_registry(c)
@@ -143,16 +195,18 @@ def run_reference(args):
     name = args.workload
     ni, nj, nk, ntr, scheme = workload_shape(name)
     c, CS, Reg, huv, units, nks = cpu_sample_setup(name, args.cfl, args.cpu_levels)
-    threads = min(os.cpu_count() or 1, nks)     # the oracle threads over k like the reference (:147,247)
+    cores = os.cpu_count() or 1
+    threads = min(cores, nks)     # the oracle threads over k like the reference (:147,247)
     sec, nit = cpu_time_steps(c, CS, Reg, huv, args.steps, args.warmup, threads)
     val = units / sec
-    sample = "%dx%dx%d of %d levels, %d tracers, %s, cfl99=%.2f (%d iteration(s)), oracle OpenMP over k" % (
-        ni, nj, nks, nk, ntr, scheme, args.cfl, nit)
+    sample = "%dx%dx%d-level slab of the %d-level workload, %d tracers, %s, cfl99=%.2f (%d iteration(s) per call), " \
+             "oracle (C++ port, OpenMP over k) on %d of the box's %d host cores" % (
+                 ni, nj, nks, nk, ntr, scheme, args.cfl, nit, threads, cores)
     out = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
            "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-           "config": {"workload": name, "ni": ni, "nj": nj, "nk": nk, "ntr": ntr, "scheme": scheme,
-                      "cfl99": args.cfl, "sample": sample},
+           "config": shared_config(name, ni, nj, nk, ntr, scheme, args.cfl),
+           "iterations_per_call": nit, "host_cores": cores,
            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(out))
@@ -198,6 +252,7 @@ def run_native(args):
     plan.set_ntr(ntr)
     if args.fast is not None:
         plan.set_option("fast", args.fast)      # A/B runs: 1 = the round-1 streaming kernels
+    apply_env_options(plan)
     for m in range(ntr):
         t = c.tracer(m)
         plan.upload_tracer(m, t)
@@ -253,18 +308,37 @@ def run_native(args):
     if os.path.exists(tr_path):
         try:
             roofline["traffic"] = json.load(open(tr_path)).get(name, {}).get(dom)
+            roofline["traffic_source"] = "profiles/traffic.json (ncu dram__bytes capture of this kernel at this shape, not re-measured in this run)"
         except Exception:
             pass
 
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
            "dtype": "f64", "data": "synthetic",
-           "config": {"workload": name, "ni": ni, "nj": nj, "nk": nk, "ntr": ntr, "scheme": scheme,
-                      "halo": 4, "cfl99": args.cfl, "iterations_per_call": nit, "layout": "1x1",
-                      "l2": "inputs_exceed_l2 (%.1f GB resident)" % (plan.device_bytes / 1e9),
-                      "fma_contraction": "off"},
+           "config": shared_config(name, ni, nj, nk, ntr, scheme, args.cfl),
+           "iterations_per_call": nit, "resident_gb": plan.device_bytes / 1e9,
            "roofline": roofline, "gpu_launches": int(launches), "clocks": clocks,
-           "per_call_ms": {"min": min(per_call), "max": max(per_call)}}
+           "per_call_ms": {"min": min(per_call), "median": sorted(per_call)[len(per_call) // 2], "max": max(per_call)}}
+    # ocean-only rate (land included in `value`, the ocean-only count reported alongside)
+    mT = np.asarray(c.G.mask2dT)
+    n_ocean = float(c.G.interior(mT).sum())
+    out["ocean_cell_tracer_updates_per_s"] = n_ocean * nk * ntr / (ms_step * 1e-3)
+    out["ocean_fraction"] = n_ocean / (ni * nj)
+    # layout-invariance witness: MOM bitcount checksum of every tracer after the timed calls (N = 2/4/8 print the same)
+    try:
+        sums = tracer_checksums(plan, c.G, nk, ntr)
+        out["checksum"] = {"value": fold_checksums(sums), "calls": args.warmup + args.steps,
+                           "tracer0_mod_bc": sums[0] % BC_MODULUS, "tracer_last_mod_bc": sums[-1] % BC_MODULUS,
+                           "what": "MOM bitcount checksum (MOM_checksums.F90:1396-1404,2407-2414) of each tracer's "
+                                   "computational domain after warmup+steps calls, folded over tracers"}
+    except Exception as e:
+        out["checksum"] = {"error": str(e)[:200]}
+    # parity at the benchmarked shape: a slab of the workload's own state, one call, against the CPU oracle, bitwise
+    if not args.no_parity:
+        try:
+            out["parity_slab"] = run_parity_slab(plan, c, ntr, scheme)
+        except Exception as e:
+            out["parity_slab"] = {"error": str(e)[:300]}
 
     # ---- e2e, state resident (the integration BASELINE.json's north_star describes: the 50 passive tracers stay
     # in HBM; each step the host hands over h_end, uhtr, vhtr and the two active tracers T, S from pinned memory
@@ -286,13 +360,72 @@ def run_native(args):
     # ---- cpu baseline ----------------------------------------------------------
     if not args.no_cpu:
         cc, CSc, Regc, huv, u_s, nks = cpu_sample_setup(name, args.cfl, args.cpu_levels)
-        threads = min(os.cpu_count() or 1, nks)
-        sec, nit_c = cpu_time_steps(cc, CSc, Regc, huv, 1, 0, threads)
-        out["cpu_baseline"] = {"value": u_s / sec, "unit": UNIT, "cores": threads, "kind": "port",
-                               "sample": "%dx%dx%d of %d levels, %d tracers, %s, 1 call, %.1f s, oracle OpenMP over k"
-                                         % (ni, nj, nks, nk, ntr, scheme, sec)}
+        cores = os.cpu_count() or 1
+        threads = min(cores, nks)
+        sec, nit_c = cpu_time_steps(cc, CSc, Regc, huv, 2, 1, threads)
+        out["cpu_baseline"] = {"value": u_s / sec, "unit": UNIT, "cores": threads, "kind": "port", "host_cores": cores,
+                               "sample": "%dx%dx%d-level slab of the %d-level workload, %d tracers, %s, 1 warm-up + 2 timed "
+                                         "calls of %.1f s, oracle (C++ port, OpenMP over k) on %d of %d host cores"
+                                         % (ni, nj, nks, nk, ntr, scheme, sec, threads, cores)}
     print(json.dumps(out))
     return 0
+
+
+def _stats_ms(per):
+    p = sorted(per)
+    return {"min": p[0] * 1e3, "median": p[len(p) // 2] * 1e3, "max": p[-1] * 1e3}
+
+
+def run_parity_slab(plan, c, ntr, scheme, levels=4):
+    """Parity AT the benchmarked shape.  Levels are independent in advect_tracer (every loop is per k; a level that
+    converged is skipped, :248-267), so a slab of the workload's own inputs has, level by level, the answer of the full
+    run: the tracers are reset to their synthetic initial state, ONE call runs on the GPU at full size, and `levels`
+    levels spread over the column are compared bit for bit with the CPU oracle run on exactly those levels (the
+    oracle is the checker here, never the thing measured)."""
+    import numpy as np
+    import torch
+    from mom6_b200 import capi, synth
+    from mom6_b200.tracer_advect import tracer_advect_init
+    from mom6_b200.types import TracerRegistry, register_tracer, VerticalGrid
+    from oracle import oracle
+    G, nk = c.G, c.GV.ke
+    ks = sorted(set(int(round(x)) for x in np.linspace(0, nk - 1, min(levels, nk))))
+    kt = torch.as_tensor(ks, device="cuda")
+    t0 = time.perf_counter()
+    Reg = TracerRegistry()
+    for m in range(ntr):
+        t = c.tracer(m)
+        plan.upload_tracer(m, t)
+        register_tracer(np.ascontiguousarray(t.index_select(0, kt).cpu().numpy()), Reg, name="tr%02d" % m,
+                        underflow_conc=c.conc_underflow(m))
+        del t
+    nit_g = plan.advect_resident(c.dt)
+    GVs = VerticalGrid(ke=len(ks), Angstrom_H=c.GV.Angstrom_H, H_subroundoff=c.GV.H_subroundoff)
+    CS = tracer_advect_init(None, G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}, None, None)
+    h, u, v = (np.ascontiguousarray(a.index_select(0, kt).cpu().numpy()) for a in (c.h_end, c.uhtr, c.vhtr))
+    nit_o = oracle.advect_tracer(h, u, v, None, c.dt, G, GVs, None, CS, Reg, nthreads=len(ks))
+    buf = torch.empty(G.shape_h(nk), dtype=torch.float64, device="cuda")
+    bad, worst, detail = 0, 0.0, None
+    for m in range(ntr):
+        plan.download_tracer(m, buf)
+        got = np.ascontiguousarray(G.interior(buf.index_select(0, kt).cpu().numpy()))
+        want = np.ascontiguousarray(G.interior(Reg.Tr[m].t))
+        ne = got.view(np.uint64) != want.view(np.uint64)
+        if ne.any():
+            bad += 1
+            worst = max(worst, float(np.abs(got - want).max()))
+            if detail is None:
+                w = np.argwhere(ne)
+                mT = G.interior(np.asarray(G.mask2dT))
+                detail = {"tracer": m, "cells": int(ne.sum()), "per_level": [int(ne[q].sum()) for q in range(len(ks))],
+                          "on_land": int((ne & (mT[None] < 0.5)).sum()),
+                          "first": [[int(x) for x in w[q]] + [float(got[tuple(w[q])]), float(want[tuple(w[q])])] for q in range(min(4, len(w)))],
+                          "j_range": [int(w[:, 1].min()), int(w[:, 1].max())], "i_range": [int(w[:, 2].min()), int(w[:, 2].max())]}
+    return {"result": "bitwise" if bad == 0 else "MISMATCH in %d of %d tracers (max abs %g)" % (bad, ntr, worst),
+            "levels": ks, "tracers": ntr, "cells_compared": int(G.ni * G.nj * len(ks) * ntr),
+            "iterations_gpu_full_column": int(nit_g), "iterations_oracle_slab": int(nit_o), "first_mismatch": detail,
+            "oracle": "oracle/advect_ref.cpp (pinned against the translated reference, tests/test_f2c_reference.py)",
+            "seconds": time.perf_counter() - t0}
 
 
 def run_e2e_resident(args, plan, c, units):
@@ -323,13 +456,15 @@ def run_e2e_resident(args, plan, c, units):
     for _ in range(args.e2e_warmup):
         step()
     torch.cuda.synchronize()
-    t0 = time.perf_counter()
+    per = []
     for _ in range(args.e2e_steps):
+        t0 = time.perf_counter()
         step()
-    torch.cuda.synchronize()
-    sec = (time.perf_counter() - t0) / args.e2e_steps
+        torch.cuda.synchronize()
+        per.append(time.perf_counter() - t0)
+    sec = sum(per) / len(per)
     return {"value": units / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-            "ms_per_step": sec * 1e3, "steps": args.e2e_steps,
+            "ms_per_step": sec * 1e3, "steps": args.e2e_steps, "warmup": args.e2e_warmup, "ms_per_step_stats": _stats_ms(per),
             "call": "mom6adv_upload_field(h_end,uhtr,vhtr) + mom6adv_upload_tracer(T,S) -> mom6adv_advect_resident -> "
                     "mom6adv_download_tracer(T,S); 50 passive tracers resident in HBM",
             "result_probe": float(ht[0][0, c.G.jsc, c.G.isc])}
@@ -374,15 +509,18 @@ def run_e2e(args, name):
     for _ in range(args.e2e_warmup):
         advect_tracer(h, u, v, None, dt, G, GV, None, CS, Reg)
     torch.cuda.synchronize()
-    t0 = time.perf_counter()
+    per = []
     for _ in range(args.e2e_steps):
+        t0 = time.perf_counter()
         advect_tracer(h, u, v, None, dt, G, GV, None, CS, Reg)   # returns after the D2H copies completed
-    torch.cuda.synchronize()
-    sec = (time.perf_counter() - t0) / args.e2e_steps
+        torch.cuda.synchronize()
+        per.append(time.perf_counter() - t0)
+    sec = sum(per) / len(per)
     chk = float(keep[0].numpy()[0, G.jsc, G.isc])
     tracer_advect_end(CS)
     return {"value": ni * nj * nk * ntr / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-            "d2h_bytes_per_step": int(d2h), "ms_per_step": sec * 1e3, "steps": args.e2e_steps,
+            "d2h_bytes_per_step": int(d2h), "ms_per_step": sec * 1e3, "steps": args.e2e_steps, "warmup": args.e2e_warmup,
+            "ms_per_step_stats": _stats_ms(per),
             "call": "mom6_b200.tracer_advect.advect_tracer -> mom6adv_advect (MIRROR mode, pinned host arrays)",
             "result_probe": chk}
 
@@ -396,8 +534,10 @@ def main():
     ap.add_argument("--workload", default="OM4_025")
     ap.add_argument("--cfl", type=float, default=0.45, help="99th percentile upwind CFL of the synthetic transports")
     ap.add_argument("--cpu-levels", type=int, default=0, help="levels in the bounded CPU sample")
-    ap.add_argument("--e2e-steps", type=int, default=2)
-    ap.add_argument("--e2e-warmup", type=int, default=1)
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--e2e-warmup", type=int, default=2)
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of a slab of the workload")
+    ap.add_argument("--layout", default=None, help="multi-GPU LAYOUT as IxJ (default: strips in j)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--e2e-only", action="store_true", help="print only the e2e leg (pipeline tuning)")

@@ -217,6 +217,9 @@ double mom6adv_last_advect_ms(const mom6adv_plan *plan);
 long long mom6adv_kernel_launches(const mom6adv_plan *plan);
 /* Bytes of HBM held by the plan. */
 long long mom6adv_device_bytes(const mom6adv_plan *plan);
+/* Bytes the group passes (MOM_tracer_advect.F90:206) of this rank have listed for exchange with its neighbours since
+ * plan creation (peer loads or NCCL messages; the dirty-tile skip may move fewer). */
+long long mom6adv_halo_bytes(const mom6adv_plan *plan);
 /* Options: "profile" 0/1 -- time every kernel class of advect calls with CUDA
  * events on the plan's stream (resets the accumulators); "fast" 0/1/2 -- 0 forces
  * the generic thread-per-cell sweeps, 2 (default) uses the streaming kernels

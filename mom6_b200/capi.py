@@ -128,6 +128,7 @@ SYMBOLS = {
     "mom6adv_last_advect_ms": (C.c_double, [_P]),
     "mom6adv_kernel_launches": (C.c_longlong, [_P]),
     "mom6adv_device_bytes": (C.c_longlong, [_P]),
+    "mom6adv_halo_bytes": (C.c_longlong, [_P]),
     "mom6adv_set_option": (C.c_int, [_P, C.c_char_p, C.c_int]),
     "mom6adv_kernel_class_time": (C.c_int, [_P, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]),
     "mom6adv_stream": (C.c_void_p, [_P]),
@@ -154,6 +155,17 @@ class Mom6AdvError(RuntimeError):
     def __init__(self, status: int, msg: str):
         super().__init__("mom6adv status %d: %s" % (status, msg))
         self.status = status
+
+
+def _order_after_torch(*arrays) -> None:
+    """The plan works on its own non-blocking stream.  A torch CUDA tensor handed to it may still be being written by
+    kernels queued on torch's stream (and, once the caller drops it, its memory may be handed to the next tensor):
+    wait for torch's stream before the library reads or writes such a tensor."""
+    for a in arrays:
+        if a is not None and getattr(a, "is_cuda", False):
+            import torch
+            torch.cuda.current_stream(a.device).synchronize()
+            return
 
 
 def ptr(a) -> Optional[int]:
@@ -284,17 +296,24 @@ class Plan:
     def advect(self, h_end, uhtr, vhtr, dt, x_first=-1, vol_prev=None, max_iter_in=-1, update_vol_prev=-1,
                uhr_out=None, vhr_out=None) -> int:
         n = C.c_int(0)
+        _order_after_torch(h_end, uhtr, vhtr, vol_prev, uhr_out, vhr_out)
         self._ck(self._l.mom6adv_advect(self._h, ptr(h_end), ptr(uhtr), ptr(vhtr), float(dt), int(x_first),
                                         ptr(vol_prev), int(max_iter_in), int(update_vol_prev), ptr(uhr_out),
                                         ptr(vhr_out), C.byref(n)))
         return n.value
 
     # -- RESIDENT --------------------------------------------------------------
-    def upload_tracer(self, m, src): self._ck(self._l.mom6adv_upload_tracer(self._h, m, ptr(src)))
-    def download_tracer(self, m, dst): self._ck(self._l.mom6adv_download_tracer(self._h, m, ptr(dst)))
-    def upload_field(self, f, src): self._ck(self._l.mom6adv_upload_field(self._h, f, ptr(src)))
-    def download_field(self, f, dst): self._ck(self._l.mom6adv_download_field(self._h, f, ptr(dst)))
-    def download_diag(self, m, kind, dst): self._ck(self._l.mom6adv_download_diag(self._h, m, kind, ptr(dst)))
+    # (each of these returns after the plan's stream has finished with the array)
+    def upload_tracer(self, m, src):
+        _order_after_torch(src); self._ck(self._l.mom6adv_upload_tracer(self._h, m, ptr(src)))
+    def download_tracer(self, m, dst):
+        _order_after_torch(dst); self._ck(self._l.mom6adv_download_tracer(self._h, m, ptr(dst)))
+    def upload_field(self, f, src):
+        _order_after_torch(src); self._ck(self._l.mom6adv_upload_field(self._h, f, ptr(src)))
+    def download_field(self, f, dst):
+        _order_after_torch(dst); self._ck(self._l.mom6adv_download_field(self._h, f, ptr(dst)))
+    def download_diag(self, m, kind, dst):
+        _order_after_torch(dst); self._ck(self._l.mom6adv_download_diag(self._h, m, kind, ptr(dst)))
 
     def advect_resident(self, dt, x_first=-1, max_iter_in=-1, use_vol_prev=0, update_vol_prev=0) -> int:
         n = C.c_int(0)
@@ -307,6 +326,7 @@ class Plan:
     # -- either side of advect_tracer --------------------------
     def accumulate_transports(self, uh, vh, dt):
         """uhtr += uh*dt ; vhtr += vh*dt on the resident fields (MOM_dynamics_split_RK2.F90:1045-1052)."""
+        _order_after_torch(uh, vh)
         self._ck(self._l.mom6adv_accumulate_transports(self._h, ptr(uh), ptr(vh), float(dt)))
 
     def zero_transports(self):
@@ -315,6 +335,7 @@ class Plan:
 
     def column_diag(self, m, kind, h_diag, H_to_m, out2d):
         """Vertical sums of post_tracer_transport_diagnostics (MOM_tracer_registry.F90:725-815) for resident tracer m."""
+        _order_after_torch(h_diag, out2d)
         self._ck(self._l.mom6adv_column_diag(self._h, int(m), int(kind), ptr(h_diag), float(H_to_m), ptr(out2d)))
     def set_option(self, key: str, value: int): self._ck(self._l.mom6adv_set_option(self._h, key.encode(), value))
 
@@ -332,6 +353,8 @@ class Plan:
     def kernel_launches(self) -> int: return int(self._l.mom6adv_kernel_launches(self._h))
     @property
     def device_bytes(self) -> int: return int(self._l.mom6adv_device_bytes(self._h))
+    @property
+    def halo_bytes(self) -> int: return int(self._l.mom6adv_halo_bytes(self._h))
 
 
 NOALLOC_MAX_COLUMNS = 8388608
@@ -340,6 +363,10 @@ NOALLOC_MAX_COLUMNS = 8388608
 def zint100_noalloc(h_diag, t, ni: int, nj: int, nk: int, H_to_m: float, out2d, stream: int = 0) -> None:
     """mom6adv_zint100_noalloc: the 100 m column integral on the caller's DEVICE arrays (ni, nj, nk) -> (ni, nj), with
     the library's fixed scratch and no allocation (no counterpart in the reference; see include/mom6adv.h)."""
+    if not stream:
+        pass      # default stream: ordered with torch's default stream by CUDA itself
+    else:
+        _order_after_torch(h_diag, t, out2d)
     buf = C.create_string_buffer(256)
     rc = lib().mom6adv_zint100_noalloc(ptr(h_diag), ptr(t), int(ni), int(nj), int(nk), float(H_to_m), ptr(out2d),
                                        stream or None, buf, 256)

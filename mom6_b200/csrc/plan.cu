@@ -1677,6 +1677,7 @@ extern "C" int mom6adv_sync(mom6adv_plan *plan) {
 extern "C" double mom6adv_last_advect_ms(const mom6adv_plan *plan) { return plan ? plan->last_ms : 0.0; }
 extern "C" long long mom6adv_kernel_launches(const mom6adv_plan *plan) { return plan ? plan->launches : 0; }
 extern "C" long long mom6adv_device_bytes(const mom6adv_plan *plan) { return plan ? plan->dev_bytes : 0; }
+extern "C" long long mom6adv_halo_bytes(const mom6adv_plan *plan) { return plan ? plan->halo_bytes_sent : 0; }
 
 extern "C" void *mom6adv_stream(const mom6adv_plan *plan) { return plan ? (void *)plan->stream : nullptr; }
 

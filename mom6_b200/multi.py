@@ -87,6 +87,13 @@ def cut_local(c_global, layout, pe):
     return G, cut(decomp.cut_h, c_global.h_end), cut(decomp.cut_u, c_global.uhtr), cut(decomp.cut_v, c_global.vhtr), cut
 
 
+def plan_halo_bytes(plan) -> int:
+    try:
+        return int(plan.halo_bytes)
+    except Exception:
+        return 0
+
+
 def bench_multi(args, name, world, rank, local_rank, peak, peak_src):
     """bench.py body for N > 1: the named global grid split over N GPUs (strong scaling)."""
     import json
@@ -97,6 +104,10 @@ def bench_multi(args, name, world, rank, local_rank, peak, peak_src):
     import bench as B
     ni, nj, nk, ntr, scheme = B.workload_shape(name)
     layout = choose_layout(world, ni, nj)
+    if getattr(args, "layout", None):      # --layout IxJ: a 2-D decomposition (MOM6's LAYOUT, src/framework/MOM_domains.F90:66)
+        layout = tuple(int(x) for x in args.layout.lower().split("x"))
+        if layout[0] * layout[1] != world:
+            raise SystemExit("--layout %s does not match %d ranks" % (args.layout, world))
     pe = rank_to_pe(rank, layout)
     c = synth.make_case(ni, nj, nk, ntr, cfl=args.cfl, device="cuda")
     G, h, u, v, cut = cut_local(c, layout, pe)
@@ -106,6 +117,7 @@ def bench_multi(args, name, world, rank, local_rank, peak, peak_src):
     plan.set_option("overlap", int(os.environ.get("MOM6ADV_OVERLAP", "1")))
     plan.set_option("dirty", int(os.environ.get("MOM6ADV_DIRTY", "1")))
     plan.set_option("pull2", int(os.environ.get("MOM6ADV_PULL2", "1")))
+    B.apply_env_options(plan)
     comm_init_plan(plan, G)
     plan.set_ntr(ntr)
     for m in range(ntr):
@@ -154,14 +166,28 @@ def bench_multi(args, name, world, rank, local_rank, peak, peak_src):
     ach = alg_launch / (dom_avg * 1e-3) / 1e9
     b_alg = (16.0 * ntr + 24.0) * N
     halo_ms = kc["halo"][0] / args.steps
+    # layout-invariance witness: the per-tracer bitcount sums of all ranks add up to the 1-GPU sums
+    try:
+        sums = torch.tensor(B.tracer_checksums(plan, G, nk, ntr), device="cuda", dtype=torch.int64)
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM)
+        sums = [int(x) for x in sums.tolist()]
+        checksum = {"value": B.fold_checksums(sums), "calls": args.warmup + args.steps,
+                    "tracer0_mod_bc": sums[0] % B.BC_MODULUS, "tracer_last_mod_bc": sums[-1] % B.BC_MODULUS,
+                    "what": "MOM bitcount checksum of each tracer's computational domain summed over ranks "
+                            "(sum_across_PEs, MOM_checksums.F90:1396-1404), folded over tracers: equals the 1-GPU value"}
+    except Exception as e:
+        checksum = {"error": str(e)[:200]}
+    halo_bytes = torch.tensor([float(plan_halo_bytes(plan)) / max(args.steps + args.warmup, 1)], device="cuda", dtype=torch.float64)
+    dist.all_reduce(halo_bytes, op=dist.ReduceOp.MAX)
     if rank == 0:
         out = {"metric": B.METRIC, "value": units / (ms_step * 1e-3), "unit": B.UNIT, "n_gpus": world,
                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-               "config": {"workload": name, "ni": ni, "nj": nj, "nk": nk, "ntr": ntr, "scheme": scheme, "halo": 4,
-                          "cfl99": args.cfl, "iterations_per_call": nit, "layout": "%dx%d" % tuple(layout),
-                          "l2": "inputs_exceed_l2 (%.1f GB resident per GPU)" % (plan.device_bytes / 1e9),
-                          "fma_contraction": "off", "halo_exchange": ("peer-memory loads over NVLink (CUDA IPC), all-reduce fences" if int(os.environ.get("MOM6ADV_PULL", "1")) else "GPU pack -> NCCL send/recv (NVLink) -> GPU unpack")},
+               "config": B.shared_config(name, ni, nj, nk, ntr, scheme, args.cfl, layout="%dx%d" % tuple(layout)),
+               "iterations_per_call": nit, "resident_gb_per_gpu": plan.device_bytes / 1e9, "checksum": checksum,
+               "halo_exchange": {"how": ("peer-memory loads over NVLink (CUDA IPC), all-reduce fences" if int(os.environ.get("MOM6ADV_PULL", "1")) else "GPU pack -> NCCL send/recv (NVLink) -> GPU unpack"),
+                                 "bytes_pulled_per_call_max_rank": float(halo_bytes.item()),
+                                 "nvlink_frac_of_900GBs_if_fully_exposed": (float(halo_bytes.item()) / 900e9) / max(halo_ms * 1e-3, 1e-9)},
                "roofline": {"bound": "hbm", "kernel": "k_%s (rank 0 block)" % dom, "achieved": ach, "peak": peak,
                             "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": peak_src,
                             "avg_launch_ms": dom_avg, "alg_bytes_per_launch": alg_launch,

@@ -83,11 +83,12 @@ def _smooth(x, y, rng, nmodes, kmax, periodic_x=True):
 def make_case(ni: int, nj: int, nk: int, ntr: int, halo: int = 4, seed: int = SEED0,
               device: str = "cpu", cyclic_x: bool = True, cyclic_y: bool = False,
               symmetric: bool = True, land: bool = True, cfl: float = 0.3,
-              first_direction: int = 0, dt: float = 3600.0, dt_baroclinic: float = 900.0) -> SynthCase:
+              first_direction: int = 0, dt: float = 3600.0, dt_baroclinic: float = 900.0,
+              tripolar_n: bool = False) -> SynthCase:
     """Build grid + h_end/uhtr/vhtr.  ``cfl`` is the approximate 99th-percentile
     upwind CFL of the transports (values near/above 0.5 engage the flux
     limiter and force residual iterations)."""
-    dom = MOMDomain(ni, nj, cyclic_x=cyclic_x, cyclic_y=cyclic_y, symmetric=symmetric)
+    dom = MOMDomain(ni, nj, cyclic_x=cyclic_x, cyclic_y=cyclic_y, symmetric=symmetric, tripolar_n=tripolar_n)
     G = OceanGrid(ni, nj, halo=halo, symmetric=symmetric, first_direction=first_direction, domain=dom)
     GV = VerticalGrid.default(nk)
     rng = _rng(seed)
@@ -235,7 +236,7 @@ def _wrap_cols(G, dom, a, lo_index, n_global, fill):
     return a
 
 
-def _wrap_rows(G, dom, a, lo_index, n_global, fill):
+def _wrap_rows(G, dom, a, lo_index, n_global, fill, fold=False):
     n = a.shape[-2]
     gidx = torch.arange(n, device=a.device) + lo_index
     outside = (gidx < 1) | (gidx > n_global)
@@ -246,12 +247,24 @@ def _wrap_rows(G, dom, a, lo_index, n_global, fill):
         return a.index_select(-2, src)
     a = a.clone()
     a[..., outside, :] = fill
+    if fold and dom.tripolar_n:
+        # tripolar north fold of an h-point field (src/framework/MOM_domains.F90:184-191; FMS FOLD_NORTH_EDGE): halo row
+        # njg + d holds row njg + 1 - d with the columns reversed, ig -> nig + 1 - ig (columns are already x-wrapped)
+        ncol = a.shape[-1]
+        ig = torch.arange(ncol, device=a.device) + (G.isd + G.ioff)
+        csrc = (dom.nig + 1 - ig) - (G.isd + G.ioff)
+        ok = (csrc >= 0) & (csrc < ncol)
+        for r in torch.nonzero(gidx > n_global).flatten().tolist():
+            rs = (2 * n_global + 1 - int(gidx[r])) - lo_index
+            if 0 <= rs < n:
+                row = a[..., rs, :].index_select(-1, csrc.clamp(0, ncol - 1))
+                a[..., r, :] = torch.where(ok, row, torch.full_like(row, fill))
     return a
 
 
 def _wrap_h(G, dom, a, in_x=None, in_y=None, fill=0.0):
     a = _wrap_cols(G, dom, a, G.isd + G.ioff, dom.nig, fill)
-    return _wrap_rows(G, dom, a, G.jsd + G.joff, dom.njg, fill)
+    return _wrap_rows(G, dom, a, G.jsd + G.joff, dom.njg, fill, fold=True)
 
 
 def _finish_u(G, dom, uh):
@@ -417,3 +430,24 @@ def make_obc_case(ni: int = 40, nj: int = 34, nk: int = 3, ntr: int = 5, cfl: fl
     OBC = OceanOBC(OBC_pe=True, segment=segs, open_u_BCs_exist_globally=True, open_v_BCs_exist_globally=True,
                    specified_u_BCs_exist_globally=True, specified_v_BCs_exist_globally=True)
     return c, OBC
+
+
+def transposed_case(c: "SynthCase", Reg):
+    """The same problem with i and j exchanged (the reference's index-rotation standard, .testing/Makefile:384,455,596, in
+    its simplest form): grid metrics and masks transposed, uhtr <-> vhtr, REENTRANT_X <-> REENTRANT_Y, every tracer
+    transposed.  Advecting it with the sweep order flipped must give the transposed answer.  Symmetric memory only.
+    Returns (G2, h2, u2, v2, Reg2) with numpy arrays."""
+    from .types import TracerRegistry, register_tracer
+    G, D = c.G, c.G.Domain
+    assert G.symmetric, "transposition needs symmetric memory (u and v arrays of matching shapes)"
+    D2 = MOMDomain(D.njg, D.nig, cyclic_x=D.cyclic_y, cyclic_y=D.cyclic_x, symmetric=True)
+    G2 = OceanGrid(G.nj, G.ni, halo=G.jsc - G.jsd, jhalo=G.isc - G.isd, symmetric=True,
+                   first_direction=G.first_direction + 1, domain=D2)
+    tr2 = lambda a: np.ascontiguousarray(np.swapaxes(np.asarray(a), -1, -2))
+    G2.areaT, G2.IareaT, G2.mask2dT = tr2(G.areaT), tr2(G.IareaT), tr2(G.mask2dT)
+    G2.mask2dCu, G2.mask2dCv = tr2(G.mask2dCv), tr2(G.mask2dCu)
+    h2, u2, v2 = tr2(c.h_end.cpu().numpy()), tr2(c.vhtr.cpu().numpy()), tr2(c.uhtr.cpu().numpy())
+    Reg2 = TracerRegistry()
+    for tr in Reg.Tr[:Reg.ntr]:
+        register_tracer(tr2(tr.t), Reg2, name=getattr(tr, "name", "tr"), underflow_conc=tr.conc_underflow)
+    return G2, h2, u2, v2, Reg2

@@ -336,3 +336,38 @@ def test_cuda_equals_translated_reference(scheme):
         advect_tracer(h, u, v, None, c.dt, c.G, c.GV, None, CSg, Rg, uhr_out=uo_g, vhr_out=vo_g)
     tracer_advect_end(CSg)
     _assert_bitwise(c, Rr, Rg, (uo_r, vo_r, uo_g, vo_g), diags=True)
+
+
+# ---- topologies and shapes the first round never ran end to end on the device ------------------------------------------
+@pytest.mark.parametrize("kw", [dict(tripolar_n=True), dict(cyclic_y=True), dict(cyclic_x=False, cyclic_y=True)])
+@pytest.mark.parametrize("scheme", ["PPM", "PLM"])
+def test_tripolar_and_cyclic_y_bitwise(kw, scheme):
+    """1-PE group pass through the tripolar north fold and through REENTRANT_Y, with transport crossing the seam."""
+    c, Ro, Rg, outs, nit = _run_pair(48, 36, 3, 5, scheme, cfl=0.9, ncalls=2, **kw)
+    _assert_bitwise(c, Ro, Rg, outs)
+
+
+@pytest.mark.parametrize("scheme", ["PPM", "PLM"])
+def test_transposed_case_bitwise(scheme):
+    """The i <-> j transposed problem (y sweep first) on the device equals the transposed 1-PE answer of the original."""
+    c = synth.make_case(70, 45, 3, 5, cfl=0.9)
+    params = {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}
+    CSo = tracer_advect_init(None, c.G, None, params, None, None)
+    Ro = synth.bind_registry(c)
+    G2, h2, u2, v2, R2 = synth.transposed_case(c, synth.bind_registry(c))
+    oracle.advect_tracer(c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy(), None, c.dt, c.G, c.GV, None, CSo, Ro, x_first_in=True)
+    CSg = tracer_advect_init(None, G2, None, params, None, None)
+    advect_tracer(h2, u2, v2, None, c.dt, G2, c.GV, None, CSg, R2, x_first_in=False)
+    tracer_advect_end(CSg)
+    for m in range(Ro.ntr):
+        a = np.ascontiguousarray(np.swapaxes(c.G.interior(Ro.Tr[m].t), -1, -2))
+        b = np.ascontiguousarray(G2.interior(R2.Tr[m].t))
+        assert np.array_equal(a.view(np.uint64), b.view(np.uint64)), "tracer %d" % m
+
+
+def test_om4_1_full_shape_bitwise():
+    """BASELINE.json configs[2] at its full shape: 360 x 210 x 75, T/S + 20 passive tracers, PPM."""
+    ni, nj, nk, ntr, scheme = synth.CONFIGS["OM4_1"]
+    c, Ro, Rg, outs, nit = _run_pair(ni, nj, nk, ntr, scheme, cfl=0.45)
+    assert nit >= 2
+    _assert_bitwise(c, Ro, Rg, outs)
