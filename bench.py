@@ -253,10 +253,14 @@ def run_native(args):
     if args.fast is not None:
         plan.set_option("fast", args.fast)      # A/B runs: 1 = the round-1 streaming kernels
     apply_env_options(plan)
+    diag_flag = np.zeros(8)      # RESIDENT mode: a non-NULL pointer only says "associated" (the values stay in HBM)
     for m in range(ntr):
         t = c.tracer(m)
         plan.upload_tracer(m, t)
-        plan.bind_tracer(m, None, c.conc_underflow(m))
+        if m < args.diags:       # --diags N: ad_x and ad_y on the first N tracers (T_adx, T_ady, S_adx, S_ady of a diag_table)
+            plan.bind_tracer(m, None, c.conc_underflow(m), ad_x=diag_flag, ad_y=diag_flag)
+        else:
+            plan.bind_tracer(m, None, c.conc_underflow(m))
         del t
     plan.upload_field(capi.F_H_END, c.h_end)
     plan.upload_field(capi.F_UHTR, c.uhtr)
@@ -316,7 +320,7 @@ def run_native(args):
            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
            "dtype": "f64", "data": "synthetic",
            "config": shared_config(name, ni, nj, nk, ntr, scheme, args.cfl),
-           "iterations_per_call": nit, "resident_gb": plan.device_bytes / 1e9,
+           "iterations_per_call": nit, "resident_gb": plan.device_bytes / 1e9, "tracers_with_ad_x_ad_y": int(args.diags),
            "roofline": roofline, "gpu_launches": int(launches), "clocks": clocks,
            "per_call_ms": {"min": min(per_call), "median": sorted(per_call)[len(per_call) // 2], "max": max(per_call)}}
     # ocean-only rate (land included in `value`, the ocean-only count reported alongside)
@@ -536,6 +540,7 @@ def main():
     ap.add_argument("--cpu-levels", type=int, default=0, help="levels in the bounded CPU sample")
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--e2e-warmup", type=int, default=2)
+    ap.add_argument("--diags", type=int, default=0, help="associate ad_x and ad_y on the first N tracers (diagnostic-path timing)")
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of a slab of the workload")
     ap.add_argument("--layout", default=None, help="multi-GPU LAYOUT as IxJ (default: strips in j)")
     ap.add_argument("--no-e2e", action="store_true")

@@ -16,8 +16,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libmom6adv_b200.so")
-SOURCES = ["kernels.cu", "plan.cu", "fast_x.cu", "fast_y.cu", "fast_x_v1.cu", "fast_y_v1.cu", "sparse.cu", "halo.cu", "obc.cu", "step.cu", "noalloc.cu"]
-HEADERS = ["internal.cuh", "kernels.h", "fast_common.cuh", "fast_common_v1.cuh", "obc.cuh", os.path.join("..", "..", "include", "mom6adv.h")]
+SOURCES = ["kernels.cu", "plan.cu", "fast_x.cu", "fast_y.cu", "sparse.cu", "halo.cu", "obc.cu", "step.cu", "noalloc.cu"]
+HEADERS = ["internal.cuh", "kernels.h", "fast_common.cuh", "obc.cuh", os.path.join("..", "..", "include", "mom6adv.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-fmad=false", "-lineinfo",
               "-std=c++17", "-Xcompiler", "-fPIC", "-shared"]

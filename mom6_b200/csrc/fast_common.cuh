@@ -180,7 +180,7 @@ __device__ __forceinline__ double underflow(double o, double cu) {
 template <int SCHEME, bool FACEACT>
 __device__ __forceinline__ void sweep4(double (&T)[6], const double (&hh)[5], const double (&hcs)[5], const double (&gqs)[5],
                                        const double (&hl)[4], const double (&ih)[4], const double (&mm)[4],
-                                       const unsigned flg, double (&o)[4]) {
+                                       const unsigned flg, double (&o)[4], double (&fl)[5]) {
   const unsigned FULL = 0xffffffffu;
     T[0] = __shfl_up_sync(FULL, T[4], 1);
     T[5] = __shfl_down_sync(FULL, T[1], 1);
@@ -192,7 +192,7 @@ __device__ __forceinline__ void sweep4(double (&T)[6], const double (&hh)[5], co
 #pragma unroll
       for (int n = 0; n < 4; n++) s[n] = slope_f(a[n + 1], a[n], A2[n + 1], A2[n], T[n + 2] - T[n], mm[n]);
     }
-    double fl[5];      // flux through face n
+    // fl[n]: flux through face n (returned: the flux diagnostics of the DIAG sweeps use it)
     if (SCHEME == SCHEME_PLM) {
       // face n is fed by cell n-1 (hh >= 0) or cell n (hh < 0); own cells are 0..3, cell 4 is the east neighbour's
       const double s_e = __shfl_down_sync(FULL, s[0], 1);
@@ -258,4 +258,12 @@ __device__ __forceinline__ void sweep4(double (&T)[6], const double (&hh)[5], co
       const double upd = (T[n + 1] * hl[n] - (fl[n + 1] - fl[n])) * ih[n];
       o[n] = ((flg >> (5 + n)) & 1u) ? upd : T[n + 1];
     }
+}
+
+template <int SCHEME, bool FACEACT>
+__device__ __forceinline__ void sweep4(double (&T)[6], const double (&hh)[5], const double (&hcs)[5], const double (&gqs)[5],
+                                       const double (&hl)[4], const double (&ih)[4], const double (&mm)[4],
+                                       const unsigned flg, double (&o)[4]) {
+  double fl[5];
+  sweep4<SCHEME, FACEACT>(T, hh, hcs, gqs, hl, ih, mm, flg, o, fl);
 }

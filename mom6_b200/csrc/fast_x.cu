@@ -43,9 +43,13 @@ __device__ __forceinline__ void x_copy_through(const TrTable &tt, long long q0, 
 #ifndef XMINB
 #define XMINB 4
 #endif
-template <int SCHEME>
+// DIAG: the tracers of this launch have ad_x and / or advection_xy associated (dg, same order as tt): the face fluxes
+// sweep4 leaves in registers are accumulated where the reference does (:665-667, :671-676).  The plain instantiation
+// (every other tracer) is unchanged by it.
+template <int SCHEME, bool DIAG>
 __global__ void __launch_bounds__(128, XMINB)
-k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const double *__restrict__ hcv,
+k_x_fast(Geom g, Range rg, TrTable tt, DiagTable dg, const double *__restrict__ IareaT, double Idt,
+         const double *__restrict__ hhv, const double *__restrict__ hcv,
          const double *__restrict__ gqv, const double *__restrict__ hlstv, const double *__restrict__ ihv,
          const double *__restrict__ mmv, const int *__restrict__ entry, const int *__restrict__ domore_k, int wbase,
          int wj_lo, int wj_hi,        // rows (Fortran j) this launch owns; the others belong to another launch of the sweep
@@ -100,7 +104,10 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
   for (int n = 0; n < 4; n++) flg |= ((ih[n] > 0.0) ? (32u << n) : 0u) | (inr[n] ? (512u << n) : 0u);
   // no stored cell of this warp's 128 columns is updated (land, or no transport left on any of their faces):
   // every output equals its input whatever the fluxes are, so the tile is copied through
-  if (!__any_sync(FULL, st && (flg & 0x1e0u) != 0u)) { x_copy_through(tt, q0, st, inr); return; }
+  // (DIAG: the east face of lane 30's last cell also counts when lane 31's first cell -- a stored cell of the NEXT tile --
+  // is updated: ad_x accumulates where do_i(i) .or. do_i(i+1), :665)
+  if (!__any_sync(FULL, (st && (flg & 0x1e0u) != 0u) || (DIAG && lane == 31 && (flg & 0x20u) != 0u))) { x_copy_through(tt, q0, st, inr); return; }
+  const unsigned de_flg = DIAG ? __shfl_down_sync(FULL, flg, 1) : 0u;
   const bool st_ok = st && !(edge && (flg & 0x1e0u) != 0u);      // (an edge lane never holds an updated cell; if it did, its value would need a neighbour it lacks)
   asm volatile("" : "+r"(flg));      // opaque: keeps the compiler from re-deriving the bits with FP64 compares per tracer
   // signed flux factors (face_flux_sgn): PPM wants -hc, -gq on faces fed from the low side, PLM +gq there
@@ -112,6 +119,12 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
     gqs[n] = neg_if(gq[n], SCHEME == SCHEME_PLM ? !lo : lo);
   }
 
+  double ia[4] = {0, 0, 0, 0};
+  if (DIAG) {
+    const long long q2 = (long long)c0 + (long long)g.P * rj;
+    const double2 a0 = *reinterpret_cast<const double2 *>(IareaT + q2), a1 = *reinterpret_cast<const double2 *>(IareaT + q2 + 2);
+    ia[0] = a0.x; ia[1] = a0.y; ia[2] = a1.x; ia[3] = a1.y;
+  }
   // two tracers in flight ahead of the one being computed: one iteration of the loop is shorter than a loaded
   // HBM round trip (ncu: 17 % of the samples sat on the first use of a one-deep prefetch)
   double2 n0 = *reinterpret_cast<const double2 *>(tt.src[0] + q0);
@@ -132,7 +145,26 @@ k_x_fast(Geom g, Range rg, TrTable tt, const double *__restrict__ hhv, const dou
       asm volatile("prefetch.global.L2 [%0];" ::"l"(tt.src[m + XL2PF] + q0));
 #endif
     double o[4];
-    sweep4<SCHEME, false>(T, hh, hcs, gqs, hl, ih, mm, flg, o);
+    if (DIAG) {
+      double fl[5];
+      sweep4<SCHEME, false>(T, hh, hcs, gqs, hl, ih, mm, flg, o, fl);
+      if (st_ok) {
+        // do_i of this lane's cells (bits 5..8) and of the east neighbour's first cell (de_flg, fetched before the loop)
+        const unsigned dn = (flg >> 5) & 0xfu;
+        const unsigned de = (de_flg >> 5) & 1u;
+        const unsigned dnx = (dn >> 1) | ((lane == 31 ? 0u : de) << 3);      // do_i of cell n+1
+        double *__restrict__ ad = dg.ad[m];
+        double *__restrict__ axy = dg.axy[m];
+#pragma unroll
+        for (int n = 0; n < 4; n++) {
+          // face I = east face of cell n, stored at the cell's own index: do_i(i) .or. do_i(i+1)  (:665-667)
+          if (ad && (((dn | dnx) >> n) & 1u)) ad[q0 + n] = ad[q0 + n] + fl[n + 1] * Idt;
+          if (axy && ((dn >> n) & 1u)) axy[q0 + n] = axy[q0 + n] - (fl[n + 1] - fl[n]) * Idt * ia[n];      // :671-676
+        }
+      }
+    } else {
+      sweep4<SCHEME, false>(T, hh, hcs, gqs, hl, ih, mm, flg, o);
+    }
     const double cu = tt.cu[m];
     if (cu > 0.0) {      // warp-uniform: most tracers carry no underflow threshold
 #pragma unroll
@@ -149,7 +181,8 @@ int x_fast_tiles(const Geom &g, int wbase) { return (g.ied + g.coff - (wbase + 4
 
 void launch_x_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
                    const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm,
-                   const int *entry, const int *domore_k, int wbase, int wj_lo, int wj_hi) {
+                   const int *entry, const int *domore_k, int wbase, int wj_lo, int wj_hi,
+                   const DiagTable *dg, const double *IareaT, double Idt) {
   wj_lo = std::max(wj_lo, g.jsd); wj_hi = std::min(wj_hi, g.jed);
   if (wj_lo > wj_hi) return;
   int ntx = x_fast_tiles(g, wbase), edge = 0;
@@ -164,7 +197,14 @@ void launch_x_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const Tr
         wb2 + XT_USE * (nt2 - 1) + 128 <= g.P) { wbase = wb2; ntx = nt2; edge = 1; }
   }
   dim3 grid(ntx, (wj_hi - wj_lo + 1 + 3) / 4, g.nk);
-  if (scheme == SCHEME_PLM) k_x_fast<SCHEME_PLM><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi, edge);
-  else if (scheme == SCHEME_PPM_CW) k_x_fast<SCHEME_PPM_CW><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi, edge);
-  else k_x_fast<SCHEME_PPM_H3><<<grid, 128, 0, s>>>(g, rg, tt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi, edge);
+  static const DiagTable none = {};
+#define XL(S)                                                                                                          \
+  do {                                                                                                                 \
+    if (dg) k_x_fast<S, true><<<grid, 128, 0, s>>>(g, rg, tt, *dg, IareaT, Idt, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi, edge); \
+    else k_x_fast<S, false><<<grid, 128, 0, s>>>(g, rg, tt, none, nullptr, 0.0, hh, hc, gq, hlst, ihnew, mm, entry, domore_k, wbase, wj_lo, wj_hi, edge); \
+  } while (0)
+  if (scheme == SCHEME_PLM) XL(SCHEME_PLM);
+  else if (scheme == SCHEME_PPM_CW) XL(SCHEME_PPM_CW);
+  else XL(SCHEME_PPM_H3);
+#undef XL
 }

@@ -39,6 +39,13 @@ struct TrTable {
   int n;
 };
 
+// Flux-diagnostic pointers of the tracers of a TrTable (same order); nullptr = unassociated.
+//   ad: ad_x or ad_y of the sweep's direction (:665-667 / :1070-1076), axy: advection_xy (:671-676 / :1051-1056)
+struct DiagTable {
+  double *ad[MOM6ADV_MAXT];
+  double *axy[MOM6ADV_MAXT];
+};
+
 // ---- gfortran intrinsic semantics (argument-order compare-select) -----------
 __device__ __forceinline__ double gmax2(double a, double b) { return (b > a) ? b : a; }
 __device__ __forceinline__ double gmin2(double a, double b) { return (b < a) ? b : a; }

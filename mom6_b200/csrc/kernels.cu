@@ -557,6 +557,78 @@ void launch_tracer_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Ran
 }
 
 // ---------------------------------------------------------------------------
+// Flux diagnostics of a sweep without the sweep (:665-667,671-676 / :1051-1056,1070-1076): the same face fluxes as
+// k_tracer_sweep, from the tracers' values BEFORE the sweep, accumulated into ad_x | ad_y and advection_xy of the tracers
+// that have them.  The streaming y march updates in place and carries no diagnostics; this runs in front of it for the
+// handful of tracers a diag_table asks for, so that one T_ady no longer takes the whole registry off the fast path.
+// ---------------------------------------------------------------------------
+// One thread = one column of a FD_ROWS-row segment, marching north with the 7-point tracer window in registers, so
+// that every tracer value is read once (plus the window's lead-in per segment) instead of once per stencil point.
+#define FD_ROWS 64
+template <int SCHEME>
+__global__ void __launch_bounds__(TPB)
+k_flux_diag_y(Geom g, Range rg, const TracerDev *__restrict__ tr, int ntr, int src,
+              const double *__restrict__ hh, const double *__restrict__ cflv, const double *__restrict__ ihnewv,
+              const double *__restrict__ mmv, const double *__restrict__ IareaT,
+              const int *__restrict__ entry, const int *__restrict__ domore_k, double Idt) {
+  const int ci = blockIdx.x * blockDim.x + threadIdx.x, k0 = blockIdx.z;
+  if (ci >= g.P || domore_k[k0] <= 0) return;
+  const int i = ci - g.coff;
+  if (i < rg.is || i > rg.ie) return;                 // faces and cells of the sweep lie in columns is..ie
+  constexpr int W = (SCHEME == SCHEME_PPM_CW) ? 3 : 2;
+  const int P = g.P;
+  // cell rows this thread visits: faces J in [js-1, je] are the high faces of cells j in [js-1, je]
+  const int rlo = max(rg.js - 1 + g.roff, blockIdx.y * FD_ROWS), rhi = min(rg.je + g.roff, blockIdx.y * FD_ROWS + FD_ROWS - 1);
+  if (rlo > rhi) return;
+  const int *__restrict__ ent = entry + k0 * g.R;
+  const long long col = (long long)ci + g.plane * k0;
+  for (int m = 0; m < ntr; m++) {
+    double *ad = tr[m].ad_y;
+    double *axy = tr[m].adv_xy;
+    if (!ad && !axy) continue;
+    const double *__restrict__ tin = tr[m].buf[src] + col;
+    double t[7];                                      // T(r-3 .. r+3) of the current row r
+#pragma unroll
+    for (int s = -3; s < 3; s++) { const int rr = rlo + s; t[s + 3] = (s >= -W && rr >= 0 && rr < g.R) ? tin[(long long)P * rr] : 0.0; }
+    for (int r = rlo; r <= rhi; r++) {
+      t[6] = (W == 3 && r + 3 < g.R) ? tin[(long long)P * (r + 3)] : 0.0;
+      if (W == 2) t[5] = (r + 2 < g.R) ? tin[(long long)P * (r + 2)] : 0.0;
+      const int j = r - g.roff;
+      const long long q = col + (long long)P * r, q2 = (long long)ci + (long long)P * r;
+      const bool in_rng = (j >= rg.js && j <= rg.je);
+      const bool act_hi = (j >= rg.js - 1 && j <= rg.je) && ent[r];
+      const bool act_lo = in_rng && ent[r - 1];
+      const bool do_i = in_rng && ihnewv[q] > 0.0;
+      const bool do_nxt = (j + 1 >= rg.js && j + 1 <= rg.je) && (ihnewv[q + P] > 0.0);
+      const bool diag_hi = act_hi && (do_i || do_nxt);
+      if (do_i || diag_hi) {
+        double mm[5];
+#pragma unroll
+        for (int s = -2; s <= 2; s++) mm[s + 2] = mmv[q2 + (long long)s * P];
+        double f_hi = 0.0, f_lo = 0.0;
+        if (act_hi) f_hi = face_flux<SCHEME>(&t[1], &mm[1], hh[q], cflv[q]);
+        if (do_i && axy) {
+          if (act_lo) f_lo = face_flux<SCHEME>(&t[0], &mm[0], hh[q - P], cflv[q - P]);
+          axy[q] = axy[q] - (f_hi - f_lo) * Idt * IareaT[q2];
+        }
+        if (ad && diag_hi) ad[q] = ad[q] + f_hi * Idt;
+      }
+#pragma unroll
+      for (int s = 0; s < 6; s++) t[s] = t[s + 1];
+    }
+  }
+}
+void launch_flux_diag(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TracerDev *tr, int ntr, int src,
+                      const double *hh, const double *cfl, const double *ihnew, const double *mm, const double *IareaT,
+                      const int *entry, const int *domore_k, double Idt) {
+  (void)dir;      // y only: the x sweep carries its diagnostics itself (k_x_fast<.., true>)
+  dim3 grid((g.P + TPB - 1) / TPB, (g.R + FD_ROWS - 1) / FD_ROWS, g.nk);
+  if (scheme == SCHEME_PLM) k_flux_diag_y<SCHEME_PLM><<<grid, TPB, 0, s>>>(g, rg, tr, ntr, src, hh, cfl, ihnew, mm, IareaT, entry, domore_k, Idt);
+  else if (scheme == SCHEME_PPM_CW) k_flux_diag_y<SCHEME_PPM_CW><<<grid, TPB, 0, s>>>(g, rg, tr, ntr, src, hh, cfl, ihnew, mm, IareaT, entry, domore_k, Idt);
+  else k_flux_diag_y<SCHEME_PPM_H3><<<grid, TPB, 0, s>>>(g, rg, tr, ntr, src, hh, cfl, ihnew, mm, IareaT, entry, domore_k, Idt);
+}
+
+// ---------------------------------------------------------------------------
 // ad2d_x / ad2d_y (:691-699 / :1078-1084): vertical sums of the face fluxes in
 // the reference's k order.  One thread per face column walks k = 1..nk and
 // recomputes the flux from the sweep's (still intact) input buffer.
@@ -565,7 +637,10 @@ template <int SCHEME, int DIR>
 __global__ void k_ad2d(Geom g, Range rg, const TracerDev *__restrict__ tr, int ntr, int src,
                        const double *__restrict__ hh, const double *__restrict__ cflv,
                        const double *__restrict__ ihnewv, const double *__restrict__ mmv,
-                       const int *__restrict__ entry, const int *__restrict__ domore_k, double Idt) {
+                       const int *__restrict__ entry, const int *__restrict__ domore_k, double Idt,
+                       const int *__restrict__ tflags) {
+  // tflags (list-driven residual trips, nullable): Ihnew of a cell is current only where the mass update visited its
+  // 32-column tile (bit 1); elsewhere no cell changes in this sweep
   int ci = blockIdx.x * blockDim.x + threadIdx.x, rj = blockIdx.y;
   if (ci >= g.P) return;
   const int i = ci - g.coff, j = rj - g.roff;
@@ -588,7 +663,14 @@ __global__ void k_ad2d(Geom g, Range rg, const TracerDev *__restrict__ tr, int n
     for (int k0 = 0; k0 < g.nk; k0++) {
       if (domore_k[k0] <= 0 || !entry[k0 * g.R + rj]) continue;
       const long long q = q2 + g.plane * k0;
-      const bool d = (cur_in && ihnewv[q] > 0.0) || (nxt_in && ihnewv[q + st] > 0.0);
+      bool vc = true, vn = true;
+      if (tflags) {
+        const int W5 = g.P >> 5;
+        vc = (tflags[(k0 * g.R + rj) * W5 + (ci >> 5)] & 2) != 0;
+        vn = (DIR == 0) ? ((ci + 1 < g.P) && (tflags[(k0 * g.R + rj) * W5 + ((ci + 1) >> 5)] & 2) != 0)
+                        : ((rj + 1 < g.R) && (tflags[(k0 * g.R + rj + 1) * W5 + (ci >> 5)] & 2) != 0);
+      }
+      const bool d = (cur_in && vc && ihnewv[q] > 0.0) || (nxt_in && vn && ihnewv[q + st] > 0.0);
       if (!d) continue;
       double t[6];
 #pragma unroll
@@ -600,9 +682,9 @@ __global__ void k_ad2d(Geom g, Range rg, const TracerDev *__restrict__ tr, int n
 }
 void launch_ad2d(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TracerDev *tr, int ntr, int src,
                  const double *hh, const double *cfl, const double *ihnew, const double *mm, const int *entry,
-                 const int *domore_k, double Idt) {
+                 const int *domore_k, double Idt, const int *tflags) {
   dim3 grid((g.P + TPB - 1) / TPB, g.R, 1);
-#define AD2D(S, D) k_ad2d<S, D><<<grid, TPB, 0, s>>>(g, rg, tr, ntr, src, hh, cfl, ihnew, mm, entry, domore_k, Idt)
+#define AD2D(S, D) k_ad2d<S, D><<<grid, TPB, 0, s>>>(g, rg, tr, ntr, src, hh, cfl, ihnew, mm, entry, domore_k, Idt, tflags)
   if (scheme == SCHEME_PLM) { if (dir == 0) AD2D(SCHEME_PLM, 0); else AD2D(SCHEME_PLM, 1); }
   else if (scheme == SCHEME_PPM_CW) { if (dir == 0) AD2D(SCHEME_PPM_CW, 0); else AD2D(SCHEME_PPM_CW, 1); }
   else { if (dir == 0) AD2D(SCHEME_PPM_H3, 0); else AD2D(SCHEME_PPM_H3, 1); }

@@ -28,7 +28,7 @@ void launch_tracer_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Ran
                          const double *mm, const double *IareaT, const int *entry, const int *domore_k, double Idt);
 void launch_ad2d(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TracerDev *tr, int ntr, int src,
                  const double *hh, const double *cfl, const double *ihnew, const double *mm, const int *entry,
-                 const int *domore_k, double Idt);
+                 const int *domore_k, double Idt, const int *tflags = nullptr);
 void launch_halo_apply(cudaStream_t s, long long plane, int nk, const int *dst, const int *src,
                        const signed char *sgn, int n, double *const *fields, int nfields);
 void launch_halo_pack(cudaStream_t s, long long plane, int nk, const int *src, const signed char *sgn, int n,
@@ -60,24 +60,22 @@ void launch_publish(cudaStream_t s, int *host_mapped, const int *dev, int n);
 int x_fast_tiles(const Geom &g, int wbase);
 void launch_x_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
                    const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm, const int *entry,
-                   const int *domore_k, int wbase, int wj_lo, int wj_hi);
+                   const int *domore_k, int wbase, int wj_lo, int wj_hi,
+                   const DiagTable *dg = nullptr, const double *IareaT = nullptr, double Idt = 0.0);
 void launch_y_fast(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
                    const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm, const int *entry,
                    const int *domore_k);
-
-// fast_x_v1.cu / fast_y_v1.cu: the round-1 streaming kernels, selectable with option "fast" = 1 for A/B timing
-void launch_x_fast_v1(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
-                      const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm, const int *entry,
-                      const int *domore_k, int wbase, int wj_lo, int wj_hi);
-void launch_y_fast_v1(cudaStream_t s, int scheme, const Geom &g, Range rg, const TrTable &tt, const double *hh,
-                      const double *hc, const double *gq, const double *hlst, const double *ihnew, const double *mm, const int *entry,
-                      const int *domore_k);
-
+// ad_x | ad_y and advection_xy of the tracers that have them, from the sweep's INPUT values (kernels.cu): run before an
+// in-place sweep.  Needs CFL itself (cfl), not the streaming kernels' factors.
+void launch_flux_diag(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TracerDev *tr, int ntr, int src,
+                      const double *hh, const double *cfl, const double *ihnew, const double *mm, const double *IareaT,
+                      const int *entry, const int *domore_k, double Idt);
 // sparse.cu: list-driven tracer update of the residual iterations
 void launch_sparse_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TrTable &tt,
                          const int *list, const int *cnt_dev, int nsm, const double *hh, const double *cfl,
                          const double *hlst, const double *ihnew, const double *mm, const int *entry,
-                         unsigned char *dirty);
+                         unsigned char *dirty, const DiagTable *dg = nullptr, const double *IareaT = nullptr,
+                         double Idt = 0.0, const int *tflags = nullptr);
 
 // step.cu: transport accumulation and column diagnostics either side of advect_tracer
 void launch_accumulate(cudaStream_t s, const Geom &g, double *acc, const double *add, double dt, int ilo, int ihi,

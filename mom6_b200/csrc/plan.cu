@@ -98,7 +98,7 @@ struct mom6adv_plan {
   long long launches = 0;
   long long dev_bytes = 0;
   int opt_fused = 0;
-  int opt_fast = 2;      // 0 generic kernels, 1 round-1 streaming kernels (kept for A/B timing), 2 current streaming kernels
+  int opt_fast = 2;      // 0 generic thread-per-cell kernels (A/B timing, literal restatement), non-zero: streaming kernels
   // multi-GPU (LAYOUT = npi,npj): one rank per GPU, NCCL over NVLink
   bool multi = false;
   ncclComm_t comm = nullptr;
@@ -1078,12 +1078,12 @@ static int sweep_impl(mom6adv_plan *plan, int dir, Range rg, double Idt, int sch
     for (int d = 0; d < 5; d++) if (plan->tr[m].diag[d]) any_diag = true;
   }
   if (plan->obc_active) return sweep_obc(plan, dir, rg, Idt, scheme);
-  const bool split_rows = plan->pull_pending && dir == 0 && plan->opt_fast && !any_diag && itt == 1;
+  const bool split_rows = plan->pull_pending && dir == 0 && plan->opt_fast && itt == 1;
   if (plan->pull_pending && !split_rows) {            // any other consumer needs the halo rows now
     CK(cudaStreamWaitEvent(s, plan->ev_pull_done, 0));
     plan->pull_pending = false;
   }
-  if (plan->opt_fast && !any_diag) {
+  if (plan->opt_fast) {
     // streaming kernels (fast.cu): mass fields as below, then all tracers in chunks of MOM6ADV_MAXT
     const bool x = (dir == 0);
     int *dom = x ? plan->domore_u : plan->domore_v, *ent = x ? plan->entry_u : plan->entry_v;
@@ -1121,24 +1121,55 @@ static int sweep_impl(mom6adv_plan *plan, int dir, Range rg, double Idt, int sch
       } else {
         // dense trip of the streaming path: nothing reads CFL itself (k_x_fast / k_y_ring take hc, gq), so it is not written
         CK(cudaMemsetAsync(plan->sum_dev + 4 + dir, 0, sizeof(int), s));
-        launch_mass_flux(s, dir, g, rg, res, plan->hprev, plan->areaT, min_h, ent, dom, plan->hh, nullptr,
-                         plan->hc, plan->gq, scheme == SCHEME_PLM);
+        launch_mass_flux(s, dir, g, rg, res, plan->hprev, plan->areaT, min_h, ent, dom, plan->hh, (any_ad2d || (!x && any_diag)) ? plan->cfl : nullptr,
+                         plan->hc, plan->gq, scheme == SCHEME_PLM);      // (CFL itself: only k_ad2d / k_flux_diag read it)
         launch_mass_update(s, dir, g, rg, res, plan->hprev, plan->hh, plan->areaT, x ? plan->uh_neglect : plan->vh_neglect,
                            h_neglect, ent, plan->domore_k, plan->hlst, plan->ihnew, nullptr, nullptr, 0, plan->sum_dev + 4 + dir);
       }
       plan->launches += 3;
     }
+    // Tracers with a flux diagnostic of this direction (ad_x | ad_y) or advection_xy go through the DIAG instantiation of
+    // the same kernels, as a launch of their own; every other tracer takes the plain one: one associated diagnostic no
+    // longer moves the whole registry onto the generic kernels.  ad2d_x / ad2d_y are k-ORDERED sums (:691-699 /
+    // :1078-1084): k_ad2d walks k per face column from the sweep's input values -- before the in-place y sweep, after
+    // the out-of-place x sweep.
+    struct Batch { TrTable tt; DiagTable dg; bool diag; };
+    std::vector<Batch> batches;
+    // y: the in-place march carries no diagnostics; ad_y / advection_xy of the tracers that have them come from
+    // k_flux_diag in front of it (below), so every tracer takes the plain kernel.  (A DIAG instantiation of the march was
+    // built and measured: the diagnostic warp's read-modify-write per step is latency-bound while its CTA-mates wait
+    // for the ring -- 43.6 ms instead of 31.6 ms per sweep for ad_y on two tracers, profiles/r02_diag_path.md.)
+    std::vector<char> in_diag(plan->ntr, 0);
+    bool any_dirdiag = false;
+    for (int m = plan->m_lo; m < plan->m_hi; m++)
+      if (plan->tr[m].diag[x ? 0 : 1] || plan->tr[m].diag[4]) { any_dirdiag = true; if (x || sparse) in_diag[m] = 1; }
+    for (int pass = 0; pass < 2; pass++) {
+      Batch b; b.tt.n = 0; b.diag = (pass == 1); memset(&b.dg, 0, sizeof b.dg);
+      for (int m = plan->m_lo; m < plan->m_hi; m++) {
+        const TracerSlot &ts = plan->tr[m];
+        const bool d = in_diag[m] != 0;
+        if (d != b.diag) continue;
+        const int n = b.tt.n++;
+        b.tt.src[n] = ts.buf[plan->cur]; b.tt.cu[n] = ts.conc_underflow;
+        b.tt.dst[n] = sparse ? ts.buf[1 - plan->cur] : (x ? ts.buf[1 - plan->cur] : ts.buf[plan->cur]);
+        b.dg.ad[n] = ts.diag[x ? 0 : 1]; b.dg.axy[n] = ts.diag[4];
+        if (b.tt.n == MOM6ADV_MAXT) { batches.push_back(b); b.tt.n = 0; memset(&b.dg, 0, sizeof b.dg); }
+      }
+      if (b.tt.n > 0) batches.push_back(b);
+    }
+    const double *mmd = x ? plan->mmx : plan->mmy;
+    auto ad2d = [&]() {
+      launch_ad2d(s, scheme, dir, g, rg, plan->tr_dev + plan->m_lo, plan->m_hi - plan->m_lo, plan->cur, plan->hh, plan->cfl,
+                  plan->ihnew, mmd, ent, plan->domore_k, Idt, sparse ? plan->tflags : nullptr);
+      plan->launches++;
+    };
     if (sparse) {
       ProfScope pt(plan, MOM6ADV_KC_SPARSE);
-      for (int m0 = plan->m_lo; m0 < plan->m_hi; m0 += MOM6ADV_MAXT) {
-        TrTable tt;
-        tt.n = std::min(MOM6ADV_MAXT, plan->m_hi - m0);
-        for (int m = 0; m < tt.n; m++) {
-          const TracerSlot &ts = plan->tr[m0 + m];
-          tt.src[m] = ts.buf[plan->cur]; tt.dst[m] = ts.buf[1 - plan->cur]; tt.cu[m] = ts.conc_underflow;
-        }
-        launch_sparse_sweep(s, scheme, dir, g, rg, tt, plan->sp_list, plan->sum_dev + 1, plan->nsm, plan->hh, plan->cfl,
-                            plan->hlst, plan->ihnew, x ? plan->mmx : plan->mmy, ent, plan->dirty);
+      if (any_ad2d) ad2d();      // (reads the live buffers, which the list-driven update changes only afterwards)
+      for (const Batch &b : batches) {
+        launch_sparse_sweep(s, scheme, dir, g, rg, b.tt, plan->sp_list, plan->sum_dev + 1, plan->nsm, plan->hh, plan->cfl,
+                            plan->hlst, plan->ihnew, mmd, ent, plan->dirty, b.diag ? &b.dg : nullptr, plan->IareaT, Idt,
+                            plan->tflags);
         plan->launches += 2;
       }
       plan->sparse_sweeps++;
@@ -1147,33 +1178,44 @@ static int sweep_impl(mom6adv_plan *plan, int dir, Range rg, double Idt, int sch
     }
     plan->dense_sweeps++;
     ProfScope pt(plan, x ? MOM6ADV_KC_TRACER_X : MOM6ADV_KC_TRACER_Y);
-    for (int m0 = plan->m_lo; m0 < plan->m_hi; m0 += MOM6ADV_MAXT) {
-      TrTable tt;
-      tt.n = std::min(MOM6ADV_MAXT, plan->m_hi - m0);
-      for (int m = 0; m < tt.n; m++) {
-        const TracerSlot &ts = plan->tr[m0 + m];
-        tt.src[m] = ts.buf[plan->cur];
-        tt.dst[m] = x ? ts.buf[1 - plan->cur] : ts.buf[plan->cur];
-        tt.cu[m] = ts.conc_underflow;
-      }
-      auto xf = (plan->opt_fast == 1) ? launch_x_fast_v1 : launch_x_fast;
-      auto yf = (plan->opt_fast == 1) ? launch_y_fast_v1 : launch_y_fast;
-      if (x && split_rows) {
-        // rows of the computational domain first; the halo rows once their tracer values have arrived
-        xf(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
-                      plan->domore_k, plan->wbase, g.jsc, g.jec);
-        if (plan->pull_pending) { CK(cudaStreamWaitEvent(s, plan->ev_pull_done, 0)); plan->pull_pending = false; }
-        xf(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
-                      plan->domore_k, plan->wbase, g.jsd, g.jsc - 1);
-        xf(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
-                      plan->domore_k, plan->wbase, g.jec + 1, g.jed);
-        plan->launches += 2;
-      } else if (x) xf(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
-                           plan->domore_k, plan->wbase, g.jsd, g.jed);
-      else yf(s, scheme, g, rg, tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmy, ent,
-                         plan->domore_k);
+    if (!x && any_ad2d) ad2d();
+    if (!x && any_dirdiag) {
+      launch_flux_diag(s, scheme, 1, g, rg, plan->tr_dev + plan->m_lo, plan->m_hi - plan->m_lo, plan->cur, plan->hh, plan->cfl,
+                       plan->ihnew, plan->mmy, plan->IareaT, ent, plan->domore_k, Idt);
       plan->launches++;
     }
+    bool first = true;
+    for (const Batch &b : batches) {
+      const DiagTable *dg = b.diag ? &b.dg : nullptr;
+      if (x && split_rows) {
+        // rows of the computational domain first; the halo rows once their tracer values have arrived
+        launch_x_fast(s, scheme, g, rg, b.tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
+                      plan->domore_k, plan->wbase, g.jsc, g.jec, dg, plan->IareaT, Idt);
+        plan->launches++;
+      } else if (x) {
+        launch_x_fast(s, scheme, g, rg, b.tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
+                      plan->domore_k, plan->wbase, g.jsd, g.jed, dg, plan->IareaT, Idt);
+        plan->launches++;
+      } else {
+        launch_y_fast(s, scheme, g, rg, b.tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmy, ent,
+                      plan->domore_k);
+        plan->launches++;
+      }
+      first = false;
+    }
+    (void)first;
+    if (x && split_rows) {
+      if (plan->pull_pending) { CK(cudaStreamWaitEvent(s, plan->ev_pull_done, 0)); plan->pull_pending = false; }
+      for (const Batch &b : batches) {
+        const DiagTable *dg = b.diag ? &b.dg : nullptr;
+        launch_x_fast(s, scheme, g, rg, b.tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
+                      plan->domore_k, plan->wbase, g.jsd, g.jsc - 1, dg, plan->IareaT, Idt);
+        launch_x_fast(s, scheme, g, rg, b.tt, plan->hh, plan->hc, plan->gq, plan->hlst, plan->ihnew, plan->mmx, ent,
+                      plan->domore_k, plan->wbase, g.jec + 1, g.jed, dg, plan->IareaT, Idt);
+        plan->launches += 2;
+      }
+    }
+    if (x && any_ad2d) ad2d();             // (plan->cur still names the sweep's input buffers)
     if (x) plan->cur = 1 - plan->cur;      // x is out of place, y in place
     CK(cudaGetLastError());
     return 0;
@@ -1269,7 +1311,9 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
   for (itt = 1; itt <= max_iter; itt++) {                                   // :203
     if (isv > is - stencil) {                                               // :205
       bool defer = false;
-      if (itt == 1 && x_first && plan->opt_overlap && plan->opt_fast && plan->dom.npi == 1) {
+      // (deferred only when the convergence all-reduce of this trip is certain to follow -- nsten_halo == 1 and more
+      // than one trip allowed: it is what orders the neighbours' deferred reads before anybody's next writes)
+      if (itt == 1 && x_first && plan->opt_overlap && plan->opt_fast && plan->dom.npi == 1 && halo_min / stencil == 1 && max_iter > 1) {
         defer = true;
         for (int m = m_lo; m < m_hi; m++) for (int d = 0; d < 5; d++) if (plan->tr[m].diag[d]) defer = false;
       }

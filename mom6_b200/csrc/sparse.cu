@@ -16,7 +16,8 @@ template <int SCHEME, int DIR>
 __global__ void __launch_bounds__(128)
 k_sparse_compute(Geom g, Range rg, TrTable tt, const int *__restrict__ list, const int *__restrict__ cnt_dev,
                  const double *__restrict__ hh, const double *__restrict__ cflv, const double *__restrict__ hlstv,
-                 const double *__restrict__ ihv, const double *__restrict__ mmv, const int *__restrict__ entry) {
+                 const double *__restrict__ ihv, const double *__restrict__ mmv, const int *__restrict__ entry,
+                 DiagTable dg, const double *__restrict__ IareaT, double Idt, const int *__restrict__ tflags) {
   // The list length is read on the device: the host never waits for it (one grid of fixed size strides over the
   // list).  New values go to the tracer's IDLE ping-pong buffer at the cell's own index (tt.dst), so the staging
   // capacity is the whole field and the list cannot overflow: there is no dense fall-back to decide on the host.
@@ -42,6 +43,18 @@ k_sparse_compute(Geom g, Range rg, TrTable tt, const int *__restrict__ list, con
     double mm[5];
 #pragma unroll
     for (int s = -2; s <= 2; s++) mm[s + 2] = mmv[q2 + s * st];
+    // Flux diagnostics (:665-667,671-676 / :1051-1056,1070-1076).  Every listed cell has do_i true.  A face between two
+    // listed cells is accumulated ONCE: by its low-side cell (as that cell's high face); a listed cell takes its low
+    // face only when the cell below it is not updated (its tile was not visited by the mass update -- tflags bit 1
+    // clear, its Ihnew is then stale -- or its Ihnew is zero).
+    bool lo_mine = false;
+    if (tflags) {
+      const long long ql = q - st;
+      const int k0l = k0, reml = rem - st;      // (same level: a listed cell is never in the first row / column of a plane)
+      const int tl = (k0l * g.R + reml / g.P) * (g.P >> 5) + ((reml % g.P) >> 5);
+      lo_mine = !((tflags[tl] & 2) && ihv[ql] > 0.0);
+    }
+    const double iarea = IareaT ? IareaT[q2] : 0.0;
     for (int m = blockIdx.y; m < tt.n; m += gridDim.y) {
       const double *__restrict__ tin = tt.src[m];
       double t[7];
@@ -51,6 +64,15 @@ k_sparse_compute(Geom g, Range rg, TrTable tt, const int *__restrict__ list, con
       if (act_hi) f_hi = face_flux<SCHEME>(&t[1], &mm[1], uh_hi, cf_hi);
       if (act_lo) f_lo = face_flux<SCHEME>(&t[0], &mm[0], uh_lo, cf_lo);
       double out = (t[3] * hl - (f_hi - f_lo)) * ih;
+      if (tflags) {
+        double *__restrict__ ad = dg.ad[m];
+        double *__restrict__ axy = dg.axy[m];
+        if (ad) {
+          if (act_hi) ad[q] = ad[q] + f_hi * Idt;
+          if (act_lo && lo_mine) ad[q - st] = ad[q - st] + f_lo * Idt;
+        }
+        if (axy) axy[q] = axy[q] - (f_hi - f_lo) * Idt * iarea;
+      }
       const double cu = tt.cu[m];
       if (cu > 0.0 && fabs(out) < cu) out = 0.0;
       tt.dst[m][q] = out;
@@ -79,9 +101,12 @@ k_sparse_scatter(TrTable tt, const int *__restrict__ list, const int *__restrict
 void launch_sparse_sweep(cudaStream_t s, int scheme, int dir, const Geom &g, Range rg, const TrTable &tt,
                          const int *list, const int *cnt_dev, int nsm, const double *hh, const double *cfl,
                          const double *hlst, const double *ihnew, const double *mm, const int *entry,
-                         unsigned char *dirty) {
+                         unsigned char *dirty, const DiagTable *dg, const double *IareaT, double Idt, const int *tflags) {
   dim3 grid(nsm * 2, tt.n < 8 ? tt.n : 8, 1);      // a residual trip lists 1e3-1e5 cells: enough threads, few idle CTAs
-#define SP(S, D) k_sparse_compute<S, D><<<grid, 128, 0, s>>>(g, rg, tt, list, cnt_dev, hh, cfl, hlst, ihnew, mm, entry)
+  static const DiagTable none = {};
+  const DiagTable &dgt = dg ? *dg : none;
+  const int *tf = dg ? tflags : nullptr;
+#define SP(S, D) k_sparse_compute<S, D><<<grid, 128, 0, s>>>(g, rg, tt, list, cnt_dev, hh, cfl, hlst, ihnew, mm, entry, dgt, dg ? IareaT : nullptr, Idt, tf)
   if (scheme == SCHEME_PLM) { if (dir == 0) SP(SCHEME_PLM, 0); else SP(SCHEME_PLM, 1); }
   else if (scheme == SCHEME_PPM_CW) { if (dir == 0) SP(SCHEME_PPM_CW, 0); else SP(SCHEME_PPM_CW, 1); }
   else { if (dir == 0) SP(SCHEME_PPM_H3, 0); else SP(SCHEME_PPM_H3, 1); }

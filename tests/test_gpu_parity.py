@@ -371,3 +371,49 @@ def test_om4_1_full_shape_bitwise():
     c, Ro, Rg, outs, nit = _run_pair(ni, nj, nk, ntr, scheme, cfl=0.45)
     assert nit >= 2
     _assert_bitwise(c, Ro, Rg, outs)
+
+
+# ---- flux diagnostics on the streaming path (DIAG instantiations, list-driven trips, k-ordered ad2d) ---------------------
+def _partial_diags(c, which):
+    """Registry in which tracer m carries the diagnostics named in which[m] (a tuple of attribute names)."""
+    Reg = synth.bind_registry(c)
+    G, nk = c.G, c.GV.ke
+    shapes = {"ad_x": G.shape_u(nk), "ad_y": G.shape_v(nk), "ad2d_x": G.shape_u(), "ad2d_y": G.shape_v(),
+              "advection_xy": G.shape_h(nk)}
+    for m, names in which.items():
+        for n in names:
+            setattr(Reg.Tr[m], n, np.full(shapes[n], np.nan))
+    return Reg
+
+
+@pytest.mark.parametrize("scheme", ["PPM", "PLM", "PPM:H3"])
+@pytest.mark.parametrize("x_first", [True, False])
+@pytest.mark.parametrize("cfl", [0.5, 1.6])
+def test_partial_diagnostics_on_the_streaming_path(scheme, x_first, cfl):
+    """T carries ad_x / ad_y (the routine T_adx, T_ady of production diag_tables, MOM_tracer_registry.F90:406-407), S
+    advection_xy only, one passive tracer the 2-D sums, one everything, the others nothing: the registry is split into
+    a DIAG launch and a plain launch of the same kernels; cfl 1.6 adds list-driven residual trips."""
+    which = {0: ("ad_x", "ad_y"), 1: ("advection_xy",), 3: ("ad2d_x", "ad2d_y"),
+             5: ("ad_x", "ad_y", "ad2d_x", "ad2d_y", "advection_xy"), 6: ("ad_y",)}
+    c = synth.make_case(150, 61, 3, 8, cfl=cfl)
+    params = {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}
+    CSo = tracer_advect_init(None, c.G, None, params, None, None)
+    CSg = tracer_advect_init(None, c.G, None, params, None, None)
+    Ro, Rg = _partial_diags(c, which), _partial_diags(c, which)
+    h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
+    for _ in range(2):
+        no = oracle.advect_tracer(h, u, v, None, c.dt, c.G, c.GV, None, CSo, Ro, x_first_in=x_first)
+        ng = advect_tracer(h, u, v, None, c.dt, c.G, c.GV, None, CSg, Rg, x_first_in=x_first)
+        assert no == ng
+    if cfl > 1.0:
+        assert ng >= 3, "the case was meant to exercise the list-driven residual trips"
+    tracer_advect_end(CSg)
+    G = c.G
+    eq = lambda a, b: np.array_equal(np.ascontiguousarray(a).view(np.uint64), np.ascontiguousarray(b).view(np.uint64))
+    for m in range(c.ntr):
+        assert eq(G.interior(Ro.Tr[m].t), G.interior(Rg.Tr[m].t)), "tracer %d" % m
+        for n in which.get(m, ()):
+            cut = G.interior_u if n in ("ad_x", "ad2d_x") else G.interior_v if n in ("ad_y", "ad2d_y") else G.interior
+            a, b = cut(getattr(Ro.Tr[m], n)), cut(getattr(Rg.Tr[m], n))
+            assert eq(a, b), "%s of tracer %d: max abs %g" % (n, m, np.abs(a - b).max())
+            assert np.abs(a).max() > 0.0

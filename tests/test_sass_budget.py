@@ -36,7 +36,7 @@ def _counts(out):
 
 def test_x_sweep_hot_loop_budget():
     # one iteration of the tracer loop = 4 cells of one tracer; rare regions (denormal /6, overshoot fix, underflow) skipped
-    n, f64, other, ops = _counts(_run("k_x_fastILi1E", "--hot"))
+    n, f64, other, ops = _counts(_run("k_x_fastILi1ELb0E", "--hot"))
     assert f64 <= 160, (n, f64, other)            # 155: the reference's arithmetic, each quantity once
     assert other <= 200, (n, f64, other)          # 186 (first generation: 318)
     assert ops.get("DSETP", 0) <= 10              # no per-tracer rebuilding of the tracer-independent flags
@@ -45,9 +45,9 @@ def test_x_sweep_hot_loop_budget():
 
 @pytest.mark.parametrize("scheme", [0, 1, 2])
 def test_sweeps_do_not_spill_and_producer_is_uniform(scheme):
-    n, f64, other, ops = _counts(_run("k_y_ringILi%dE" % scheme, "--all"))
+    n, f64, other, ops = _counts(_run("k_y_ringILi%dELb0E" % scheme, "--all"))
     assert ops.get("LDL", 0) + ops.get("STL", 0) <= 6, ops          # at most a couple of spilled words outside the march
     assert ops.get("UBLKCP", 0) >= 7                                  # bulk copies issued from uniform registers ...
     assert ops.get("ELECT", 0) <= 2 and ops.get("R2UR", 0) <= 12, ops   # ... not through a per-lane ELECT / R2UR loop
-    nx, fx, ox, opsx = _counts(_run("k_x_fastILi%dE" % scheme, "--all"))
+    nx, fx, ox, opsx = _counts(_run("k_x_fastILi%dELb0E" % scheme, "--all"))
     assert opsx.get("LDL", 0) + opsx.get("STL", 0) == 0, opsx
