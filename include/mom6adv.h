@@ -221,18 +221,20 @@ long long mom6adv_device_bytes(const mom6adv_plan *plan);
  * plan creation (peer loads or NCCL messages; the dirty-tile skip may move fewer). */
 long long mom6adv_halo_bytes(const mom6adv_plan *plan);
 /* Options: "profile" 0/1 -- time every kernel class of advect calls with CUDA
- * events on the plan's stream (resets the accumulators); "fast" 0/1/2 -- 0 forces
- * the generic thread-per-cell sweeps, 2 (default) uses the streaming kernels
- * whenever no flux diagnostic is associated, 1 their first generation (kept for A/B timing); "sparse" 0/1 -- 1 (default)
- * updates only the cells next to faces with residual transport on trips >= 2;
- * "mirror_chunk" n -- tracers per pipeline stage of mom6adv_advect (default 4,
+ * events on the plan's stream (resets the accumulators); "fast" 0/1 -- 1 (default; any non-zero value) uses the
+ * streaming kernels, flux diagnostics included, 0 forces the generic thread-per-cell sweeps (A/B timing);
+ * "sparse" 0/1 -- 1 (default) updates only the cells next to faces with residual transport on trips >= 2;
+ * "sparse_cap" n -- estimated list length above which a residual trip takes the dense kernels instead (0 = cells/16;
+ * a hint: either choice gives the same bits);
+ * "mirror_chunk" n -- tracers per pipeline stage of mom6adv_advect (default 2,
  * 0 = one stage: upload everything, compute, download everything);
  * "mirror_ahead" n -- uploads queued n chunks in front of the compute (default 2); "trace" 0/1
  * -- mom6adv_advect prints its copy-stream and compute times to stderr;
  * "pull" 0/1 -- multi-block plans: 1 (default) fills halos by loading the
  * neighbour GPU's fields directly (CUDA IPC + NVLink), 0 packs and uses NCCL
- * send/recv; choose before the first advect call; "overlap" 0/1 -- 1 (default):
- * on 1 x N layouts the tracer halo rows of the first pass travel under the x
+ * send/recv; choose before the first advect call; "pull2" 0/1 -- 1 (default): 16-byte pair-list peer loads;
+ * "dirty" 0/1 -- 1 (default): after a list-driven trip the tracer pulls skip the tiles the owner has not changed;
+ * "overlap" 0/1 -- 1 (default): on 1 x N layouts the tracer halo rows of the first pass travel under the x
  * sweep of the interior rows. */
 int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value);
 /* Kernel classes of the per-class timers: the stand-ins for the reference's
