@@ -14,13 +14,12 @@
 module MOM_tracer_advect
 
 use, intrinsic :: iso_c_binding, only : c_int, c_double, c_ptr, c_char, c_null_ptr, c_null_char, c_loc, &
-                                        c_associated, c_f_pointer, c_long_long
+                                        c_associated, c_f_pointer, c_long_long, c_intptr_t
 use MOM_coms,            only : PE_here, root_PE, num_PEs, broadcast
 use MOM_cpu_clock,       only : cpu_clock_id, cpu_clock_begin, cpu_clock_end
 use MOM_cpu_clock,       only : CLOCK_MODULE, CLOCK_ROUTINE
 use MOM_diag_mediator,   only : diag_ctrl, time_type
 use MOM_domains,         only : sum_across_PEs
-use mpp_domains_mod,     only : CYCLIC_GLOBAL_DOMAIN, FOLD_NORTH_EDGE   ! the values MOM_domain_type%X_FLAGS/Y_FLAGS hold
 use MOM_error_handler,   only : MOM_error, FATAL, WARNING
 use MOM_file_parser,     only : get_param, log_version, param_file_type
 use MOM_grid,            only : ocean_grid_type
@@ -46,8 +45,11 @@ type, public :: tracer_advect_CS ; private
   logical :: useHuynhStencilBug = .false. !< Legacy too-narrow stencil for PPM:H3
   type(c_ptr) :: plan = c_null_ptr   !< mom6adv_plan* (created on the first advect_tracer call)
   integer :: ntr_bound = -1          !< Reg%ntr the plan was last bound with
-  integer(kind=c_long_long) :: reg_hash = 0 !< hash of the registry's pointers at the last bind
+  integer(kind=c_intptr_t) :: reg_hash = 0 !< signature of the registry (pointers, underflow values) at the last bind
   logical :: obc_was_set = .false.   !< an OBC table is active in the plan
+  logical :: reentrant_x = .false.   !< REENTRANT_X, as MOM_domains_init reads it (src/framework/MOM_domains.F90:184-191)
+  logical :: reentrant_y = .false.   !< REENTRANT_Y
+  logical :: tripolar_N = .false.    !< TRIPOLAR_N
 end type tracer_advect_CS
 
 integer :: id_clock_advect !< (Ocean advect tracer): the whole GPU call incl. host<->device copies
@@ -238,10 +240,12 @@ subroutine make_plan(G, GV, CS)
   cd%nig = G%Domain%niglobal ; cd%njg = G%Domain%njglobal
   cd%npi = npi ; cd%npj = npj ; cd%pi = pi ; cd%pj = pj
   cd%ioff = G%idg_offset ; cd%joff = G%jdg_offset        ! global index = local index + offset
-  ! topology flags as create_MOM_domain stored them (config_src/infra/FMS2/MOM_domain_infra.F90:1345-1366)
-  cd%cyclic_x = merge(1, 0, G%Domain%X_FLAGS == CYCLIC_GLOBAL_DOMAIN)
-  cd%cyclic_y = merge(1, 0, G%Domain%Y_FLAGS == CYCLIC_GLOBAL_DOMAIN)
-  cd%tripolar_n = merge(1, 0, G%Domain%Y_FLAGS == FOLD_NORTH_EDGE)
+  ! topology: the parameters create_MOM_domain turns into X_FLAGS / Y_FLAGS (config_src/infra/FMS2/MOM_domain_infra.F90:
+  ! 1345-1366), read by tracer_advect_init from the parameter file -- MOM6 keeps FMS behind config_src/infra, so no
+  ! mpp_domains_mod constant is used here
+  cd%cyclic_x = merge(1, 0, CS%reentrant_x)
+  cd%cyclic_y = merge(1, 0, CS%reentrant_y .and. .not.CS%tripolar_N)
+  cd%tripolar_n = merge(1, 0, CS%tripolar_N)
   call check_rc(mom6adv_plan_create(cg, cc, cd, -1_c_int, CS%plan), c_null_ptr, "plan_create")
   if (npi*npj > 1) then
     ! global compute extents of every layout column / row: each PE contributes its own, the rest are zero
@@ -261,20 +265,26 @@ subroutine make_plan(G, GV, CS)
   endif
 end subroutine make_plan
 
-!> A cheap signature of the registry: the plan is re-bound only when ntr or any pointer changed.
+!> A cheap signature of the registry: the plan is re-bound only when ntr, a tracer's storage, its underflow value or the
+!! address of any of its diagnostic arrays changed.  Circular shifts and exclusive-ors only: no signed overflow.
 function registry_hash(Reg) result(h)
   type(tracer_registry_type), intent(in) :: Reg !< tracer registry
-  integer(kind=c_long_long) :: h
+  integer(kind=c_intptr_t) :: h
   integer :: m
-  h = Reg%ntr
+  h = int(Reg%ntr, c_intptr_t)
   do m=1,Reg%ntr
-    h = h*31 + transfer(c_loc(Reg%Tr(m)%t), h)
-    if (associated(Reg%Tr(m)%ad_x)) h = h*31 + 1
-    if (associated(Reg%Tr(m)%ad_y)) h = h*31 + 2
-    if (associated(Reg%Tr(m)%ad2d_x)) h = h*31 + 3
-    if (associated(Reg%Tr(m)%ad2d_y)) h = h*31 + 4
-    if (associated(Reg%Tr(m)%advection_xy)) h = h*31 + 5
+    call mix(h, transfer(c_loc(Reg%Tr(m)%t), h))
+    call mix(h, transfer(real(Reg%Tr(m)%conc_underflow, c_double), h))
+    call mix(h, transfer(ptr3(Reg%Tr(m)%ad_x), h)) ; call mix(h, transfer(ptr3(Reg%Tr(m)%ad_y), h))
+    call mix(h, transfer(ptr2(Reg%Tr(m)%ad2d_x), h)) ; call mix(h, transfer(ptr2(Reg%Tr(m)%ad2d_y), h))
+    call mix(h, transfer(ptr3(Reg%Tr(m)%advection_xy), h))
   enddo
+contains
+  subroutine mix(acc, v)
+    integer(kind=c_intptr_t), intent(inout) :: acc !< running signature
+    integer(kind=c_intptr_t), intent(in)    :: v   !< value folded in
+    acc = ieor(ishftc(acc, 7), v)
+  end subroutine mix
 end function registry_hash
 
 !> Pointer of an optional diagnostic array, null when unassociated.
@@ -315,7 +325,7 @@ subroutine advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first
   real, dimension(SZI_(G),SZJB_(G),SZK_(GV)), target, &
                  optional, intent(out)   :: vhr_out !< remaining meridional flux [H L2 ~> m3 or kg]
   integer(c_int) :: xf, mi, uv, nit
-  integer(kind=c_long_long) :: h
+  integer(kind=c_intptr_t) :: h
   type(c_ptr) :: p_vol, p_uo, p_vo
   integer :: m
 
@@ -342,7 +352,9 @@ subroutine advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first
   ! the OBC argument (:64): segment tables and tracer reservoirs go to the device on every call (tres evolves)
   call pass_obc(OBC, CS)
 
-  xf = -1 ; if (present(x_first_in)) xf = merge(1, 0, x_first_in)
+  ! the reference re-reads G%first_direction on every call (:126; MOM.F90:1372 toggles it under
+  ! ALTERNATE_FIRST_DIRECTION), so the order is always passed explicitly
+  xf = merge(1, 0, MOD(G%first_direction,2) == 0) ; if (present(x_first_in)) xf = merge(1, 0, x_first_in)
   mi = -1 ; if (present(max_iter_in)) mi = max_iter_in
   uv = -1 ; if (present(update_vol_prev)) uv = merge(1, 0, update_vol_prev)
   p_vol = c_null_ptr ; if (present(vol_prev)) p_vol = c_loc(vol_prev)
@@ -362,8 +374,10 @@ subroutine pass_obc(OBC, CS)
   type(mom6adv_obc), target :: o
   type(mom6adv_obc_segment), allocatable, target :: segs(:)
   type(mom6adv_obc_tracer),  allocatable, target :: trs(:)
-  type(OBC_segment_type), pointer :: segment => NULL()
+  type(OBC_segment_type), pointer :: segment
   integer :: n, m, nt, off
+
+  segment => NULL()
 
   if (.not. associated(OBC)) then
     if (CS%obc_was_set) call check_rc(mom6adv_set_obc(CS%plan, c_null_ptr), CS%plan, "set_obc")
@@ -430,6 +444,10 @@ subroutine tracer_advect_init(Time, G, US, param_file, diag, CS)
   call get_param(param_file, mdl, "DT", CS%dt, fail_if_missing=.true., &
                  desc="The (baroclinic) dynamics time step.", units="s", scale=US%s_to_T)
   call get_param(param_file, mdl, "DEBUG", CS%debug, default=.false.)
+  ! grid connectivity for the device-side group pass (logged by MOM_domains_init already)
+  call get_param(param_file, mdl, "REENTRANT_X", CS%reentrant_x, default=.true., do_not_log=.true.)
+  call get_param(param_file, mdl, "REENTRANT_Y", CS%reentrant_y, default=.false., do_not_log=.true.)
+  call get_param(param_file, mdl, "TRIPOLAR_N", CS%tripolar_N, default=.false., do_not_log=.true.)
   call get_param(param_file, mdl, "TRACER_ADVECTION_SCHEME", mesg, &
                  desc="The horizontal transport scheme for tracers:\n"//&
                       "  PLM    - Piecewise Linear Method\n"//&

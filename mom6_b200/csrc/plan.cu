@@ -405,6 +405,13 @@ extern "C" int mom6adv_comm_init(mom6adv_plan *plan, const char *id128, const in
   if (plan->comm || !plan->peers.empty() || plan->halo[0].n || plan->halo[1].n || plan->halo[2].n)
     return fail(plan, MOM6ADV_ERR_INVALID, "comm_init: called twice");
   CK(cudaSetDevice(plan->device));
+  {
+    // the exchange lists are built for every rank from the layout alone (halo.cu rank_geo): local indexing with the data
+    // domain starting at 1 (config_src/infra/FMS2/MOM_domain_infra.F90:1815-1821) and equal halos on both sides
+    const Geom &g0 = plan->g;
+    if (g0.isd != 1 || g0.jsd != 1 || (g0.isc - g0.isd) != (g0.ied - g0.iec) || (g0.jsc - g0.jsd) != (g0.jed - g0.jec))
+      return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "comm_init: multi-block plans need local indexing (isd = jsd = 1) and symmetric halos");
+  }
   ExchangeSpec x;
   exchange_spec(plan->g, plan->dom, ibeg, iend, jbeg, jend, x);
   x.depth = exch_depth(plan);
@@ -1271,6 +1278,17 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
   const Geom &g = plan->g;
   cudaStream_t s = plan->stream;
   CK(cudaSetDevice(plan->device));
+  if (plan->multi && plan->comm && plan->opt_pull) {
+    // the remap decision is collective: a registry re-bound on some ranks only must not leave the others outside
+    // setup_ipc's collectives (one 4-byte all-reduce per call)
+    if (!plan->bar_dev) { int rc = dev_alloc(plan, &plan->bar_dev, 4); if (rc) return rc; }
+    int need = (plan->tr_dirty || plan->ipc_ntr != plan->ntr) ? 1 : 0;
+    CK(cudaMemcpyAsync(plan->bar_dev + 2, &need, sizeof(int), cudaMemcpyHostToDevice, s));
+    CKN(ncclAllReduce(plan->bar_dev + 2, plan->bar_dev + 2, 1, ncclInt, ncclMax, plan->comm, s));
+    CK(cudaMemcpyAsync(&need, plan->bar_dev + 2, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    if (need && plan->ipc_ntr >= 0) plan->ipc_ntr = -2;
+  }
   { int rc = sync_tracer_table(plan); if (rc) return rc; }
   { int rc = setup_ipc(plan); if (rc) return rc; }
   { int rc = size_peer_buffers(plan); if (rc) return rc; }

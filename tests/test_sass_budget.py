@@ -45,7 +45,7 @@ def test_x_sweep_hot_loop_budget():
 
 @pytest.mark.parametrize("scheme", [0, 1, 2])
 def test_sweeps_do_not_spill_and_producer_is_uniform(scheme):
-    n, f64, other, ops = _counts(_run("k_y_ringILi%dELb0E" % scheme, "--all"))
+    n, f64, other, ops = _counts(_run("k_y_ringILi%dE" % scheme, "--all"))
     assert ops.get("LDL", 0) + ops.get("STL", 0) <= 6, ops          # at most a couple of spilled words outside the march
     assert ops.get("UBLKCP", 0) >= 7                                  # bulk copies issued from uniform registers ...
     assert ops.get("ELECT", 0) <= 2 and ops.get("R2UR", 0) <= 12, ops   # ... not through a per-lane ELECT / R2UR loop
