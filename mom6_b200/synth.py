@@ -451,3 +451,21 @@ def transposed_case(c: "SynthCase", Reg):
     for tr in Reg.Tr[:Reg.ntr]:
         register_tracer(tr2(tr.t), Reg2, name=getattr(tr, "name", "tr"), underflow_conc=tr.conc_underflow)
     return G2, h2, u2, v2, Reg2
+
+
+def make_khdt(c: "SynthCase", strength: float = 0.3, seed: int = 11):
+    """khdt_x (jsd:jed, IsdB:IedB) and khdt_y (JsdB:JedB, isd:ied) as tracer_hordiff's 2-D set-up would leave them
+    (MOM_tracer_hor_diff.F90:273-366): Khtr*dt*(open face width / tracer-point distance), zero at closed faces, with
+    valid halos.  `strength` ~ khdt / areaT: the diffusive CFL 2*(sum of the four khdt)/areaT is about 8*strength, so
+    0.3 asks for three iterations (:368-387)."""
+    G = c.G
+    rng = np.random.default_rng(seed)
+    a = np.asarray(G.areaT)
+    kx = np.zeros(G.shape_u()); ky = np.zeros(G.shape_v())
+    oI = G.pI(G.isd)      # u column of face I = isd (between cells isd and isd+1)
+    n = G.nid - 1
+    kx[:, oI:oI + n] = strength * np.minimum(a[:, :-1], a[:, 1:]) * (0.6 + 0.4 * rng.random((G.njd, n)))
+    oJ = G.pJ(G.jsd)
+    n = G.njd - 1
+    ky[oJ:oJ + n, :] = strength * np.minimum(a[:-1, :], a[1:, :]) * (0.6 + 0.4 * rng.random((n, G.nid)))
+    return np.ascontiguousarray(kx * np.asarray(G.mask2dCu)), np.ascontiguousarray(ky * np.asarray(G.mask2dCv))

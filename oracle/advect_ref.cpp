@@ -1085,3 +1085,73 @@ extern "C" double ora_efp_to_real(const long long limbs[6]) {
   for (int i = 0; i < 6; i++) r = r + pr[i] * (double)limbs[i];
   return r;
 }
+
+// ---------------------------------------------------------------------------
+// tracer_hordiff, the along-layer diffusion iteration:
+// /root/reference/src/tracer/MOM_tracer_hor_diff.F90:539-607 restated.  khdt_x / khdt_y (2-D, :186-366), num_itts
+// (:368-387), h_neglect (:205) and Idt (:204) are the caller's, exactly as the loop finds them in the reference.
+// Pinned against the translated reference lines (oracle/f2c, tests/test_hordiff.py).
+// ---------------------------------------------------------------------------
+extern "C" int ora_tracer_hordiff(const ora_grid *Gp, ora_tracer *Tr, int ntr, const double *h, const double *khdt_x,
+                                  const double *khdt_y, int num_itts, double h_neglect, int Diffuse_ML_interior,
+                                  int nkml, int nk_rho_varies, double ML_KhTr_scale, const ora_domain *dom,
+                                  ora_pass_fn pass, void *ctx) {
+  const ora_grid &G = *Gp;
+  if (!dom && !pass) return 1;
+  const int is = G.isc, ie = G.iec, js = G.jsc, je = G.jec, nz = G.nk;
+  const long nih = G.ied - G.isd + 1, njh = G.jed - G.jsd + 1;
+  const long niu = G.IedB - G.IsdB + 1, njv = G.JedB - G.JsdB + 1;
+  auto H = [&](int i, int j, int k) -> double { return h[(i - G.isd) + nih * ((j - G.jsd) + njh * (long)(k - 1))]; };
+  auto KX = [&](int I, int j) -> double { return khdt_x[(I - G.IsdB) + niu * (long)(j - G.jsd)]; };
+  auto KY = [&](int i, int J) -> double { return khdt_y[(i - G.isd) + nih * (long)(J - G.JsdB)]; };
+  auto IA = [&](int i, int j) -> double { return G.IareaT[(i - G.isd) + nih * (long)(j - G.jsd)]; };
+  // the tracer-only group pass (CS%pass_t, :540): the emulation moves uhr/vhr/hprev too -- give it scratch fields
+  std::vector<double> su((size_t)niu * njh * nz, 0.0), sv((size_t)nih * njv * nz, 0.0), sh((size_t)nih * njh * nz, 0.0);
+  SingleCtx sctx;
+  if (!pass) {
+    sctx.rank.G = G; sctx.rank.ioff = -(G.isc - 1); sctx.rank.joff = -(G.jsc - 1);
+    sctx.rank.Tr = Tr; sctx.dom = dom; sctx.ntr = ntr;
+    pass = single_pass; ctx = &sctx;
+  }
+  std::vector<double> Coef_x((size_t)niu * njh), Coef_y((size_t)nih * njv), Ihdxdy((size_t)nih * njh), dTr((size_t)nih * njh);
+  auto CX = [&](int I, int j) -> double & { return Coef_x[(I - G.IsdB) + niu * (long)(j - G.jsd)]; };
+  auto CY = [&](int i, int J) -> double & { return Coef_y[(i - G.isd) + nih * (long)(J - G.JsdB)]; };
+  const double I_numitts = 1.0 / ((double)num_itts);                                   // :380 / :384 / :386
+  for (int itt = 1; itt <= num_itts; itt++) {                                         // :539
+    pass(ctx, su.data(), sv.data(), sh.data(), Tr, ntr);                              // :540
+    for (int k = 1; k <= nz; k++) {                                                   // :542
+      double scale = I_numitts;                                                       // :543
+      if (Diffuse_ML_interior) {                                                      // :544-550
+        if (k <= nkml) {
+          if (ML_KhTr_scale <= 0.0) continue;
+          scale = I_numitts * ML_KhTr_scale;
+        }
+        if ((k > nkml) && (k <= nk_rho_varies)) continue;
+      }
+      for (int J = js - 1; J <= je; J++) for (int i = is; i <= ie; i++)               // :552-555
+        CY(i, J) = ((scale * KY(i, J)) * 2.0 * (H(i, J, k) * H(i, J + 1, k))) / (H(i, J, k) + H(i, J + 1, k) + h_neglect);
+      for (int j = js; j <= je; j++) {                                                // :557-566
+        for (int I = is - 1; I <= ie; I++)
+          CX(I, j) = ((scale * KX(I, j)) * 2.0 * (H(I, j, k) * H(I + 1, j, k))) / (H(I, j, k) + H(I + 1, j, k) + h_neglect);
+        for (int i = is; i <= ie; i++) Ihdxdy[(i - G.isd) + nih * (long)(j - G.jsd)] = IA(i, j) / (H(i, j, k) + h_neglect);
+      }
+      for (int m = 0; m < ntr; m++) {                                                 // :568-595
+        double *t = Tr[m].t + nih * njh * (long)(k - 1);
+        auto T = [&](int i, int j) -> double & { return t[(i - G.isd) + nih * (long)(j - G.jsd)]; };
+        for (int j = js; j <= je; j++) for (int i = is; i <= ie; i++)
+          dTr[(i - G.isd) + nih * (long)(j - G.jsd)] = Ihdxdy[(i - G.isd) + nih * (long)(j - G.jsd)] *
+              ((CX(i - 1, j) * (T(i - 1, j) - T(i, j)) - CX(i, j) * (T(i, j) - T(i + 1, j))) +
+               (CY(i, j - 1) * (T(i, j - 1) - T(i, j)) - CY(i, j) * (T(i, j) - T(i, j + 1))));
+        // (df_x / df_y / df2d_* diagnostics :576-591: not part of this restatement)
+        for (int j = js; j <= je; j++) for (int i = is; i <= ie; i++) T(i, j) = T(i, j) + dTr[(i - G.isd) + nih * (long)(j - G.jsd)];
+      }
+    }
+    for (int m = 0; m < ntr; m++) if (Tr[m].conc_underflow > 0.0) {                   // :600-605
+      for (int k = 1; k <= nz; k++) for (int j = js; j <= je; j++) for (int i = is; i <= ie; i++) {
+        double &v = Tr[m].t[(i - G.isd) + nih * ((j - G.jsd) + njh * (long)(k - 1))];
+        if (std::fabs(v) < Tr[m].conc_underflow) v = 0.0;
+      }
+    }
+  }
+  return 0;
+}

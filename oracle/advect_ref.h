@@ -151,6 +151,13 @@ int ora_advect_tracer_multi(int nranks, ora_rank *ranks, const ora_domain *dom,
 void ora_group_pass(int nranks, ora_rank *ranks, const ora_domain *dom,
                     double **uhr, double **vhr, double **hprev, int ntr);
 
+/* tracer_hordiff, the along-layer diffusion iteration: MOM_tracer_hor_diff.F90:539-607.
+ * h (isd:ied, jsd:jed, nk); khdt_x (IsdB:IedB, jsd:jed) and khdt_y (isd:ied, JsdB:JedB) as the reference's 2-D set-up
+ * (:186-366) leaves them; num_itts (:368-387); h_neglect = GV%H_subroundoff (:205).  df_* diagnostics are not restated. */
+int ora_tracer_hordiff(const ora_grid *G, ora_tracer *Tr, int ntr, const double *h, const double *khdt_x,
+                       const double *khdt_y, int num_itts, double h_neglect, int Diffuse_ML_interior, int nkml,
+                       int nk_rho_varies, double ML_KhTr_scale, const ora_domain *dom, ora_pass_fn pass, void *ctx);
+
 /* MOM bitcount checksum of a 2-D/3-D array section
  * (src/framework/MOM_checksums.F90:2407-2414 bitcount, :1396-1404 use). */
 long long ora_bitcount_chksum(const double *a, long long n);

@@ -135,15 +135,18 @@ struct hor_index_type { int isd = 0, ied = 0, jsd = 0, jed = 0, isdb = 0, iedb =
 struct mom_domain_type { int dummy = 0; };
 struct ocean_grid_type {
   int isc = 0, iec = 0, jsc = 0, jec = 0, isd = 0, ied = 0, jsd = 0, jed = 0, isdb = 0, iedb = 0, jsdb = 0, jedb = 0, ke = 0;
+  int iscb = 0, iecb = 0, jscb = 0, jecb = 0;
   int first_direction = 0;
   mom_domain_type *domain = nullptr;
   Arr<double, 2> areat, iareat, mask2dt, mask2dcu, mask2dcv;
 };
-struct verticalgrid_type { int ke = 0; double angstrom_h = 0, h_subroundoff = 0; };
+struct verticalgrid_type { int ke = 0; double angstrom_h = 0, h_subroundoff = 0; int nkml = 0, nk_rho_varies = 0; };
 struct unit_scale_type { double s_to_t = 1.0; };
 struct tracer_type {
   Arr<double, 3> t, ad_x, ad_y, advection_xy;
   Arr<double, 2> ad2d_x, ad2d_y;
+  Arr<double, 3> df_x, df_y;          // MOM_tracer_hor_diff.F90:576-591
+  Arr<double, 2> df2d_x, df2d_y;
   double conc_underflow = 0.0;
 };
 struct tracer_registry_type { int ntr = 0; Arr<tracer_type, 1> tr; };
@@ -157,6 +160,12 @@ struct tracer_advect_cs {
   diag_ctrl *diag = nullptr;
   lbool debug = 0, useppm = 0, usehuynh = 0, usehuynhstencilbug = 0;
   group_pass_type pass_uhr_vhr_t_hprev;
+};
+// tracer_hor_diff_CS members the along-layer loop reads (MOM_tracer_hor_diff.F90:539-607)
+struct tracer_hor_diff_cs {
+  lbool diffuse_ml_interior = 0, show_call_tree = 0;
+  double ml_khtr_scale = 0.0;
+  group_pass_type pass_t;
 };
 struct obc_segment_tracer_type { Arr<double, 3> tres; double obc_inflow_conc = 0; int ntr_index = 0; };
 struct segment_tracer_registry_type { int ntseg = 0; Arr<obc_segment_tracer_type, 1> tr; };
@@ -177,6 +186,7 @@ struct ocean_obc_type {
 static const int obc_none = 0, obc_direction_n = 100, obc_direction_s = 200, obc_direction_e = 300, obc_direction_w = 400;
 static const int fatal = 1, warning = 2;
 static int id_clock_advect = 1, id_clock_pass = 2, id_clock_sync = 3;
+#define F2C_HAS_HORDIFF 1
 
 inline void cpu_clock_begin(int) {}
 inline void cpu_clock_end(int) {}

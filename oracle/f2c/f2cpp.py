@@ -583,18 +583,36 @@ def signature(sub: Sub) -> str:
     return "void %s(%s)" % (sub.name, ", ".join(ps))
 
 
+def translate_range(text: str, lo: int, hi: int, arrays, src_name: str) -> str:
+    """Translate the statements whose first line lies in [lo, hi] (a run of balanced blocks inside a subroutine) into a
+    bare C++ statement list: the including wrapper declares every variable the statements use (same names, case-folded).
+    For code that lives in the middle of a subroutine too entangled to translate whole (tracer_hordiff)."""
+    body = [(ln, st) for ln, st in statements(text) if lo <= ln <= hi]
+    sub = Sub("range_%d_%d" % (lo, hi), [], lo)
+    sub.body = body
+    return translate_body(sub, set(arrays), src_name, header=False)
+
+
 def translate_sub(sub: Sub, all_subs, src_name: str) -> str:
     arrays = {n for n, d in sub.decls.items() if d.dims}
+    return translate_body(sub, arrays, src_name, header=True)
+
+
+def translate_body(sub: Sub, arrays, src_name: str, header: bool) -> str:
     em = Emitter(arrays)
-    out = ["// %s:%d  subroutine %s" % (src_name, sub.line, sub.name), signature(sub) + " {"]
+    out = ["// %s:%d  subroutine %s" % (src_name, sub.line, sub.name), signature(sub) + " {"] if header else \
+          ["// %s:%d-%d (statement range)" % (src_name, sub.body[0][0], sub.body[-1][0])]
     ind = 1
 
     def put(s, ln=None):
         out.append("  " * ind + s + ("   // :%d" % ln if ln else ""))
 
+    if not header:
+        sub = Sub(sub.name, [], sub.line) if False else sub
+
     # scalars first (array bounds may use them only after the executable part sets them -- Fortran automatic arrays
     # take their bounds from dummy arguments, which are all set at entry)
-    for name, d in sub.decls.items():
+    for name, d in (sub.decls.items() if header else []):
         if name in sub.args:
             continue
         t = ctype(d.base)
@@ -604,7 +622,7 @@ def translate_sub(sub: Sub, all_subs, src_name: str) -> str:
             put("%s *%s = nullptr;" % (t, cname(name)) if d.attrs.get("pointer") else "%s %s;" % (t, cname(name)))
         else:
             put("%s %s = f_uninit<%s>();" % (t, cname(name), t))
-    for name, d in sub.decls.items():
+    for name, d in (sub.decls.items() if header else []):
         if not d.dims:
             continue
         t = ctype(d.base)
@@ -725,7 +743,8 @@ def translate_sub(sub: Sub, all_subs, src_name: str) -> str:
         stmt(ln, st)
     if ind != 1:
         raise F2CError("%s: unbalanced blocks (indent %d at end)" % (sub.name, ind))
-    out.append("}")
+    if header:
+        out.append("}")
     return "\n".join(out)
 
 
@@ -775,6 +794,11 @@ def main(argv):
         return 2
     path, wanted = argv[1], [a.lower() for a in argv[2:]]
     text = open(path).read()
+    if wanted and wanted[0] == "--range":      # f2cpp.py FILE --range LO HI [array names...]
+        lo, hi = int(wanted[1]), int(wanted[2])
+        print("// GENERATED by oracle/f2c/f2cpp.py from %s lines %d-%d -- do not edit, do not commit." % (path, lo, hi))
+        print(translate_range(text, lo, hi, wanted[3:], path.split("/")[-1]))
+        return 0
     subs = collect_subs(text, set(wanted))
     missing = [w for w in wanted if w not in subs]
     if missing:

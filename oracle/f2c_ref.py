@@ -20,6 +20,7 @@ _SRC = "/root/reference/src/tracer/MOM_tracer_advect.F90"
 _libs = {}
 
 VARIANTS = {"": "libref_f2c.so", "lt": "libref_f2c_lt.so", "mm": "libref_f2c_mm.so", "chk": "libref_f2c_chk.so"}
+_EXTRA = ("libref_f2c_hordiff.so",)
 
 
 def available() -> bool:
@@ -29,7 +30,7 @@ def available() -> bool:
 def build(force: bool = False) -> bool:
     """Translate + compile when the reference source is present; returns whether the libraries exist."""
     ora.build()
-    have = all(os.path.exists(os.path.join(_REF_DIR, v)) for v in VARIANTS.values())
+    have = all(os.path.exists(os.path.join(_REF_DIR, v)) for v in list(VARIANTS.values()) + list(_EXTRA))
     if os.path.exists(_SRC) and (force or not have):
         if force:
             subprocess.run(["make", "-C", os.path.join(_HERE, "f2c"), "clean"], check=True, capture_output=True)
@@ -73,3 +74,26 @@ def advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first_in=Non
     if rc != 0:
         raise RuntimeError("translated reference advect_tracer failed (FATAL): %d" % rc)
     return npass.value
+
+
+_hd = None
+
+
+def tracer_hordiff(h, khdt_x, khdt_y, num_itts, dt, G, GV, Reg, Diffuse_ML_interior=False, nkml=0, nk_rho_varies=0,
+                   ML_KhTr_scale=0.0) -> None:
+    """The translated lines MOM_tracer_hor_diff.F90:539-607 (oracle/f2c/hordiff_wrap.cpp, bounds-checked build)."""
+    global _hd
+    if _hd is None:
+        lib()      # builds everything and loads libref_f2c.so, which the hordiff library links against
+        _hd = C.CDLL(os.path.join(_REF_DIR, "libref_f2c_hordiff.so"))
+        _hd.ref_tracer_hordiff.restype = C.c_int
+        _hd.ref_tracer_hordiff.argtypes = [C.POINTER(ora.ora_grid), C.POINTER(ora.ora_tracer), C.c_int, ora._dp, ora._dp,
+                                           ora._dp, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.c_double,
+                                           C.c_double, C.POINTER(ora.ora_domain), C.c_void_p, C.c_void_p]
+    g, dom = ora.make_grid(G, GV), ora.make_domain(G.Domain)
+    tr = ora.make_tracers(Reg)
+    rc = _hd.ref_tracer_hordiff(C.byref(g), tr, Reg.ntr, ora._p(h), ora._p(khdt_x), ora._p(khdt_y), int(num_itts),
+                                float(GV.H_subroundoff), int(bool(Diffuse_ML_interior)), int(nkml), int(nk_rho_varies),
+                                float(ML_KhTr_scale), float(dt), C.byref(dom), None, None)
+    if rc != 0:
+        raise RuntimeError("translated tracer_hordiff loop failed: %d" % rc)

@@ -97,6 +97,10 @@ def lib():
         _lib.ora_advect_tracer_multi.argtypes = [
             C.c_int, C.POINTER(ora_rank), C.POINTER(ora_domain), C.POINTER(ora_cs),
             C.c_int, C.c_double, C.c_int, C.c_int, C.c_int]
+        _lib.ora_tracer_hordiff.restype = C.c_int
+        _lib.ora_tracer_hordiff.argtypes = [C.POINTER(ora_grid), C.POINTER(ora_tracer), C.c_int, _dp, _dp, _dp, C.c_int,
+                                            C.c_double, C.c_int, C.c_int, C.c_int, C.c_double, C.POINTER(ora_domain),
+                                            C.c_void_p, C.c_void_p]
         _lib.ora_bitcount_chksum.restype = C.c_longlong
         _lib.ora_bitcount_chksum.argtypes = [_dp, C.c_longlong]
         _lib.ora_efp_sum.restype = None
@@ -209,6 +213,36 @@ def advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first_in=Non
     if rc != 0:
         raise RuntimeError("oracle advect_tracer failed: %d" % rc)
     return nit.value
+
+
+def tracer_hordiff(h, khdt_x, khdt_y, num_itts, G, GV, Reg, Diffuse_ML_interior=False, nkml=0, nk_rho_varies=0,
+                   ML_KhTr_scale=0.0) -> None:
+    """The along-layer diffusion iteration of tracer_hordiff (MOM_tracer_hor_diff.F90:539-607) on Reg.Tr[m].t in place;
+    khdt_x / khdt_y / num_itts as the reference's 2-D set-up (:186-387) leaves them."""
+    g, dom = make_grid(G, GV), make_domain(G.Domain)
+    tr = make_tracers(Reg)
+    rc = lib().ora_tracer_hordiff(C.byref(g), tr, Reg.ntr, _p(h), _p(khdt_x), _p(khdt_y), int(num_itts),
+                                  float(GV.H_subroundoff), int(bool(Diffuse_ML_interior)), int(nkml), int(nk_rho_varies),
+                                  float(ML_KhTr_scale), C.byref(dom), None, None)
+    if rc != 0:
+        raise RuntimeError("oracle tracer_hordiff failed: %d" % rc)
+
+
+def hordiff_num_itts(khdt_x, khdt_y, G, check_diffusive_CFL=True, max_diff_CFL=-1.0) -> int:
+    """num_itts as MOM_tracer_hor_diff.F90:368-387 computes it (single PE: max_across_PEs is the identity)."""
+    import math
+    if check_diffusive_CFL:
+        kx, ky, ia = khdt_x, khdt_y, G.IareaT
+        j0, j1, i0, i1 = G.pj(G.jsc), G.pj(G.jec), G.pi(G.isc), G.pi(G.iec)
+        J0, I0 = G.pJ(G.jsc), G.pI(G.isc)
+        nj, ni = j1 - j0 + 1, i1 - i0 + 1
+        cfl = 2.0 * ((kx[j0:j1 + 1, I0 - 1:I0 - 1 + ni] + kx[j0:j1 + 1, I0:I0 + ni]) +
+                     (ky[J0 - 1:J0 - 1 + nj, i0:i1 + 1] + ky[J0:J0 + nj, i0:i1 + 1])) * ia[j0:j1 + 1, i0:i1 + 1]
+        mx = max(0.0, float(cfl.max()))
+        return max(1, math.ceil(mx - 4.0 * np.finfo(np.float64).eps))
+    if max_diff_CFL > 0.0:
+        return max(1, math.ceil(max_diff_CFL - 4.0 * np.finfo(np.float64).eps))
+    return 1
 
 
 def advect_tracer_multi(ranks: Sequence[dict], dom, CS, dt, x_first_in=None, max_iter_in=None,
