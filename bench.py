@@ -353,6 +353,14 @@ def run_native(args):
         except Exception as e:      # never lose the main line over the extra leg
             out["e2e_resident"] = {"error": str(e)[:200]}
 
+    # ---- the widened row beside the path: tracer_hordiff's iteration on the same resident state,
+    # timed the same way (its own warm-ups, the plan's events around the call's kernels); not part of `value` ----------
+    if not args.no_hordiff:
+        try:
+            out["hordiff"] = run_hordiff_leg(plan, c, ni, nj, nk, ntr, peak)
+        except Exception as e:
+            out["hordiff"] = {"error": str(e)[:200]}
+
     # free the resident plan before the e2e / cpu legs
     plan.destroy()
     del plan, c
@@ -373,6 +381,37 @@ def run_native(args):
                                          % (ni, nj, nks, nk, ntr, scheme, sec, threads, cores)}
     print(json.dumps(out))
     return 0
+
+
+def run_hordiff_leg(plan, c, ni, nj, nk, ntr, peak, calls=3, warmup=2):
+    """mom6adv_hordiff (MOM_tracer_hor_diff.F90:539-607) on the resident tracers: ms per call and the roofline of the
+    iteration kernel (algorithmic bytes per iteration = (16*ntr + 24) * cells; the single-iteration call isolates the
+    coefficient kernel and the two 2-D uploads).  scripts/bench_hordiff.py is the stand-alone form with its parity slab."""
+    import numpy as np
+    from mom6_b200 import synth, tracer_hor_diff
+    kx, ky = synth.make_khdt(c, 0.3)
+    nit = tracer_hor_diff.num_itts_from_cfl(kx, ky, c.G)
+    hneg = c.GV.H_subroundoff
+    for _ in range(warmup):
+        plan.hordiff(kx, ky, nit, hneg)
+    l0 = plan.kernel_launches
+    per, one = [], []
+    for _ in range(calls):
+        plan.hordiff(kx, ky, nit, hneg)
+        per.append(plan.last_advect_ms)
+    launches = plan.kernel_launches - l0
+    for _ in range(calls):
+        plan.hordiff(kx, ky, 1, hneg)
+        one.append(plan.last_advect_ms)
+    ms, ms1 = float(np.median(per)), float(np.median(one))
+    it_ms = (ms - ms1) / (nit - 1) if nit > 1 else ms
+    alg = (16.0 * ntr + 24.0) * ni * nj * nk
+    return {"what": "mom6adv_hordiff: the diffusion iteration of tracer_hordiff on the resident tracers",
+            "num_itts": nit, "ms_per_call": ms, "ms_per_iteration": it_ms, "ms_coefficients_and_uploads": ms1 - it_ms,
+            "tracer_cell_updates_per_s": ni * nj * nk * ntr * nit / (ms * 1e-3), "gpu_launches": int(launches),
+            "calls": calls, "warmup": warmup,
+            "roofline": {"bound": "hbm", "kernel": "k_hd_tile", "achieved": alg / (it_ms * 1e-3) / 1e9, "peak": peak,
+                         "unit": "GB/s", "frac": alg / (it_ms * 1e-3) / 1e9 / peak, "alg_bytes_per_launch": alg}}
 
 
 def _stats_ms(per):
@@ -541,6 +580,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--e2e-warmup", type=int, default=2)
     ap.add_argument("--diags", type=int, default=0, help="associate ad_x and ad_y on the first N tracers (diagnostic-path timing)")
+    ap.add_argument("--no-hordiff", action="store_true", help="skip the tracer_hordiff leg (N=1)")
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle comparison of a slab of the workload")
     ap.add_argument("--layout", default=None, help="multi-GPU LAYOUT as IxJ (default: strips in j)")
     ap.add_argument("--no-e2e", action="store_true")

@@ -34,6 +34,7 @@ implicit none ; private
 public advect_tracer
 public tracer_advect_init
 public tracer_advect_end
+public tracer_hordiff_iterate
 
 !> Control structure: the reference's members (:30-40) plus the GPU plan handle.
 type, public :: tracer_advect_CS ; private
@@ -187,6 +188,16 @@ interface
     real(c_double), value :: H_to_m
     integer(c_int) :: rc
   end function mom6adv_column_diag
+
+  !> The diffusion iteration of tracer_hordiff on the resident tracers (replaces MOM_tracer_hor_diff.F90:539-607)
+  function mom6adv_hordiff(plan, h, khdt_x, khdt_y, num_itts, h_neglect, diffuse_ml_interior, nkml, nk_rho_varies, &
+                           ml_khtr_scale, want_df) bind(c, name="mom6adv_hordiff") result(rc)
+    import :: c_int, c_ptr, c_double
+    type(c_ptr), value :: plan, h, khdt_x, khdt_y   !< h = C_NULL_PTR: the resident h_end of the last advect_tracer call
+    integer(c_int), value :: num_itts, diffuse_ml_interior, nkml, nk_rho_varies, want_df
+    real(c_double), value :: h_neglect, ml_khtr_scale
+    integer(c_int) :: rc
+  end function mom6adv_hordiff
 end interface
 
 contains
@@ -475,6 +486,30 @@ subroutine tracer_advect_init(Time, G, US, param_file, diag, CS)
 end subroutine tracer_advect_init
 
 !> Release the GPU plan and the control structure (:1153-1158).
+!> The loop "do itt=1,num_itts ... enddo" of tracer_hordiff (MOM_tracer_hor_diff.F90:539-607) on the tracers the last
+!! advect_tracer call left in HBM: call this from tracer_hordiff in place of that loop, with the routine's own khdt_x,
+!! khdt_y and num_itts.  It lives in this module because the plan handle is private to it.  any_df: one of
+!! df_x/df_y/df2d_x/df2d_y is associated on some tracer (not produced on the device: the call is then refused).
+subroutine tracer_hordiff_iterate(CS, G, GV, khdt_x, khdt_y, num_itts, Diffuse_ML_interior, ML_KhTr_scale, any_df)
+  type(tracer_advect_CS),  pointer    :: CS     !< control structure of MOM_tracer_advect (owns the GPU plan)
+  type(ocean_grid_type),   intent(in) :: G      !< ocean grid structure
+  type(verticalGrid_type), intent(in) :: GV     !< ocean vertical grid structure
+  real, dimension(SZIB_(G),SZJ_(G)), target, intent(in) :: khdt_x !< Khtr*dt*dy/dx at u points [L2 ~> m2]
+  real, dimension(SZI_(G),SZJB_(G)), target, intent(in) :: khdt_y !< Khtr*dt*dx/dy at v points [L2 ~> m2]
+  integer,                 intent(in) :: num_itts            !< iterations (:368-387, after max_across_PEs)
+  logical,                 intent(in) :: Diffuse_ML_interior !< CS%Diffuse_ML_interior of tracer_hor_diff_CS
+  real,                    intent(in) :: ML_KhTr_scale       !< CS%ML_KhTr_scale of tracer_hor_diff_CS
+  logical,                 intent(in) :: any_df              !< a diffusive-flux diagnostic is wanted
+  integer(c_int) :: rc
+  if (.not.associated(CS)) call MOM_error(FATAL, "tracer_hordiff_iterate: tracer_advect_init has not been called")
+  if (.not.c_associated(CS%plan)) call MOM_error(FATAL, "tracer_hordiff_iterate: no advect_tracer call has made the plan yet")
+  rc = mom6adv_hordiff(CS%plan, c_null_ptr, c_loc(khdt_x), c_loc(khdt_y), int(num_itts, c_int), &
+                       real(GV%H_subroundoff, c_double), merge(1_c_int, 0_c_int, Diffuse_ML_interior), &
+                       int(GV%nkml, c_int), int(GV%nk_rho_varies, c_int), real(ML_KhTr_scale, c_double), &
+                       merge(1_c_int, 0_c_int, any_df))
+  call check_rc(rc, CS%plan, "tracer_hordiff_iterate")
+end subroutine tracer_hordiff_iterate
+
 subroutine tracer_advect_end(CS)
   type(tracer_advect_CS), pointer :: CS !< module control structure
   integer(c_int) :: rc

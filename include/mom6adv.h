@@ -189,6 +189,23 @@ int mom6adv_sync(mom6adv_plan *plan);
  * associated, h_diag ignored), ZINT (:796-802), ZINT_100M (:745-766,805-811); out2d is an (isd:ied, jsd:jed) array,
  * zero outside the computational domain like the reference's work2d. */
 int mom6adv_accumulate_transports(mom6adv_plan *plan, const double *uh, const double *vh, double dt);
+/* mom6adv_hordiff replaces the iteration loop of tracer_hordiff, the call that follows advect_tracer in step_tracer
+ * (src/core/MOM.F90:1441):
+ *   do itt=1,num_itts ; do_group_pass(CS%pass_t) ; Coef_x/Coef_y/Ihdxdy ; dTr ; t = t + dTr ; conc_underflow ; enddo
+ * (src/tracer/MOM_tracer_hor_diff.F90:539-607) on the plan's RESIDENT tracers (all bound tracers, as Reg%Tr(1:ntr)).
+ *   h          layer thickness (isd:ied, jsd:jed, nk), host or device; NULL = the resident H_END field (step_tracer
+ *              passes the same h to advect_tracer's h_end and to tracer_hordiff)
+ *   khdt_x     (IsdB:IedB, jsd:jed) and khdt_y (isd:ied, JsdB:JedB): Khtr * dt * (face width / distance) as the
+ *              reference's 2-D set-up leaves them (:186-366), host or device, valid on faces is-1..ie / js-1..je
+ *   num_itts   :368-387 (the reference's max_across_PEs stays with the caller); I_numitts = 1/num_itts
+ *   h_neglect  GV%H_subroundoff (:151)
+ *   Diffuse_ML_interior, nkml, nk_rho_varies, ML_KhTr_scale   the level rule of :543-550
+ * The df_x / df_y / df2d_x / df2d_y diagnostics (:576-591) are not produced: the call fails with
+ * MOM6ADV_ERR_UNSUPPORTED rather than skip them silently if want_df is non-zero.  Epipycnal diffusion (:609-) and the
+ * khdt set-up stay with the caller. */
+int mom6adv_hordiff(mom6adv_plan *plan, const double *h, const double *khdt_x, const double *khdt_y, int num_itts,
+                    double h_neglect, int Diffuse_ML_interior, int nkml, int nk_rho_varies, double ML_KhTr_scale,
+                    int want_df);
 int mom6adv_zero_transports(mom6adv_plan *plan);
 enum { MOM6ADV_CD_ADV_XY_2D = 0, MOM6ADV_CD_ZINT = 1, MOM6ADV_CD_ZINT_100M = 2 };
 int mom6adv_column_diag(mom6adv_plan *plan, int m, int kind, const double *h_diag, double H_to_m, double *out2d);

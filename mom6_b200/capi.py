@@ -108,6 +108,7 @@ SYMBOLS = {
     "mom6adv_exchange_list": (C.c_int, [C.POINTER(mom6adv_grid), C.POINTER(mom6adv_domain), C.POINTER(C.c_int),
                                         C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int, C.c_int,
                                         C.c_int, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_int)]),
+    "mom6adv_hordiff": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int]),
     "mom6adv_set_obc": (C.c_int, [_P, C.POINTER(mom6adv_obc)]),
     "mom6adv_set_ntr": (C.c_int, [_P, C.c_int]),
     "mom6adv_bind_tracer": (C.c_int, [_P, C.c_int, _P, C.c_double, _P, _P, _P, _P, _P]),
@@ -328,6 +329,15 @@ class Plan:
         """uhtr += uh*dt ; vhtr += vh*dt on the resident fields (MOM_dynamics_split_RK2.F90:1045-1052)."""
         _order_after_torch(uh, vh)
         self._ck(self._l.mom6adv_accumulate_transports(self._h, ptr(uh), ptr(vh), float(dt)))
+
+    def hordiff(self, khdt_x, khdt_y, num_itts, h_neglect, h=None, Diffuse_ML_interior=False, nkml=0, nk_rho_varies=0,
+                ML_KhTr_scale=0.0, want_df=False):
+        """The diffusion iteration of tracer_hordiff (MOM_tracer_hor_diff.F90:539-607) on the resident tracers; h=None
+        uses the resident H_END field (MOM.F90:1441 passes advect_tracer's h_end)."""
+        _order_after_torch(khdt_x, khdt_y, h)
+        self._ck(self._l.mom6adv_hordiff(self._h, ptr(h) if h is not None else None, ptr(khdt_x), ptr(khdt_y),
+                                         int(num_itts), float(h_neglect), int(bool(Diffuse_ML_interior)), int(nkml),
+                                         int(nk_rho_varies), float(ML_KhTr_scale), int(bool(want_df))))
 
     def zero_transports(self):
         """CS%uhtr(:,:,:) = 0.0 ; CS%vhtr(:,:,:) = 0.0 (MOM.F90:1465-1466)."""

@@ -46,6 +46,12 @@ struct DiagTable {
   double *axy[MOM6ADV_MAXT];
 };
 
+// tracer_hordiff's per-call scalars (MOM_tracer_hor_diff.F90:380-386, :543-550)
+struct HdParams {
+  double I_numitts, ml_scale, h_neglect;
+  int diffuse_ml, nkml, nk_rho_varies;
+};
+
 // ---- gfortran intrinsic semantics (argument-order compare-select) -----------
 __device__ __forceinline__ double gmax2(double a, double b) { return (b > a) ? b : a; }
 __device__ __forceinline__ double gmin2(double a, double b) { return (b < a) ? b : a; }

@@ -114,3 +114,9 @@ inline bool halo_point_used(int pos, int i, int j, int isc, int iec, int jsc, in
   return j >= jlo && j <= jec + depth;
 }
 void build_halo_exchange(const Geom &g, const ExchangeSpec &x, int me, HaloBuild local[3], std::vector<PeerBuild> &peers);
+
+// hordiff.cu: the diffusion iteration of tracer_hordiff (MOM_tracer_hor_diff.F90:539-607)
+void launch_hd_coef(cudaStream_t s, const Geom &g, const HdParams &p, const double *h, const double *khdt_x,
+                    const double *khdt_y, const double *IareaT, double *cx, double *cy, double *ihd);
+void launch_hd_apply(cudaStream_t s, const Geom &g, const HdParams &p, const TrTable &tt, const double *cx,
+                     const double *cy, const double *ihd);

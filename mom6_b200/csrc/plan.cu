@@ -78,6 +78,7 @@ struct mom6adv_plan {
   int *domore_u = nullptr, *domore_v = nullptr, *entry_u = nullptr, *entry_v = nullptr, *domore_k = nullptr;
   int *sum_dev = nullptr, *sum_host = nullptr, *sum_host_dev = nullptr;   // sum_host: mapped pinned; sum_host_dev: its device alias
   double *staging = nullptr;
+  double *khdt_x = nullptr, *khdt_y = nullptr;      // mom6adv_hordiff: 2-D diffusivity-times-dt fields (allocated on first use)
   double *stage_in = nullptr;        // MIRROR pipeline: ring of contiguous upload slots (slots x chunk x Fortran-layout tracer)
   long long stage_in_elems = 0;
   long long staging_elems = 0;
@@ -607,6 +608,8 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   }
   if (plan->comm) ncclCommDestroy(plan->comm);
   if (plan->sp_list) cudaFree(plan->sp_list);
+  if (plan->khdt_x) cudaFree(plan->khdt_x);
+  if (plan->khdt_y) cudaFree(plan->khdt_y);
   if (plan->dirty) cudaFree(plan->dirty);
   for (auto &s : plan->tr) free_slot(s);
   if (plan->tr_dev) cudaFree(plan->tr_dev);
@@ -920,7 +923,7 @@ static int setup_ipc(mom6adv_plan *plan) {
   return 0;
 }
 
-static int group_pass(mom6adv_plan *plan, bool first_of_call, bool defer_tracers) {
+static int group_pass(mom6adv_plan *plan, bool first_of_call, bool defer_tracers, bool tracers_only = false) {
   const Geom &g = plan->g;
   cudaStream_t s = plan->stream;
   ProfScope ps(plan, MOM6ADV_KC_HALO);
@@ -929,7 +932,9 @@ static int group_pass(mom6adv_plan *plan, bool first_of_call, bool defer_tracers
   double **tab = plan->halo_fields_dev + plan->cur * (3 + plan->ntr);
   // field-table segments by stagger: h = hprev + the active tracers, u = uhr, v = vhr
   struct Seg { double **t; int n; };
-  const Seg segs[3][2] = {{{tab + 2, 1}, {tab + 3 + plan->m_lo, nact}}, {{tab + 0, 1}, {nullptr, 0}}, {{tab + 1, 1}, {nullptr, 0}}};
+  // tracers_only: CS%pass_t of tracer_hordiff (MOM_tracer_hor_diff.F90:540) -- no hprev / uhr / vhr
+  const int nm = tracers_only ? 0 : 1;
+  const Seg segs[3][2] = {{{tab + 2, nm}, {tab + 3 + plan->m_lo, nact}}, {{tab + 0, nm}, {nullptr, 0}}, {{tab + 1, nm}, {nullptr, 0}}};
   // (1) halo points whose source lies in this rank's own block (cyclic wrap / fold onto itself)
   for (int pos = 0; pos < 3; pos++) for (const Seg &sg : segs[pos]) if (sg.n > 0) {
     launch_halo_apply(s, g.plane, g.nk, plan->halo[pos].dst, plan->halo[pos].src, plan->halo[pos].sgn, plan->halo[pos].n, sg.t, sg.n);
@@ -949,7 +954,7 @@ static int group_pass(mom6adv_plan *plan, bool first_of_call, bool defer_tracers
       auto pull = [&](cudaStream_t st, int q) {
         for (PeerLists &p : plan->peers) {
           double **ptab = p.fields_dev + plan->cur * (3 + plan->ntr);
-          const Seg psegs[3][2] = {{{ptab + 2, 1}, {ptab + 3 + plan->m_lo, nact}}, {{ptab + 0, 1}, {nullptr, 0}}, {{ptab + 1, 1}, {nullptr, 0}}};
+          const Seg psegs[3][2] = {{{ptab + 2, nm}, {ptab + 3 + plan->m_lo, nact}}, {{ptab + 0, nm}, {nullptr, 0}}, {{ptab + 1, nm}, {nullptr, 0}}};
           // the tracers' pull skips tiles the owner has not touched since the last pass (after a list-driven trip:
           // nearly all of the strip); the first pass of a call and the mass fields (3 of 55) are pulled whole
           const unsigned char *pd = nullptr;
@@ -979,7 +984,7 @@ static int group_pass(mom6adv_plan *plan, bool first_of_call, bool defer_tracers
         }
       };
       for (PeerLists &p : plan->peers)
-        plan->halo_bytes_sent += 8LL * g.nk * ((long long)(1 + nact) * p.n_recv[0] + p.n_recv[1] + p.n_recv[2]);
+        plan->halo_bytes_sent += 8LL * g.nk * ((long long)(nm + nact) * p.n_recv[0] + nm * (p.n_recv[1] + p.n_recv[2]));
       { ProfScope pw(plan, MOM6ADV_KC_EXCH_WIRE);
         pull(s, 0);
         if (!defer_tracers) pull(s, 1);
@@ -1021,8 +1026,8 @@ static int group_pass(mom6adv_plan *plan, bool first_of_call, bool defer_tracers
     { ProfScope pw(plan, MOM6ADV_KC_EXCH_WIRE);
     CKN(ncclGroupStart());
     for (PeerLists &p : plan->peers) {
-      const long long ns = (long long)g.nk * ((long long)(1 + nact) * p.n_send[0] + p.n_send[1] + p.n_send[2]);
-      const long long nr = (long long)g.nk * ((long long)(1 + nact) * p.n_recv[0] + p.n_recv[1] + p.n_recv[2]);
+      const long long ns = (long long)g.nk * ((long long)(nm + nact) * p.n_send[0] + nm * (p.n_send[1] + p.n_send[2]));
+      const long long nr = (long long)g.nk * ((long long)(nm + nact) * p.n_recv[0] + nm * (p.n_recv[1] + p.n_recv[2]));
       if (ns) CKN(ncclSend(p.sendbuf, (size_t)ns, ncclDouble, p.rank, plan->comm, s));
       if (nr) CKN(ncclRecv(p.recvbuf, (size_t)nr, ncclDouble, p.rank, plan->comm, s));
       plan->halo_bytes_sent += 8 * ns;
@@ -1265,19 +1270,10 @@ static int sweep_impl(mom6adv_plan *plan, int dir, Range rg, double Idt, int sch
 // advect_tracer :112-320 on the resident fields.
 // The tracers [m_lo, m_hi) are advected; the tracer-independent part (uhr, vhr, hprev, flags) is the same
 // whatever the range, which is what lets MIRROR mode pipeline chunks of tracers against the PCIe copies.
-static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_iter_in, bool use_vol_prev,
-                      bool update_vol_prev, int *n_iter_out, int m_lo, int m_hi) {
-  if (n_iter_out) *n_iter_out = 0;
-  if (plan->ntr == 0) return MOM6ADV_OK;                                   // :124
-  if (m_lo < 0 || m_hi > plan->ntr || m_lo >= m_hi) return fail(plan, MOM6ADV_ERR_INVALID, "advect: bad tracer range");
-  for (int m = m_lo; m < m_hi; m++) {
-    if (!plan->tr[m].buf[0]) return fail(plan, MOM6ADV_ERR_NOT_INIT, "advect: tracer storage missing");
-    if (plan->tr[m].cur != plan->tr[m_lo].cur) return fail(plan, MOM6ADV_ERR_INVALID, "advect: tracer buffers out of step");
-  }
-  plan->m_lo = m_lo; plan->m_hi = m_hi; plan->cur = plan->tr[m_lo].cur;
-  const Geom &g = plan->g;
+// Device tracer table, neighbour mappings and message buffers for the registry as it stands (start of every call
+// that makes group passes).
+static int prepare_exchange(mom6adv_plan *plan) {
   cudaStream_t s = plan->stream;
-  CK(cudaSetDevice(plan->device));
   if (plan->multi && plan->comm && plan->opt_pull) {
     // the remap decision is collective: a registry re-bound on some ranks only must not leave the others outside
     // setup_ipc's collectives (one 4-byte all-reduce per call)
@@ -1292,6 +1288,23 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
   { int rc = sync_tracer_table(plan); if (rc) return rc; }
   { int rc = setup_ipc(plan); if (rc) return rc; }
   { int rc = size_peer_buffers(plan); if (rc) return rc; }
+  return 0;
+}
+
+static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_iter_in, bool use_vol_prev,
+                      bool update_vol_prev, int *n_iter_out, int m_lo, int m_hi) {
+  if (n_iter_out) *n_iter_out = 0;
+  if (plan->ntr == 0) return MOM6ADV_OK;                                   // :124
+  if (m_lo < 0 || m_hi > plan->ntr || m_lo >= m_hi) return fail(plan, MOM6ADV_ERR_INVALID, "advect: bad tracer range");
+  for (int m = m_lo; m < m_hi; m++) {
+    if (!plan->tr[m].buf[0]) return fail(plan, MOM6ADV_ERR_NOT_INIT, "advect: tracer storage missing");
+    if (plan->tr[m].cur != plan->tr[m_lo].cur) return fail(plan, MOM6ADV_ERR_INVALID, "advect: tracer buffers out of step");
+  }
+  plan->m_lo = m_lo; plan->m_hi = m_hi; plan->cur = plan->tr[m_lo].cur;
+  const Geom &g = plan->g;
+  cudaStream_t s = plan->stream;
+  CK(cudaSetDevice(plan->device));
+  { int rc = prepare_exchange(plan); if (rc) return rc; }
   const int is = g.isc, ie = g.iec, js = g.jsc, je = g.jec;
   int stencil = 2;                                                          // :118
   const bool use_PPM_stencil = plan->cfg.usePPM && !plan->cfg.useHuynhStencilBug;   // :129
@@ -1545,6 +1558,73 @@ extern "C" int mom6adv_column_diag(mom6adv_plan *plan, int m, int kind, const do
   int rc = download(plan, out2d, out, g.isd, g.jsd, 1);
   if (rc) return rc;
   CK(cudaStreamSynchronize(plan->stream));
+  return MOM6ADV_OK;
+}
+
+// ---------------------------------------------------------------------------
+// tracer_hordiff's diffusion iteration (MOM_tracer_hor_diff.F90:539-607) on the resident tracers; kernels in hordiff.cu.
+// Scratch: Coef_x -> hh, Coef_y -> cfl, Ihdxdy -> hlst (advect_tracer's per-sweep work fields, free between calls).
+// ---------------------------------------------------------------------------
+extern "C" int mom6adv_hordiff(mom6adv_plan *plan, const double *h, const double *khdt_x, const double *khdt_y,
+                               int num_itts, double h_neglect, int Diffuse_ML_interior, int nkml, int nk_rho_varies,
+                               double ML_KhTr_scale, int want_df) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "hordiff: plan not initialised");
+  if (want_df) return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "hordiff: the df_x / df_y / df2d_x / df2d_y diagnostics are not implemented");
+  if (!khdt_x || !khdt_y) return fail(plan, MOM6ADV_ERR_INVALID, "hordiff: NULL khdt_x / khdt_y");
+  if (num_itts < 1) return fail(plan, MOM6ADV_ERR_INVALID, "hordiff: num_itts must be >= 1");
+  if (plan->ntr == 0) return MOM6ADV_OK;
+  const Geom &g = plan->g;
+  for (int m = 0; m < plan->ntr; m++) {
+    if (!plan->tr[m].buf[0]) return fail(plan, MOM6ADV_ERR_NOT_INIT, "hordiff: tracer storage missing");
+    if (plan->tr[m].cur != plan->tr[0].cur) return fail(plan, MOM6ADV_ERR_INVALID, "hordiff: tracer buffers out of step");
+  }
+  if (std::min(std::min(g.isc - g.isd, g.ied - g.iec), std::min(g.jsc - g.jsd, g.jed - g.jec)) < 1)
+    return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "hordiff: needs a halo of at least one point");
+  CK(cudaSetDevice(plan->device));
+  cudaStream_t s = plan->stream;
+  plan->m_lo = 0; plan->m_hi = plan->ntr; plan->cur = plan->tr[0].cur;
+  { int rc = prepare_exchange(plan); if (rc) return rc; }
+  if (!plan->khdt_x) {
+    int rc = dev_alloc(plan, &plan->khdt_x, g.plane); if (rc) return rc;
+    rc = dev_alloc(plan, &plan->khdt_y, g.plane); if (rc) return rc;
+  }
+  int rc;
+  if (h) { if ((rc = upload(plan, plan->h_end, h, g.isd, g.jsd, g.nk))) return rc; CK(cudaStreamSynchronize(s)); }
+  if ((rc = upload(plan, plan->khdt_x, khdt_x, g.IsdB, g.jsd, 1))) return rc;
+  CK(cudaStreamSynchronize(s));              // the staging buffer is reused by the next upload
+  if ((rc = upload(plan, plan->khdt_y, khdt_y, g.isd, g.JsdB, 1))) return rc;
+
+  HdParams hp;
+  hp.I_numitts = 1.0 / ((double)num_itts);                                  // :380 / :384 / :386
+  hp.ml_scale = ML_KhTr_scale; hp.h_neglect = h_neglect;
+  hp.diffuse_ml = Diffuse_ML_interior ? 1 : 0; hp.nkml = nkml; hp.nk_rho_varies = nk_rho_varies;
+  CK(cudaEventRecord(plan->ev0, s));
+  launch_hd_coef(s, g, hp, plan->h_end, plan->khdt_x, plan->khdt_y, plan->IareaT, plan->hh, plan->cfl, plan->hlst);   // :552-566
+  plan->launches++;
+  for (int itt = 1; itt <= num_itts; itt++) {                               // :539
+    // every rank's previous iteration must be complete before its rows are read: the opening fence each time
+    { int rc2 = group_pass(plan, true, false, true); if (rc2) return rc2; } // :540
+    const int src = plan->cur;
+    for (int m0 = 0; m0 < plan->ntr; m0 += MOM6ADV_MAXT) {
+      TrTable tt;
+      tt.n = std::min(MOM6ADV_MAXT, plan->ntr - m0);
+      for (int q = 0; q < tt.n; q++) {
+        const TracerSlot &ts = plan->tr[m0 + q];
+        tt.src[q] = ts.buf[src]; tt.dst[q] = ts.buf[1 - src]; tt.cu[q] = ts.conc_underflow;
+      }
+      launch_hd_apply(s, g, hp, tt, plan->hh, plan->cfl, plan->hlst);       // :568-605
+      plan->launches++;
+    }
+    CK(cudaGetLastError());
+    plan->cur = 1 - src;
+    for (int m = 0; m < plan->ntr; m++) plan->tr[m].cur = plan->cur;
+  }
+  if (plan->dirty) CK(cudaMemsetAsync(plan->dirty + (g.plane >> 5) * g.nk, 1, 1, s));   // every tracer cell may have changed
+  CK(cudaEventRecord(plan->ev1, s));
+  CK(cudaStreamSynchronize(s));
+  float ms = 0.f;
+  CK(cudaEventElapsedTime(&ms, plan->ev0, plan->ev1));
+  plan->last_ms = ms;
   return MOM6ADV_OK;
 }
 

@@ -228,23 +228,6 @@ def tracer_hordiff(h, khdt_x, khdt_y, num_itts, G, GV, Reg, Diffuse_ML_interior=
         raise RuntimeError("oracle tracer_hordiff failed: %d" % rc)
 
 
-def hordiff_num_itts(khdt_x, khdt_y, G, check_diffusive_CFL=True, max_diff_CFL=-1.0) -> int:
-    """num_itts as MOM_tracer_hor_diff.F90:368-387 computes it (single PE: max_across_PEs is the identity)."""
-    import math
-    if check_diffusive_CFL:
-        kx, ky, ia = khdt_x, khdt_y, G.IareaT
-        j0, j1, i0, i1 = G.pj(G.jsc), G.pj(G.jec), G.pi(G.isc), G.pi(G.iec)
-        J0, I0 = G.pJ(G.jsc), G.pI(G.isc)
-        nj, ni = j1 - j0 + 1, i1 - i0 + 1
-        cfl = 2.0 * ((kx[j0:j1 + 1, I0 - 1:I0 - 1 + ni] + kx[j0:j1 + 1, I0:I0 + ni]) +
-                     (ky[J0 - 1:J0 - 1 + nj, i0:i1 + 1] + ky[J0:J0 + nj, i0:i1 + 1])) * ia[j0:j1 + 1, i0:i1 + 1]
-        mx = max(0.0, float(cfl.max()))
-        return max(1, math.ceil(mx - 4.0 * np.finfo(np.float64).eps))
-    if max_diff_CFL > 0.0:
-        return max(1, math.ceil(max_diff_CFL - 4.0 * np.finfo(np.float64).eps))
-    return 1
-
-
 def advect_tracer_multi(ranks: Sequence[dict], dom, CS, dt, x_first_in=None, max_iter_in=None,
                         update_vol_prev=None) -> List[int]:
     """Emulated multi-PE run.  Each entry of ``ranks`` is a dict with keys

@@ -7,7 +7,7 @@ properties diffusion must have.  GPU (marked): the CUDA entry point mom6adv_hord
 import numpy as np
 import pytest
 
-from mom6_b200 import synth
+from mom6_b200 import synth, tracer_hor_diff
 from oracle import f2c_ref, oracle
 
 eq = lambda a, b: np.array_equal(np.ascontiguousarray(a).view(np.uint64), np.ascontiguousarray(b).view(np.uint64))
@@ -16,7 +16,7 @@ eq = lambda a, b: np.array_equal(np.ascontiguousarray(a).view(np.uint64), np.asc
 def _case(ni=37, nj=29, nk=4, ntr=4, strength=0.3, **kw):
     c = synth.make_case(ni, nj, nk, ntr, cfl=0.4, **kw)
     kx, ky = synth.make_khdt(c, strength)
-    nit = oracle.hordiff_num_itts(kx, ky, c.G)
+    nit = tracer_hor_diff.num_itts_from_cfl(kx, ky, c.G)
     return c, kx, ky, nit
 
 
@@ -53,3 +53,119 @@ def test_diffusion_properties():
         assert b[:, ocean].max() <= a[:, ocean].max() + 1e-12 and b[:, ocean].min() >= a[:, ocean].min() - 1e-12
         s0, s1 = oracle.efp_sum(a * vol)[1], oracle.efp_sum(b * vol)[1]
         assert abs(s1 - s0) <= 1e-11 * abs(s0)
+
+
+# ---- the CUDA entry point (through the C ABI) against the oracle -------------------------------------------------
+def _gpu_plan(c, scheme="PPM"):
+    from mom6_b200 import capi
+    from mom6_b200.tracer_advect import tracer_advect_init
+    CS = tracer_advect_init(None, c.G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}, None, None)
+    p = capi.Plan(c.G, c.GV, CS)
+    p.set_ntr(c.ntr)
+    R0 = synth.bind_registry(c)
+    for m in range(c.ntr):
+        p.upload_tracer(m, R0.Tr[m].t)
+        p.bind_tracer(m, None, c.conc_underflow(m))
+    return p, CS
+
+
+def _download(p, c):
+    outs = []
+    for m in range(c.ntr):
+        o = np.zeros(c.G.shape_h(c.GV.ke))
+        p.download_tracer(m, o)
+        outs.append(o)
+    return outs
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kw", [dict(), dict(cyclic_x=False), dict(symmetric=False), dict(cyclic_y=True), dict(tripolar_n=True)])
+@pytest.mark.parametrize("ml", [None, (2, 3, 0.5), (2, 3, 0.0)])
+def test_cuda_hordiff_bitwise(kw, ml):
+    c, kx, ky, nit = _case(ni=70, nj=29, nk=4, ntr=7, **kw)       # 7 tracers: one group of four and three singles
+    Ro = synth.bind_registry(c)
+    h = c.h_end.numpy()
+    args = dict(Diffuse_ML_interior=ml is not None, nkml=ml[0] if ml else 0, nk_rho_varies=ml[1] if ml else 0,
+                ML_KhTr_scale=ml[2] if ml else 0.0)
+    oracle.tracer_hordiff(h, kx, ky, nit, c.G, c.GV, Ro, **args)
+    p, _ = _gpu_plan(c)
+    p.hordiff(kx, ky, nit, c.GV.H_subroundoff, h=h, **args)
+    for m, o in enumerate(_download(p, c)):
+        # whole arrays, halos as the last pass left them -- less the outermost halo ROW on either side: the plan's pass
+        # moves the nsten_halo*stencil rows advect_tracer can read (3 of 4 here), the reference's all of them
+        assert eq(o[:, 1:-1, :], Ro.Tr[m].t[:, 1:-1, :]), "tracer %d" % m
+    p.destroy()
+
+
+@pytest.mark.gpu
+def test_cuda_hordiff_underflow_many_tracers_device_inputs():
+    """More tracers than one kernel table holds (64), conc_underflow active, khdt handed over as device tensors."""
+    import torch
+    c, kx, ky, nit = _case(ni=33, nj=17, nk=2, ntr=70)
+    Ro = synth.bind_registry(c)
+    cu = [c.conc_underflow(m) for m in range(c.ntr)]
+    assert any(v > 0.0 for v in cu)
+    h = c.h_end.numpy()
+    # push part of each tracer under its threshold so that :600-605 acts
+    for m in range(c.ntr):
+        if cu[m] > 0.0:      # the whole field around the threshold: part of it ends below, part above
+            a = np.abs(c.G.interior(Ro.Tr[m].t))
+            Ro.Tr[m].t *= cu[m] / np.median(a[a > 0.0])
+    start = [tr.t.copy() for tr in Ro.Tr]
+    oracle.tracer_hordiff(h, kx, ky, nit, c.G, c.GV, Ro)
+    for m in range(c.ntr):
+        if cu[m] > 0.0:
+            z = (c.G.interior(Ro.Tr[m].t) == 0.0) & (c.G.interior(start[m]) != 0.0)
+            assert z.any() and not z.all()
+    p, _ = _gpu_plan(c)
+    for m in range(c.ntr):
+        p.upload_tracer(m, start[m])
+    p.upload_field(__import__("mom6_b200.capi", fromlist=["x"]).F_H_END, h)
+    p.hordiff(torch.from_numpy(kx).cuda(), torch.from_numpy(ky).cuda(), nit, c.GV.H_subroundoff)      # h=None: resident H_END
+    for m, o in enumerate(_download(p, c)):
+        assert eq(o[:, 1:-1, :], Ro.Tr[m].t[:, 1:-1, :]), "tracer %d" % m
+    p.destroy()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("scheme", ["PPM", "PLM"])
+def test_step_tracer_sequence_bitwise(scheme):
+    """advect_tracer then tracer_hordiff, twice, all resident (MOM.F90:1437-1441)."""
+    from mom6_b200 import capi
+    from mom6_b200.tracer_advect import tracer_advect_init
+    c, kx, ky, nit = _case(ni=60, nj=44, nk=3, ntr=5)
+    h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
+    CSo = tracer_advect_init(None, c.G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}, None, None)
+    Ro = synth.bind_registry(c)
+    p, CS = _gpu_plan(c, scheme)
+    CS._plan = p
+    p.upload_field(capi.F_H_END, h); p.upload_field(capi.F_UHTR, u); p.upload_field(capi.F_VHTR, v)
+    for _ in range(2):
+        oracle.advect_tracer(h, u, v, None, c.dt, c.G, c.GV, None, CSo, Ro)
+        oracle.tracer_hordiff(h, kx, ky, nit, c.G, c.GV, Ro)
+        p.advect_resident(c.dt)
+        tracer_hor_diff.tracer_hordiff_iterate(CS, c.G, c.GV, kx, ky, nit)      # the host mirror of the Fortran wrapper
+    for m, o in enumerate(_download(p, c)):
+        assert eq(c.G.interior(o), c.G.interior(Ro.Tr[m].t)), "tracer %d" % m
+    CS._plan = None
+    p.destroy()
+
+
+@pytest.mark.gpu
+def test_cuda_hordiff_rejects_what_it_does_not_do():
+    from mom6_b200 import capi
+    c, kx, ky, nit = _case(ni=20, nj=12, nk=2, ntr=2)
+    p, _ = _gpu_plan(c)
+    with pytest.raises(capi.Mom6AdvError):
+        p.hordiff(kx, ky, nit, c.GV.H_subroundoff, want_df=True)
+    with pytest.raises(capi.Mom6AdvError):
+        p.hordiff(kx, ky, 0, c.GV.H_subroundoff)
+    p.destroy()
+
+
+def test_host_mirror_fails_loudly_without_a_plan():
+    from mom6_b200.tracer_advect import tracer_advect_init
+    c, kx, ky, nit = _case(ni=12, nj=10, nk=2, ntr=1)
+    CS = tracer_advect_init(None, c.G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": "PLM"}, None, None)
+    with pytest.raises(RuntimeError):
+        tracer_hor_diff.tracer_hordiff_iterate(CS, c.G, c.GV, kx, ky, nit)
