@@ -25,6 +25,7 @@
 #include <cstring>
 #include <thread>
 #include <vector>
+#include <limits>
 #include <mutex>
 #include <condition_variable>
 #ifdef _OPENMP
@@ -1153,5 +1154,141 @@ extern "C" int ora_tracer_hordiff(const ora_grid *Gp, ora_tracer *Tr, int ntr, c
       }
     }
   }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// The iteration loop of offline_advection_ale:
+// /root/reference/src/tracer/MOM_offline_main.F90:254-312 (set-up), :320-411 (loop), :414-415 (epilogue), with
+// remaining_transport_sum (:615-650) and reproducing_sum_2d (src/framework/MOM_coms.F90:119-213,219-318) restated.
+// The ALE step inside the loop (:346-380, other modules) is NOT restated: the call is refused unless
+// MODULO(iter, off_ale_mod) /= 0 for every iteration it can run.  The debug/print branches (:327-332, :392-395) only
+// write messages.  pass_var / pass_vector are the oracle's group-pass emulation on (h_new) and (uhtr_sub, vhtr_sub).
+// ---------------------------------------------------------------------------
+namespace {
+// reproducing_sum_2d of a non-NaN array section, MOM_coms.F90:119-213 (overflow_check default .true.) + :285
+double repro_sum_2d(const double *a, long nrow_stride, int i0, int i1, int j0, int j1) {
+  const double r_prec = 70368744177664.0;            // 2.0**46, :28
+  const long long prec = 1LL << 46;                  // :27
+  const double I_prec = 1.0 / r_prec;                // :29
+  const int max_count_prec = (1 << (63 - 46)) - 1;   // :30
+  const double pr[6] = {r_prec * r_prec, r_prec, 1.0, 1.0 / r_prec, 1.0 / (r_prec * r_prec), 1.0 / (r_prec * r_prec * r_prec)};
+  const double I_pr[6] = {1.0 / (r_prec * r_prec), 1.0 / r_prec, 1.0, r_prec, r_prec * r_prec, r_prec * r_prec * r_prec};
+  long long s[6] = {0, 0, 0, 0, 0, 0};
+  auto incr = [&](double r) {                        // increment_ints_faster :597-626
+    const int sgn = (r < 0.0) ? -1 : 1;
+    double rs = std::fabs(r);
+    for (int i = 0; i < 6; i++) {
+      const long long ival = (long long)(rs * I_pr[i]);
+      rs = rs - ival * pr[i];
+      s[i] = s[i] + sgn * ival;
+    }
+  };
+  auto carry = [&]() {                               // carry_overflow :629-649 (the same first loop as regularize_ints)
+    for (int i = 5; i >= 1; i--) if (std::llabs(s[i]) >= prec) {
+      const int num_carry = (int)(s[i] * I_prec);
+      s[i] = s[i] - num_carry * prec;
+      s[i - 1] = s[i - 1] + num_carry;
+    }
+  };
+  const long ni = i1 - i0 + 1, nj = j1 - j0 + 1;
+  if (ni * nj < max_count_prec) {                    // :156-160
+    for (int j = j0; j <= j1; j++) for (int i = i0; i <= i1; i++) incr(a[i + nrow_stride * j]);
+    carry();
+  } else {                                           // :161-167 (rows shorter than max_count_prec)
+    for (int j = j0; j <= j1; j++) { for (int i = i0; i <= i1; i++) incr(a[i + nrow_stride * j]); carry(); }
+  }
+  // (sum_across_PEs of the integers: one PE) ; regularize_ints :653-691
+  carry();
+  bool positive = true;
+  for (int i = 0; i < 6; i++) if (std::llabs(s[i]) > 0) { if (s[i] < 0) positive = false; break; }
+  if (positive) { for (int i = 5; i >= 1; i--) if (s[i] < 0) { s[i] += prec; s[i - 1] -= 1; } }
+  else { for (int i = 5; i >= 1; i--) if (s[i] > 0) { s[i] -= prec; s[i - 1] += 1; } }
+  double r = 0.0;                                    // ints_to_real :550-559
+  for (int i = 0; i < 6; i++) r = r + pr[i] * (double)s[i];
+  return r;
+}
+}  // namespace
+
+extern "C" double ora_remaining_transport_sum(const ora_grid *Gp, const double *uhtr, const double *vhtr, const double *h_new,
+                                              double H_to_kg_m2, double L_to_m, double kg_m2_to_H, double m_to_L) {
+  const ora_grid &G = *Gp;                           // MOM_offline_main.F90:615-650
+  const int is = G.isc, ie = G.iec, js = G.jsc, je = G.jec, nz = G.nk;
+  const long nih = G.ied - G.isd + 1, njh = G.jed - G.jsd + 1, niu = G.IedB - G.IsdB + 1, njv = G.JedB - G.JsdB + 1;
+  auto U = [&](int I, int j, int k) { return uhtr[(I - G.IsdB) + niu * ((j - G.jsd) + njh * (long)(k - 1))]; };
+  auto V = [&](int i, int J, int k) { return vhtr[(i - G.isd) + nih * ((J - G.JsdB) + njv * (long)(k - 1))]; };
+  auto H = [&](int i, int j, int k) { return h_new[(i - G.isd) + nih * ((j - G.jsd) + njh * (long)(k - 1))]; };
+  const double HL2_to_kg_scale = H_to_kg_m2 * (L_to_m * L_to_m);                            // :636
+  std::vector<double> col((size_t)nih * njh, 0.0);                                          // :638
+  for (int k = 1; k <= nz; k++) for (int j = js; j <= je; j++) for (int i = is; i <= ie; i++) {   // :639-644
+    const double trans_cell = (std::fabs(U(i - 1, j, k)) + std::fabs(U(i, j, k))) + (std::fabs(V(i, j - 1, k)) + std::fabs(V(i, j, k)));
+    const double a = 1.0e-16 * H(i, j, k), b = G.H_subroundoff;
+    const double mx = (b > a) ? b : a;               // MAX(a, b), gfortran's compare-select
+    const long q = (i - G.isd) + nih * (long)(j - G.jsd);
+    if (trans_cell > mx * G.areaT[q]) col[q] = col[q] + HL2_to_kg_scale * trans_cell;
+  }
+  // :647-648; array indices of reproducing_sum start at 1: is+(1-isd) .. ie+(1-isd)
+  return 0.5 * kg_m2_to_H * (m_to_L * m_to_L) * repro_sum_2d(col.data(), nih, is - G.isd, ie - G.isd, js - G.jsd, je - G.jsd);
+}
+
+extern "C" int ora_offline_advection_loop(const ora_grid *Gp, const ora_cs *CS, ora_tracer *Tr, int ntr, double *h_pre,
+                                          double *uhtr, double *vhtr, double dt_offline, int num_off_iter, int off_ale_mod,
+                                          int x_before_y_in, double min_residual, double H_to_kg_m2, double L_to_m,
+                                          double kg_m2_to_H, double m_to_L, const ora_domain *dom, const ora_obc *OBC,
+                                          int *converged_out, int *n_iter_out, double *tot_residual_out, int nthreads) {
+  const ora_grid &G = *Gp;
+  if (!dom) return 1;
+  for (int iter = 1; iter <= num_off_iter; iter++)
+    if (off_ale_mod <= 0 || iter % off_ale_mod == 0) return 2;       // the ALE step (:346-380) is not restated
+  const int is = G.isc, ie = G.iec, js = G.jsc, je = G.jec, nz = G.nk;
+  const long nih = G.ied - G.isd + 1, njh = G.jed - G.jsd + 1, niu = G.IedB - G.IsdB + 1, njv = G.JedB - G.JsdB + 1;
+  const size_t nh = (size_t)nih * njh * nz, nu = (size_t)niu * njh * nz, nv = (size_t)nih * njv * nz;
+  auto qh = [&](int i, int j, int k) { return (size_t)((i - G.isd) + nih * ((j - G.jsd) + njh * (long)(k - 1))); };
+  auto qu = [&](int I, int j, int k) { return (size_t)((I - G.IsdB) + niu * ((j - G.jsd) + njh * (long)(k - 1))); };
+  auto qv = [&](int i, int J, int k) { return (size_t)((i - G.isd) + nih * ((J - G.JsdB) + njv * (long)(k - 1))); };
+  bool x_before_y = x_before_y_in != 0;                                             // :254
+  std::vector<double> h_new(nh, 0.0), h_vol(nh, 0.0), uhtr_sub(nu, 0.0), vhtr_sub(nv, 0.0);   // :270-273
+  bool converged = false;                                                           // :276
+  for (size_t q = 0; q < nu; q++) uhtr_sub[q] = uhtr[q];                            // :298-300 (whole data domain)
+  for (size_t q = 0; q < nv; q++) vhtr_sub[q] = vhtr[q];                            // :301-303
+  for (int k = 1; k <= nz; k++) for (int j = js; j <= je; j++) for (int i = is; i <= ie; i++) h_new[qh(i, j, k)] = h_pre[qh(i, j, k)];   // :304-306
+  double tot_residual = ora_remaining_transport_sum(Gp, uhtr, vhtr, h_new.data(), H_to_kg_m2, L_to_m, kg_m2_to_H, m_to_L);   // :312
+  int nrec = 0;
+  if (tot_residual_out) tot_residual_out[nrec] = tot_residual;
+  nrec++;
+  double prev_tot_residual = std::numeric_limits<double>::quiet_NaN();   // the reference leaves it unset before :409 (first iteration)
+  SingleCtx sctx;
+  sctx.rank.G = G; sctx.rank.ioff = -(G.isc - 1); sctx.rank.joff = -(G.jsc - 1); sctx.rank.Tr = Tr; sctx.dom = dom; sctx.ntr = 0;
+  int iter;
+  for (iter = 1; iter <= num_off_iter; iter++) {                                    // :320
+    for (int k = 1; k <= nz; k++) for (int j = js; j <= je; j++) for (int i = is; i <= ie; i++) {
+      h_vol[qh(i, j, k)] = h_new[qh(i, j, k)] * G.areaT[(i - G.isd) + nih * (long)(j - G.jsd)];   // :323
+      h_pre[qh(i, j, k)] = h_new[qh(i, j, k)];                                                    // :324
+    }
+    int rc = ora_advect_tracer_obc(Gp, CS, Tr, ntr, h_pre, uhtr_sub.data(), vhtr_sub.data(), dt_offline, x_before_y ? 1 : 0,
+                                   h_vol.data(), 1, 1, uhtr, vhtr, dom, nullptr, nullptr, nullptr, nullptr, nthreads, OBC);   // :334-336
+    if (rc) return rc;
+    x_before_y = !x_before_y;                                                       // :339
+    for (int k = 1; k <= nz; k++) for (int j = js; j <= je; j++) for (int i = is; i <= ie; i++)
+      h_new[qh(i, j, k)] = h_vol[qh(i, j, k)] * G.IareaT[(i - G.isd) + nih * (long)(j - G.jsd)];  // :342-344
+    for (int k = 1; k <= nz; k++) for (int j = js; j <= je; j++) for (int i = is; i <= ie; i++) {     // :382-385
+      uhtr_sub[qu(i, j, k)] = uhtr[qu(i, j, k)];
+      vhtr_sub[qv(i, j, k)] = vhtr[qv(i, j, k)];
+    }
+    single_pass(&sctx, uhtr_sub.data(), vhtr_sub.data(), h_new.data(), Tr, 0);      // :386-387 pass_var(h_new) ; pass_vector(uhtr_sub, vhtr_sub)
+    tot_residual = ora_remaining_transport_sum(Gp, uhtr, vhtr, h_new.data(), H_to_kg_m2, L_to_m, kg_m2_to_H, m_to_L);   // :391
+    if (tot_residual_out) tot_residual_out[nrec] = tot_residual;
+    nrec++;
+    if (tot_residual == 0.0) { converged = true; break; }                           // :397-402
+    if ((tot_residual == prev_tot_residual) || (tot_residual < min_residual)) { converged = false; break; }   // :404-407
+    prev_tot_residual = tot_residual;                                               // :409
+  }
+  for (size_t q = 0; q < nh; q++) h_pre[q] = h_new[q];                              // :414
+  {                                                                                 // :415 pass_vector(uhtr, vhtr)
+    std::vector<double> sh(nh, 0.0);
+    single_pass(&sctx, uhtr, vhtr, sh.data(), Tr, 0);
+  }
+  if (converged_out) *converged_out = converged ? 1 : 0;
+  if (n_iter_out) *n_iter_out = (iter > num_off_iter) ? num_off_iter : iter;       // iterations run
   return 0;
 }

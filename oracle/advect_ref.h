@@ -158,6 +158,19 @@ int ora_tracer_hordiff(const ora_grid *G, ora_tracer *Tr, int ntr, const double 
                        const double *khdt_y, int num_itts, double h_neglect, int Diffuse_ML_interior, int nkml,
                        int nk_rho_varies, double ML_KhTr_scale, const ora_domain *dom, ora_pass_fn pass, void *ctx);
 
+/* The iteration loop of offline_advection_ale: MOM_offline_main.F90:254-312, 320-411, 414-415,
+ * without the ALE step inside the loop (:346-380): returns 2 if MODULO(iter, off_ale_mod) == 0 for an iteration it may
+ * run.  h_pre, uhtr, vhtr are the routine's intent(inout) arrays (whole data domain); tot_residual_out (nullable,
+ * num_off_iter+1 values) receives remaining_transport_sum at :312 and at :391 of every iteration run. */
+int ora_offline_advection_loop(const ora_grid *G, const ora_cs *CS, ora_tracer *Tr, int ntr, double *h_pre, double *uhtr,
+                               double *vhtr, double dt_offline, int num_off_iter, int off_ale_mod, int x_before_y,
+                               double min_residual, double H_to_kg_m2, double L_to_m, double kg_m2_to_H, double m_to_L,
+                               const ora_domain *dom, const ora_obc *OBC, int *converged, int *n_iter,
+                               double *tot_residual_out, int nthreads);
+/* remaining_transport_sum, MOM_offline_main.F90:615-650 (reproducing_sum_2d of MOM_coms.F90 restated) */
+double ora_remaining_transport_sum(const ora_grid *G, const double *uhtr, const double *vhtr, const double *h_new,
+                                   double H_to_kg_m2, double L_to_m, double kg_m2_to_H, double m_to_L);
+
 /* MOM bitcount checksum of a 2-D/3-D array section
  * (src/framework/MOM_checksums.F90:2407-2414 bitcount, :1396-1404 use). */
 long long ora_bitcount_chksum(const double *a, long long n);

@@ -128,6 +128,8 @@ inline double f_epsilon(double) { return DBL_EPSILON; }
 inline double f_real(int a) { return (double)a; }
 inline double f_real(double a) { return a; }
 inline double f_pow(double a, int b) { if (b == 2) return a * a; if (b == 3) return (a * a) * a; return std::pow(a, b); }
+// keyword arguments name=value of a call arrive as kw_name(value): a tag the callee's C++ overload may use; these pass through
+template <class T> inline T kw_clock(T v) { return v; }
 inline int f_trips(int lo, int hi, int st) { const int n = (hi - lo + st) / st; return n > 0 ? n : 0; }
 
 // ---- stand-ins for the modules MOM_tracer_advect.F90 uses (members as it reads them, names case-folded) ------------
@@ -137,11 +139,13 @@ struct ocean_grid_type {
   int isc = 0, iec = 0, jsc = 0, jec = 0, isd = 0, ied = 0, jsd = 0, jed = 0, isdb = 0, iedb = 0, jsdb = 0, jedb = 0, ke = 0;
   int iscb = 0, iecb = 0, jscb = 0, jecb = 0;
   int first_direction = 0;
+  int hi = 0;      // G%HI (hor_index_type): only handed to checksum calls
   mom_domain_type *domain = nullptr;
   Arr<double, 2> areat, iareat, mask2dt, mask2dcu, mask2dcv;
 };
-struct verticalgrid_type { int ke = 0; double angstrom_h = 0, h_subroundoff = 0; int nkml = 0, nk_rho_varies = 0; };
-struct unit_scale_type { double s_to_t = 1.0; };
+struct verticalgrid_type { int ke = 0; double angstrom_h = 0, h_subroundoff = 0; int nkml = 0, nk_rho_varies = 0;
+                           double h_to_mks = 1.0, h_to_kg_m2 = 1.0, kg_m2_to_h = 1.0; };      // MOM_offline_main.F90:636,647
+struct unit_scale_type { double s_to_t = 1.0, l_to_m = 1.0, m_to_l = 1.0; };
 struct tracer_type {
   Arr<double, 3> t, ad_x, ad_y, advection_xy;
   Arr<double, 2> ad2d_x, ad2d_y;

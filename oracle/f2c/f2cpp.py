@@ -694,22 +694,34 @@ def translate_body(sub: Sub, arrays, src_name: str, header: bool) -> str:
         if st == "cycle":
             put("continue;", ln)
             return
+        if re.match(r"^write\s*\(", st):
+            # formatted output into a message string / unit: no effect on any arithmetic
+            put("/* %s */;" % st.replace("*/", "* /"), ln)
+            return
         m = re.match(r"^call\s+(\w+)\s*(\(.*\))?$", st)
         if m:
             name = m.group(1)
-            args = []
+            args = []      # (keyword or None, expression)
             if m.group(2):
-                r = parse_expr(name + m.group(2))
-                args = r.parts[0][1]
+                inner = m.group(2).strip()[1:-1]
+                for piece in split_top(inner):
+                    piece = piece.strip()
+                    k = re.match(r"^(\w+)\s*=(?!=)\s*(.*)$", piece)
+                    if k:
+                        args.append((k.group(1), parse_expr(k.group(2))))
+                    else:
+                        args.append((None, parse_expr(piece)))
             if name == "mom_error":
-                put("f_mom_error(%s);" % ", ".join(em.e(a) for a in args), ln)
+                put("f_mom_error(%s);" % ", ".join(em.e(a) for _, a in args), ln)
                 return
             a_txt = []
-            for a in args:
+            for kw, a in args:
                 if isinstance(a, Ref) and em.whole(a.parts[-1][1]):
-                    a_txt.append(em.ref(a))
+                    t = em.ref(a)
                 else:
-                    a_txt.append(em.e(a))
+                    t = em.e(a)
+                # keyword argument name=expr: a tagged value the callee's C++ overload sorts into its optional slot
+                a_txt.append("kw_%s(%s)" % (cname(kw), t) if kw else t)
             put("%s(%s);" % (cname(name), ", ".join(a_txt)), ln)
             return
         # pointer assignment

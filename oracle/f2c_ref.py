@@ -20,7 +20,7 @@ _SRC = "/root/reference/src/tracer/MOM_tracer_advect.F90"
 _libs = {}
 
 VARIANTS = {"": "libref_f2c.so", "lt": "libref_f2c_lt.so", "mm": "libref_f2c_mm.so", "chk": "libref_f2c_chk.so"}
-_EXTRA = ("libref_f2c_hordiff.so",)
+_EXTRA = ("libref_f2c_hordiff.so", "libref_f2c_offline.so")
 
 
 def available() -> bool:
@@ -97,3 +97,20 @@ def tracer_hordiff(h, khdt_x, khdt_y, num_itts, dt, G, GV, Reg, Diffuse_ML_inter
                                 float(ML_KhTr_scale), float(dt), C.byref(dom), None, None)
     if rc != 0:
         raise RuntimeError("translated tracer_hordiff loop failed: %d" % rc)
+
+
+_off = None
+
+
+def offline_advection_loop(h_pre, uhtr, vhtr, dt_offline, num_off_iter, G, GV, CS, Reg, x_before_y=True, off_ale_mod=10 ** 6,
+                           min_residual=0.0, H_to_kg_m2=1.0, L_to_m=1.0, kg_m2_to_H=1.0, m_to_L=1.0):
+    """The translated lines MOM_offline_main.F90:270-415 and :634-648 around the translated advect_tracer
+    (oracle/f2c/offline_wrap.cpp, bounds-checked build).  Same returns as oracle.offline_advection_loop."""
+    global _off
+    if _off is None:
+        lib()
+        _off = C.CDLL(os.path.join(_REF_DIR, "libref_f2c_offline.so"))
+        _off.ref_offline_advection_loop.restype = C.c_int
+        _off.ref_offline_advection_loop.argtypes = ora._offline_argtypes()
+    return ora._offline_call(_off.ref_offline_advection_loop, h_pre, uhtr, vhtr, dt_offline, num_off_iter, G, GV, CS, Reg,
+                             x_before_y, off_ale_mod, min_residual, H_to_kg_m2, L_to_m, kg_m2_to_H, m_to_L, None, 1)

@@ -81,6 +81,12 @@ def build(force: bool = False) -> str:
     return _LIB_PATH
 
 
+def _offline_argtypes():
+    return [C.POINTER(ora_grid), C.POINTER(ora_cs), C.POINTER(ora_tracer), C.c_int, _dp, _dp, _dp, C.c_double, C.c_int, C.c_int,
+            C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, C.POINTER(ora_domain), C.c_void_p,
+            C.POINTER(C.c_int), C.POINTER(C.c_int), _dp, C.c_int]
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -101,6 +107,10 @@ def lib():
         _lib.ora_tracer_hordiff.argtypes = [C.POINTER(ora_grid), C.POINTER(ora_tracer), C.c_int, _dp, _dp, _dp, C.c_int,
                                             C.c_double, C.c_int, C.c_int, C.c_int, C.c_double, C.POINTER(ora_domain),
                                             C.c_void_p, C.c_void_p]
+        _lib.ora_offline_advection_loop.restype = C.c_int
+        _lib.ora_offline_advection_loop.argtypes = _offline_argtypes()
+        _lib.ora_remaining_transport_sum.restype = C.c_double
+        _lib.ora_remaining_transport_sum.argtypes = [C.POINTER(ora_grid), _dp, _dp, _dp, C.c_double, C.c_double, C.c_double, C.c_double]
         _lib.ora_bitcount_chksum.restype = C.c_longlong
         _lib.ora_bitcount_chksum.argtypes = [_dp, C.c_longlong]
         _lib.ora_efp_sum.restype = None
@@ -226,6 +236,37 @@ def tracer_hordiff(h, khdt_x, khdt_y, num_itts, G, GV, Reg, Diffuse_ML_interior=
                                   float(ML_KhTr_scale), C.byref(dom), None, None)
     if rc != 0:
         raise RuntimeError("oracle tracer_hordiff failed: %d" % rc)
+
+
+def _offline_call(fn, h_pre, uhtr, vhtr, dt_offline, num_off_iter, G, GV, CS, Reg, x_before_y, off_ale_mod, min_residual,
+                  H_to_kg_m2, L_to_m, kg_m2_to_H, m_to_L, OBC, nthreads):
+    g, cs, dom = make_grid(G, GV), make_cs(CS), make_domain(G.Domain)
+    tr = make_tracers(Reg)
+    obc, _keep = make_obc(OBC)
+    conv, nit = C.c_int(0), C.c_int(0)
+    res = np.full(num_off_iter + 1, np.nan)
+    rc = fn(C.byref(g), C.byref(cs), tr, Reg.ntr, _p(h_pre), _p(uhtr), _p(vhtr), float(dt_offline), int(num_off_iter),
+            int(off_ale_mod), int(bool(x_before_y)), float(min_residual), float(H_to_kg_m2), float(L_to_m), float(kg_m2_to_H),
+            float(m_to_L), C.byref(dom), C.byref(obc) if obc is not None else None, C.byref(conv), C.byref(nit), _p(res),
+            int(nthreads))
+    if rc != 0:
+        raise RuntimeError("offline advection loop failed: %d" % rc)
+    return bool(conv.value), nit.value, res[:nit.value + 1].copy()
+
+
+def offline_advection_loop(h_pre, uhtr, vhtr, dt_offline, num_off_iter, G, GV, CS, Reg, x_before_y=True, off_ale_mod=10 ** 6,
+                           min_residual=0.0, H_to_kg_m2=1.0, L_to_m=1.0, kg_m2_to_H=1.0, m_to_L=1.0, OBC=None, nthreads=1):
+    """The iteration loop of offline_advection_ale (MOM_offline_main.F90:254-312, 320-411, 414-415) without its ALE step;
+    h_pre, uhtr, vhtr and Reg.Tr[m].t are updated in place.  Returns (converged, iterations run, remaining_transport_sum
+    at :312 and after every iteration)."""
+    return _offline_call(lib().ora_offline_advection_loop, h_pre, uhtr, vhtr, dt_offline, num_off_iter, G, GV, CS, Reg,
+                         x_before_y, off_ale_mod, min_residual, H_to_kg_m2, L_to_m, kg_m2_to_H, m_to_L, OBC, nthreads)
+
+
+def remaining_transport_sum(uhtr, vhtr, h_new, G, GV, H_to_kg_m2=1.0, L_to_m=1.0, kg_m2_to_H=1.0, m_to_L=1.0) -> float:
+    g = make_grid(G, GV)
+    return float(lib().ora_remaining_transport_sum(C.byref(g), _p(uhtr), _p(vhtr), _p(h_new), float(H_to_kg_m2), float(L_to_m),
+                                                   float(kg_m2_to_H), float(m_to_L)))
 
 
 def advect_tracer_multi(ranks: Sequence[dict], dom, CS, dt, x_first_in=None, max_iter_in=None,

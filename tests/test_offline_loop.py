@@ -1,0 +1,81 @@
+"""The iteration loop of offline_advection_ale:
+/root/reference/src/tracer/MOM_offline_main.F90:254-312, 320-411, 414-415 with remaining_transport_sum (:615-650).
+
+CPU: the hand-written oracle (oracle/advect_ref.cpp: ora_offline_advection_loop) against those lines of the UNMODIFIED
+reference file translated statement by statement, running around the translated advect_tracer (oracle/f2c, bounds-checked):
+tracers, h_pre, uhtr, vhtr, the convergence flag, the iteration count and every remaining_transport_sum, bitwise.
+GPU (marked): mom6adv_offline_advect through the C ABI against the oracle, bitwise."""
+import numpy as np
+import pytest
+
+from mom6_b200 import synth
+from mom6_b200.tracer_advect import tracer_advect_init
+from oracle import f2c_ref, oracle
+
+eq = lambda a, b: np.array_equal(np.ascontiguousarray(a).view(np.uint64), np.ascontiguousarray(b).view(np.uint64))
+UNITS = dict(H_to_kg_m2=1035.0, L_to_m=1.0, kg_m2_to_H=1.0 / 1035.0, m_to_L=1.0)
+
+
+def _case(scheme="PPM", cfl=2.4, ni=37, nj=29, nk=3, ntr=3, **kw):
+    c = synth.make_case(ni, nj, nk, ntr, cfl=cfl, **kw)
+    CS = tracer_advect_init(None, c.G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": scheme}, None, None)
+    return c, CS
+
+
+def _run(fn, c, CS, num_off_iter, x_before_y=True, min_residual=0.0, **kw):
+    Reg = synth.bind_registry(c)
+    h, u, v = c.h_end.numpy().copy(), c.uhtr.numpy().copy(), c.vhtr.numpy().copy()
+    conv, nit, res = fn(h, u, v, c.dt, num_off_iter, c.G, c.GV, CS, Reg, x_before_y=x_before_y, min_residual=min_residual,
+                        **UNITS, **kw)
+    return Reg, h, u, v, conv, nit, res
+
+
+@pytest.mark.skipif(not f2c_ref.available(), reason="neither oracle/_ref nor /root/reference present")
+@pytest.mark.parametrize("kw", [dict(), dict(cyclic_x=False), dict(symmetric=False), dict(cyclic_y=True), dict(tripolar_n=True)])
+@pytest.mark.parametrize("scheme,x_before_y", [("PPM", True), ("PLM", False), ("PPM:H3", True)])
+def test_oracle_equals_translated_reference_loop(kw, scheme, x_before_y):
+    c, CS = _case(scheme, **kw)
+    a = _run(oracle.offline_advection_loop, c, CS, 8, x_before_y)
+    b = _run(f2c_ref.offline_advection_loop, c, CS, 8, x_before_y)
+    assert a[5] == b[5] and a[4] == b[4], (a[4:6], b[4:6])
+    assert a[5] >= 2                                  # more than one trip through the loop
+    assert eq(a[6], b[6]), (a[6], b[6])               # every remaining_transport_sum
+    for m in range(c.ntr):
+        assert eq(a[0].Tr[m].t, b[0].Tr[m].t), "tracer %d" % m
+    assert eq(a[1], b[1]) and eq(a[2], b[2]) and eq(a[3], b[3])      # h_pre, uhtr, vhtr: whole arrays
+
+
+@pytest.mark.skipif(not f2c_ref.available(), reason="neither oracle/_ref nor /root/reference present")
+def test_exit_paths():
+    """Converged (remaining transport exactly 0), iteration cap, and the min_residual exit -- same in both."""
+    c, CS = _case("PPM", cfl=0.4)
+    for fn in (oracle.offline_advection_loop, f2c_ref.offline_advection_loop):
+        Reg, h, u, v, conv, nit, res = _run(fn, c, CS, 6)
+        assert conv and res[-1] == 0.0 and nit <= 2, (conv, nit, res)
+    c, CS = _case("PPM", cfl=2.4)
+    out = []
+    for fn in (oracle.offline_advection_loop, f2c_ref.offline_advection_loop):
+        Reg, h, u, v, conv, nit, res = _run(fn, c, CS, 2)
+        assert not conv and nit == 2 and res[-1] > 0.0
+        out.append(res)
+        Reg, h, u, v, conv, nit, res = _run(fn, c, CS, 8, min_residual=0.5 * res[1])
+        assert not conv and res[-1] < 0.5 * out[-1][1]
+        out.append((nit, res))
+    assert eq(out[0], out[2]) and out[1][0] == out[3][0] and eq(out[1][1], out[3][1])
+
+
+def test_remaining_transport_sum_is_order_invariant_and_exact():
+    """reproducing_sum's point: the value does not depend on the order of the columns, and for integers it is exact."""
+    c, CS = _case("PLM", ni=24, nj=20, nk=2, ntr=1)
+    G = c.G
+    h, u, v = c.h_end.numpy(), c.uhtr.numpy(), c.vhtr.numpy()
+    r0 = oracle.remaining_transport_sum(u, v, h, G, c.GV, **UNITS)
+    assert r0 > 0.0
+    Gt, ht, ut, vt = synth.transposed_fields(c) if hasattr(synth, "transposed_fields") else (None, None, None, None)
+    if Gt is not None:
+        assert oracle.remaining_transport_sum(ut, vt, ht, Gt, c.GV, **UNITS) == r0
+    # integers: |u| = 3 on every face of the computational domain, v = 0, unit scales -> 0.5 * (3 + 3) per cell and level
+    u2, v2 = np.zeros_like(u), np.zeros_like(v)
+    u2[:, G.pj(G.jsc):G.pj(G.jec) + 1, G.pI(G.isc) - 1:G.pI(G.iec) + 1] = 3.0
+    n = (G.iec - G.isc + 1) * (G.jec - G.jsc + 1) * c.GV.ke
+    assert oracle.remaining_transport_sum(u2, v2, h, G, c.GV) == 3.0 * n
