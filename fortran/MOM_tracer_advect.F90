@@ -35,6 +35,7 @@ public advect_tracer
 public tracer_advect_init
 public tracer_advect_end
 public tracer_hordiff_iterate
+public offline_advection_iterate
 
 !> Control structure: the reference's members (:30-40) plus the GPU plan handle.
 type, public :: tracer_advect_CS ; private
@@ -198,6 +199,27 @@ interface
     real(c_double), value :: h_neglect, ml_khtr_scale
     integer(c_int) :: rc
   end function mom6adv_hordiff
+
+  !> The iteration loop of offline_advection_ale on the resident fields (replaces MOM_offline_main.F90:320-411)
+  function mom6adv_offline_advect(plan, dt_offline, num_off_iter, off_ale_mod, x_before_y, min_residual, h_to_kg_m2, &
+                                  l_to_m, kg_m2_to_h, m_to_l, converged, n_iter, tot_residual) &
+                                  bind(c, name="mom6adv_offline_advect") result(rc)
+    import :: c_int, c_ptr, c_double
+    type(c_ptr), value :: plan, tot_residual    !< tot_residual: c_loc of num_off_iter+1 reals, or c_null_ptr
+    real(c_double), value :: dt_offline, min_residual, h_to_kg_m2, l_to_m, kg_m2_to_h, m_to_l
+    integer(c_int), value :: num_off_iter, off_ale_mod, x_before_y
+    integer(c_int), intent(out) :: converged, n_iter
+    integer(c_int) :: rc
+  end function mom6adv_offline_advect
+
+  function mom6adv_upload_field(plan, field, src) bind(c, name="mom6adv_upload_field") result(rc)
+    import :: c_int, c_ptr
+    type(c_ptr), value :: plan, src ; integer(c_int), value :: field ; integer(c_int) :: rc
+  end function mom6adv_upload_field
+  function mom6adv_download_field(plan, field, dst) bind(c, name="mom6adv_download_field") result(rc)
+    import :: c_int, c_ptr
+    type(c_ptr), value :: plan, dst ; integer(c_int), value :: field ; integer(c_int) :: rc
+  end function mom6adv_download_field
 end interface
 
 contains
@@ -509,6 +531,43 @@ subroutine tracer_hordiff_iterate(CS, G, GV, khdt_x, khdt_y, num_itts, Diffuse_M
                        merge(1_c_int, 0_c_int, any_df))
   call check_rc(rc, CS%plan, "tracer_hordiff_iterate")
 end subroutine tracer_hordiff_iterate
+
+!> The part of offline_advection_ale between "Copy over the horizontal mass fluxes" and its end
+!! (MOM_offline_main.F90:298-415) for runs that keep ALE out of the loop (off_ale_mod > num_off_iter): call this from
+!! offline_advection_ale in place of those lines.  h_pre, uhtr and vhtr go up once and come back once; the tracers
+!! stay in HBM (they were put there by the last advect_tracer call or by the registry's first binding).
+subroutine offline_advection_iterate(CS, G, GV, US, h_pre, uhtr, vhtr, dt_offline, num_off_iter, off_ale_mod, &
+                                     x_before_y, min_residual, converged)
+  type(tracer_advect_CS),  pointer    :: CS     !< control structure of MOM_tracer_advect (owns the GPU plan)
+  type(ocean_grid_type),   intent(in) :: G      !< ocean grid structure
+  type(verticalGrid_type), intent(in) :: GV     !< ocean vertical grid structure
+  type(unit_scale_type),   intent(in) :: US     !< a dimensional unit scaling type
+  real, dimension(SZI_(G),SZJ_(G),SZK_(GV)),  target, intent(inout) :: h_pre !< layer thicknesses [H ~> m or kg m-2]
+  real, dimension(SZIB_(G),SZJ_(G),SZK_(GV)), target, intent(inout) :: uhtr  !< zonal mass transport [H L2 ~> m3 or kg]
+  real, dimension(SZI_(G),SZJB_(G),SZK_(GV)), target, intent(inout) :: vhtr  !< meridional mass transport [H L2 ~> m3 or kg]
+  real,    intent(in)  :: dt_offline   !< CS%dt_offline of offline_transport_CS [T ~> s]
+  integer, intent(in)  :: num_off_iter !< CS%num_off_iter
+  integer, intent(in)  :: off_ale_mod  !< CS%off_ale_mod
+  logical, intent(in)  :: x_before_y   !< CS%x_before_y
+  real,    intent(in)  :: min_residual !< CS%min_residual [H L2 ~> m3 or kg]
+  logical, intent(out) :: converged    !< true if no mass transport remains
+  integer(c_int) :: rc, conv, nit
+  integer(c_int), parameter :: F_H_END = 0, F_UHTR = 1, F_VHTR = 2, F_UHR = 4, F_VHR = 5   ! mom6adv.h field ids
+  if (.not.associated(CS)) call MOM_error(FATAL, "offline_advection_iterate: tracer_advect_init has not been called")
+  if (.not.c_associated(CS%plan)) call MOM_error(FATAL, "offline_advection_iterate: the GPU plan does not exist yet")
+  call check_rc(mom6adv_upload_field(CS%plan, F_H_END, c_loc(h_pre)), CS%plan, "offline_advection_iterate")
+  call check_rc(mom6adv_upload_field(CS%plan, F_UHTR, c_loc(uhtr)), CS%plan, "offline_advection_iterate")
+  call check_rc(mom6adv_upload_field(CS%plan, F_VHTR, c_loc(vhtr)), CS%plan, "offline_advection_iterate")
+  rc = mom6adv_offline_advect(CS%plan, real(dt_offline, c_double), int(num_off_iter, c_int), int(off_ale_mod, c_int), &
+                              merge(1_c_int, 0_c_int, x_before_y), real(min_residual, c_double), &
+                              real(GV%H_to_kg_m2, c_double), real(US%L_to_m, c_double), real(GV%kg_m2_to_H, c_double), &
+                              real(US%m_to_L, c_double), conv, nit, c_null_ptr)
+  call check_rc(rc, CS%plan, "offline_advection_iterate")
+  converged = (conv /= 0)
+  call check_rc(mom6adv_download_field(CS%plan, F_H_END, c_loc(h_pre)), CS%plan, "offline_advection_iterate")
+  call check_rc(mom6adv_download_field(CS%plan, F_UHR, c_loc(uhtr)), CS%plan, "offline_advection_iterate")
+  call check_rc(mom6adv_download_field(CS%plan, F_VHR, c_loc(vhtr)), CS%plan, "offline_advection_iterate")
+end subroutine offline_advection_iterate
 
 subroutine tracer_advect_end(CS)
   type(tracer_advect_CS), pointer :: CS !< module control structure

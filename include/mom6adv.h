@@ -189,6 +189,22 @@ int mom6adv_sync(mom6adv_plan *plan);
  * associated, h_diag ignored), ZINT (:796-802), ZINT_100M (:745-766,805-811); out2d is an (isd:ied, jsd:jed) array,
  * zero outside the computational domain like the reference's work2d. */
 int mom6adv_accumulate_transports(mom6adv_plan *plan, const double *uh, const double *vh, double dt);
+/* mom6adv_offline_advect replaces the iteration loop of offline_advection_ale (SURVEY.md 8f rank 4;
+ * src/tracer/MOM_offline_main.F90:254-312 set-up, :320-411 loop, :414-415 epilogue) with remaining_transport_sum
+ * (:615-650) and its reproducing sum (src/framework/MOM_coms.F90:119-213) on the RESIDENT fields:
+ *   in : H_END = h_pre, UHTR = uhtr, VHTR = vhtr (mom6adv_upload_field), the resident tracers
+ *   out: H_END = h_pre (:414), UHR = uhtr and VHR = vhtr, the remaining transports after :415 (mom6adv_download_field),
+ *        the tracers; *converged (:276, :400, :405), *n_iter = trips through the loop, tot_residual[0..*n_iter] =
+ *        remaining_transport_sum at :312 and at :391 of every trip (NULL to skip)
+ * Each trip calls advect_tracer with x_first_in = x_before_y (flipped every trip, :339), vol_prev = h_vol,
+ * max_iter_in = 1, update_vol_prev = .true., uhr_out = uhtr, vhr_out = vhtr (:334-336).  dt_offline, num_off_iter,
+ * off_ale_mod, x_before_y, min_residual are the offline_transport_CS members; H_to_kg_m2, kg_m2_to_H are GV's and L_to_m,
+ * m_to_L are US's (:636, :647).  The ALE step inside the loop (:346-380) is other modules' work and is not built: the
+ * call returns MOM6ADV_ERR_UNSUPPORTED if MODULO(iter, off_ale_mod) == 0 for any iter <= num_off_iter; multi-block
+ * plans likewise.  Halos of the outputs are valid to the plan's exchange depth. */
+int mom6adv_offline_advect(mom6adv_plan *plan, double dt_offline, int num_off_iter, int off_ale_mod, int x_before_y,
+                           double min_residual, double H_to_kg_m2, double L_to_m, double kg_m2_to_H, double m_to_L,
+                           int *converged, int *n_iter, double *tot_residual);
 /* mom6adv_hordiff replaces the iteration loop of tracer_hordiff, the call that follows advect_tracer in step_tracer
  * (src/core/MOM.F90:1441):
  *   do itt=1,num_itts ; do_group_pass(CS%pass_t) ; Coef_x/Coef_y/Ihdxdy ; dTr ; t = t + dTr ; conc_underflow ; enddo

@@ -16,7 +16,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libmom6adv_b200.so")
-SOURCES = ["kernels.cu", "plan.cu", "fast_x.cu", "fast_y.cu", "sparse.cu", "halo.cu", "obc.cu", "step.cu", "noalloc.cu", "hordiff.cu"]
+SOURCES = ["kernels.cu", "plan.cu", "fast_x.cu", "fast_y.cu", "sparse.cu", "halo.cu", "obc.cu", "step.cu", "noalloc.cu", "hordiff.cu", "offline.cu"]
 HEADERS = ["internal.cuh", "kernels.h", "fast_common.cuh", "obc.cuh", os.path.join("..", "..", "include", "mom6adv.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-fmad=false", "-lineinfo",

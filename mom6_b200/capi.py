@@ -109,6 +109,8 @@ SYMBOLS = {
                                         C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_int, C.c_int,
                                         C.c_int, C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_int)]),
     "mom6adv_hordiff": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int]),
+    "mom6adv_offline_advect": (C.c_int, [_P, C.c_double, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
+                                         C.c_double, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_int), _P]),
     "mom6adv_set_obc": (C.c_int, [_P, C.POINTER(mom6adv_obc)]),
     "mom6adv_set_ntr": (C.c_int, [_P, C.c_int]),
     "mom6adv_bind_tracer": (C.c_int, [_P, C.c_int, _P, C.c_double, _P, _P, _P, _P, _P]),
@@ -338,6 +340,18 @@ class Plan:
         self._ck(self._l.mom6adv_hordiff(self._h, ptr(h) if h is not None else None, ptr(khdt_x), ptr(khdt_y),
                                          int(num_itts), float(h_neglect), int(bool(Diffuse_ML_interior)), int(nkml),
                                          int(nk_rho_varies), float(ML_KhTr_scale), int(bool(want_df))))
+
+    def offline_advect(self, dt_offline, num_off_iter, x_before_y=True, off_ale_mod=10 ** 6, min_residual=0.0,
+                       H_to_kg_m2=1.0, L_to_m=1.0, kg_m2_to_H=1.0, m_to_L=1.0):
+        """The iteration loop of offline_advection_ale (MOM_offline_main.F90:254-415) on the resident fields.
+        Returns (converged, trips, remaining_transport_sum before the loop and after every trip)."""
+        conv, nit = C.c_int(0), C.c_int(0)
+        res = np.full(int(num_off_iter) + 1, np.nan)
+        self._ck(self._l.mom6adv_offline_advect(self._h, float(dt_offline), int(num_off_iter), int(off_ale_mod),
+                                                int(bool(x_before_y)), float(min_residual), float(H_to_kg_m2), float(L_to_m),
+                                                float(kg_m2_to_H), float(m_to_L), C.byref(conv), C.byref(nit),
+                                                res.ctypes.data))
+        return bool(conv.value), nit.value, res[:nit.value + 1].copy()
 
     def zero_transports(self):
         """CS%uhtr(:,:,:) = 0.0 ; CS%vhtr(:,:,:) = 0.0 (MOM.F90:1465-1466)."""

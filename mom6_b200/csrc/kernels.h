@@ -120,3 +120,11 @@ void launch_hd_coef(cudaStream_t s, const Geom &g, const HdParams &p, const doub
                     const double *khdt_y, const double *IareaT, double *cx, double *cy, double *ihd);
 void launch_hd_apply(cudaStream_t s, const Geom &g, const HdParams &p, const TrTable &tt, const double *cx,
                      const double *cy, const double *ihd);
+
+// offline.cu: the iteration loop of offline_advection_ale (MOM_offline_main.F90:254-415), element-wise parts
+void launch_off_init(cudaStream_t s, const Geom &g, double *h);
+void launch_off_vol(cudaStream_t s, const Geom &g, const double *h, const double *areaT, double *vol);
+void launch_off_post(cudaStream_t s, const Geom &g, const double *vol, const double *IareaT, double *h, const double *uhr,
+                     const double *vhr, double *usub, double *vsub);
+void launch_off_residual(cudaStream_t s, const Geom &g, const double *u, const double *v, const double *h,
+                         const double *areaT, double Hsub, double HL2_to_kg_scale, unsigned long long *acc);

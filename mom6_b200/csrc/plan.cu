@@ -13,6 +13,7 @@
 #include <cstring>
 #include <string>
 #include <vector>
+#include <limits>
 #include <chrono>
 
 #define MOM6ADV_VERSION "mom6adv-b200 0.1 (sm_100a)"
@@ -78,6 +79,8 @@ struct mom6adv_plan {
   int *domore_u = nullptr, *domore_v = nullptr, *entry_u = nullptr, *entry_v = nullptr, *domore_k = nullptr;
   int *sum_dev = nullptr, *sum_host = nullptr, *sum_host_dev = nullptr;   // sum_host: mapped pinned; sum_host_dev: its device alias
   double *staging = nullptr;
+  double **off_tab = nullptr;                       // mom6adv_offline_advect: [h_end, uhtr, vhtr, uhr, vhr] for its passes
+  unsigned long long *off_acc = nullptr;            // ... and the six integers of its reproducing sum
   double *khdt_x = nullptr, *khdt_y = nullptr;      // mom6adv_hordiff: 2-D diffusivity-times-dt fields (allocated on first use)
   double *stage_in = nullptr;        // MIRROR pipeline: ring of contiguous upload slots (slots x chunk x Fortran-layout tracer)
   long long stage_in_elems = 0;
@@ -608,6 +611,8 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   }
   if (plan->comm) ncclCommDestroy(plan->comm);
   if (plan->sp_list) cudaFree(plan->sp_list);
+  if (plan->off_tab) cudaFree(plan->off_tab);
+  if (plan->off_acc) cudaFree(plan->off_acc);
   if (plan->khdt_x) cudaFree(plan->khdt_x);
   if (plan->khdt_y) cudaFree(plan->khdt_y);
   if (plan->dirty) cudaFree(plan->dirty);
@@ -1632,6 +1637,110 @@ extern "C" int mom6adv_advect_resident(mom6adv_plan *plan, double dt, int x_firs
                                        int use_vol_prev, int update_vol_prev, int *n_iter) {
   if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "advect: tracer_advect_init must be called before advect_tracer");
   return run_advect(plan, dt, x_first, max_iter_in, use_vol_prev != 0, update_vol_prev > 0, n_iter, 0, plan->ntr);
+}
+
+// ---------------------------------------------------------------------------
+// The iteration loop of offline_advection_ale (MOM_offline_main.F90:254-312, 320-411, 414-415) on the resident fields;
+// element-wise kernels and the reproducing sum in offline.cu.  Field roles: see the head of offline.cu.
+// ---------------------------------------------------------------------------
+static int offline_residual(mom6adv_plan *plan, const double *u, const double *v, double HL2_to_kg_scale, double scale_out,
+                            double *out) {
+  cudaStream_t s = plan->stream;
+  CK(cudaMemsetAsync(plan->off_acc, 0, sizeof(unsigned long long) * 6, s));
+  launch_off_residual(s, plan->g, u, v, plan->h_end, plan->areaT, plan->H_subroundoff, HL2_to_kg_scale, plan->off_acc);
+  plan->launches++;
+  long long ints[6];
+  CK(cudaMemcpyAsync(ints, plan->off_acc, sizeof ints, cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  // (sum_across_PEs of the integers: single block) ; regularize_ints, MOM_coms.F90:653-691
+  const long long prec = 1LL << 46;
+  const double r_prec = 70368744177664.0, I_prec = 1.0 / 70368744177664.0;
+  for (int i = 5; i >= 1; i--) if (std::llabs(ints[i]) >= prec) {
+    const int num_carry = (int)(ints[i] * I_prec);
+    ints[i] = ints[i] - num_carry * prec;
+    ints[i - 1] = ints[i - 1] + num_carry;
+  }
+  bool positive = true;
+  for (int i = 0; i < 6; i++) if (std::llabs(ints[i]) > 0) { if (ints[i] < 0) positive = false; break; }
+  if (positive) { for (int i = 5; i >= 1; i--) if (ints[i] < 0) { ints[i] += prec; ints[i - 1] -= 1; } }
+  else { for (int i = 5; i >= 1; i--) if (ints[i] > 0) { ints[i] -= prec; ints[i - 1] += 1; } }
+  const double pr[6] = {r_prec * r_prec, r_prec, 1.0, 1.0 / r_prec, 1.0 / (r_prec * r_prec), 1.0 / (r_prec * r_prec * r_prec)};
+  double r = 0.0;                                                            // ints_to_real :550-559
+  for (int i = 0; i < 6; i++) r = r + pr[i] * (double)ints[i];
+  *out = scale_out * r;                                                      // MOM_offline_main.F90:647-648
+  return 0;
+}
+
+extern "C" int mom6adv_offline_advect(mom6adv_plan *plan, double dt_offline, int num_off_iter, int off_ale_mod,
+                                      int x_before_y_in, double min_residual, double H_to_kg_m2, double L_to_m,
+                                      double kg_m2_to_H, double m_to_L, int *converged_out, int *n_iter_out,
+                                      double *tot_residual_out) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "offline_advect: plan not initialised");
+  if (converged_out) *converged_out = 0;
+  if (n_iter_out) *n_iter_out = 0;
+  if (plan->multi) return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "offline_advect: multi-block plans are not supported (the loop's pass_var / pass_vector and its sum across PEs are single-block here)");
+  if (num_off_iter < 1) return fail(plan, MOM6ADV_ERR_INVALID, "offline_advect: num_off_iter must be >= 1");
+  for (int iter = 1; iter <= num_off_iter; iter++)
+    if (off_ale_mod <= 0 || iter % off_ale_mod == 0)
+      return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "offline_advect: the ALE step inside the loop (MODULO(iter, off_ale_mod) == 0) is not built; keep the Fortran loop for such runs");
+  if (plan->ntr == 0) return fail(plan, MOM6ADV_ERR_INVALID, "offline_advect: no tracers registered");
+  const Geom &g = plan->g;
+  CK(cudaSetDevice(plan->device));
+  cudaStream_t s = plan->stream;
+  int rc;
+  if (!plan->vol_prev && (rc = dev_alloc(plan, &plan->vol_prev, field_elems(plan)))) return rc;
+  if (!plan->off_tab) {
+    double *tab[5] = {plan->h_end, plan->uhtr, plan->vhtr, plan->uhr, plan->vhr};
+    CK(cudaMalloc((void **)&plan->off_tab, sizeof tab));
+    CK(cudaMemcpy(plan->off_tab, tab, sizeof tab, cudaMemcpyHostToDevice));
+    CK(cudaMalloc((void **)&plan->off_acc, sizeof(unsigned long long) * 6));
+  }
+  auto pass1 = [&](int pos, int slot) {      // pass_var / one component of pass_vector on the single-block lists
+    launch_halo_apply(s, g.plane, g.nk, plan->halo[pos].dst, plan->halo[pos].src, plan->halo[pos].sgn, plan->halo[pos].n,
+                      plan->off_tab + slot, 1);
+    plan->launches++;
+  };
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  CK(cudaEventRecord(e0, s));
+  bool x_before_y = x_before_y_in != 0;                                      // :254
+  const double HL2_to_kg_scale = H_to_kg_m2 * (L_to_m * L_to_m);             // :636
+  const double rts_scale = 0.5 * kg_m2_to_H * (m_to_L * m_to_L);             // :647
+  launch_off_init(s, g, plan->h_end);                                        // :270, :304-306 (uhtr_sub = uhtr, vhtr_sub = vhtr: the same fields)
+  plan->launches++;
+  double tot_residual = 0.0, prev_tot_residual = std::numeric_limits<double>::quiet_NaN();   // (unset before :409)
+  if ((rc = offline_residual(plan, plan->uhtr, plan->vhtr, HL2_to_kg_scale, rts_scale, &tot_residual))) return rc;   // :312
+  int nrec = 0;
+  if (tot_residual_out) tot_residual_out[nrec] = tot_residual;
+  nrec++;
+  bool converged = false;                                                    // :276
+  int iter;
+  for (iter = 1; iter <= num_off_iter; iter++) {                             // :320
+    launch_off_vol(s, g, plan->h_end, plan->areaT, plan->vol_prev);          // :322-325
+    plan->launches++;
+    if ((rc = run_advect(plan, dt_offline, x_before_y ? 1 : 0, 1, true, true, nullptr, 0, plan->ntr))) return rc;   // :334-336
+    x_before_y = !x_before_y;                                                // :339
+    launch_off_post(s, g, plan->vol_prev, plan->IareaT, plan->h_end, plan->uhr, plan->vhr, plan->uhtr, plan->vhtr);   // :342-344, :382-385
+    plan->launches++;
+    pass1(0, 0); pass1(1, 1); pass1(2, 2);                                   // :386-387
+    if ((rc = offline_residual(plan, plan->uhr, plan->vhr, HL2_to_kg_scale, rts_scale, &tot_residual))) return rc;   // :391
+    if (tot_residual_out) tot_residual_out[nrec] = tot_residual;
+    nrec++;
+    if (tot_residual == 0.0) { converged = true; break; }                    // :397-402
+    if ((tot_residual == prev_tot_residual) || (tot_residual < min_residual)) { converged = false; break; }   // :404-407
+    prev_tot_residual = tot_residual;                                        // :409
+  }
+  pass1(1, 3); pass1(2, 4);                                                  // :415 pass_vector(uhtr, vhtr)  (:414: h_pre is h_new already)
+  CK(cudaEventRecord(e1, s));
+  CK(cudaStreamSynchronize(s));
+  float ms = 0.f;
+  CK(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  plan->last_ms = ms;
+  CK(cudaGetLastError());
+  if (converged_out) *converged_out = converged ? 1 : 0;
+  if (n_iter_out) *n_iter_out = iter > num_off_iter ? num_off_iter : iter;
+  return MOM6ADV_OK;
 }
 
 // ---------------------------------------------------------------------------

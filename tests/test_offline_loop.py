@@ -79,3 +79,65 @@ def test_remaining_transport_sum_is_order_invariant_and_exact():
     u2[:, G.pj(G.jsc):G.pj(G.jec) + 1, G.pI(G.isc) - 1:G.pI(G.iec) + 1] = 3.0
     n = (G.iec - G.isc + 1) * (G.jec - G.jsc + 1) * c.GV.ke
     assert oracle.remaining_transport_sum(u2, v2, h, G, c.GV) == 3.0 * n
+
+
+# ---- the CUDA entry point (through the C ABI) against the oracle -------------------------------------------------
+def _gpu_run(c, CS, num_off_iter, x_before_y=True, min_residual=0.0):
+    from mom6_b200 import capi
+    p = capi.Plan(c.G, c.GV, CS)
+    p.set_ntr(c.ntr)
+    R0 = synth.bind_registry(c)
+    for m in range(c.ntr):
+        p.upload_tracer(m, R0.Tr[m].t)
+        p.bind_tracer(m, None, c.conc_underflow(m))
+    p.upload_field(capi.F_H_END, c.h_end.numpy()); p.upload_field(capi.F_UHTR, c.uhtr.numpy()); p.upload_field(capi.F_VHTR, c.vhtr.numpy())
+    conv, nit, res = p.offline_advect(c.dt, num_off_iter, x_before_y=x_before_y, min_residual=min_residual, **UNITS)
+    nk = c.GV.ke
+    T = []
+    for m in range(c.ntr):
+        o = np.zeros(c.G.shape_h(nk)); p.download_tracer(m, o); T.append(o)
+    h, u, v = np.zeros(c.G.shape_h(nk)), np.zeros(c.G.shape_u(nk)), np.zeros(c.G.shape_v(nk))
+    p.download_field(capi.F_H_END, h); p.download_field(capi.F_UHR, u); p.download_field(capi.F_VHR, v)
+    p.destroy()
+    return T, h, u, v, conv, nit, res
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kw", [dict(), dict(cyclic_x=False), dict(symmetric=False), dict(cyclic_y=True), dict(tripolar_n=True)])
+@pytest.mark.parametrize("scheme,x_before_y", [("PPM", True), ("PLM", False), ("PPM:H3", True)])
+def test_cuda_offline_loop_bitwise(kw, scheme, x_before_y):
+    c, CS = _case(scheme, ni=70, nj=29, **kw)
+    Ro, h, u, v, conv, nit, res = _run(oracle.offline_advection_loop, c, CS, 8, x_before_y)
+    Tg, hg, ug, vg, convg, nitg, resg = _gpu_run(c, CS, 8, x_before_y)
+    assert (conv, nit) == (convg, nitg) and nit >= 2
+    assert eq(res, resg), (res, resg)                       # every remaining_transport_sum, bitwise
+    G = c.G
+    for m in range(c.ntr):
+        assert eq(G.interior(Ro.Tr[m].t), G.interior(Tg[m])), "tracer %d" % m
+    # h_pre, uhtr, vhtr: whole arrays less the outermost halo row either side (the plan's pass moves the rows
+    # advect_tracer can read, the reference's pass_var / pass_vector all of them)
+    assert eq(h[:, 1:-1, :], hg[:, 1:-1, :])
+    assert eq(G.interior_u(u), G.interior_u(ug)) and eq(G.interior_v(v), G.interior_v(vg))
+    assert eq(u[:, 1:-1, :], ug[:, 1:-1, :]) and eq(v[:, 2:-1, :], vg[:, 2:-1, :])
+
+
+@pytest.mark.gpu
+def test_cuda_offline_loop_exit_paths_and_refusals():
+    from mom6_b200 import capi
+    c, CS = _case("PPM", cfl=0.4)
+    T, h, u, v, conv, nit, res = _gpu_run(c, CS, 6)
+    Ro, ho, uo, vo, convo, nito, reso = _run(oracle.offline_advection_loop, c, CS, 6)
+    assert conv and convo and nit == nito and eq(res, reso) and res[-1] == 0.0
+    c, CS = _case("PPM", cfl=2.4)
+    Ro, ho, uo, vo, convo, nito, reso = _run(oracle.offline_advection_loop, c, CS, 8, min_residual=1e30)
+    T, h, u, v, conv, nit, res = _gpu_run(c, CS, 8, min_residual=1e30)
+    assert (not conv) and nit == nito == 1 and eq(res, reso)
+    for m in range(c.ntr):
+        assert eq(c.G.interior(Ro.Tr[m].t), c.G.interior(T[m]))
+    p = capi.Plan(c.G, c.GV, CS)
+    p.set_ntr(1)
+    with pytest.raises(capi.Mom6AdvError):
+        p.offline_advect(c.dt, 4, off_ale_mod=2)          # the ALE step is not built: refused, not skipped
+    with pytest.raises(capi.Mom6AdvError):
+        p.offline_advect(c.dt, 0)
+    p.destroy()
