@@ -200,8 +200,9 @@ int mom6adv_accumulate_transports(mom6adv_plan *plan, const double *uh, const do
  * max_iter_in = 1, update_vol_prev = .true., uhr_out = uhtr, vhr_out = vhtr (:334-336).  dt_offline, num_off_iter,
  * off_ale_mod, x_before_y, min_residual are the offline_transport_CS members; H_to_kg_m2, kg_m2_to_H are GV's and L_to_m,
  * m_to_L are US's (:636, :647).  The ALE step inside the loop (:346-380) is other modules' work and is not built: the
- * call returns MOM6ADV_ERR_UNSUPPORTED if MODULO(iter, off_ale_mod) == 0 for any iter <= num_off_iter; multi-block
- * plans likewise.  Halos of the outputs are valid to the plan's exchange depth. */
+ * call returns MOM6ADV_ERR_UNSUPPORTED if MODULO(iter, off_ale_mod) == 0 for any iter <= num_off_iter.  On a multi-block
+ * plan the call is collective (group passes, an all-reduce of the sum's six integers).  Halos of the outputs are valid to
+ * the plan's exchange depth. */
 int mom6adv_offline_advect(mom6adv_plan *plan, double dt_offline, int num_off_iter, int off_ale_mod, int x_before_y,
                            double min_residual, double H_to_kg_m2, double L_to_m, double kg_m2_to_H, double m_to_L,
                            int *converged, int *n_iter, double *tot_residual);
@@ -268,7 +269,9 @@ long long mom6adv_halo_bytes(const mom6adv_plan *plan);
  * send/recv; choose before the first advect call; "pull2" 0/1 -- 1 (default): 16-byte pair-list peer loads;
  * "dirty" 0/1 -- 1 (default): after a list-driven trip the tracer pulls skip the tiles the owner has not changed;
  * "overlap" 0/1 -- 1 (default): on 1 x N layouts the tracer halo rows of the first pass travel under the x
- * sweep of the interior rows. */
+ * sweep of the interior rows; "obc_multi" 0/1 -- 0 (default): mom6adv_set_obc refuses an associated OBC on a
+ * multi-block plan; 1: EXPERIMENTAL, every rank hands over its own clipped, locally indexed segments -- equal to the
+ * 1-PE run on layouts split in y only, not yet on layouts split in x. */
 int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value);
 /* Kernel classes of the per-class timers: the stand-ins for the reference's
  * (Ocean advect tracer) / (Ocean tracer halo updates) / (Ocean tracer global

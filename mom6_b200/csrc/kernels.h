@@ -123,6 +123,8 @@ void launch_hd_apply(cudaStream_t s, const Geom &g, const HdParams &p, const TrT
 
 // offline.cu: the iteration loop of offline_advection_ale (MOM_offline_main.F90:254-415), element-wise parts
 void launch_off_init(cudaStream_t s, const Geom &g, double *h);
+void launch_off_halos(cudaStream_t s, const Geom &g, bool keep_w, bool keep_s, const double *hprev, const double *uhr,
+                      const double *vhr, double *h, double *usub, double *vsub);
 void launch_off_vol(cudaStream_t s, const Geom &g, const double *h, const double *areaT, double *vol);
 void launch_off_post(cudaStream_t s, const Geom &g, const double *vol, const double *IareaT, double *h, const double *uhr,
                      const double *vhr, double *usub, double *vsub);

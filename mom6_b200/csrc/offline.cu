@@ -43,6 +43,25 @@ k_off_post(Geom g, const double *__restrict__ vol, const double *__restrict__ Ia
   vsub[q] = vhr[q];
 }
 
+// After the group pass of (hprev = h_new, uhr, vhr): everything outside the copies of :382-385 (i = is..ie, j = js..je)
+// goes to h_new, uhtr_sub, vhtr_sub.  That includes the symmetric-memory boundary faces is-1 / js-1 where they have an
+// owner: pass_vector delivers the neighbouring PE's (or the periodic image's) value of that same face, which is the
+// value this PE computed for it itself -- uhr / vhr hold it.  On a closed edge of the global domain the face has no
+// owner and keeps its value (keep_w / keep_s).
+__global__ void __launch_bounds__(OFF_TX * OFF_TY)
+k_off_halos(Geom g, int keep_w, int keep_s, const double *__restrict__ hprev, const double *__restrict__ uhr,
+            const double *__restrict__ vhr, double *__restrict__ h, double *__restrict__ usub, double *__restrict__ vsub) {
+  const int col = blockIdx.x * OFF_TX + threadIdx.x, row = blockIdx.y * OFF_TY + threadIdx.y, k = blockIdx.z;
+  if (col >= g.P || row >= g.R) return;
+  const int i = col - g.coff, j = row - g.roff;
+  const long long q = (long long)row * g.P + col + g.plane * k;
+  const bool iin = (i >= g.isc && i <= g.iec), jin = (j >= g.jsc && j <= g.jec);
+  if (iin && jin) return;
+  if (i >= g.isd && i <= g.ied && j >= g.jsd && j <= g.jed) h[q] = hprev[q];
+  if (i >= g.IsdB && i <= g.ied && j >= g.jsd && j <= g.jed && !(keep_w && i == g.isc - 1 && jin)) usub[q] = uhr[q];
+  if (i >= g.isd && i <= g.ied && j >= g.JsdB && j <= g.jed && !(keep_s && j == g.jsc - 1 && iin)) vsub[q] = vhr[q];
+}
+
 // remaining_transport_sum, :638-644, and the conversion of each column's value to extended-fixed-point integers
 // (MOM_coms.F90:597-626 increment_ints_faster).  The integer sums are order-independent, so a block sums its columns'
 // integers, carries exactly (every limb below 2**46 again) and adds them to six global accumulators; the host finishes
@@ -95,6 +114,11 @@ k_off_residual(Geom g, const double *__restrict__ u, const double *__restrict__ 
 void launch_off_init(cudaStream_t s, const Geom &g, double *h) {
   dim3 grid((g.P + OFF_TX - 1) / OFF_TX, (g.R + OFF_TY - 1) / OFF_TY, g.nk), block(OFF_TX, OFF_TY);
   k_off_init<<<grid, block, 0, s>>>(g, h);
+}
+void launch_off_halos(cudaStream_t s, const Geom &g, bool keep_w, bool keep_s, const double *hprev, const double *uhr,
+                      const double *vhr, double *h, double *usub, double *vsub) {
+  dim3 grid((g.P + OFF_TX - 1) / OFF_TX, (g.R + OFF_TY - 1) / OFF_TY, g.nk), block(OFF_TX, OFF_TY);
+  k_off_halos<<<grid, block, 0, s>>>(g, keep_w ? 1 : 0, keep_s ? 1 : 0, hprev, uhr, vhr, h, usub, vsub);
 }
 void launch_off_vol(cudaStream_t s, const Geom &g, const double *h, const double *areaT, double *vol) {
   dim3 grid((g.iec - g.isc + OFF_TX) / OFF_TX, (g.jec - g.jsc + OFF_TY) / OFF_TY, g.nk), block(OFF_TX, OFF_TY);

@@ -79,8 +79,7 @@ struct mom6adv_plan {
   int *domore_u = nullptr, *domore_v = nullptr, *entry_u = nullptr, *entry_v = nullptr, *domore_k = nullptr;
   int *sum_dev = nullptr, *sum_host = nullptr, *sum_host_dev = nullptr;   // sum_host: mapped pinned; sum_host_dev: its device alias
   double *staging = nullptr;
-  double **off_tab = nullptr;                       // mom6adv_offline_advect: [h_end, uhtr, vhtr, uhr, vhr] for its passes
-  unsigned long long *off_acc = nullptr;            // ... and the six integers of its reproducing sum
+  unsigned long long *off_acc = nullptr;            // mom6adv_offline_advect: the six integers of its reproducing sum
   double *khdt_x = nullptr, *khdt_y = nullptr;      // mom6adv_hordiff: 2-D diffusivity-times-dt fields (allocated on first use)
   double *stage_in = nullptr;        // MIRROR pipeline: ring of contiguous upload slots (slots x chunk x Fortran-layout tracer)
   long long stage_in_elems = 0;
@@ -126,6 +125,7 @@ struct mom6adv_plan {
   int opt_sp_cap = 0;                // estimated list length above which a residual trip takes the dense kernels (0: cells/16)
   // open boundaries (mom6adv_set_obc)
   bool obc_active = false;
+  bool obc_global = false;                  // some PE has an open boundary (the *_exist_globally flags): every rank keeps to dense trips
   int obc_flags[4] = {0, 0, 0, 0};          // open_u, open_v, specified_u, specified_v ..._BCs_exist_globally
   std::vector<ObcSeg> obc_segs;
   std::vector<ObcTr> obc_trs;
@@ -136,6 +136,7 @@ struct mom6adv_plan {
   long long obc_cond_bytes = 0;
   double *obc_ttmp = nullptr, *obc_slope = nullptr, *obc_fx = nullptr, *obc_hh2 = nullptr, *maskT = nullptr;
   int opt_trace = 0;                 // print the MIRROR pipeline's copy/compute times to stderr
+  int opt_obc_multi = 0;             // experimental: accept open boundaries on a multi-block plan (see mom6adv_set_obc)
   int opt_sparse = 1;                // list-driven tracer update on residual iterations (sparse.cu)
   int *sp_list = nullptr; int sp_cap = 0;      // cells the residual trip updates (capacity: every cell, it cannot overflow)
   long long est_cells[2] = {-1, -1};      // host's estimate of the next trip's list length per direction (-1: unknown)
@@ -611,7 +612,6 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   }
   if (plan->comm) ncclCommDestroy(plan->comm);
   if (plan->sp_list) cudaFree(plan->sp_list);
-  if (plan->off_tab) cudaFree(plan->off_tab);
   if (plan->off_acc) cudaFree(plan->off_acc);
   if (plan->khdt_x) cudaFree(plan->khdt_x);
   if (plan->khdt_y) cudaFree(plan->khdt_y);
@@ -656,8 +656,17 @@ extern "C" int mom6adv_set_obc(mom6adv_plan *plan, const mom6adv_obc *obc) {
   CK(cudaSetDevice(plan->device));
   CK(cudaStreamSynchronize(plan->stream));
   free_obc(plan);
+  plan->obc_global = obc && (obc->open_u_BCs_exist_globally || obc->open_v_BCs_exist_globally ||
+                             obc->specified_u_BCs_exist_globally || obc->specified_v_BCs_exist_globally);
   if (!obc || !obc->OBC_pe) return MOM6ADV_OK;                 // unassociated / no segment on this PE (:442, :580)
-  if (plan->multi) return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "set_obc: open boundaries on a multi-block plan are not supported");
+  // Multi-block plans: refused unless the option "obc_multi" is set.  With it every rank hands over ITS segments,
+  // clipped to its data domain and in its local indices, exactly as setup_segment_indices leaves segment%HI on each PE
+  // (MOM_open_boundary.F90:1296-1328); a rank whose segments are all off its tile passes OBC_pe = false and takes the
+  // plain sweeps.  State of that path: layouts split in y (1 x N) equal the 1-PE run bitwise
+  // for all three schemes; layouts split in x differ from it in the SECOND trip of a call at a handful of cells next to
+  // the N/S segments (first trip, both sweep orders: equal, remaining transports included) -- cause not found.
+  if (plan->multi && !plan->opt_obc_multi)
+    return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "set_obc: open boundaries on a multi-block plan are not supported (experimental: option obc_multi)");
   if (obc->number_of_segments < 0 || (obc->number_of_segments > 0 && !obc->segment))
     return fail(plan, MOM6ADV_ERR_INVALID, "set_obc: bad segment list");
   const Geom &g = plan->g;
@@ -672,6 +681,11 @@ extern "C" int mom6adv_set_obc(mom6adv_plan *plan, const mom6adv_obc *obc) {
     sg.isd = h.isd; sg.ied = h.ied; sg.jsd = h.jsd; sg.jed = h.jed;
     sg.IsdB = h.IsdB; sg.IedB = h.IedB; sg.JsdB = h.JsdB; sg.JedB = h.JedB;
     sg.ntseg = std::max(h.ntseg, 0); sg.tr_off = (int)plan->obc_trs.size();
+    if (!sg.is_ew && !sg.is_ns) {      // a segment that is not on this PE (MOM_open_boundary.F90:1443-1447 return before the flags are set): keeps its number, does nothing
+      sg.has_reg = false; sg.ntseg = 0; sg.cond_off = cond_bytes;
+      plan->obc_segs.push_back(sg);
+      continue;
+    }
     if (sg.is_ew == sg.is_ns) return fail(plan, MOM6ADV_ERR_INVALID, "set_obc: a segment must be either E/W or N/S");
     // the faces and the cells next to them must lie inside the data domain (the reference indexes them unchecked)
     const bool ok = sg.is_ew ? (sg.IsdB - 2 >= g.isd && sg.IsdB + 3 <= g.ied && sg.jsd >= g.jsd && sg.jed <= g.jed && sg.jsd <= sg.jed)
@@ -769,7 +783,13 @@ static int sweep_obc(mom6adv_plan *plan, int dir, Range rg, double Idt, int sche
     if (a2) { launch_obc_ad2d(s, dir, g, rg, a2, plan->obc_fx, plan->ihnew, ent, plan->domore_k, Idt); plan->launches++; }
     plan->launches += 2;
   }
-  plan->cur = 1 - plan->cur;
+  // x is out of place; y too, but its result goes back into the buffer it read, so that the live buffer alternates
+  // exactly as on the streaming path (x flips, y in place): on a multi-block plan the ranks without a segment take
+  // that path, and the neighbours' pulls address the live buffer by the common count of flips
+  if (x) plan->cur = 1 - plan->cur;
+  else
+    for (int m = plan->m_lo; m < plan->m_hi; m++)
+      CK(cudaMemcpyAsync(plan->tr[m].buf[plan->cur], plan->tr[m].buf[1 - plan->cur], sizeof(double) * fe, cudaMemcpyDeviceToDevice, s));
   CK(cudaGetLastError());
   return 0;
 }
@@ -928,17 +948,19 @@ static int setup_ipc(mom6adv_plan *plan) {
   return 0;
 }
 
-static int group_pass(mom6adv_plan *plan, bool first_of_call, bool defer_tracers, bool tracers_only = false) {
+enum { PASS_ALL = 0, PASS_TRACERS = 1, PASS_MASS = 2 };
+static int group_pass(mom6adv_plan *plan, bool first_of_call, bool defer_tracers, int what = PASS_ALL) {
   const Geom &g = plan->g;
   cudaStream_t s = plan->stream;
   ProfScope ps(plan, MOM6ADV_KC_HALO);
   // u list -> uhr, v list -> vhr, h list -> hprev + tracers (live buffer)
-  const int nact = plan->m_hi - plan->m_lo;
+  // PASS_MASS: uhr, vhr, hprev without the tracers (the offline loop's pass_var / pass_vector, MOM_offline_main.F90:386-387)
+  const int nact = (what == PASS_MASS) ? 0 : plan->m_hi - plan->m_lo;
   double **tab = plan->halo_fields_dev + plan->cur * (3 + plan->ntr);
   // field-table segments by stagger: h = hprev + the active tracers, u = uhr, v = vhr
   struct Seg { double **t; int n; };
   // tracers_only: CS%pass_t of tracer_hordiff (MOM_tracer_hor_diff.F90:540) -- no hprev / uhr / vhr
-  const int nm = tracers_only ? 0 : 1;
+  const int nm = (what == PASS_TRACERS) ? 0 : 1;
   const Seg segs[3][2] = {{{tab + 2, nm}, {tab + 3 + plan->m_lo, nact}}, {{tab + 0, nm}, {nullptr, 0}}, {{tab + 1, nm}, {nullptr, 0}}};
   // (1) halo points whose source lies in this rank's own block (cyclic wrap / fold onto itself)
   for (int pos = 0; pos < 3; pos++) for (const Seg &sg : segs[pos]) if (sg.n > 0) {
@@ -1094,7 +1116,10 @@ static int sweep_impl(mom6adv_plan *plan, int dir, Range rg, double Idt, int sch
     if (plan->tr[m].diag[dir == 0 ? 2 : 3]) any_ad2d = true;
     for (int d = 0; d < 5; d++) if (plan->tr[m].diag[d]) any_diag = true;
   }
-  if (plan->obc_active) return sweep_obc(plan, dir, rg, Idt, scheme);
+  if (plan->obc_active) {
+    if (plan->pull_pending) { CK(cudaStreamWaitEvent(s, plan->ev_pull_done, 0)); plan->pull_pending = false; }
+    return sweep_obc(plan, dir, rg, Idt, scheme);
+  }
   const bool split_rows = plan->pull_pending && dir == 0 && plan->opt_fast && itt == 1;
   if (plan->pull_pending && !split_rows) {            // any other consumer needs the halo rows now
     CK(cudaStreamWaitEvent(s, plan->ev_pull_done, 0));
@@ -1110,7 +1135,7 @@ static int sweep_impl(mom6adv_plan *plan, int dir, Range rg, double Idt, int sch
     // buffers, so the list cannot overflow and the host never waits inside a sweep.  Whether a trip is worth the
     // list-driven kernels is a host-side HINT from the previous trip's counts (either choice gives the same bits).
     const long long dense_above = plan->opt_sp_cap > 0 ? plan->opt_sp_cap : std::max<long long>(4096, field_elems(plan) / 16);
-    bool sparse = plan->opt_sparse && itt >= 2 && field_elems(plan) < (1LL << 31) &&
+    bool sparse = plan->opt_sparse && itt >= 2 && !(plan->multi && plan->obc_global) && field_elems(plan) < (1LL << 31) &&
                   (plan->est_cells[dir] < 0 || plan->est_cells[dir] <= dense_above);
     plan->est_dense[dir] = !sparse;
     if (sparse && !plan->sp_list) {
@@ -1349,7 +1374,7 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
       bool defer = false;
       // (deferred only when the convergence all-reduce of this trip is certain to follow -- nsten_halo == 1 and more
       // than one trip allowed: it is what orders the neighbours' deferred reads before anybody's next writes)
-      if (itt == 1 && x_first && plan->opt_overlap && plan->opt_fast && plan->dom.npi == 1 && halo_min / stencil == 1 && max_iter > 1) {
+      if (itt == 1 && x_first && plan->opt_overlap && plan->opt_fast && !plan->obc_active && plan->dom.npi == 1 && halo_min / stencil == 1 && max_iter > 1) {
         defer = true;
         for (int m = m_lo; m < m_hi; m++) for (int d = 0; d < 5; d++) if (plan->tr[m].diag[d]) defer = false;
       }
@@ -1390,6 +1415,10 @@ static int run_advect(mom6adv_plan *plan, double dt, int x_first_in, int max_ite
       launch_sum_domore_k(s, plan->domore_k, g.nk, plan->sum_dev);          // :307 do_any
       plan->launches += 1;
     }
+    // multi-block: the list-driven trip leaves the live buffer where it is and the dense one flips it, so every rank
+    // must take the same kind of trip -- the hint becomes the maximum over the ranks
+    if (plan->multi && plan->comm && (test || itt == 1))
+      CKN(ncclAllReduce(plan->sum_dev + 4, plan->sum_dev + 4, 2, ncclInt, ncclMax, plan->comm, s));
     if (test || want_est) {
       launch_publish(s, plan->sum_host_dev, plan->sum_dev, 6);
       CK(cudaStreamSynchronize(s));
@@ -1608,7 +1637,7 @@ extern "C" int mom6adv_hordiff(mom6adv_plan *plan, const double *h, const double
   plan->launches++;
   for (int itt = 1; itt <= num_itts; itt++) {                               // :539
     // every rank's previous iteration must be complete before its rows are read: the opening fence each time
-    { int rc2 = group_pass(plan, true, false, true); if (rc2) return rc2; } // :540
+    { int rc2 = group_pass(plan, true, false, PASS_TRACERS); if (rc2) return rc2; } // :540
     const int src = plan->cur;
     for (int m0 = 0; m0 < plan->ntr; m0 += MOM6ADV_MAXT) {
       TrTable tt;
@@ -1649,10 +1678,12 @@ static int offline_residual(mom6adv_plan *plan, const double *u, const double *v
   CK(cudaMemsetAsync(plan->off_acc, 0, sizeof(unsigned long long) * 6, s));
   launch_off_residual(s, plan->g, u, v, plan->h_end, plan->areaT, plan->H_subroundoff, HL2_to_kg_scale, plan->off_acc);
   plan->launches++;
+  if (plan->multi && plan->comm)                                             // sum_across_PEs of the integers, MOM_coms.F90:195-197
+    CKN(ncclAllReduce(plan->off_acc, plan->off_acc, 6, ncclUint64, ncclSum, plan->comm, s));
   long long ints[6];
   CK(cudaMemcpyAsync(ints, plan->off_acc, sizeof ints, cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
-  // (sum_across_PEs of the integers: single block) ; regularize_ints, MOM_coms.F90:653-691
+  // regularize_ints, MOM_coms.F90:653-691
   const long long prec = 1LL << 46;
   const double r_prec = 70368744177664.0, I_prec = 1.0 / 70368744177664.0;
   for (int i = 5; i >= 1; i--) if (std::llabs(ints[i]) >= prec) {
@@ -1678,31 +1709,28 @@ extern "C" int mom6adv_offline_advect(mom6adv_plan *plan, double dt_offline, int
   if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "offline_advect: plan not initialised");
   if (converged_out) *converged_out = 0;
   if (n_iter_out) *n_iter_out = 0;
-  if (plan->multi) return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "offline_advect: multi-block plans are not supported (the loop's pass_var / pass_vector and its sum across PEs are single-block here)");
   if (num_off_iter < 1) return fail(plan, MOM6ADV_ERR_INVALID, "offline_advect: num_off_iter must be >= 1");
   for (int iter = 1; iter <= num_off_iter; iter++)
     if (off_ale_mod <= 0 || iter % off_ale_mod == 0)
       return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "offline_advect: the ALE step inside the loop (MODULO(iter, off_ale_mod) == 0) is not built; keep the Fortran loop for such runs");
   if (plan->ntr == 0) return fail(plan, MOM6ADV_ERR_INVALID, "offline_advect: no tracers registered");
+  if (plan->multi && !plan->comm) return fail(plan, MOM6ADV_ERR_COMM, "offline_advect: mom6adv_comm_init has not been called on this multi-block plan");
   const Geom &g = plan->g;
   CK(cudaSetDevice(plan->device));
   cudaStream_t s = plan->stream;
   int rc;
   if (!plan->vol_prev && (rc = dev_alloc(plan, &plan->vol_prev, field_elems(plan)))) return rc;
-  if (!plan->off_tab) {
-    double *tab[5] = {plan->h_end, plan->uhtr, plan->vhtr, plan->uhr, plan->vhr};
-    CK(cudaMalloc((void **)&plan->off_tab, sizeof tab));
-    CK(cudaMemcpy(plan->off_tab, tab, sizeof tab, cudaMemcpyHostToDevice));
-    CK(cudaMalloc((void **)&plan->off_acc, sizeof(unsigned long long) * 6));
-  }
-  auto pass1 = [&](int pos, int slot) {      // pass_var / one component of pass_vector on the single-block lists
-    launch_halo_apply(s, g.plane, g.nk, plan->halo[pos].dst, plan->halo[pos].src, plan->halo[pos].sgn, plan->halo[pos].n,
-                      plan->off_tab + slot, 1);
-    plan->launches++;
-  };
+  if (!plan->off_acc) CK(cudaMalloc((void **)&plan->off_acc, sizeof(unsigned long long) * 6));
+  const size_t fb = sizeof(double) * (size_t)field_elems(plan);
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
   CK(cudaEventRecord(e0, s));
+  plan->m_lo = 0; plan->m_hi = plan->ntr; plan->cur = plan->tr[0].cur;
+  if ((rc = prepare_exchange(plan))) return rc;
+  // symmetric memory: the boundary faces is-1 / js-1 have an owner unless they lie on a closed edge of the global domain
+  const bool symmetric = (g.IsdB == g.isd - 1);
+  const bool keep_w = symmetric && !plan->dom.cyclic_x && (g.isc - 1 + plan->dom.ioff < 1);
+  const bool keep_s = symmetric && !plan->dom.cyclic_y && (g.jsc - 1 + plan->dom.joff < 1);
   bool x_before_y = x_before_y_in != 0;                                      // :254
   const double HL2_to_kg_scale = H_to_kg_m2 * (L_to_m * L_to_m);             // :636
   const double rts_scale = 0.5 * kg_m2_to_H * (m_to_L * m_to_L);             // :647
@@ -1721,8 +1749,14 @@ extern "C" int mom6adv_offline_advect(mom6adv_plan *plan, double dt_offline, int
     if ((rc = run_advect(plan, dt_offline, x_before_y ? 1 : 0, 1, true, true, nullptr, 0, plan->ntr))) return rc;   // :334-336
     x_before_y = !x_before_y;                                                // :339
     launch_off_post(s, g, plan->vol_prev, plan->IareaT, plan->h_end, plan->uhr, plan->vhr, plan->uhtr, plan->vhtr);   // :342-344, :382-385
-    plan->launches++;
-    pass1(0, 0); pass1(1, 1); pass1(2, 2);                                   // :386-387
+    // :386-387 pass_var(h_new) ; pass_vector(uhtr_sub, vhtr_sub) through the plan's group pass, which moves hprev, uhr
+    // and vhr: h_new rides in hprev; uhr / vhr ARE uhtr / vhtr, equal to uhtr_sub / vhtr_sub on the computational
+    // faces, and their halo faces take the owner's value of the same face (the bits this rank computed itself).  The
+    // halos then go where the reference has them: h_new's, uhtr_sub's, vhtr_sub's.
+    CK(cudaMemcpyAsync(plan->hprev, plan->h_end, fb, cudaMemcpyDeviceToDevice, s));
+    if ((rc = group_pass(plan, true, false, PASS_MASS))) return rc;
+    launch_off_halos(s, g, keep_w, keep_s, plan->hprev, plan->uhr, plan->vhr, plan->h_end, plan->uhtr, plan->vhtr);
+    plan->launches += 2;
     if ((rc = offline_residual(plan, plan->uhr, plan->vhr, HL2_to_kg_scale, rts_scale, &tot_residual))) return rc;   // :391
     if (tot_residual_out) tot_residual_out[nrec] = tot_residual;
     nrec++;
@@ -1730,7 +1764,7 @@ extern "C" int mom6adv_offline_advect(mom6adv_plan *plan, double dt_offline, int
     if ((tot_residual == prev_tot_residual) || (tot_residual < min_residual)) { converged = false; break; }   // :404-407
     prev_tot_residual = tot_residual;                                        // :409
   }
-  pass1(1, 3); pass1(2, 4);                                                  // :415 pass_vector(uhtr, vhtr)  (:414: h_pre is h_new already)
+  // :414 h_pre is h_new already ; :415 pass_vector(uhtr, vhtr): uhr / vhr were passed in place after the last trip
   CK(cudaEventRecord(e1, s));
   CK(cudaStreamSynchronize(s));
   float ms = 0.f;
@@ -1946,6 +1980,7 @@ extern "C" int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value
   if (!strcmp(key, "dirty")) { plan->opt_dirty = value; return MOM6ADV_OK; }
   if (!strcmp(key, "pull2")) { plan->opt_pull2 = value; return MOM6ADV_OK; }
   if (!strcmp(key, "sparse")) { plan->opt_sparse = value; return MOM6ADV_OK; }
+  if (!strcmp(key, "obc_multi")) { plan->opt_obc_multi = value; return MOM6ADV_OK; }
   if (!strcmp(key, "mirror_chunk")) { plan->opt_chunk = value; return MOM6ADV_OK; }
   if (!strcmp(key, "mirror_ahead")) { plan->opt_ahead = value; return MOM6ADV_OK; }
   if (!strcmp(key, "pull")) { if (plan->ipc_ntr >= 0 && value != plan->opt_pull) return fail(plan, MOM6ADV_ERR_INVALID, "set_option: pull must be chosen before the first advect call"); plan->opt_pull = value; return MOM6ADV_OK; }

@@ -88,3 +88,52 @@ def paste_interior(Gg: OceanGrid, G: OceanGrid, a_global: np.ndarray, a_local: n
     gi0 = G.isc + G.ioff - Gg.ioff - Gg.isd
     gj0 = G.jsc + G.joff - Gg.joff - Gg.jsd
     a_global[..., gj0:gj0 + G.nj, gi0:gi0 + G.ni] = G.interior(a_local)
+
+
+def cut_obc(OBC, Gg: OceanGrid, G: OceanGrid):
+    """The ocean_OBC_type a PE holds for the global open boundaries OBC: every segment's index ranges moved into local
+    index space and clipped to the PE's data domain as setup_segment_indices does
+    (/root/reference/src/core/MOM_open_boundary.F90:1296-1328), `on_pe` by the rule of setup_u_point_obc /
+    setup_v_point_obc (:1443-1447: the face at least two points inside the data domain, the range overlapping it), the
+    reservoirs cut to the local segment shape.  A segment that is not on the PE keeps its place in the list with
+    is_E_or_W = is_N_or_S = False and no registry (:1446 returns before they are set), so segment numbers agree on all
+    PEs.  OBC_pe is true where any segment is on the PE; the *_exist_globally flags are global."""
+    from .types import OceanOBC, OBCSegment, OBCSegmentTracer, SegmentHI
+    if OBC is None:
+        return None
+    di, dj = G.ioff - Gg.ioff, G.joff - Gg.joff        # local = global-grid index - d
+    clip = lambda v, lo, hi: min(max(v, lo), hi)
+    segs, any_on = [], False
+    for sg in OBC.segment:
+        H = sg.HI
+        hi = SegmentHI(isd=clip(H.isd - di, G.isd, G.ied), ied=clip(H.ied - di, G.isd, G.ied),
+                       jsd=clip(H.jsd - dj, G.jsd, G.jed), jed=clip(H.jed - dj, G.jsd, G.jed),
+                       IsdB=clip(H.IsdB - di, G.IsdB, G.IedB), IedB=clip(H.IedB - di, G.IsdB, G.IedB),
+                       JsdB=clip(H.JsdB - dj, G.JsdB, G.JedB), JedB=clip(H.JedB - dj, G.JsdB, G.JedB))
+        if sg.is_E_or_W:
+            I_obc, Js_obc, Je_obc = H.IsdB - di, H.JsdB - dj, H.JedB - dj
+            on = not (I_obc <= G.IsdB + 1 or I_obc >= G.IedB - 1) and not (Je_obc <= G.JsdB or Js_obc >= G.JedB)
+        else:
+            J_obc, Is_obc, Ie_obc = H.JsdB - dj, H.IsdB - di, H.IedB - di
+            on = not (J_obc <= G.JsdB + 1 or J_obc >= G.JedB - 1) and not (Ie_obc <= G.IsdB or Is_obc >= G.IedB)
+        if not on:
+            segs.append(OBCSegment(direction=sg.direction, specified=sg.specified, HI=hi, tr_Reg=None))
+            continue
+        any_on = True
+        reg = None
+        if sg.tr_Reg is not None:
+            reg = []
+            for t in sg.tr_Reg:
+                tres = None
+                if t.tres is not None:
+                    if sg.is_E_or_W:      # [k, j, I] over (IsdB:IedB, jsd:jed)
+                        tres = np.ascontiguousarray(t.tres[:, hi.jsd + dj - H.jsd:hi.jed + dj - H.jsd + 1, hi.IsdB + di - H.IsdB:hi.IedB + di - H.IsdB + 1])
+                    else:                 # [k, J, i] over (isd:ied, JsdB:JedB)
+                        tres = np.ascontiguousarray(t.tres[:, hi.JsdB + dj - H.JsdB:hi.JedB + dj - H.JsdB + 1, hi.isd + di - H.isd:hi.ied + di - H.isd + 1])
+                reg.append(OBCSegmentTracer(ntr_index=t.ntr_index, tres=tres, OBC_inflow_conc=t.OBC_inflow_conc))
+        segs.append(OBCSegment(direction=sg.direction, is_E_or_W=sg.is_E_or_W, is_N_or_S=sg.is_N_or_S, specified=sg.specified,
+                               HI=hi, tr_Reg=reg))
+    return OceanOBC(OBC_pe=any_on, segment=segs, open_u_BCs_exist_globally=OBC.open_u_BCs_exist_globally,
+                    open_v_BCs_exist_globally=OBC.open_v_BCs_exist_globally,
+                    specified_u_BCs_exist_globally=OBC.specified_u_BCs_exist_globally,
+                    specified_v_BCs_exist_globally=OBC.specified_v_BCs_exist_globally)

@@ -1276,6 +1276,13 @@ extern "C" int ora_offline_advection_loop(const ora_grid *Gp, const ora_cs *CS, 
       vhtr_sub[qv(i, j, k)] = vhtr[qv(i, j, k)];
     }
     single_pass(&sctx, uhtr_sub.data(), vhtr_sub.data(), h_new.data(), Tr, 0);      // :386-387 pass_var(h_new) ; pass_vector(uhtr_sub, vhtr_sub)
+    // Symmetric memory: :382-385 leaves the boundary faces is-1 / js-1 to pass_vector, which delivers the neighbouring
+    // PE's (single PE: the periodic image's) value of the same face; a closed boundary has none and keeps its value.
+    // (The group-pass emulation used for advect_tracer counts those faces as computational and does not move them.)
+    if (dom->symmetric) {
+      if (dom->cyclic_x) for (int k = 1; k <= nz; k++) for (int j = G.jsd; j <= G.jed; j++) uhtr_sub[qu(is - 1, j, k)] = uhtr_sub[qu(ie, j, k)];
+      if (dom->cyclic_y) for (int k = 1; k <= nz; k++) for (int i = G.isd; i <= G.ied; i++) vhtr_sub[qv(i, js - 1, k)] = vhtr_sub[qv(i, je, k)];
+    }
     tot_residual = ora_remaining_transport_sum(Gp, uhtr, vhtr, h_new.data(), H_to_kg_m2, L_to_m, kg_m2_to_H, m_to_L);   // :391
     if (tot_residual_out) tot_residual_out[nrec] = tot_residual;
     nrec++;

@@ -67,7 +67,17 @@ void pass_fields(double *u, double *v, double *h) {
   ora_group_pass(1, &g_pass->rank, g_pass->dom, pu, pv, ph, 0);
 }
 template <class D> void pass_var(Arr<double, 3> h, D &&) { pass_fields(nullptr, nullptr, h.d); }
-template <class D> void pass_vector(Arr<double, 3> u, Arr<double, 3> v, D &&) { pass_fields(u.d, v.d, nullptr); }
+template <class D> void pass_vector(Arr<double, 3> u, Arr<double, 3> v, D &&) {
+  pass_fields(u.d, v.d, nullptr);
+  // symmetric memory: the boundary faces is-1 / js-1 take the neighbouring PE's (here: the periodic image's) value of
+  // the same face; the group-pass emulation counts them as computational and leaves them, so it is done here
+  const ora_grid &G = g_pass->rank.G;
+  const ora_domain *dom = g_pass->dom;
+  if (dom->symmetric) {
+    if (dom->cyclic_x) for (int k = u.lo[2]; k <= u.hi[2]; k++) for (int j = G.jsd; j <= G.jed; j++) u(G.isc - 1, j, k) = u(G.iec, j, k);
+    if (dom->cyclic_y) for (int k = v.lo[2]; k <= v.hi[2]; k++) for (int i = G.isd; i <= G.ied; i++) v(i, G.jsc - 1, k) = v(i, G.jec, k);
+  }
+}
 
 // reproducing_sum_2d(array, isr, ier, jsr, jer), MOM_coms.F90:219-318 with reproducing_EFP_sum_2d :119-213
 double reproducing_sum(Arr<double, 2> array, int isr, int ier, int jsr, int jer) {
