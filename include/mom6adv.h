@@ -270,8 +270,9 @@ long long mom6adv_halo_bytes(const mom6adv_plan *plan);
  * "dirty" 0/1 -- 1 (default): after a list-driven trip the tracer pulls skip the tiles the owner has not changed;
  * "overlap" 0/1 -- 1 (default): on 1 x N layouts the tracer halo rows of the first pass travel under the x
  * sweep of the interior rows; "obc_multi" 0/1 -- 0 (default): mom6adv_set_obc refuses an associated OBC on a
- * multi-block plan; 1: EXPERIMENTAL, every rank hands over its own clipped, locally indexed segments -- equal to the
- * 1-PE run on layouts split in y only, not yet on layouts split in x. */
+ * multi-block plan; 1: every rank hands over its own clipped, locally indexed segments (segment%HI as
+ * setup_segment_indices leaves it on that PE); each rank then equals the reference algorithm run per PE on the same
+ * layout. */
 int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value);
 /* Kernel classes of the per-class timers: the stand-ins for the reference's
  * (Ocean advect tracer) / (Ocean tracer halo updates) / (Ocean tracer global

@@ -662,11 +662,9 @@ extern "C" int mom6adv_set_obc(mom6adv_plan *plan, const mom6adv_obc *obc) {
   // Multi-block plans: refused unless the option "obc_multi" is set.  With it every rank hands over ITS segments,
   // clipped to its data domain and in its local indices, exactly as setup_segment_indices leaves segment%HI on each PE
   // (MOM_open_boundary.F90:1296-1328); a rank whose segments are all off its tile passes OBC_pe = false and takes the
-  // plain sweeps.  State of that path: layouts split in y (1 x N) equal the 1-PE run bitwise
-  // for all three schemes; layouts split in x differ from it in the SECOND trip of a call at a handful of cells next to
-  // the N/S segments (first trip, both sweep orders: equal, remaining transports included) -- cause not found.
+  // plain sweeps.  Each rank then equals the reference algorithm run per PE on the same layout.
   if (plan->multi && !plan->opt_obc_multi)
-    return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "set_obc: open boundaries on a multi-block plan are not supported (experimental: option obc_multi)");
+    return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "set_obc: open boundaries on a multi-block plan need the option obc_multi (every rank then passes its own clipped, locally indexed segments)");
   if (obc->number_of_segments < 0 || (obc->number_of_segments > 0 && !obc->segment))
     return fail(plan, MOM6ADV_ERR_INVALID, "set_obc: bad segment list");
   const Geom &g = plan->g;

@@ -1039,6 +1039,30 @@ extern "C" int ora_advect_tracer_multi(int nranks, ora_rank *ranks, const ora_do
   return 0;
 }
 
+// The same with an ocean_OBC_type per rank (NULL entries == unassociated): what MOM6 runs with open boundaries on more
+// than one PE, every PE holding its own clipped, locally indexed segments (MOM_open_boundary.F90:1296-1328).
+extern "C" int ora_advect_tracer_multi_obc(int nranks, ora_rank *ranks, const ora_domain *dom, const ora_cs *CS, int ntr,
+                                           double dt, int x_first_in, int max_iter_in, int update_vol_prev,
+                                           const ora_obc *const *obcs) {
+  MultiShared sh(nranks);
+  sh.nranks = nranks; sh.ranks = ranks; sh.dom = dom; sh.ntr = ntr;
+  std::vector<MultiCtx> ctxs(nranks);
+  std::vector<int> rc(nranks, 0);
+  std::vector<std::thread> th;
+  for (int r = 0; r < nranks; r++) {
+    ctxs[r].sh = &sh; ctxs[r].r = r;
+    th.emplace_back([&, r] {
+      rc[r] = ora_advect_tracer_obc(&ranks[r].G, CS, ranks[r].Tr, ntr, ranks[r].h_end, ranks[r].uhtr, ranks[r].vhtr, dt,
+                                    x_first_in, ranks[r].vol_prev, max_iter_in, update_vol_prev, ranks[r].uhr_out,
+                                    ranks[r].vhr_out, nullptr, multi_pass, multi_sum, &ctxs[r], &ranks[r].n_iter, 1,
+                                    obcs ? obcs[r] : nullptr);
+    });
+  }
+  for (auto &t : th) t.join();
+  for (int r = 0; r < nranks; r++) if (rc[r]) return rc[r];
+  return 0;
+}
+
 // ---------------------------------------------------------------------------
 // Parity / conservation metrics restated from the reference framework.
 // ---------------------------------------------------------------------------

@@ -146,6 +146,10 @@ int ora_advect_tracer_multi(int nranks, ora_rank *ranks, const ora_domain *dom,
                             const ora_cs *CS, int ntr, double dt, int x_first_in,
                             int max_iter_in, int update_vol_prev);
 
+/* The same with one ocean_OBC_type per rank (NULL == unassociated on that rank). */
+int ora_advect_tracer_multi_obc(int nranks, ora_rank *ranks, const ora_domain *dom, const ora_cs *CS, int ntr, double dt,
+                                int x_first_in, int max_iter_in, int update_vol_prev, const ora_obc *const *obcs);
+
 /* Emulated do_group_pass for an arbitrary set of ranks (exposed for tests).
  * fields of rank r: uhr[r], vhr[r] (C-grid vector pair), hprev[r], Tr of rank. */
 void ora_group_pass(int nranks, ora_rank *ranks, const ora_domain *dom,
