@@ -1814,9 +1814,27 @@ static int get(mom6adv_plan *plan, cudaStream_t st, double *dst, const double *d
 // repeated per chunk from the resident h_end/uhtr/vhtr: a few ms against the
 // ~75 ms a chunk spends on the bus.
 // ---------------------------------------------------------------------------
+static int advect_mirror(mom6adv_plan *plan, const double *h_end, const double *uhtr, const double *vhtr,
+                         double dt, int x_first, double *vol_prev, int max_iter_in, int update_vol_prev,
+                         double *uhr_out, double *vhr_out, int *n_iter);
 extern "C" int mom6adv_advect(mom6adv_plan *plan, const double *h_end, const double *uhtr, const double *vhtr,
                               double dt, int x_first, double *vol_prev, int max_iter_in, int update_vol_prev,
                               double *uhr_out, double *vhr_out, int *n_iter) {
+  const int rc = advect_mirror(plan, h_end, uhtr, vhtr, dt, x_first, vol_prev, max_iter_in, update_vol_prev, uhr_out,
+                               vhr_out, n_iter);
+  if (rc != MOM6ADV_OK && plan) {
+    // a failed call must not leave copies in flight against the caller's host arrays: drain the three streams
+    // (errors of the drain itself are not reported over the one that brought us here)
+    if (plan->s_in) cudaStreamSynchronize(plan->s_in);
+    if (plan->s_out) cudaStreamSynchronize(plan->s_out);
+    if (plan->stream) cudaStreamSynchronize(plan->stream);
+    cudaGetLastError();
+  }
+  return rc;
+}
+static int advect_mirror(mom6adv_plan *plan, const double *h_end, const double *uhtr, const double *vhtr,
+                         double dt, int x_first, double *vol_prev, int max_iter_in, int update_vol_prev,
+                         double *uhr_out, double *vhr_out, int *n_iter) {
   if (n_iter) *n_iter = 0;
   if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "advect: tracer_advect_init must be called before advect_tracer");
   if (plan->ntr == 0) return MOM6ADV_OK;   // :124
