@@ -51,3 +51,19 @@ def test_sweeps_do_not_spill_and_producer_is_uniform(scheme):
     assert ops.get("ELECT", 0) <= 2 and ops.get("R2UR", 0) <= 12, ops   # ... not through a per-lane ELECT / R2UR loop
     nx, fx, ox, opsx = _counts(_run("k_x_fastILi%dELb0E" % scheme, "--all"))
     assert opsx.get("LDL", 0) + opsx.get("STL", 0) == 0, opsx
+
+
+def test_hordiff_iteration_kernel_stages_through_shared_memory():
+    """k_hd_tile (tracer_hordiff's iteration): the tracer tiles arrive by asynchronous
+    global->shared copies (LDGSTS + LDGDEPBAR groups), the stencil is read from shared memory, nothing spills, and the
+    register count keeps three 512-thread blocks on an SM (65536 / (3 * 512) = 42)."""
+    n, f64, other, ops = _counts(_run("k_hd_tile", "--all"))
+    assert ops.get("LDGSTS", 0) >= 2 and ops.get("LDGDEPBAR", 0) >= 2, ops
+    assert ops.get("LDS.64", 0) + ops.get("LDS", 0) >= 5, ops
+    assert "LDL" not in ops and "STL" not in ops, ops
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    r = subprocess.run(["cuobjdump", "-res-usage", LIB], capture_output=True, text=True, timeout=300)
+    m = re.search(r"Function _Z9k_hd_tile[^\n]*:\s*\n\s*REG:(\d+)", r.stdout)
+    assert m, "k_hd_tile not found in the resource usage listing"
+    assert int(m.group(1)) <= 42, m.group(1)
