@@ -411,7 +411,16 @@ def run_hordiff_leg(plan, c, ni, nj, nk, ntr, peak, calls=3, warmup=2):
             "tracer_cell_updates_per_s": ni * nj * nk * ntr * nit / (ms * 1e-3), "gpu_launches": int(launches),
             "calls": calls, "warmup": warmup,
             "roofline": {"bound": "hbm", "kernel": "k_hd_tile", "achieved": alg / (it_ms * 1e-3) / 1e9, "peak": peak,
-                         "unit": "GB/s", "frac": alg / (it_ms * 1e-3) / 1e9 / peak, "alg_bytes_per_launch": alg}}
+                         "unit": "GB/s", "frac": alg / (it_ms * 1e-3) / 1e9 / peak, "alg_bytes_per_launch": alg,
+                         "traffic": _recorded_traffic("k_hd_tile") if (ni, nj, nk, ntr) == (1440, 1080, 75, 52) else None}}
+
+
+def _recorded_traffic(kernel, workload="OM4_025"):
+    """dram bytes per launch of `kernel` from the committed ncu capture (profiles/traffic.json), or None."""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(workload, {}).get(kernel)
+    except Exception:
+        return None
 
 
 def _stats_ms(per):
