@@ -80,6 +80,7 @@ struct mom6adv_plan {
   int *sum_dev = nullptr, *sum_host = nullptr, *sum_host_dev = nullptr;   // sum_host: mapped pinned; sum_host_dev: its device alias
   double *staging = nullptr;
   unsigned long long *off_acc = nullptr;            // mom6adv_offline_advect: the six integers of its reproducing sum
+  cudaEvent_t ev_off0 = nullptr, ev_off1 = nullptr;  // ... and the events around the whole loop (run_advect uses ev0 / ev1 inside it)
   double *khdt_x = nullptr, *khdt_y = nullptr;      // mom6adv_hordiff: 2-D diffusivity-times-dt fields (allocated on first use)
   double *stage_in = nullptr;        // MIRROR pipeline: ring of contiguous upload slots (slots x chunk x Fortran-layout tracer)
   long long stage_in_elems = 0;
@@ -613,6 +614,7 @@ extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
   if (plan->comm) ncclCommDestroy(plan->comm);
   if (plan->sp_list) cudaFree(plan->sp_list);
   if (plan->off_acc) cudaFree(plan->off_acc);
+  if (plan->ev_off0) { cudaEventDestroy(plan->ev_off0); cudaEventDestroy(plan->ev_off1); }
   if (plan->khdt_x) cudaFree(plan->khdt_x);
   if (plan->khdt_y) cudaFree(plan->khdt_y);
   if (plan->dirty) cudaFree(plan->dirty);
@@ -1720,8 +1722,8 @@ extern "C" int mom6adv_offline_advect(mom6adv_plan *plan, double dt_offline, int
   if (!plan->vol_prev && (rc = dev_alloc(plan, &plan->vol_prev, field_elems(plan)))) return rc;
   if (!plan->off_acc) CK(cudaMalloc((void **)&plan->off_acc, sizeof(unsigned long long) * 6));
   const size_t fb = sizeof(double) * (size_t)field_elems(plan);
-  cudaEvent_t e0 = nullptr, e1 = nullptr;
-  CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  if (!plan->ev_off0) { CK(cudaEventCreate(&plan->ev_off0)); CK(cudaEventCreate(&plan->ev_off1)); }
+  cudaEvent_t e0 = plan->ev_off0, e1 = plan->ev_off1;
   CK(cudaEventRecord(e0, s));
   plan->m_lo = 0; plan->m_hi = plan->ntr; plan->cur = plan->tr[0].cur;
   if ((rc = prepare_exchange(plan))) return rc;
@@ -1767,7 +1769,6 @@ extern "C" int mom6adv_offline_advect(mom6adv_plan *plan, double dt_offline, int
   CK(cudaStreamSynchronize(s));
   float ms = 0.f;
   CK(cudaEventElapsedTime(&ms, e0, e1));
-  cudaEventDestroy(e0); cudaEventDestroy(e1);
   plan->last_ms = ms;
   CK(cudaGetLastError());
   if (converged_out) *converged_out = converged ? 1 : 0;
