@@ -1117,10 +1117,11 @@ extern "C" double ora_efp_to_real(const long long limbs[6]) {
 // (:368-387), h_neglect (:205) and Idt (:204) are the caller's, exactly as the loop finds them in the reference.
 // Pinned against the translated reference lines (oracle/f2c, tests/test_hordiff.py).
 // ---------------------------------------------------------------------------
-extern "C" int ora_tracer_hordiff(const ora_grid *Gp, ora_tracer *Tr, int ntr, const double *h, const double *khdt_x,
-                                  const double *khdt_y, int num_itts, double h_neglect, int Diffuse_ML_interior,
-                                  int nkml, int nk_rho_varies, double ML_KhTr_scale, const ora_domain *dom,
-                                  ora_pass_fn pass, void *ctx) {
+static int hordiff_impl(const ora_grid *Gp, ora_tracer *Tr, int ntr, const double *h, const double *khdt_x,
+                        const double *khdt_y, int num_itts, double h_neglect, int Diffuse_ML_interior,
+                        int nkml, int nk_rho_varies, double ML_KhTr_scale, const ora_domain *dom,
+                        ora_pass_fn pass, void *ctx, double Idt, double *const *df_x, double *const *df_y,
+                        double *const *df2d_x, double *const *df2d_y) {
   const ora_grid &G = *Gp;
   if (!dom && !pass) return 1;
   const int is = G.isc, ie = G.iec, js = G.jsc, je = G.jec, nz = G.nk;
@@ -1167,7 +1168,27 @@ extern "C" int ora_tracer_hordiff(const ora_grid *Gp, ora_tracer *Tr, int ntr, c
           dTr[(i - G.isd) + nih * (long)(j - G.jsd)] = Ihdxdy[(i - G.isd) + nih * (long)(j - G.jsd)] *
               ((CX(i - 1, j) * (T(i - 1, j) - T(i, j)) - CX(i, j) * (T(i, j) - T(i + 1, j))) +
                (CY(i, j - 1) * (T(i, j - 1) - T(i, j)) - CY(i, j) * (T(i, j) - T(i, j + 1))));
-        // (df_x / df_y / df2d_* diagnostics :576-591: not part of this restatement)
+        // diffusive-flux diagnostics, :576-591 (accumulated over iterations; the caller zeroes them, :388-405).
+        // G%IscB = isc-1 in symmetric memory, isc otherwise (MOM_hor_index.F90:87-96); G%IecB = iec.
+        {
+          const int IscB = (G.IsdB == G.isd - 1) ? G.isc - 1 : G.isc, JscB = (G.JsdB == G.jsd - 1) ? G.jsc - 1 : G.jsc;
+          if (df_x && df_x[m]) for (int j = js; j <= je; j++) for (int I = IscB; I <= G.iec; I++) {
+            double &d = df_x[m][(I - G.IsdB) + niu * ((j - G.jsd) + njh * (long)(k - 1))];
+            d = d + CX(I, j) * (T(I, j) - T(I + 1, j)) * Idt;                                      // :577-578
+          }
+          if (df_y && df_y[m]) for (int J = JscB; J <= G.jec; J++) for (int i = is; i <= ie; i++) {
+            double &d = df_y[m][(i - G.isd) + nih * ((J - G.JsdB) + njv * (long)(k - 1))];
+            d = d + CY(i, J) * (T(i, J) - T(i, J + 1)) * Idt;                                      // :581-582
+          }
+          if (df2d_x && df2d_x[m]) for (int j = js; j <= je; j++) for (int I = IscB; I <= G.iec; I++) {
+            double &d = df2d_x[m][(I - G.IsdB) + niu * (long)(j - G.jsd)];
+            d = d + CX(I, j) * (T(I, j) - T(I + 1, j)) * Idt;                                      // :585-586
+          }
+          if (df2d_y && df2d_y[m]) for (int J = JscB; J <= G.jec; J++) for (int i = is; i <= ie; i++) {
+            double &d = df2d_y[m][(i - G.isd) + nih * (long)(J - G.JsdB)];
+            d = d + CY(i, J) * (T(i, J) - T(i, J + 1)) * Idt;                                      // :589-590
+          }
+        }
         for (int j = js; j <= je; j++) for (int i = is; i <= ie; i++) T(i, j) = T(i, j) + dTr[(i - G.isd) + nih * (long)(j - G.jsd)];
       }
     }
@@ -1179,6 +1200,25 @@ extern "C" int ora_tracer_hordiff(const ora_grid *Gp, ora_tracer *Tr, int ntr, c
     }
   }
   return 0;
+}
+
+extern "C" int ora_tracer_hordiff(const ora_grid *Gp, ora_tracer *Tr, int ntr, const double *h, const double *khdt_x,
+                                  const double *khdt_y, int num_itts, double h_neglect, int Diffuse_ML_interior,
+                                  int nkml, int nk_rho_varies, double ML_KhTr_scale, const ora_domain *dom,
+                                  ora_pass_fn pass, void *ctx) {
+  return hordiff_impl(Gp, Tr, ntr, h, khdt_x, khdt_y, num_itts, h_neglect, Diffuse_ML_interior, nkml, nk_rho_varies,
+                      ML_KhTr_scale, dom, pass, ctx, 0.0, nullptr, nullptr, nullptr, nullptr);
+}
+
+// The same with the diffusive-flux diagnostics df_x / df_y / df2d_x / df2d_y (:576-591): arrays of ntr pointers, NULL
+// entries (or a NULL array) == unassociated; Idt = 1/dt (:204).  The arrays accumulate: zero them first (:388-405).
+extern "C" int ora_tracer_hordiff_df(const ora_grid *Gp, ora_tracer *Tr, int ntr, const double *h, const double *khdt_x,
+                                     const double *khdt_y, int num_itts, double h_neglect, int Diffuse_ML_interior,
+                                     int nkml, int nk_rho_varies, double ML_KhTr_scale, const ora_domain *dom,
+                                     ora_pass_fn pass, void *ctx, double Idt, double *const *df_x, double *const *df_y,
+                                     double *const *df2d_x, double *const *df2d_y) {
+  return hordiff_impl(Gp, Tr, ntr, h, khdt_x, khdt_y, num_itts, h_neglect, Diffuse_ML_interior, nkml, nk_rho_varies,
+                      ML_KhTr_scale, dom, pass, ctx, Idt, df_x, df_y, df2d_x, df2d_y);
 }
 
 // ---------------------------------------------------------------------------

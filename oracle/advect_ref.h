@@ -175,6 +175,13 @@ int ora_offline_advection_loop(const ora_grid *G, const ora_cs *CS, ora_tracer *
 double ora_remaining_transport_sum(const ora_grid *G, const double *uhtr, const double *vhtr, const double *h_new,
                                    double H_to_kg_m2, double L_to_m, double kg_m2_to_H, double m_to_L);
 
+/* tracer_hordiff's iteration with its diffusive-flux diagnostics df_x / df_y / df2d_x / df2d_y (:576-591): arrays of ntr
+ * pointers, NULL == unassociated; Idt = 1/dt; the arrays accumulate over iterations and must be zeroed first (:388-405). */
+int ora_tracer_hordiff_df(const ora_grid *G, ora_tracer *Tr, int ntr, const double *h, const double *khdt_x,
+                          const double *khdt_y, int num_itts, double h_neglect, int Diffuse_ML_interior, int nkml,
+                          int nk_rho_varies, double ML_KhTr_scale, const ora_domain *dom, ora_pass_fn pass, void *ctx,
+                          double Idt, double *const *df_x, double *const *df_y, double *const *df2d_x, double *const *df2d_y);
+
 /* MOM bitcount checksum of a 2-D/3-D array section
  * (src/framework/MOM_checksums.F90:2407-2414 bitcount, :1396-1404 use). */
 long long ora_bitcount_chksum(const double *a, long long n);

@@ -21,10 +21,11 @@ void hd_pass(void *c, group_pass_type &g) {
 }
 }  // namespace
 
-extern "C" int ref_tracer_hordiff(const ora_grid *G, ora_tracer *Tr, int ntr_in, const double *h_in, const double *khdt_x_in,
-                                  const double *khdt_y_in, int num_itts, double h_neglect, int Diffuse_ML_interior,
-                                  int nkml, int nk_rho_varies, double ML_KhTr_scale, double dt, const ora_domain *dom,
-                                  ora_pass_fn pass, void *ctx) {
+static int hordiff_ref_impl(const ora_grid *G, ora_tracer *Tr, int ntr_in, const double *h_in, const double *khdt_x_in,
+                            const double *khdt_y_in, int num_itts, double h_neglect, int Diffuse_ML_interior,
+                            int nkml, int nk_rho_varies, double ML_KhTr_scale, double dt, const ora_domain *dom,
+                            ora_pass_fn pass, void *ctx, double *const *df_x, double *const *df_y,
+                            double *const *df2d_x, double *const *df2d_y) {
   if (!pass && !dom) return 1;
   ocean_grid_type g;
   g.isc = G->isc; g.iec = G->iec; g.jsc = G->jsc; g.jec = G->jec;
@@ -45,6 +46,11 @@ extern "C" int ref_tracer_hordiff(const ora_grid *G, ora_tracer *Tr, int ntr_in,
   for (int m = 1; m <= ntr_in; m++) {
     reg->tr(m).t = Arr<double, 3>::view(Tr[m - 1].t, {hi_, hj_, kk});
     reg->tr(m).conc_underflow = Tr[m - 1].conc_underflow;
+    // the diffusive-flux diagnostics, associated where the caller hands an array (MOM_tracer_types.F90 shapes)
+    if (df_x && df_x[m - 1]) reg->tr(m).df_x = Arr<double, 3>::view(df_x[m - 1], {ui_, hj_, kk});
+    if (df_y && df_y[m - 1]) reg->tr(m).df_y = Arr<double, 3>::view(df_y[m - 1], {hi_, vj_, kk});
+    if (df2d_x && df2d_x[m - 1]) reg->tr(m).df2d_x = Arr<double, 2>::view(df2d_x[m - 1], {ui_, hj_});
+    if (df2d_y && df2d_y[m - 1]) reg->tr(m).df2d_y = Arr<double, 2>::view(df2d_y[m - 1], {hi_, vj_});
   }
   // the subroutine's own variables, with the shapes it declares them with (:150-180)
   Arr<double, 3> h = Arr<double, 3>::view(const_cast<double *>(h_in), {hi_, hj_, kk});
@@ -73,4 +79,22 @@ extern "C" int ref_tracer_hordiff(const ora_grid *G, ora_tracer *Tr, int ntr_in,
   } catch (const std::string &) { rc = 1; }
   f2c_current_host = nullptr;
   return rc;
+}
+
+extern "C" int ref_tracer_hordiff(const ora_grid *G, ora_tracer *Tr, int ntr_in, const double *h_in, const double *khdt_x_in,
+                                  const double *khdt_y_in, int num_itts, double h_neglect, int Diffuse_ML_interior,
+                                  int nkml, int nk_rho_varies, double ML_KhTr_scale, double dt, const ora_domain *dom,
+                                  ora_pass_fn pass, void *ctx) {
+  return hordiff_ref_impl(G, Tr, ntr_in, h_in, khdt_x_in, khdt_y_in, num_itts, h_neglect, Diffuse_ML_interior, nkml,
+                          nk_rho_varies, ML_KhTr_scale, dt, dom, pass, ctx, nullptr, nullptr, nullptr, nullptr);
+}
+
+// with the df_x / df_y / df2d_x / df2d_y diagnostics of :576-591 (same conventions as ora_tracer_hordiff_df)
+extern "C" int ref_tracer_hordiff_df(const ora_grid *G, ora_tracer *Tr, int ntr_in, const double *h_in, const double *khdt_x_in,
+                                     const double *khdt_y_in, int num_itts, double h_neglect, int Diffuse_ML_interior,
+                                     int nkml, int nk_rho_varies, double ML_KhTr_scale, double dt, const ora_domain *dom,
+                                     ora_pass_fn pass, void *ctx, double *const *df_x, double *const *df_y,
+                                     double *const *df2d_x, double *const *df2d_y) {
+  return hordiff_ref_impl(G, Tr, ntr_in, h_in, khdt_x_in, khdt_y_in, num_itts, h_neglect, Diffuse_ML_interior, nkml,
+                          nk_rho_varies, ML_KhTr_scale, dt, dom, pass, ctx, df_x, df_y, df2d_x, df2d_y);
 }

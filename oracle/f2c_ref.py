@@ -80,7 +80,7 @@ _hd = None
 
 
 def tracer_hordiff(h, khdt_x, khdt_y, num_itts, dt, G, GV, Reg, Diffuse_ML_interior=False, nkml=0, nk_rho_varies=0,
-                   ML_KhTr_scale=0.0) -> None:
+                   ML_KhTr_scale=0.0, df=None) -> None:
     """The translated lines MOM_tracer_hor_diff.F90:539-607 (oracle/f2c/hordiff_wrap.cpp, bounds-checked build)."""
     global _hd
     if _hd is None:
@@ -92,6 +92,17 @@ def tracer_hordiff(h, khdt_x, khdt_y, num_itts, dt, G, GV, Reg, Diffuse_ML_inter
                                            C.c_double, C.POINTER(ora.ora_domain), C.c_void_p, C.c_void_p]
     g, dom = ora.make_grid(G, GV), ora.make_domain(G.Domain)
     tr = ora.make_tracers(Reg)
+    if df is not None:      # the df_x / df_y / df2d_x / df2d_y diagnostics of :576-591 (same dict as oracle.tracer_hordiff)
+        tabs = ora.df_pointer_tables(df, Reg.ntr)
+        f = _hd.ref_tracer_hordiff_df
+        f.restype = C.c_int
+        rc = f(C.byref(g), tr, C.c_int(Reg.ntr), ora._p(h), ora._p(khdt_x), ora._p(khdt_y), C.c_int(int(num_itts)),
+               C.c_double(float(GV.H_subroundoff)), C.c_int(int(bool(Diffuse_ML_interior))), C.c_int(int(nkml)),
+               C.c_int(int(nk_rho_varies)), C.c_double(float(ML_KhTr_scale)), C.c_double(float(dt)), C.byref(dom), None, None,
+               *tabs)
+        if rc != 0:
+            raise RuntimeError("translated tracer_hordiff loop (df) failed: %d" % rc)
+        return
     rc = _hd.ref_tracer_hordiff(C.byref(g), tr, Reg.ntr, ora._p(h), ora._p(khdt_x), ora._p(khdt_y), int(num_itts),
                                 float(GV.H_subroundoff), int(bool(Diffuse_ML_interior)), int(nkml), int(nk_rho_varies),
                                 float(ML_KhTr_scale), float(dt), C.byref(dom), None, None)

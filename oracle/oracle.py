@@ -225,12 +225,38 @@ def advect_tracer(h_end, uhtr, vhtr, OBC, dt, G, GV, US, CS, Reg, x_first_in=Non
     return nit.value
 
 
+def df_pointer_tables(df, ntr):
+    """df = {"df_x": [array or None per tracer], ...} -> four (c_void_p * ntr) tables (None entries == unassociated)."""
+    out = []
+    for key in ("df_x", "df_y", "df2d_x", "df2d_y"):
+        tab = (C.c_void_p * max(ntr, 1))()
+        for m, a in enumerate((df or {}).get(key) or []):
+            if a is not None:
+                assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+                tab[m] = a.ctypes.data
+        out.append(tab)
+    return out
+
+
 def tracer_hordiff(h, khdt_x, khdt_y, num_itts, G, GV, Reg, Diffuse_ML_interior=False, nkml=0, nk_rho_varies=0,
-                   ML_KhTr_scale=0.0) -> None:
+                   ML_KhTr_scale=0.0, df=None, dt=None) -> None:
     """The along-layer diffusion iteration of tracer_hordiff (MOM_tracer_hor_diff.F90:539-607) on Reg.Tr[m].t in place;
-    khdt_x / khdt_y / num_itts as the reference's 2-D set-up (:186-387) leaves them."""
+    khdt_x / khdt_y / num_itts as the reference's 2-D set-up (:186-387) leaves them.  df (optional): the diffusive-flux
+    diagnostics of :576-591 as {"df_x": [...], "df_y": [...], "df2d_x": [...], "df2d_y": [...]}, one array or None per
+    tracer, accumulated in place (zero them first, :388-405); needs dt (Idt = 1/dt, :204)."""
     g, dom = make_grid(G, GV), make_domain(G.Domain)
     tr = make_tracers(Reg)
+    if df is not None:
+        tabs = df_pointer_tables(df, Reg.ntr)
+        f = lib().ora_tracer_hordiff_df
+        f.restype = C.c_int
+        rc = f(C.byref(g), tr, C.c_int(Reg.ntr), _p(h), _p(khdt_x), _p(khdt_y), C.c_int(int(num_itts)),
+               C.c_double(float(GV.H_subroundoff)), C.c_int(int(bool(Diffuse_ML_interior))), C.c_int(int(nkml)),
+               C.c_int(int(nk_rho_varies)), C.c_double(float(ML_KhTr_scale)), C.byref(dom), None, None,
+               C.c_double(1.0 / float(dt)), *tabs)
+        if rc != 0:
+            raise RuntimeError("oracle tracer_hordiff (df) failed: %d" % rc)
+        return
     rc = lib().ora_tracer_hordiff(C.byref(g), tr, Reg.ntr, _p(h), _p(khdt_x), _p(khdt_y), int(num_itts),
                                   float(GV.H_subroundoff), int(bool(Diffuse_ML_interior)), int(nkml), int(nk_rho_varies),
                                   float(ML_KhTr_scale), C.byref(dom), None, None)

@@ -36,6 +36,37 @@ def test_oracle_equals_translated_reference_lines(kw, ml):
         assert eq(Ro.Tr[m].t, Rr.Tr[m].t), "tracer %d" % m      # whole arrays, halos included
 
 
+@pytest.mark.skipif(not f2c_ref.available(), reason="neither oracle/_ref nor /root/reference present")
+@pytest.mark.parametrize("kw", [dict(), dict(cyclic_x=False, symmetric=False), dict(tripolar_n=True)])
+def test_oracle_df_diagnostics_equal_translated_reference_lines(kw):
+    """df_x / df_y / df2d_x / df2d_y (:576-591), some tracers with all four, one with two, one with none."""
+    c, kx, ky, nit = _case(**kw)
+    G, nk = c.G, c.GV.ke
+
+    def fresh():
+        z3u, z3v = (lambda: np.zeros(G.shape_u(nk))), (lambda: np.zeros(G.shape_v(nk)))
+        z2u, z2v = (lambda: np.zeros(G.shape_u())), (lambda: np.zeros(G.shape_v()))
+        return {"df_x": [z3u(), None, z3u(), None], "df_y": [z3v(), None, None, None],
+                "df2d_x": [z2u(), z2u(), None, None], "df2d_y": [z2v(), z2v(), None, None]}
+
+    Ro, Rr, dfo, dfr = synth.bind_registry(c), synth.bind_registry(c), fresh(), fresh()
+    h = c.h_end.numpy()
+    oracle.tracer_hordiff(h, kx, ky, nit, c.G, c.GV, Ro, df=dfo, dt=c.dt)
+    f2c_ref.tracer_hordiff(h, kx, ky, nit, c.dt, c.G, c.GV, Rr, df=dfr)
+    for m in range(c.ntr):
+        assert eq(Ro.Tr[m].t, Rr.Tr[m].t), "tracer %d" % m
+    for key in dfo:
+        for m, (a, b) in enumerate(zip(dfo[key], dfr[key])):
+            if a is not None:
+                assert eq(a, b), (key, m)
+                assert np.abs(a).max() > 0.0
+    # and the tracers are the ones the call without diagnostics gives
+    Rp = synth.bind_registry(c)
+    oracle.tracer_hordiff(h, kx, ky, nit, c.G, c.GV, Rp)
+    for m in range(c.ntr):
+        assert eq(Ro.Tr[m].t, Rp.Tr[m].t)
+
+
 def test_diffusion_properties():
     """Constant tracers stay constant (bitwise); extrema do not grow; sum(T*h*areaT) is conserved to roundoff."""
     c, kx, ky, nit = _case(ni=30, nj=24, nk=3, ntr=3, cyclic_x=False)     # closed: the random khdt is not periodic
