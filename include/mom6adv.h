@@ -170,7 +170,7 @@ int mom6adv_upload_tracer(mom6adv_plan *plan, int m, const double *src);
 int mom6adv_download_tracer(mom6adv_plan *plan, int m, double *dst);
 int mom6adv_upload_field(mom6adv_plan *plan, int field, const double *src);
 int mom6adv_download_field(mom6adv_plan *plan, int field, double *dst);
-/* kind: 0 ad_x, 1 ad_y, 2 ad2d_x, 3 ad2d_y, 4 advection_xy */
+/* kind: 0 ad_x, 1 ad_y, 2 ad2d_x, 3 ad2d_y, 4 advection_xy; 5 df_x, 6 df_y, 7 df2d_x, 8 df2d_y (mom6adv_bind_tracer_df) */
 int mom6adv_download_diag(mom6adv_plan *plan, int m, int kind, double *dst);
 /* Runs the algorithm on the resident fields; no host<->device traffic except
  * the per-iteration convergence word.  use_vol_prev: take hprev from the
@@ -189,6 +189,20 @@ int mom6adv_sync(mom6adv_plan *plan);
  * associated, h_diag ignored), ZINT (:796-802), ZINT_100M (:745-766,805-811); out2d is an (isd:ied, jsd:jed) array,
  * zero outside the computational domain like the reference's work2d. */
 int mom6adv_accumulate_transports(mom6adv_plan *plan, const double *uh, const double *vh, double dt);
+/* The same call with tracer_hordiff's diffusive-flux diagnostics (src/tracer/MOM_tracer_hor_diff.F90:388-405 zeroing,
+ * :576-591 accumulation; Reg%Tr(m)%df_x, df_y, df2d_x, df2d_y of src/tracer/MOM_tracer_types.F90).
+ * mom6adv_bind_tracer_df says which of the four are associated for tracer m (non-NULL = associated; the values live in HBM);
+ * mom6adv_hordiff_diag runs the iteration and fills them (dt is tracer_hordiff's dt: Idt = 1/dt, :204);
+ * mom6adv_download_diag fetches them with kind 5 df_x, 6 df_y, 7 df2d_x, 8 df2d_y.
+ * STATE: built after the round's GPU time was spent -- the kernels have not run on a GPU.  The oracle for them
+ * (ora_tracer_hordiff_df) is pinned against the translated reference lines; mom6adv_hordiff_diag returns
+ * MOM6ADV_ERR_UNSUPPORTED unless the option "hordiff_df" is set. */
+int mom6adv_bind_tracer_df(mom6adv_plan *plan, int m, const double *df_x, const double *df_y, const double *df2d_x,
+                           const double *df2d_y);
+int mom6adv_hordiff_diag(mom6adv_plan *plan, const double *h, const double *khdt_x, const double *khdt_y, int num_itts,
+                         double h_neglect, int Diffuse_ML_interior, int nkml, int nk_rho_varies, double ML_KhTr_scale,
+                         double dt);
+
 /* mom6adv_offline_advect replaces the iteration loop of offline_advection_ale (SURVEY.md 8f rank 4;
  * src/tracer/MOM_offline_main.F90:254-312 set-up, :320-411 loop, :414-415 epilogue) with remaining_transport_sum
  * (:615-650) and its reproducing sum (src/framework/MOM_coms.F90:119-213) on the RESIDENT fields:

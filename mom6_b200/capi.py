@@ -111,6 +111,8 @@ SYMBOLS = {
     "mom6adv_hordiff": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int]),
     "mom6adv_offline_advect": (C.c_int, [_P, C.c_double, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
                                          C.c_double, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_int), _P]),
+    "mom6adv_bind_tracer_df": (C.c_int, [_P, C.c_int, _P, _P, _P, _P]),
+    "mom6adv_hordiff_diag": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double]),
     "mom6adv_set_obc": (C.c_int, [_P, C.POINTER(mom6adv_obc)]),
     "mom6adv_set_ntr": (C.c_int, [_P, C.c_int]),
     "mom6adv_bind_tracer": (C.c_int, [_P, C.c_int, _P, C.c_double, _P, _P, _P, _P, _P]),
@@ -340,6 +342,20 @@ class Plan:
         self._ck(self._l.mom6adv_hordiff(self._h, ptr(h) if h is not None else None, ptr(khdt_x), ptr(khdt_y),
                                          int(num_itts), float(h_neglect), int(bool(Diffuse_ML_interior)), int(nkml),
                                          int(nk_rho_varies), float(ML_KhTr_scale), int(bool(want_df))))
+
+    def bind_tracer_df(self, m, df_x=None, df_y=None, df2d_x=None, df2d_y=None):
+        """Which of tracer_hordiff's diffusive-flux diagnostics tracer m has (non-None = associated; values stay in HBM,
+        download_diag kinds 5..8)."""
+        self._ck(self._l.mom6adv_bind_tracer_df(self._h, int(m), ptr(df_x), ptr(df_y), ptr(df2d_x), ptr(df2d_y)))
+
+    def hordiff_diag(self, khdt_x, khdt_y, num_itts, h_neglect, dt, h=None, Diffuse_ML_interior=False, nkml=0,
+                     nk_rho_varies=0, ML_KhTr_scale=0.0):
+        """hordiff() with the df_* diagnostics of the tracers bound by bind_tracer_df (MOM_tracer_hor_diff.F90:576-591).
+        Needs the option hordiff_df: the path has not run on a GPU yet."""
+        _order_after_torch(khdt_x, khdt_y, h)
+        self._ck(self._l.mom6adv_hordiff_diag(self._h, ptr(h) if h is not None else None, ptr(khdt_x), ptr(khdt_y),
+                                              int(num_itts), float(h_neglect), int(bool(Diffuse_ML_interior)), int(nkml),
+                                              int(nk_rho_varies), float(ML_KhTr_scale), float(dt)))
 
     def offline_advect(self, dt_offline, num_off_iter, x_before_y=True, off_ale_mod=10 ** 6, min_residual=0.0,
                        H_to_kg_m2=1.0, L_to_m=1.0, kg_m2_to_H=1.0, m_to_L=1.0):

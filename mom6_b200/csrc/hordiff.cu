@@ -130,6 +130,79 @@ k_hd_tile(Geom g, HdParams p, const __grid_constant__ TrTable tt, const double *
   }
 }
 
+// ---- the diffusive-flux diagnostics, :576-591 (only launched when a tracer has one associated) ----------------------
+// One iteration's contribution, from the tracer values BEFORE the update (the live buffers) and the coefficient fields:
+//   df_x(I,j,k) += Coef_x(I,j) * (t(i,j,k) - t(i+1,j,k)) * Idt      j = js..je, I = G%IscB..G%IecB      (:576-579)
+//   df_y(i,J,k) += Coef_y(i,J) * (t(i,j,k) - t(i,j+1,k)) * Idt      J = G%JscB..G%JecB, i = is..ie      (:580-583)
+// G%IscB = isc-1 in symmetric memory and isc otherwise (MOM_hor_index.F90:87-96); levels the call skips (:544-550) get
+// nothing.  Thread per point, tracer loop inside; every (point, tracer) is touched by one thread only.
+__global__ void __launch_bounds__(HD_TX * HD_TY)
+k_hd_df3(Geom g, HdParams p, const __grid_constant__ TrTable tt, const __grid_constant__ DfTable df,
+         const double *__restrict__ cx, const double *__restrict__ cy, double Idt, int IscB, int JscB) {
+  const int col = blockIdx.x * HD_TX + threadIdx.x, row = blockIdx.y * HD_TY + threadIdx.y, k = blockIdx.z;
+  if (col >= g.P || row >= g.R) return;
+  double scale;
+  if (!hd_level(p, k + 1, scale)) return;
+  const int i = col - g.coff, j = row - g.roff;
+  const long long q = (long long)row * g.P + col + g.plane * k;
+  const bool fx = (j >= g.jsc && j <= g.jec && i >= IscB && i <= g.iec);
+  const bool fy = (i >= g.isc && i <= g.iec && j >= JscB && j <= g.jec);
+  if (!fx && !fy) return;
+  const double cxq = fx ? cx[q] : 0.0, cyq = fy ? cy[q] : 0.0;
+  for (int m = 0; m < tt.n; m++) {
+    double *dx = df.dfx[m], *dy = df.dfy[m];
+    if (!dx && !dy) continue;
+    const double *t = tt.src[m];
+    const double c = t[q];
+    if (dx && fx) dx[q] = dx[q] + cxq * (c - t[q + 1]) * Idt;
+    if (dy && fy) dy[q] = dy[q] + cyq * (c - t[q + g.P]) * Idt;
+  }
+}
+
+// df2d_x / df2d_y (:584-591): the same terms summed over k into a 2-D field, k ascending as the reference's loop nest
+// visits them (one thread walks the column of a face).
+__global__ void __launch_bounds__(HD_TX * HD_TY)
+k_hd_df2(Geom g, HdParams p, const __grid_constant__ TrTable tt, const __grid_constant__ DfTable df,
+         const double *__restrict__ cx, const double *__restrict__ cy, double Idt, int IscB, int JscB) {
+  const int col = blockIdx.x * HD_TX + threadIdx.x, row = blockIdx.y * HD_TY + threadIdx.y;
+  if (col >= g.P || row >= g.R) return;
+  const int i = col - g.coff, j = row - g.roff;
+  const long long q2 = (long long)row * g.P + col;
+  const bool fx = (j >= g.jsc && j <= g.jec && i >= IscB && i <= g.iec);
+  const bool fy = (i >= g.isc && i <= g.iec && j >= JscB && j <= g.jec);
+  if (!fx && !fy) return;
+  for (int m = 0; m < tt.n; m++) {
+    double *dx = df.d2x[m], *dy = df.d2y[m];
+    if (!dx && !dy) continue;
+    const double *t = tt.src[m];
+    double ax = (dx && fx) ? dx[q2] : 0.0, ay = (dy && fy) ? dy[q2] : 0.0;
+    for (int k = 0; k < g.nk; k++) {
+      double scale;
+      if (!hd_level(p, k + 1, scale)) continue;
+      const long long q = q2 + g.plane * k;
+      const double c = t[q];
+      if (dx && fx) ax = ax + cx[q] * (c - t[q + 1]) * Idt;
+      if (dy && fy) ay = ay + cy[q] * (c - t[q + g.P]) * Idt;
+    }
+    if (dx && fx) dx[q2] = ax;
+    if (dy && fy) dy[q2] = ay;
+  }
+}
+
+void launch_hd_df(cudaStream_t s, const Geom &g, const HdParams &p, const TrTable &tt, const DfTable &df, bool any3,
+                  bool any2, const double *cx, const double *cy, double Idt) {
+  const int IscB = (g.IsdB == g.isd - 1) ? g.isc - 1 : g.isc, JscB = (g.JsdB == g.jsd - 1) ? g.jsc - 1 : g.jsc;
+  dim3 block(HD_TX, HD_TY);
+  if (any3) {
+    dim3 grid((g.P + HD_TX - 1) / HD_TX, (g.R + HD_TY - 1) / HD_TY, g.nk);
+    k_hd_df3<<<grid, block, 0, s>>>(g, p, tt, df, cx, cy, Idt, IscB, JscB);
+  }
+  if (any2) {
+    dim3 grid((g.P + HD_TX - 1) / HD_TX, (g.R + HD_TY - 1) / HD_TY, 1);
+    k_hd_df2<<<grid, block, 0, s>>>(g, p, tt, df, cx, cy, Idt, IscB, JscB);
+  }
+}
+
 #define HD_W 64
 #define HD_H 8
 #define HD_NS 6

@@ -52,6 +52,12 @@ struct HdParams {
   int diffuse_ml, nkml, nk_rho_varies;
 };
 
+// diffusive-flux diagnostics of tracer_hordiff for the tracers of a TrTable (same order); nullptr = unassociated
+struct DfTable {
+  double *dfx[MOM6ADV_MAXT], *dfy[MOM6ADV_MAXT];      // df_x, df_y     (MOM_tracer_hor_diff.F90:576-583)
+  double *d2x[MOM6ADV_MAXT], *d2y[MOM6ADV_MAXT];      // df2d_x, df2d_y (:584-591)
+};
+
 // ---- gfortran intrinsic semantics (argument-order compare-select) -----------
 __device__ __forceinline__ double gmax2(double a, double b) { return (b > a) ? b : a; }
 __device__ __forceinline__ double gmin2(double a, double b) { return (b < a) ? b : a; }

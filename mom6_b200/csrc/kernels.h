@@ -120,6 +120,8 @@ void launch_hd_coef(cudaStream_t s, const Geom &g, const HdParams &p, const doub
                     const double *khdt_y, const double *IareaT, double *cx, double *cy, double *ihd);
 void launch_hd_apply(cudaStream_t s, const Geom &g, const HdParams &p, const TrTable &tt, const double *cx,
                      const double *cy, const double *ihd);
+void launch_hd_df(cudaStream_t s, const Geom &g, const HdParams &p, const TrTable &tt, const DfTable &df, bool any3,
+                  bool any2, const double *cx, const double *cy, double Idt);
 
 // offline.cu: the iteration loop of offline_advection_ale (MOM_offline_main.F90:254-415), element-wise parts
 void launch_off_init(cudaStream_t s, const Geom &g, double *h);

@@ -23,6 +23,7 @@ struct TracerSlot {
   double *host_diag[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // ad_x, ad_y, ad2d_x, ad2d_y, advection_xy
   double *buf[2] = {nullptr, nullptr};      // padded HBM storage (ping-pong)
   double *diag[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  double *df[4] = {nullptr, nullptr, nullptr, nullptr};      // df_x, df_y, df2d_x, df2d_y of tracer_hordiff (mom6adv_bind_tracer_df)
   double conc_underflow = 0.0;
   bool bound = false;
   int cur = 0;                              // live ping-pong buffer
@@ -137,6 +138,7 @@ struct mom6adv_plan {
   long long obc_cond_bytes = 0;
   double *obc_ttmp = nullptr, *obc_slope = nullptr, *obc_fx = nullptr, *obc_hh2 = nullptr, *maskT = nullptr;
   int opt_trace = 0;                 // print the MIRROR pipeline's copy/compute times to stderr
+  int opt_hordiff_df = 0;            // accept mom6adv_hordiff_diag (df_* diagnostics of tracer_hordiff: built, not yet run on a GPU)
   int opt_obc_multi = 0;             // experimental: accept open boundaries on a multi-block plan (see mom6adv_set_obc)
   int opt_sparse = 1;                // list-driven tracer update on residual iterations (sparse.cu)
   int *sp_list = nullptr; int sp_cap = 0;      // cells the residual trip updates (capacity: every cell, it cannot overflow)
@@ -582,6 +584,7 @@ extern "C" int mom6adv_plan_create(const mom6adv_grid *gr, const mom6adv_config 
 static void free_slot(TracerSlot &s) {
   for (int b = 0; b < 2; b++) if (s.buf[b]) { cudaFree(s.buf[b]); s.buf[b] = nullptr; }
   for (int d = 0; d < 5; d++) if (s.diag[d]) { cudaFree(s.diag[d]); s.diag[d] = nullptr; }
+  for (int d = 0; d < 4; d++) if (s.df[d]) { cudaFree(s.df[d]); s.df[d] = nullptr; }
 }
 
 extern "C" int mom6adv_plan_destroy(mom6adv_plan *plan) {
@@ -826,6 +829,24 @@ extern "C" int mom6adv_bind_tracer(mom6adv_plan *plan, int m, double *t, double 
   }
   s.bound = true;
   plan->tr_dirty = true;
+  return MOM6ADV_OK;
+}
+
+// The diffusive-flux diagnostics of tracer_hordiff (MOM_tracer_types.F90: df_x, df_y, df2d_x, df2d_y) of tracer m: a
+// non-NULL argument says "associated" -- the values live in HBM (mom6adv_hordiff_diag fills them, mom6adv_download_diag
+// kinds 5..8 fetch them); NULL frees the field.
+extern "C" int mom6adv_bind_tracer_df(mom6adv_plan *plan, int m, const double *df_x, const double *df_y,
+                                      const double *df2d_x, const double *df2d_y) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "bind_tracer_df: plan not initialised");
+  if (m < 0 || m >= plan->ntr) return fail(plan, MOM6ADV_ERR_INVALID, "bind_tracer_df: tracer index out of range");
+  CK(cudaSetDevice(plan->device));
+  TracerSlot &s = plan->tr[m];
+  const double *hd[4] = {df_x, df_y, df2d_x, df2d_y};
+  for (int d = 0; d < 4; d++) {
+    if (hd[d] && !s.df[d]) { int rc = dev_alloc(plan, &s.df[d], d >= 2 ? plan->g.plane : field_elems(plan)); if (rc) return rc; }
+    if (!hd[d] && s.df[d]) { cudaFree(s.df[d]); s.df[d] = nullptr; }
+  }
+  CK(cudaStreamSynchronize(plan->stream));
   return MOM6ADV_OK;
 }
 
@@ -1512,19 +1533,20 @@ extern "C" int mom6adv_download_tracer(mom6adv_plan *plan, int m, double *dst) {
 
 static void diag_info(const Geom &g, int kind, int *ilo, int *jlo, int *nlev) {
   *ilo = g.isd; *jlo = g.jsd; *nlev = g.nk;
-  if (kind == 0 || kind == 2) *ilo = g.IsdB;
-  if (kind == 1 || kind == 3) *jlo = g.JsdB;
-  if (kind == 2 || kind == 3) *nlev = 1;
+  if (kind == 0 || kind == 2 || kind == 5 || kind == 7) *ilo = g.IsdB;      // 5..8: df_x, df_y, df2d_x, df2d_y
+  if (kind == 1 || kind == 3 || kind == 6 || kind == 8) *jlo = g.JsdB;
+  if (kind == 2 || kind == 3 || kind == 7 || kind == 8) *nlev = 1;
 }
 
 extern "C" int mom6adv_download_diag(mom6adv_plan *plan, int m, int kind, double *dst) {
   if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "download_diag: plan not initialised");
-  if (m < 0 || m >= plan->ntr || kind < 0 || kind > 4) return fail(plan, MOM6ADV_ERR_INVALID, "download_diag: bad index");
-  if (!plan->tr[m].diag[kind]) return fail(plan, MOM6ADV_ERR_INVALID, "download_diag: diagnostic not associated");
+  if (m < 0 || m >= plan->ntr || kind < 0 || kind > 8) return fail(plan, MOM6ADV_ERR_INVALID, "download_diag: bad index");
+  const double *field = kind <= 4 ? plan->tr[m].diag[kind] : plan->tr[m].df[kind - 5];
+  if (!field) return fail(plan, MOM6ADV_ERR_INVALID, "download_diag: diagnostic not associated");
   CK(cudaSetDevice(plan->device));
   int ilo, jlo, nlev;
   diag_info(plan->g, kind, &ilo, &jlo, &nlev);
-  int rc = download(plan, dst, plan->tr[m].diag[kind], ilo, jlo, nlev);
+  int rc = download(plan, dst, field, ilo, jlo, nlev);
   if (rc) return rc;
   CK(cudaStreamSynchronize(plan->stream));
   return MOM6ADV_OK;
@@ -1599,11 +1621,36 @@ extern "C" int mom6adv_column_diag(mom6adv_plan *plan, int m, int kind, const do
 // tracer_hordiff's diffusion iteration (MOM_tracer_hor_diff.F90:539-607) on the resident tracers; kernels in hordiff.cu.
 // Scratch: Coef_x -> hh, Coef_y -> cfl, Ihdxdy -> hlst (advect_tracer's per-sweep work fields, free between calls).
 // ---------------------------------------------------------------------------
+static int hordiff_run(mom6adv_plan *plan, const double *h, const double *khdt_x, const double *khdt_y,
+                       int num_itts, double h_neglect, int Diffuse_ML_interior, int nkml, int nk_rho_varies,
+                       double ML_KhTr_scale, bool with_df, double Idt);
+
 extern "C" int mom6adv_hordiff(mom6adv_plan *plan, const double *h, const double *khdt_x, const double *khdt_y,
                                int num_itts, double h_neglect, int Diffuse_ML_interior, int nkml, int nk_rho_varies,
                                double ML_KhTr_scale, int want_df) {
   if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "hordiff: plan not initialised");
-  if (want_df) return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "hordiff: the df_x / df_y / df2d_x / df2d_y diagnostics are not implemented");
+  if (want_df) return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "hordiff: this entry point does not produce the df_x / df_y / df2d_x / df2d_y diagnostics (mom6adv_hordiff_diag does, behind the option hordiff_df)");
+  return hordiff_run(plan, h, khdt_x, khdt_y, num_itts, h_neglect, Diffuse_ML_interior, nkml, nk_rho_varies, ML_KhTr_scale,
+                     false, 0.0);
+}
+
+// The same call with the diffusive-flux diagnostics (MOM_tracer_hor_diff.F90:388-405 zeroing, :576-591 accumulation) of
+// the tracers that have them bound (mom6adv_bind_tracer_df); dt is tracer_hordiff's dt (Idt = 1/dt, :204).
+// NOT YET RUN ON A GPU (the round's GPU time was spent): refused unless the option "hordiff_df" is set.
+extern "C" int mom6adv_hordiff_diag(mom6adv_plan *plan, const double *h, const double *khdt_x, const double *khdt_y,
+                                    int num_itts, double h_neglect, int Diffuse_ML_interior, int nkml, int nk_rho_varies,
+                                    double ML_KhTr_scale, double dt) {
+  if (!plan) return fail(nullptr, MOM6ADV_ERR_NOT_INIT, "hordiff_diag: plan not initialised");
+  if (!plan->opt_hordiff_df)
+    return fail(plan, MOM6ADV_ERR_UNSUPPORTED, "hordiff_diag: the df_x / df_y / df2d_x / df2d_y path has not been verified on a GPU yet; set the option hordiff_df to use it");
+  if (!(dt > 0.0)) return fail(plan, MOM6ADV_ERR_INVALID, "hordiff_diag: dt must be > 0");
+  return hordiff_run(plan, h, khdt_x, khdt_y, num_itts, h_neglect, Diffuse_ML_interior, nkml, nk_rho_varies, ML_KhTr_scale,
+                     true, 1.0 / dt);
+}
+
+static int hordiff_run(mom6adv_plan *plan, const double *h, const double *khdt_x, const double *khdt_y,
+                       int num_itts, double h_neglect, int Diffuse_ML_interior, int nkml, int nk_rho_varies,
+                       double ML_KhTr_scale, bool with_df, double Idt) {
   if (!khdt_x || !khdt_y) return fail(plan, MOM6ADV_ERR_INVALID, "hordiff: NULL khdt_x / khdt_y");
   if (num_itts < 1) return fail(plan, MOM6ADV_ERR_INVALID, "hordiff: num_itts must be >= 1");
   if (plan->ntr == 0) return MOM6ADV_OK;
@@ -1633,6 +1680,9 @@ extern "C" int mom6adv_hordiff(mom6adv_plan *plan, const double *h, const double
   hp.ml_scale = ML_KhTr_scale; hp.h_neglect = h_neglect;
   hp.diffuse_ml = Diffuse_ML_interior ? 1 : 0; hp.nkml = nkml; hp.nk_rho_varies = nk_rho_varies;
   CK(cudaEventRecord(plan->ev0, s));
+  if (with_df)                                                              // :388-405
+    for (int m = 0; m < plan->ntr; m++) for (int d = 0; d < 4; d++) if (plan->tr[m].df[d])
+      CK(cudaMemsetAsync(plan->tr[m].df[d], 0, sizeof(double) * (size_t)(d >= 2 ? g.plane : field_elems(plan)), s));
   launch_hd_coef(s, g, hp, plan->h_end, plan->khdt_x, plan->khdt_y, plan->IareaT, plan->hh, plan->cfl, plan->hlst);   // :552-566
   plan->launches++;
   for (int itt = 1; itt <= num_itts; itt++) {                               // :539
@@ -1645,6 +1695,19 @@ extern "C" int mom6adv_hordiff(mom6adv_plan *plan, const double *h, const double
       for (int q = 0; q < tt.n; q++) {
         const TracerSlot &ts = plan->tr[m0 + q];
         tt.src[q] = ts.buf[src]; tt.dst[q] = ts.buf[1 - src]; tt.cu[q] = ts.conc_underflow;
+      }
+      if (with_df) {                                                        // :576-591, from the values before the update
+        DfTable df; bool any3 = false, any2 = false;
+        for (int q = 0; q < MOM6ADV_MAXT; q++) {
+          const TracerSlot *ts = q < tt.n ? &plan->tr[m0 + q] : nullptr;
+          df.dfx[q] = ts ? ts->df[0] : nullptr; df.dfy[q] = ts ? ts->df[1] : nullptr;
+          df.d2x[q] = ts ? ts->df[2] : nullptr; df.d2y[q] = ts ? ts->df[3] : nullptr;
+          any3 = any3 || df.dfx[q] || df.dfy[q]; any2 = any2 || df.d2x[q] || df.d2y[q];
+        }
+        if (any3 || any2) {
+          launch_hd_df(s, g, hp, tt, df, any3, any2, plan->hh, plan->cfl, Idt);
+          plan->launches += (any3 ? 1 : 0) + (any2 ? 1 : 0);
+        }
       }
       launch_hd_apply(s, g, hp, tt, plan->hh, plan->cfl, plan->hlst);       // :568-605
       plan->launches++;
@@ -1998,6 +2061,7 @@ extern "C" int mom6adv_set_option(mom6adv_plan *plan, const char *key, int value
   if (!strcmp(key, "pull2")) { plan->opt_pull2 = value; return MOM6ADV_OK; }
   if (!strcmp(key, "sparse")) { plan->opt_sparse = value; return MOM6ADV_OK; }
   if (!strcmp(key, "obc_multi")) { plan->opt_obc_multi = value; return MOM6ADV_OK; }
+  if (!strcmp(key, "hordiff_df")) { plan->opt_hordiff_df = value; return MOM6ADV_OK; }
   if (!strcmp(key, "mirror_chunk")) { plan->opt_chunk = value; return MOM6ADV_OK; }
   if (!strcmp(key, "mirror_ahead")) { plan->opt_ahead = value; return MOM6ADV_OK; }
   if (!strcmp(key, "pull")) { if (plan->ipc_ntr >= 0 && value != plan->opt_pull) return fail(plan, MOM6ADV_ERR_INVALID, "set_option: pull must be chosen before the first advect call"); plan->opt_pull = value; return MOM6ADV_OK; }

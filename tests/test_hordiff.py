@@ -200,3 +200,34 @@ def test_host_mirror_fails_loudly_without_a_plan():
     CS = tracer_advect_init(None, c.G, None, {"DT": c.dt_baroclinic, "TRACER_ADVECTION_SCHEME": "PLM"}, None, None)
     with pytest.raises(RuntimeError):
         tracer_hor_diff.tracer_hordiff_iterate(CS, c.G, c.GV, kx, ky, nit)
+
+
+@pytest.mark.gpu
+@pytest.mark.xfail(strict=False, reason="mom6adv_hordiff_diag was built after the round's GPU time was spent: never run on a GPU")
+@pytest.mark.parametrize("kw", [dict(), dict(cyclic_x=False, symmetric=False), dict(tripolar_n=True)])
+def test_cuda_hordiff_df_diagnostics_bitwise(kw):
+    """df_x / df_y / df2d_x / df2d_y on the device (option hordiff_df) against the pinned oracle."""
+    c, kx, ky, nit = _case(ni=70, nj=29, nk=4, ntr=4, **kw)
+    G, nk = c.G, c.GV.ke
+    flag = np.zeros(8)
+    has = {"df_x": [1, 0, 1, 0], "df_y": [1, 0, 0, 0], "df2d_x": [1, 1, 0, 0], "df2d_y": [1, 1, 0, 0]}
+    shp = {"df_x": G.shape_u(nk), "df_y": G.shape_v(nk), "df2d_x": G.shape_u(), "df2d_y": G.shape_v()}
+    dfo = {k: [np.zeros(shp[k]) if on else None for on in v] for k, v in has.items()}
+    Ro = synth.bind_registry(c)
+    h = c.h_end.numpy()
+    oracle.tracer_hordiff(h, kx, ky, nit, c.G, c.GV, Ro, df=dfo, dt=c.dt)
+    p, _ = _gpu_plan(c)
+    p.set_option("hordiff_df", 1)
+    for m in range(c.ntr):
+        p.bind_tracer_df(m, *[flag if has[k][m] else None for k in ("df_x", "df_y", "df2d_x", "df2d_y")])
+    p.hordiff_diag(kx, ky, nit, c.GV.H_subroundoff, c.dt, h=h)
+    for m, o in enumerate(_download(p, c)):
+        assert eq(G.interior(o), G.interior(Ro.Tr[m].t)), "tracer %d" % m
+    inner = {"df_x": G.interior_u, "df_y": G.interior_v, "df2d_x": G.interior_u, "df2d_y": G.interior_v}
+    for kind, k in enumerate(("df_x", "df_y", "df2d_x", "df2d_y")):
+        for m in range(c.ntr):
+            if has[k][m]:
+                out = np.zeros(shp[k])
+                p.download_diag(m, 5 + kind, out)
+                assert eq(inner[k](out), inner[k](dfo[k][m])), (k, m)
+    p.destroy()
