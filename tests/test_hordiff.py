@@ -202,32 +202,55 @@ def test_host_mirror_fails_loudly_without_a_plan():
         tracer_hor_diff.tracer_hordiff_iterate(CS, c.G, c.GV, kx, ky, nit)
 
 
+def _df_worker(kw, q):
+    """Runs in a process of its own: kernels that have never met a GPU must not be able to take the suite's CUDA context
+    down with them."""
+    try:
+        c, kx, ky, nit = _case(ni=70, nj=29, nk=4, ntr=4, **kw)
+        G, nk = c.G, c.GV.ke
+        flag = np.zeros(8)
+        has = {"df_x": [1, 0, 1, 0], "df_y": [1, 0, 0, 0], "df2d_x": [1, 1, 0, 0], "df2d_y": [1, 1, 0, 0]}
+        shp = {"df_x": G.shape_u(nk), "df_y": G.shape_v(nk), "df2d_x": G.shape_u(), "df2d_y": G.shape_v()}
+        dfo = {k: [np.zeros(shp[k]) if on else None for on in v] for k, v in has.items()}
+        Ro = synth.bind_registry(c)
+        h = c.h_end.numpy()
+        oracle.tracer_hordiff(h, kx, ky, nit, c.G, c.GV, Ro, df=dfo, dt=c.dt)
+        p, _ = _gpu_plan(c)
+        p.set_option("hordiff_df", 1)
+        for m in range(c.ntr):
+            p.bind_tracer_df(m, *[flag if has[k][m] else None for k in ("df_x", "df_y", "df2d_x", "df2d_y")])
+        p.hordiff_diag(kx, ky, nit, c.GV.H_subroundoff, c.dt, h=h)
+        bad = []
+        for m, o in enumerate(_download(p, c)):
+            if not eq(G.interior(o), G.interior(Ro.Tr[m].t)): bad.append("tracer %d" % m)
+        inner = {"df_x": G.interior_u, "df_y": G.interior_v, "df2d_x": G.interior_u, "df2d_y": G.interior_v}
+        for kind, k in enumerate(("df_x", "df_y", "df2d_x", "df2d_y")):
+            for m in range(c.ntr):
+                if has[k][m]:
+                    out = np.zeros(shp[k])
+                    p.download_diag(m, 5 + kind, out)
+                    if not eq(inner[k](out), inner[k](dfo[k][m])): bad.append("%s of tracer %d" % (k, m))
+                    if not np.abs(out).max() > 0.0: bad.append("%s of tracer %d is all zero" % (k, m))
+        p.destroy()
+        q.put("; ".join(bad))
+    except Exception as e:
+        q.put("raised %s: %s" % (type(e).__name__, str(e)[:300]))
+
+
 @pytest.mark.gpu
 @pytest.mark.xfail(strict=False, reason="mom6adv_hordiff_diag was built after the round's GPU time was spent: never run on a GPU")
 @pytest.mark.parametrize("kw", [dict(), dict(cyclic_x=False, symmetric=False), dict(tripolar_n=True)])
 def test_cuda_hordiff_df_diagnostics_bitwise(kw):
-    """df_x / df_y / df2d_x / df2d_y on the device (option hordiff_df) against the pinned oracle."""
-    c, kx, ky, nit = _case(ni=70, nj=29, nk=4, ntr=4, **kw)
-    G, nk = c.G, c.GV.ke
-    flag = np.zeros(8)
-    has = {"df_x": [1, 0, 1, 0], "df_y": [1, 0, 0, 0], "df2d_x": [1, 1, 0, 0], "df2d_y": [1, 1, 0, 0]}
-    shp = {"df_x": G.shape_u(nk), "df_y": G.shape_v(nk), "df2d_x": G.shape_u(), "df2d_y": G.shape_v()}
-    dfo = {k: [np.zeros(shp[k]) if on else None for on in v] for k, v in has.items()}
-    Ro = synth.bind_registry(c)
-    h = c.h_end.numpy()
-    oracle.tracer_hordiff(h, kx, ky, nit, c.G, c.GV, Ro, df=dfo, dt=c.dt)
-    p, _ = _gpu_plan(c)
-    p.set_option("hordiff_df", 1)
-    for m in range(c.ntr):
-        p.bind_tracer_df(m, *[flag if has[k][m] else None for k in ("df_x", "df_y", "df2d_x", "df2d_y")])
-    p.hordiff_diag(kx, ky, nit, c.GV.H_subroundoff, c.dt, h=h)
-    for m, o in enumerate(_download(p, c)):
-        assert eq(G.interior(o), G.interior(Ro.Tr[m].t)), "tracer %d" % m
-    inner = {"df_x": G.interior_u, "df_y": G.interior_v, "df2d_x": G.interior_u, "df2d_y": G.interior_v}
-    for kind, k in enumerate(("df_x", "df_y", "df2d_x", "df2d_y")):
-        for m in range(c.ntr):
-            if has[k][m]:
-                out = np.zeros(shp[k])
-                p.download_diag(m, 5 + kind, out)
-                assert eq(inner[k](out), inner[k](dfo[k][m])), (k, m)
-    p.destroy()
+    """df_x / df_y / df2d_x / df2d_y on the device (option hordiff_df) against the pinned oracle, in a child process."""
+    import multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    pr = ctx.Process(target=_df_worker, args=(kw, q))
+    pr.start()
+    try:
+        msg = q.get(timeout=180)
+    finally:
+        pr.join(timeout=30)
+        if pr.is_alive():
+            pr.kill()
+    assert msg == "", msg
