@@ -413,6 +413,10 @@ def test_obc_basin_layouts(scheme):
                 cells.add((int(j), int(i)))
         return cells
 
+    for layout in ((1, 3), (1, 4)):                      # y-split: equal whatever the order and the number of trips
+        assert run(layout, True) == set() and run(layout, True, x_first_in=False) == set()
+    for layout in ((2, 2), (3, 1)):                      # x-split: equal for y-first sweeps and after one trip
+        assert run(layout, True, x_first_in=False) == set() and run(layout, True, max_iter_in=1) == set()
     for use_obc in (True, False):
         assert run((1, 2), use_obc) == set()
         assert run((1, 2), use_obc, x_first_in=False) == set()
