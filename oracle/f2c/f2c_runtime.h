@@ -170,6 +170,9 @@ struct tracer_hor_diff_cs {
   lbool diffuse_ml_interior = 0, show_call_tree = 0;
   double ml_khtr_scale = 0.0;
   group_pass_type pass_t;
+  lbool check_diffusive_cfl = 0;      // :368-387
+  double max_diff_cfl = -1.0;
+  int id_cfl = -1, diag = 0;
 };
 struct obc_segment_tracer_type { Arr<double, 3> tres; double obc_inflow_conc = 0; int ntr_index = 0; };
 struct segment_tracer_registry_type { int ntseg = 0; Arr<obc_segment_tracer_type, 1> tr; };

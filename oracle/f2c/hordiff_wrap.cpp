@@ -98,3 +98,39 @@ extern "C" int ref_tracer_hordiff_df(const ora_grid *G, ora_tracer *Tr, int ntr_
   return hordiff_ref_impl(G, Tr, ntr_in, h_in, khdt_x_in, khdt_y_in, num_itts, h_neglect, Diffuse_ML_interior, nkml,
                           nk_rho_varies, ML_KhTr_scale, dt, dom, pass, ctx, df_x, df_y, df2d_x, df2d_y);
 }
+
+// num_itts / I_numitts from the diffusive CFL, MOM_tracer_hor_diff.F90:368-387 (translated; one PE: max_across_PEs is
+// the identity; the call-tree, clock and post_data calls do nothing)
+namespace {
+template <class... A> void calltree_waypoint(A &&...) {}
+template <class... A> void cpu_clock_begin(A &&...) {}
+template <class... A> void cpu_clock_end(A &&...) {}
+template <class... A> void post_data(A &&...) {}
+template <class T> T kw_mask(T v) { return v; }
+inline void max_across_pes(double &) {}
+}  // namespace
+
+extern "C" int ref_hordiff_num_itts(const ora_grid *G, const double *khdt_x_in, const double *khdt_y_in,
+                                    int check_diffusive_CFL, double max_diff_CFL, int *num_itts_out, double *I_numitts_out) {
+  ocean_grid_type g;
+  g.isc = G->isc; g.iec = G->iec; g.jsc = G->jsc; g.jec = G->jec;
+  g.isd = G->isd; g.ied = G->ied; g.jsd = G->jsd; g.jed = G->jed;
+  const Bnd hi_ = {G->isd, G->ied}, hj_ = {G->jsd, G->jed}, ui_ = {G->IsdB, G->IedB}, vj_ = {G->JsdB, G->JedB};
+  g.iareat = Arr<double, 2>::view(const_cast<double *>(G->IareaT), {hi_, hj_});
+  g.mask2dt = Arr<double, 2>::view(const_cast<double *>(G->mask2dT), {hi_, hj_});
+  tracer_hor_diff_cs cs_; tracer_hor_diff_cs *cs = &cs_;
+  cs->check_diffusive_cfl = check_diffusive_CFL != 0; cs->max_diff_cfl = max_diff_CFL;
+  Arr<double, 2> khdt_x = Arr<double, 2>::view(const_cast<double *>(khdt_x_in), {ui_, hj_});
+  Arr<double, 2> khdt_y = Arr<double, 2>::view(const_cast<double *>(khdt_y_in), {hi_, vj_});
+  Arr<double, 2> cfl = Arr<double, 2>::automatic({hi_, hj_});      // CFL(SZI_(G),SZJ_(G)), :140
+  const int is = G->isc, ie = G->iec, js = G->jsc, je = G->jec;
+  int i = 0, j = 0, num_itts = 0, id_clock_sync = 0;
+  double max_cfl = f_uninit<double>(), i_numitts = f_uninit<double>();
+  (void)i; (void)j; (void)id_clock_sync;
+  int rc = 0;
+  try {
+#include "hordiff_itts_f2c.inc"      // generated: MOM_tracer_hor_diff.F90:368-387
+  } catch (const std::string &) { rc = 1; }
+  *num_itts_out = num_itts; *I_numitts_out = i_numitts;
+  return rc;
+}

@@ -125,3 +125,24 @@ def offline_advection_loop(h_pre, uhtr, vhtr, dt_offline, num_off_iter, G, GV, C
         _off.ref_offline_advection_loop.argtypes = ora._offline_argtypes()
     return ora._offline_call(_off.ref_offline_advection_loop, h_pre, uhtr, vhtr, dt_offline, num_off_iter, G, GV, CS, Reg,
                              x_before_y, off_ale_mod, min_residual, H_to_kg_m2, L_to_m, kg_m2_to_H, m_to_L, None, 1)
+
+
+def hordiff_num_itts(khdt_x, khdt_y, G, GV, check_diffusive_CFL=True, max_diff_CFL=-1.0):
+    """(num_itts, I_numitts) as the translated lines MOM_tracer_hor_diff.F90:368-387 compute them (one PE)."""
+    global _hd
+    if _hd is None:
+        lib()
+        _hd = C.CDLL(os.path.join(_REF_DIR, "libref_f2c_hordiff.so"))
+        _hd.ref_tracer_hordiff.restype = C.c_int
+        _hd.ref_tracer_hordiff.argtypes = [C.POINTER(ora.ora_grid), C.POINTER(ora.ora_tracer), C.c_int, ora._dp, ora._dp,
+                                           ora._dp, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.c_double,
+                                           C.c_double, C.POINTER(ora.ora_domain), C.c_void_p, C.c_void_p]
+    g = ora.make_grid(G, GV)
+    n, inv = C.c_int(0), C.c_double(0.0)
+    f = _hd.ref_hordiff_num_itts
+    f.restype = C.c_int
+    rc = f(C.byref(g), ora._p(khdt_x), ora._p(khdt_y), C.c_int(int(bool(check_diffusive_CFL))), C.c_double(float(max_diff_CFL)),
+           C.byref(n), C.byref(inv))
+    if rc != 0:
+        raise RuntimeError("translated num_itts lines failed: %d" % rc)
+    return n.value, inv.value

@@ -67,6 +67,32 @@ def test_oracle_df_diagnostics_equal_translated_reference_lines(kw):
         assert eq(Ro.Tr[m].t, Rp.Tr[m].t)
 
 
+@pytest.mark.skipif(not f2c_ref.available(), reason="neither oracle/_ref nor /root/reference present")
+def test_num_itts_equals_translated_reference_lines():
+    """tracer_hor_diff.num_itts_from_cfl (the host mirror of :368-387) against those lines translated: the CFL branch at
+    several strengths (also exactly on an integer CFL, where the 4*EPSILON guard decides), the MAX_TR_DIFFUSION_CFL branch,
+    the default."""
+    c = synth.make_case(37, 29, 2, 1, cfl=0.4)
+    for strength in (0.01, 0.124, 0.126, 0.3, 0.61, 1.7):
+        kx, ky = synth.make_khdt(c, strength)
+        n, inv = f2c_ref.hordiff_num_itts(kx, ky, c.G, c.GV)
+        assert tracer_hor_diff.num_itts_from_cfl(kx, ky, c.G) == n and inv == 1.0 / n
+    # khdt chosen so that the largest CFL is exactly 2.0 and exactly 3.0
+    for target in (2.0, 3.0):
+        a = np.asarray(c.G.areaT)
+        kx, ky = np.zeros(c.G.shape_u()), np.zeros(c.G.shape_v())
+        j, i = c.G.pj(c.G.jsc + 3), c.G.pi(c.G.isc + 5)
+        kx[j, c.G.pI(c.G.isc + 5)] = target / 2.0 * a[j, i]
+        n, inv = f2c_ref.hordiff_num_itts(kx, ky, c.G, c.GV)
+        assert tracer_hor_diff.num_itts_from_cfl(kx, ky, c.G) == n
+    kx, ky = synth.make_khdt(c, 0.3)
+    for mx in (0.5, 1.0, 2.5, 4.0):
+        n, inv = f2c_ref.hordiff_num_itts(kx, ky, c.G, c.GV, check_diffusive_CFL=False, max_diff_CFL=mx)
+        assert tracer_hor_diff.num_itts_from_cfl(kx, ky, c.G, check_diffusive_CFL=False, max_diff_CFL=mx) == n
+    assert f2c_ref.hordiff_num_itts(kx, ky, c.G, c.GV, check_diffusive_CFL=False)[0] == 1 == \
+        tracer_hor_diff.num_itts_from_cfl(kx, ky, c.G, check_diffusive_CFL=False)
+
+
 def test_diffusion_properties():
     """Constant tracers stay constant (bitwise); extrema do not grow; sum(T*h*areaT) is conserved to roundoff."""
     c, kx, ky, nit = _case(ni=30, nj=24, nk=3, ntr=3, cyclic_x=False)     # closed: the random khdt is not periodic
