@@ -144,7 +144,8 @@ struct ocean_grid_type {
   Arr<double, 2> areat, iareat, mask2dt, mask2dcu, mask2dcv;
 };
 struct verticalgrid_type { int ke = 0; double angstrom_h = 0, h_subroundoff = 0; int nkml = 0, nk_rho_varies = 0;
-                           double h_to_mks = 1.0, h_to_kg_m2 = 1.0, kg_m2_to_h = 1.0; };      // MOM_offline_main.F90:636,647
+                           double h_to_mks = 1.0, h_to_kg_m2 = 1.0, kg_m2_to_h = 1.0;       // MOM_offline_main.F90:636,647
+                           double h_to_m = 1.0; };                                            // MOM_tracer_registry.F90:756
 struct unit_scale_type { double s_to_t = 1.0, l_to_m = 1.0, m_to_l = 1.0; };
 struct tracer_type {
   Arr<double, 3> t, ad_x, ad_y, advection_xy;

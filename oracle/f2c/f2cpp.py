@@ -407,6 +407,21 @@ class Emitter:
 
     def ref(self, r: Ref) -> str:
         out = ""
+        # ANY(array-section <cmp> scalar), e.g. any(frac_under_100m(:,:,k) > 0): a predicate over the section's elements
+        if len(r.parts) == 1 and r.parts[0][0] == "any" and r.parts[0][1] is not None and len(r.parts[0][1]) == 1 \
+                and isinstance(r.parts[0][1][0], Bin) and isinstance(r.parts[0][1][0].a, Ref):
+            cmp_ = r.parts[0][1][0]
+            arr = cmp_.a
+            aname, aargs = arr.parts[-1]
+            if aargs and any(isinstance(a, Section) for a in aargs):
+                for a in aargs:
+                    if isinstance(a, Section) and (a.lo is not None or a.hi is not None):
+                        raise F2CError("ANY: only full ':' sections are supported")
+                base = Ref(arr.parts[:-1] + [(aname, None)])
+                fixed = ", ".join("0" if isinstance(a, Section) else self.e(a) for a in aargs)
+                full = ", ".join("true" if isinstance(a, Section) else "false" for a in aargs)
+                return "f_any_section(%s, {%s}, {%s}, [&](double x__) { return x__ %s %s; })" % (
+                    self.ref(base), fixed, full, cmp_.op, self.e(cmp_.b))
         for k, (name, args) in enumerate(r.parts):
             first = (k == 0)
             if first and name in INTRINSICS and args is not None and len(r.parts) == 1:

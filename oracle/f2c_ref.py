@@ -20,7 +20,7 @@ _SRC = "/root/reference/src/tracer/MOM_tracer_advect.F90"
 _libs = {}
 
 VARIANTS = {"": "libref_f2c.so", "lt": "libref_f2c_lt.so", "mm": "libref_f2c_mm.so", "chk": "libref_f2c_chk.so"}
-_EXTRA = ("libref_f2c_hordiff.so", "libref_f2c_offline.so")
+_EXTRA = ("libref_f2c_hordiff.so", "libref_f2c_offline.so", "libref_f2c_step.so")
 
 
 def available() -> bool:
@@ -146,3 +146,42 @@ def hordiff_num_itts(khdt_x, khdt_y, G, GV, check_diffusive_CFL=True, max_diff_C
     if rc != 0:
         raise RuntimeError("translated num_itts lines failed: %d" % rc)
     return n.value, inv.value
+
+
+_step = None
+
+
+def _step_lib():
+    global _step
+    if _step is None:
+        lib()
+        _step = C.CDLL(os.path.join(_REF_DIR, "libref_f2c_step.so"))
+        _step.ref_accumulate_transports.restype = C.c_int
+        _step.ref_accumulate_transports.argtypes = [C.POINTER(ora.ora_grid), ora._dp, ora._dp, ora._dp, ora._dp, C.c_double]
+        _step.ref_column_diag.restype = C.c_int
+        _step.ref_column_diag.argtypes = [C.POINTER(ora.ora_grid), C.c_int, ora._dp, ora._dp, C.c_double, ora._dp,
+                                          C.POINTER(C.c_int)]
+    return _step
+
+
+def accumulate_transports(uhtr, vhtr, uh, vh, dt, G, GV) -> None:
+    """uhtr += uh*dt ; vhtr += vh*dt by the translated lines MOM_dynamics_split_RK2.F90:1045-1053 (in place)."""
+    g = ora.make_grid(G, GV)
+    rc = _step_lib().ref_accumulate_transports(C.byref(g), ora._p(uhtr), ora._p(vhtr), ora._p(uh), ora._p(vh), float(dt))
+    if rc != 0:
+        raise RuntimeError("translated transport accumulation failed: %d" % rc)
+
+
+def column_diag(kind, G, GV, field3d, h_diag, H_to_m=1.0):
+    """work2d of post_tracer_transport_diagnostics by the translated lines MOM_tracer_registry.F90:744-767, 785-788,
+    795-798, 804-807: kind 0 adv_xy_2d (field3d = advection_xy), 1 zint, 2 zint_100m (field3d = Tr%t).
+    Returns (work2d over (jsd:jed, isd:ied), khi)."""
+    import numpy as np
+    g = ora.make_grid(G, GV)
+    work = np.zeros(G.shape_h())
+    khi = C.c_int(0)
+    hd = h_diag if h_diag is not None else np.zeros_like(field3d)
+    rc = _step_lib().ref_column_diag(C.byref(g), int(kind), ora._p(field3d), ora._p(hd), float(H_to_m), ora._p(work), C.byref(khi))
+    if rc != 0:
+        raise RuntimeError("translated column diagnostics failed: %d" % rc)
+    return work, khi.value

@@ -136,3 +136,41 @@ def test_unassigned_logical_only_touches_outermost_diagnostic_faces():
     for a, b in zip(R0.Tr, R1.Tr):
         assert eq(a.t, b.t) and eq(a.advection_xy, b.advection_xy)
         assert eq(G.interior_u(a.ad_x), G.interior_u(b.ad_x)) and eq(G.interior_v(a.ad_y), G.interior_v(b.ad_y))
+
+
+# ---- the loops either side of advect_tracer ---------------------------------------------------
+@pytest.mark.parametrize("symmetric", [True, False])
+def test_side_loops_equal_translated_reference_lines(symmetric):
+    """oracle.accumulate_transports / oracle.column_diag (what the CUDA entry points of step.cu are checked against)
+    against MOM_dynamics_split_RK2.F90:1045-1053 and MOM_tracer_registry.F90:744-767, 785-788, 795-798, 804-807
+    translated statement by statement (bounds-checked build), whole arrays, bitwise."""
+    from mom6_b200 import synth
+    from oracle import oracle
+    c = synth.make_case(23, 17, 6, 2, cfl=0.5, symmetric=symmetric)
+    G, GV, nz = c.G, c.GV, c.GV.ke
+    rng = np.random.default_rng(5)
+    uh, vh = rng.standard_normal(G.shape_u(nz)), rng.standard_normal(G.shape_v(nz))
+    u0, v0 = rng.standard_normal(G.shape_u(nz)), rng.standard_normal(G.shape_v(nz))
+    ua, va, ub, vb = u0.copy(), v0.copy(), u0.copy(), v0.copy()
+    oracle.accumulate_transports(ua, va, uh, vh, 37.5, G)
+    f2c_ref.accumulate_transports(ub, vb, uh, vh, 37.5, G, GV)
+    assert np.array_equal(ua.view(np.uint64), ub.view(np.uint64)) and np.array_equal(va.view(np.uint64), vb.view(np.uint64))
+    assert not np.array_equal(ua, u0)
+    t = rng.standard_normal(G.shape_h(nz))
+    axy = rng.standard_normal(G.shape_h(nz))
+    h = 40.0 * rng.random(G.shape_h(nz))
+    h[:, G.pj(G.jsc), G.pi(G.isc)] = 0.0            # a vanished column and
+    h[0, G.pj(G.jsc + 1), G.pi(G.isc + 1)] = 500.0  # one whose first layer already crosses 100 m
+    for H_to_m in (0.75, 1.0):
+        for kind, f3 in ((0, axy), (1, t), (2, t)):
+            want, khi = f2c_ref.column_diag(kind, G, GV, f3, h, H_to_m)
+            got = oracle.column_diag(kind, G, nz, t=t, h_diag=h, H_to_m=H_to_m, advection_xy=axy)
+            assert np.array_equal(got.view(np.uint64), want.view(np.uint64)), kind
+            if kind == 2:
+                assert 1 <= khi <= nz
+    # all layers above 100 m: khi = nz and zint_100m == zint
+    hs = 0.1 * np.ones(G.shape_h(nz))
+    w100, khi = f2c_ref.column_diag(2, G, GV, t, hs, 1.0)
+    wz, _ = f2c_ref.column_diag(1, G, GV, t, hs, 1.0)
+    assert khi == nz and np.array_equal(w100.view(np.uint64), wz.view(np.uint64))
+    assert np.array_equal(oracle.column_diag(2, G, nz, t=t, h_diag=hs, H_to_m=1.0).view(np.uint64), w100.view(np.uint64))
