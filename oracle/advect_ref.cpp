@@ -1063,6 +1063,36 @@ extern "C" int ora_advect_tracer_multi_obc(int nranks, ora_rank *ranks, const or
   return 0;
 }
 
+// The same lock-step run with the per-rank routine supplied by the caller: `impl` has the argument list of
+// ref_advect_tracer_obc (oracle/f2c/ref_wrap.cpp), i.e. the UNMODIFIED reference file translated mechanically.  This is
+// how a layout question is put to the reference's own statements rather than to the restatement above.
+typedef int (*ora_rank_impl_fn)(const ora_grid *, const ora_cs *, ora_tracer *, int, const double *, const double *,
+                                const double *, double, int, double *, int, int, double *, double *, const ora_domain *,
+                                ora_pass_fn, ora_sum_fn, void *, int *, const ora_obc *);
+extern "C" int ora_advect_tracer_multi_impl(int nranks, ora_rank *ranks, const ora_domain *dom, const ora_cs *CS, int ntr,
+                                            double dt, int x_first_in, int max_iter_in, int update_vol_prev,
+                                            const ora_obc *const *obcs, void *impl_ptr) {
+  ora_rank_impl_fn impl = (ora_rank_impl_fn)impl_ptr;
+  MultiShared sh(nranks);
+  sh.nranks = nranks; sh.ranks = ranks; sh.dom = dom; sh.ntr = ntr;
+  std::vector<MultiCtx> ctxs(nranks);
+  std::vector<int> rc(nranks, 0);
+  std::vector<std::thread> th;
+  for (int r = 0; r < nranks; r++) {
+    ctxs[r].sh = &sh; ctxs[r].r = r;
+    th.emplace_back([&, r] {
+      int npass = 0;
+      rc[r] = impl(&ranks[r].G, CS, ranks[r].Tr, ntr, ranks[r].h_end, ranks[r].uhtr, ranks[r].vhtr, dt, x_first_in,
+                   ranks[r].vol_prev, max_iter_in, update_vol_prev, ranks[r].uhr_out, ranks[r].vhr_out, nullptr, multi_pass,
+                   multi_sum, &ctxs[r], &npass, obcs ? obcs[r] : nullptr);
+      ranks[r].n_iter = npass;      // (the translated routine reports its group passes, not its trips)
+    });
+  }
+  for (auto &t : th) t.join();
+  for (int r = 0; r < nranks; r++) if (rc[r]) return rc[r];
+  return 0;
+}
+
 // ---------------------------------------------------------------------------
 // Parity / conservation metrics restated from the reference framework.
 // ---------------------------------------------------------------------------

@@ -150,6 +150,11 @@ int ora_advect_tracer_multi(int nranks, ora_rank *ranks, const ora_domain *dom,
 int ora_advect_tracer_multi_obc(int nranks, ora_rank *ranks, const ora_domain *dom, const ora_cs *CS, int ntr, double dt,
                                 int x_first_in, int max_iter_in, int update_vol_prev, const ora_obc *const *obcs);
 
+/* The same lock-step run with the per-rank routine supplied by the caller (impl: a function with the argument list of
+ * ref_advect_tracer_obc, oracle/f2c/ref_wrap.cpp -- the mechanically translated reference file). */
+int ora_advect_tracer_multi_impl(int nranks, ora_rank *ranks, const ora_domain *dom, const ora_cs *CS, int ntr, double dt,
+                                 int x_first_in, int max_iter_in, int update_vol_prev, const ora_obc *const *obcs, void *impl);
+
 /* Emulated do_group_pass for an arbitrary set of ranks (exposed for tests).
  * fields of rank r: uhr[r], vhr[r] (C-grid vector pair), hprev[r], Tr of rank. */
 void ora_group_pass(int nranks, ora_rank *ranks, const ora_domain *dom,

@@ -185,3 +185,10 @@ def column_diag(kind, G, GV, field3d, h_diag, H_to_m=1.0):
     if rc != 0:
         raise RuntimeError("translated column diagnostics failed: %d" % rc)
     return work, khi.value
+
+
+def advect_tracer_multi(ranks, dom, CS, dt, x_first_in=None, max_iter_in=None, update_vol_prev=None, variant: str = ""):
+    """The emulated multi-PE run of oracle.advect_tracer_multi with the TRANSLATED REFERENCE as every PE's advect_tracer
+    (same rank dicts; "OBC" per rank optional).  Returns the number of group passes each PE made."""
+    return ora.advect_tracer_multi(ranks, dom, CS, dt, x_first_in=x_first_in, max_iter_in=max_iter_in,
+                                   update_vol_prev=update_vol_prev, impl=lib(variant).ref_advect_tracer_obc)

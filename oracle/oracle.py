@@ -296,7 +296,7 @@ def remaining_transport_sum(uhtr, vhtr, h_new, G, GV, H_to_kg_m2=1.0, L_to_m=1.0
 
 
 def advect_tracer_multi(ranks: Sequence[dict], dom, CS, dt, x_first_in=None, max_iter_in=None,
-                        update_vol_prev=None) -> List[int]:
+                        update_vol_prev=None, impl=None) -> List[int]:
     """Emulated multi-PE run.  Each entry of ``ranks`` is a dict with keys
     G, GV, Reg, h_end, uhtr, vhtr and optional vol_prev, uhr_out, vhr_out, OBC (the rank's own ocean_OBC_type)."""
     n = len(ranks)
@@ -313,12 +313,21 @@ def advect_tracer_multi(ranks: Sequence[dict], dom, CS, dt, x_first_in=None, max
         arr[r].vol_prev = _p(d.get("vol_prev"))
         arr[r].uhr_out, arr[r].vhr_out = _p(d.get("uhr_out")), _p(d.get("vhr_out"))
     cs, od = make_cs(CS), make_domain(dom)
-    if any(d.get("OBC") is not None for d in ranks):
+    if impl is not None or any(d.get("OBC") is not None for d in ranks):
         obcs = (C.POINTER(ora_obc) * n)()
         for r, d in enumerate(ranks):
             o, k = make_obc(d.get("OBC"))
             keep.append((o, k))
             obcs[r] = C.pointer(o) if o is not None else None
+        if impl is not None:      # per-rank routine supplied by the caller (the translated reference, oracle/f2c_ref.py)
+            f = lib().ora_advect_tracer_multi_impl
+            f.restype = C.c_int
+            rc = f(n, arr, C.byref(od), C.byref(cs), ranks[0]["Reg"].ntr, C.c_double(float(dt)), _opt_flag(x_first_in),
+                   -1 if max_iter_in is None else int(max_iter_in), _opt_flag(update_vol_prev), obcs,
+                   C.cast(impl, C.c_void_p))
+            if rc != 0:
+                raise RuntimeError("oracle advect_tracer_multi_impl failed: %d" % rc)
+            return [arr[r].n_iter for r in range(n)]
         f = lib().ora_advect_tracer_multi_obc
         f.restype = C.c_int
         rc = f(n, arr, C.byref(od), C.byref(cs), ranks[0]["Reg"].ntr, C.c_double(float(dt)), _opt_flag(x_first_in),

@@ -385,7 +385,7 @@ def test_obc_basin_layouts(scheme):
     recorded here so that a change of it is noticed."""
     from mom6_b200.types import TracerRegistry, register_tracer
 
-    def run(layout, use_obc, **kw):
+    def run(layout, use_obc, translated=False, **kw):
         c, OBC = synth.make_obc_case()
         if not use_obc:
             OBC = None
@@ -403,7 +403,11 @@ def test_obc_basin_layouts(scheme):
                     register_tracer(decomp.cut_h(c.G, G, tr.t), Reg, underflow_conc=tr.conc_underflow)
                 ranks.append(dict(G=G, GV=c.GV, Reg=Reg, h_end=decomp.cut_h(c.G, G, h), uhtr=decomp.cut_u(c.G, G, u),
                                   vhtr=decomp.cut_v(c.G, G, v), OBC=decomp.cut_obc(OBC, c.G, G)))
-        oracle.advect_tracer_multi(ranks, c.G.Domain, CS, c.dt, **kw)
+        if translated:
+            from oracle import f2c_ref
+            f2c_ref.advect_tracer_multi(ranks, c.G.Domain, CS, c.dt, **kw)
+        else:
+            oracle.advect_tracer_multi(ranks, c.G.Domain, CS, c.dt, **kw)
         cells = set()
         for m in range(c.ntr):
             glob = np.zeros(c.G.shape_h(c.GV.ke))
@@ -422,6 +426,14 @@ def test_obc_basin_layouts(scheme):
         assert run((1, 2), use_obc, x_first_in=False) == set()
         assert run((2, 1), use_obc, x_first_in=False) == set()
         assert run((2, 1), use_obc, max_iter_in=1) == set()
+    # the same per-PE runs with the TRANSLATED REFERENCE as every PE's advect_tracer: identical cell sets, so the layout
+    # dependence is in the reference's statements, not in the restatement
+    from oracle import f2c_ref
+    if f2c_ref.available():
+        for use_obc in (True, False):
+            assert run((2, 1), use_obc, translated=True) == run((2, 1), use_obc) != set()
+            assert run((1, 2), use_obc, translated=True) == set()
+            assert run((2, 1), use_obc, translated=True, x_first_in=False) == set()
     with_obc, without = run((2, 1), True), run((2, 1), False)
     # the same handful of cells under the northern boundary, OBC or not
     assert without and with_obc and len(with_obc | without) <= 12 and len(with_obc & without) >= 4
