@@ -7,9 +7,24 @@ import math
 import numpy as np
 
 
+def _max_across_pes(x: float) -> float:
+    """max_across_PEs (:377): torch.distributed MAX over the ranks when a process group with more than one rank exists."""
+    try:
+        import torch
+        import torch.distributed as dist
+    except Exception:
+        return x
+    if not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+        return x
+    dev = "cuda" if dist.get_backend() == "nccl" else "cpu"
+    t = torch.tensor([x], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
 def num_itts_from_cfl(khdt_x, khdt_y, G, check_diffusive_CFL=True, max_diff_CFL=-1.0) -> int:
-    """num_itts as :368-387 computes it (single PE: max_across_PEs is the identity; multi-rank callers reduce the
-    returned value with max themselves, as the reference does at :376)."""
+    """num_itts as :368-387 computes it from this rank's block, max_across_PEs (:377) included: one rank per GPU with
+    torch.distributed initialised gives every rank the global value; a single process gets its own."""
     if check_diffusive_CFL:
         kx, ky, ia = khdt_x, khdt_y, G.IareaT
         j0, j1, i0, i1 = G.pj(G.jsc), G.pj(G.jec), G.pi(G.isc), G.pi(G.iec)
@@ -17,7 +32,7 @@ def num_itts_from_cfl(khdt_x, khdt_y, G, check_diffusive_CFL=True, max_diff_CFL=
         nj, ni = j1 - j0 + 1, i1 - i0 + 1
         cfl = 2.0 * ((kx[j0:j1 + 1, I0 - 1:I0 - 1 + ni] + kx[j0:j1 + 1, I0:I0 + ni]) +
                      (ky[J0 - 1:J0 - 1 + nj, i0:i1 + 1] + ky[J0:J0 + nj, i0:i1 + 1])) * ia[j0:j1 + 1, i0:i1 + 1]
-        mx = max(0.0, float(np.asarray(cfl).max()))
+        mx = _max_across_pes(max(0.0, float(np.asarray(cfl).max())))
         return max(1, math.ceil(mx - 4.0 * np.finfo(np.float64).eps))
     if max_diff_CFL > 0.0:
         return max(1, math.ceil(max_diff_CFL - 4.0 * np.finfo(np.float64).eps))

@@ -248,3 +248,46 @@ def test_layout_choice_and_extents():
     assert multi.choose_layout(8, 2880, 256)[0] * multi.choose_layout(8, 2880, 256)[1] == 8
     ib, ie, jb, je = multi.layout_extents(10, 7, (3, 2))
     assert ib == [1, 5, 8] and ie == [4, 7, 10] and jb == [1, 5] and je == [4, 7]
+
+
+# ---- tracer_hordiff's iteration count on two real ranks: max_across_PEs(max_CFL), MOM_tracer_hor_diff.F90:377 --------
+def _gloo_num_itts_worker(rank, world, port, layout, q):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from mom6_b200 import synth, decomp, tracer_hor_diff
+        c = synth.make_case(40, 30, 2, 1, cfl=0.4)
+        kx, ky = synth.make_khdt(c, 0.05)
+        # one strong spot in rank 1's block only: rank 0 alone would ask for fewer iterations
+        a = np.asarray(c.G.areaT)
+        j, i = c.G.pj(c.G.jec - 2), c.G.pi(c.G.iec - 2)
+        kx[j, c.G.pI(c.G.iec - 2)] = 1.3 * a[j, i]
+        G = decomp.local_grid(c.G, layout, multi.rank_to_pe(rank, layout))
+        n = tracer_hor_diff.num_itts_from_cfl(decomp.cut_u(c.G, G, kx), decomp.cut_v(c.G, G, ky), G)
+        q.put((rank, n))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("layout", [(2, 1), (1, 2)])
+def test_num_itts_is_the_maximum_over_ranks(layout):
+    import torch.multiprocessing as mp
+    from mom6_b200 import synth, tracer_hor_diff
+    c = synth.make_case(40, 30, 2, 1, cfl=0.4)
+    kx, ky = synth.make_khdt(c, 0.05)
+    a = np.asarray(c.G.areaT)
+    j, i = c.G.pj(c.G.jec - 2), c.G.pi(c.G.iec - 2)
+    kx[j, c.G.pI(c.G.iec - 2)] = 1.3 * a[j, i]
+    want = tracer_hor_diff.num_itts_from_cfl(kx, ky, c.G)
+    assert want >= 3
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_gloo_num_itts_worker, args=(r, 2, port, layout, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert res == [(0, want), (1, want)], (res, want)
