@@ -8,6 +8,7 @@
 // statements.  Same argument list as ora_offline_advection_loop (oracle/advect_ref.h).
 #include "f2c_runtime.h"
 #include "../advect_ref.h"
+#include "obc_from_ora.h"
 #include <cstdlib>
 
 extern thread_local f2c_host *f2c_current_host;
@@ -157,7 +158,7 @@ extern "C" int ref_offline_advection_loop(const ora_grid *G, const ora_cs *CS, o
                                           const ora_obc *OBC, int *converged_out, int *n_iter_out, double *tot_residual_out,
                                           int nthreads) {
   (void)nthreads;
-  if (!dom || OBC) return 1;      // (open boundaries: covered by the advect_tracer comparison itself)
+  if (!dom) return 1;
   ocean_grid_type g;
   g.isc = G->isc; g.iec = G->iec; g.jsc = G->jsc; g.jec = G->jec;
   g.isd = G->isd; g.ied = G->ied; g.jsd = G->jsd; g.jed = G->jed;
@@ -190,6 +191,8 @@ extern "C" int ref_offline_advection_loop(const ora_grid *G, const ora_cs *CS, o
   offline_transport_cs cs_; offline_transport_cs *cs = &cs_;
   cs->num_off_iter = num_off_iter; cs->off_ale_mod = off_ale_mod; cs->dt_offline = dt_offline; cs->min_residual = min_residual;
   cs->tracer_adv_csp = &acs; cs->tracer_reg = &reg;
+  ObcHolder obc_holder;
+  cs->obc = obc_from_ora(OBC, obc_holder, G->nk);      // CS%OBC, handed to advect_tracer at :334
   // the routine's dummy arguments and locals with their declared shapes (:216-250)
   Arr<double, 3> h_pre = Arr<double, 3>::view(h_pre_in, {hi_, hj_, kk});
   Arr<double, 3> uhtr = Arr<double, 3>::view(uhtr_in, {ui_, hj_, kk}), vhtr = Arr<double, 3>::view(vhtr_in, {hi_, vj_, kk});

@@ -114,7 +114,7 @@ _off = None
 
 
 def offline_advection_loop(h_pre, uhtr, vhtr, dt_offline, num_off_iter, G, GV, CS, Reg, x_before_y=True, off_ale_mod=10 ** 6,
-                           min_residual=0.0, H_to_kg_m2=1.0, L_to_m=1.0, kg_m2_to_H=1.0, m_to_L=1.0):
+                           min_residual=0.0, H_to_kg_m2=1.0, L_to_m=1.0, kg_m2_to_H=1.0, m_to_L=1.0, OBC=None):
     """The translated lines MOM_offline_main.F90:270-415 and :634-648 around the translated advect_tracer
     (oracle/f2c/offline_wrap.cpp, bounds-checked build).  Same returns as oracle.offline_advection_loop."""
     global _off
@@ -124,7 +124,7 @@ def offline_advection_loop(h_pre, uhtr, vhtr, dt_offline, num_off_iter, G, GV, C
         _off.ref_offline_advection_loop.restype = C.c_int
         _off.ref_offline_advection_loop.argtypes = ora._offline_argtypes()
     return ora._offline_call(_off.ref_offline_advection_loop, h_pre, uhtr, vhtr, dt_offline, num_off_iter, G, GV, CS, Reg,
-                             x_before_y, off_ale_mod, min_residual, H_to_kg_m2, L_to_m, kg_m2_to_H, m_to_L, None, 1)
+                             x_before_y, off_ale_mod, min_residual, H_to_kg_m2, L_to_m, kg_m2_to_H, m_to_L, OBC, 1)
 
 
 def hordiff_num_itts(khdt_x, khdt_y, G, GV, check_diffusive_CFL=True, max_diff_CFL=-1.0):
